@@ -1,0 +1,149 @@
+"""TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+
+Restatement of the per-iteration loop body of scripts/fit.py:399-458 with INJECTED noise:
+* ObjectOracle.cal_distance: graspqp/src/graspqp/core/object_model.py:186-255 (TORCHSDF branch), cog :64-68
+* calculate_energy: graspqp/src/graspqp/core/energy.py:6-66 (method "gendexgrasp": fit.py passes use_gendexgrasp)
+* MalaStarOracle: graspqp/src/graspqp/core/optimizer.py:152-347
+* loop glue (z-score, weighted sum, masked commit): scripts/fit.py:381-396, 403-406, 434-458
+
+The reference draws `torch.rand(B,n_c)`, `torch.randint(C, [switch.sum()])` and `torch.rand(B)`; here they are the
+arguments u_switch (B,n_c), idx_new (B,n_c) (only entries under the switch mask are used) and u_accept (B).
+"""
+import torch
+
+from .hand import HandOracle, compute_sdf
+from .qp import graspqp_energy
+
+WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_pen=100.0, E_spen=10.0, E_joints=1.0)  # fit.py argparse defaults :90-112
+
+
+class ObjectOracle:
+    def __init__(self, face_verts_list, surface_points_list, batch_size_each, dtype=torch.float32):
+        self.face_verts_list = face_verts_list  # list of (F,3,3) float32 numpy
+        self.batch_size_each = batch_size_each
+        self.dtype = dtype
+        sp = torch.stack([torch.as_tensor(s, dtype=dtype) for s in surface_points_list], 0)
+        self.surface_points_tensor = sp.repeat_interleave(batch_size_each, dim=0)
+        self.object_scale = 1.0  # object_model.py:60 — always 1.0
+        self.cog = self.surface_points_tensor.mean(1)
+
+    def cal_distance(self, x):
+        n_points = x.shape[1]
+        xo = x.reshape(-1, self.batch_size_each * n_points, 3) / self.object_scale
+        distance, normals = [], []
+        for i, fv in enumerate(self.face_verts_list):
+            dis, sg, normal, _ = compute_sdf(xo[i], fv)
+            dis = torch.sqrt(dis + 1e-8) * (-sg)
+            distance.append(dis)
+            normals.append(normal * sg.unsqueeze(1))
+        distance = (torch.stack(distance) * self.object_scale).reshape(-1, n_points)
+        return distance, torch.stack(normals).reshape(-1, n_points, 3)
+
+
+def calculate_energy(hand, obj, svd_gain=0.1, friction=0.2, max_limit=20.0):
+    distance, contact_normal = obj.cal_distance(hand.contact_points)
+    E_dis = ((1 - torch.sum((-contact_normal) * hand.contact_normals, dim=-1)).exp() * distance.abs()).sum(-1)
+    E_fc, lam, info = graspqp_energy(hand.contact_points, contact_normal, obj.cog, friction=friction,
+                                     max_limit=max_limit, svd_gain=svd_gain)
+    th = hand.hand_pose[:, 9:]
+    E_joints = torch.sum((th > hand.joints_upper) * (th - hand.joints_upper), dim=-1) + torch.sum(
+        (th < hand.joints_lower) * (hand.joints_lower - th), dim=-1)
+    d = hand.cal_distance(obj.surface_points_tensor * obj.object_scale)
+    d = d.clone()
+    d[d <= 0] = 0
+    E_pen = d.sum(-1)
+    E_spen = hand.self_penetration()
+    return dict(E_dis=E_dis, E_fc=E_fc, E_joints=E_joints, E_pen=E_pen, E_spen=E_spen), info
+
+
+def total_energy(losses, weights=WEIGHTS):
+    e = 0
+    for k, v in losses.items():
+        e = e + weights[k] * v
+    return e
+
+
+class MalaStarOracle:
+    def __init__(self, hand, switch_possibility=0.4, starting_temperature=18.0, temperature_decay=0.95,
+                 annealing_period=30, step_size=0.005, stepsize_period=50, mu=0.98):
+        self.hand = hand
+        self.switch_possibility = switch_possibility
+        dt = hand.dtype
+        self.starting_temperature = torch.tensor(starting_temperature, dtype=dt)
+        self.temperature_decay = torch.tensor(temperature_decay, dtype=dt)
+        self.annealing_period, self.step_size_period = annealing_period, stepsize_period
+        self.step_size = torch.tensor(step_size, dtype=dt)
+        self.mu = torch.tensor(mu, dtype=dt)
+        B = hand.hand_pose.shape[0]
+        self.step = torch.zeros(B, dtype=torch.long)
+        self.ema = torch.zeros(B, hand.n_dofs + 9, dtype=dt)
+
+    def try_step(self, u_switch, idx_new):
+        h = self.hand
+        s = self.step_size * self.temperature_decay ** torch.div(self.step, self.step_size_period, rounding_mode="floor")
+        step_size = torch.zeros_like(h.hand_pose) + s[..., None]
+        gradient = h.hand_pose.grad
+        grad = (gradient ** 2).mean(0)
+        self.ema = self.mu * grad + (1 - self.mu) * self.ema
+        self.ema[torch.isnan(self.ema)] = 0
+        hand_pose = h.hand_pose - step_size * gradient / (torch.sqrt(self.ema) + 1e-6)
+        hand_pose = hand_pose.detach()
+        switch_mask = u_switch < self.switch_possibility
+        idx = h.contact_point_indices.clone()
+        idx[switch_mask] = idx_new[switch_mask]
+        self.old = dict(pose=h.hand_pose, idx=h.contact_point_indices, grad=h.hand_pose.grad)
+        h.set_parameters(hand_pose.requires_grad_(True), idx)
+        self.step += 1
+        return s
+
+    def accept_step(self, energy, new_energy, u_accept, z_score):
+        h = self.hand
+        temperature = self.starting_temperature * self.temperature_decay ** torch.div(
+            self.step, self.annealing_period, rounding_mode="floor")
+        proba = torch.distributions.normal.Normal(0.0, 1.0).cdf(z_score.detach())
+        temperature = temperature * (1 + proba)
+        accept = u_accept < torch.exp((energy - new_energy) / temperature)
+        with torch.no_grad():
+            reject = ~accept
+            h.hand_pose[reject] = self.old["pose"][reject]
+            h.contact_point_indices[reject] = self.old["idx"][reject]
+            h.hand_pose.grad[reject] = self.old["grad"][reject]
+        return accept, temperature
+
+
+class FitLoopOracle:
+    """One object of this class = the state of scripts/fit.py between iterations."""
+
+    def __init__(self, pack, face_verts_list, surface_points_list, batch_size_each, hand_pose0, idx0,
+                 dtype=torch.float32, **opt):
+        self.hand = HandOracle(pack, dtype)
+        self.obj = ObjectOracle(face_verts_list, surface_points_list, batch_size_each, dtype)
+        self.B = batch_size_each
+        self.hand.set_parameters(torch.as_tensor(hand_pose0, dtype=dtype).clone().requires_grad_(True),
+                                 torch.as_tensor(idx0).long())
+        self.opt = MalaStarOracle(self.hand, **opt)
+        self.losses, _ = calculate_energy(self.hand, self.obj)
+        self.energy = total_energy(self.losses)
+        self.energy.sum().backward()
+        self.first_grad = self.hand.hand_pose.grad.clone()
+        self.hand.hand_pose.grad.zero_()  # fit.py:396
+        self.energy = self.energy.detach()
+        self.losses = {k: v.detach().clone() for k, v in self.losses.items()}
+
+    def iterate(self, u_switch, idx_new, u_accept):
+        s = self.opt.try_step(u_switch, idx_new)
+        Eb = self.energy.view(-1, self.B)
+        z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        new_losses, info = calculate_energy(self.hand, self.obj)
+        new_energy = total_energy(new_losses)
+        new_energy.sum().backward()
+        out = dict(new_energy=new_energy.detach().clone(), new_grad=self.hand.hand_pose.grad.clone(),
+                   new_losses={k: v.detach().clone() for k, v in new_losses.items()}, z=z, s=s,
+                   proposal=self.hand.hand_pose.detach().clone(), idx_prop=self.hand.contact_point_indices.clone())
+        with torch.no_grad():
+            accept, t = self.opt.accept_step(self.energy, new_energy.detach(), u_accept, z)
+            self.energy[accept] = new_energy.detach()[accept]
+            for k, v in new_losses.items():
+                self.losses[k][accept] = v.detach()[accept]
+        out.update(accept=accept, temperature=t)
+        return out
