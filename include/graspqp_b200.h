@@ -1,0 +1,184 @@
+/* graspqp_b200 — C ABI of the B200-native GraspQP hot path (libgraspqp_b200.so).
+ *
+ * The reference (leggedrobotics/graspqp) has no plugin ABI: its seam is Python duck typing plus ONE pybind module,
+ * torchsdf._C (thirdparty/TorchSDF/torchsdf/csrc/bindings.cpp:22-27).  This header is what a binding for the hot path
+ * `per-iteration grasp-energy evaluation + MALA* update` binds instead; each entry point cites what it replaces.
+ *
+ * Conventions
+ *   - every pointer argument is a DEVICE pointer owned by the caller unless its name ends in `_host`;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
+ *   - no allocation happens after a *_create call returns; handles are immutable device-resident tables;
+ *   - return value 0 = ok, negative = error; gqp_last_error() gives the message of the calling thread's last error;
+ *   - no exceptions cross the ABI; one host thread per device (as in the reference: single Python thread).
+ *   - all floating point is fp32 (the QP's 6x6 Schur solve uses fp64 internally), indices are int32 on the device.
+ */
+#ifndef GRASPQP_B200_H
+#define GRASPQP_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GQP_OK 0
+#define GQP_ERR_ARG (-1)
+#define GQP_ERR_CUDA (-2)
+#define GQP_ERR_LIMIT (-3)
+
+typedef struct GqpMesh GqpMesh; /* triangle mesh + BVH + far-field sign grid, device resident */
+typedef struct GqpHand GqpHand; /* kinematic tree, contact candidates, penetration spheres, link meshes */
+
+int gqp_abi_version(void);
+const char *gqp_last_error(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches counter) */
+uint64_t gqp_launch_count(void);
+
+/* ---- K1: TorchSDF contract --------------------------------------------------------------------------------------
+ * replaces torchsdf._C.unbatched_triangle_distance_forward_cuda / _backward_cuda
+ *   (thirdparty/TorchSDF/torchsdf/csrc/bindings.cpp:22-27, unbatched_triangle_distance_cuda.cu:176-270).
+ * points (P,3), face_verts (F,3,3) contiguous.  Outputs dist2 (P), sign (P) int32 in {+1,-1}, normals (P,3) =
+ * unit(p - closest), clst (P,3).  Winner = first minimum in face order; arithmetic is not FMA-contracted so results
+ * are bit-identical to the host-compiled reference kernel.  Brute force over face tiles staged in shared memory. */
+int gqp_sdf_forward(const float *points, const float *face_verts, int P, int F, float *dist2, int32_t *sign,
+                    float *normals, float *clst, void *stream);
+int gqp_sdf_backward(const float *grad_dist, const float *points, const float *clst, int P, float *grad_points,
+                     void *stream);
+
+/* ---- meshes with an exact acceleration structure ------------------------------------------------------------------
+ * gqp_mesh_create builds (on the host, once) a BVH over the faces and uploads it; gqp_mesh_sdf_forward answers the
+ * same query as gqp_sdf_forward with the SAME winner (lexicographic (dist2, face index) minimum), visiting only the
+ * nodes whose box can hold a closer face.  face (P) int32 receives the winning face index (may be NULL).
+ * replaces the `face_verts`/`wp.Mesh` members of ObjectModel / HandModel (object_model.py:147-161,
+ * hand_model.py:351-372). */
+int gqp_mesh_create(const float *face_verts_host, int F, GqpMesh **out);
+void gqp_mesh_destroy(GqpMesh *m);
+int gqp_mesh_num_faces(const GqpMesh *m);
+int gqp_mesh_sdf_forward(const GqpMesh *m, const float *points, int P, float *dist2, int32_t *sign, float *normals,
+                         float *clst, int32_t *face, void *stream);
+
+/* ---- O1: ObjectModel.cal_distance (object_model.py:186-255, TORCHSDF branch) -----------------------------------------
+ * x (n_obj*batch_each, n_pts, 3); object o owns rows [o*batch_each, (o+1)*batch_each).  meshes_host = array of n_obj
+ * handles (host array of pointers).  distance = sqrt(d2+1e-8)*(-sign)*scale, normals = unit(p-c)*sign; clst kept for the
+ * backward:  grad_x = grad_distance * (-sign) * (p-c)/sqrt(d2+1e-8)  (sdf.py:60-66 chained with :243-249). */
+int gqp_object_distance_forward(const GqpMesh *const *meshes_host, int n_obj, int batch_each, int n_pts,
+                                const float *x, float scale, float *distance, float *normals, float *clst,
+                                int32_t *sign, void *stream);
+int gqp_object_distance_backward(const float *grad_distance, const float *x, const float *clst, const int32_t *sign,
+                                 int n, float scale, float *grad_x, void *stream);
+
+/* ---- hand description --------------------------------------------------------------------------------------------
+ * All arrays are HOST pointers, copied.  Frames are in the DFS order of pytorch_kinematics' chain
+ * (thirdparty/pytorch_kinematics/pytorch_kinematics/chain.py:128-138), parent index < own index.
+ * jtype: 0 fixed, 1 revolute, 2 prismatic.  frame_dof: column of hand_pose[:,9:] driving the joint, or -1.
+ * joff / loff: joint.offset and link.offset as row-major 3x4 (frame.py:98-114).
+ * link l (a "mesh link", hand_model.py:219-246) hangs on frame link_frame[l]; its faces are
+ * face_verts[face_offset[l] .. face_offset[l+1]).  cand*: contact candidates in link frames with their link id,
+ * in the reference's concatenation order (hand_model.py:1220-1267).  spheres: xyz + radius per penetration keypoint,
+ * sphere_link ascending (hand_model.py:308-324, 989-1040). */
+typedef struct GqpHandDesc {
+    int32_t n_frames, n_dofs, n_links, n_cand, n_spheres;
+    const int32_t *frame_parent_host, *frame_jtype_host, *frame_dof_host;
+    const float *frame_axis_host; /* (n_frames,3) */
+    const float *frame_joff_host; /* (n_frames,3,4) */
+    const float *frame_loff_host; /* (n_frames,3,4) */
+    const int32_t *link_frame_host;  /* (n_links) */
+    const int32_t *face_offset_host; /* (n_links+1) */
+    const float *face_verts_host;    /* (face_offset[n_links],3,3) */
+    const float *cand_host, *cand_normal_host; /* (n_cand,3) */
+    const int32_t *cand_link_host;             /* (n_cand) */
+    const float *spheres_host;                 /* (n_spheres,4) */
+    const int32_t *sphere_link_host;           /* (n_spheres) */
+    const float *joints_lower_host, *joints_upper_host; /* (n_dofs) */
+} GqpHandDesc;
+
+int gqp_hand_create(const GqpHandDesc *desc, GqpHand **out);
+void gqp_hand_destroy(GqpHand *h);
+
+/* ---- H1/H2: HandModel.set_parameters' kinematics (hand_model.py:856-865, chain.py:146-168, frame.py:98-114) -------
+ * pose (Bt, 9+n_dofs): translation, ortho6d, joint angles.  link_tf (Bt, n_links, 12): WORLD transform of every mesh
+ * link, row-major 3x4, i.e. [R_g R_l | R_g t_l + t_g].  Includes the reference's +-0.01 rad revolute perturbation.
+ * gqp_fk_backward maps d(loss)/d(link_tf) to d(loss)/d(pose) (replaces autograd through the chain, fit.py:440);
+ * grad_pose is OVERWRITTEN. */
+int gqp_fk_forward(const GqpHand *h, const float *pose, int Bt, float *link_tf, void *stream);
+int gqp_fk_backward(const GqpHand *h, const float *pose, const float *grad_link_tf, int Bt, float *grad_pose,
+                    void *stream);
+
+/* ---- H3: contact gather (hand_model.py:787-831, 1220-1267) ---------------------------------------------------------
+ * idx (Bt,n_c) int32 indices into the candidate table; cpts/cnrm (Bt,n_c,3) world position / normal.
+ * backward ACCUMULATES into grad_link_tf (Bt,n_links,12) (caller zeroes it once per step). */
+int gqp_contacts_forward(const GqpHand *h, const float *link_tf, const int32_t *idx, int Bt, int n_c, float *cpts,
+                         float *cnrm, void *stream);
+int gqp_contacts_backward(const GqpHand *h, const int32_t *idx, const float *grad_cpts, const float *grad_cnrm, int Bt,
+                          int n_c, float *grad_link_tf, void *stream);
+
+/* ---- H4: HandModel.cal_distance (hand_model.py:875-987) --------------------------------------------------------------
+ * x (n_obj, n_pts, 3): one point set per object, shared by its batch_each candidates (the reference materialises the
+ * repeat, object_model.py:181-184; x_stride_candidates != 0 selects a per-candidate (Bt,n_pts,3) set instead).
+ * dist (Bt,n_pts) = max over links of sqrt(d2+1e-8)*(-sign)   [positive inside], may be NULL;
+ * e_pen (Bt) = sum_p relu(dist) (energy.py:57-62), may be NULL;
+ * grad_link_tf (Bt,n_links,12), may be NULL: ACCUMULATES w_pen * d(e_pen)/d(link_tf). */
+int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each, int n_pts,
+                      int per_candidate_points, float *dist, float *e_pen, float w_pen, float *grad_link_tf,
+                      void *stream);
+
+/* ---- H5 + E_joints: self_penetration (hand_model.py:989-1040) and joint limits (energy.py:47-54) ------------------
+ * e_spen (Bt), e_joints (Bt); ACCUMULATES w_spen*d(e_spen) into grad_link_tf and OVERWRITES grad_pose_joints
+ * (Bt, 9+n_dofs) with w_joints*d(e_joints)/d(pose) (both may be NULL). */
+int gqp_self_pen_joints(const GqpHand *h, const float *link_tf, const float *pose, int Bt, float *e_spen,
+                        float *e_joints, float w_spen, float w_joints, float *grad_link_tf, float *grad_pose_joints,
+                        void *stream);
+
+/* ---- Q1-Q4 + E_dis: force-closure QP (span.py:263-415, qp_solver.py:60-134, registry.py:31-89) and contact-distance
+ * energy (energy.py:25-28), forward + analytic backward in one launch, a warp per candidate. -----------------------
+ * cpts/cnrm_hand (Bt,n_c,3) from gqp_contacts_forward; obj_dist (Bt,n_c), obj_nrm (Bt,n_c,3) from
+ * gqp_object_distance_forward; obj_dgrad (Bt,n_c,3) = d(obj_dist)/d(cpts) (gqp_object_distance_backward with ones);
+ * cog (n_obj,3).  Outputs e_fc, e_dis (Bt), lam (Bt,n_c) per-contact force sums (with_solution=True), and, if not
+ * NULL, grad_cpts / grad_cnrm (Bt,n_c,3) = d(w_fc*e_fc + w_dis*e_dis)/d(.), OVERWRITTEN.
+ * qp_stop_iter: NULL = run max_iter predictor-corrector iterations; else device int: leave the loop at that iteration
+ * (emulates qpth's batch-wide exit test); qp_trace (Bt,max_iter) best-residual trace or NULL. */
+typedef struct GqpFcParams {
+    float friction, torque_weight, lower, upper, ridge, svd_gain, values_gain, values_offset, eps;
+    int32_t max_iter;
+    float w_fc, w_dis;
+} GqpFcParams;
+int gqp_fc_dis_energy(const GqpFcParams *p_host, const float *cpts, const float *cnrm_hand, const float *obj_dist,
+                      const float *obj_nrm, const float *obj_dgrad, const float *cog, int n_obj, int batch_each,
+                      int n_c, float *e_fc, float *e_dis, float *lam, float *grad_cpts, float *grad_cnrm,
+                      const int32_t *qp_stop_iter, float *qp_trace, void *stream);
+/* batch-wide exit iteration of qpth's loop from the trace (one block): writes *stop_iter. */
+int gqp_fc_stop_iter(const float *qp_trace, int Bt, int max_iter, float eps, int32_t *stop_iter, void *stream);
+
+/* ---- M1/M2/M4: MALA* (optimizer.py:199-340) and the caller's bookkeeping (fit.py:403-406, 434-458) -----------------
+ * State rows are candidates.  u_switch (Bt,n_c), idx_rand (Bt,n_c) int32, u_accept (Bt): injected noise, or all NULL
+ * to draw them from Philox4x32-10 keyed (seed, iteration, row).
+ * gqp_mala_stats: grad2_mean (D) = mean over ALL rows of grad^2 (optimizer.py:231) and the per-object z-score of
+ *   `energy` (fit.py:403-406, unbiased std) -> z (Bt).   Deterministic two-pass reduction.
+ * gqp_mala_propose: ema = mu*grad2_mean + (1-mu)*ema (NaN->0); pose_new = pose - s_i*grad/(sqrt(ema)+1e-6);
+ *   idx_new = switch ? idx_rand : idx;  step += 1; step_size_out (Bt) = s_i (may be NULL).
+ * gqp_mala_accept: new_energy = sum_k w_k*losses_new[k]; T = T0*decay^(step/period)*(1+Phi(z));
+ *   accept = u < exp((E-E')/T) or reset; accepted rows copy pose_new/idx_new/grad_new/energy/losses into the state. */
+typedef struct GqpMalaParams {
+    float switch_possibility, starting_temperature, temperature_decay, step_size, mu;
+    int32_t annealing_period, stepsize_period;
+    int32_t clip_grad;
+} GqpMalaParams;
+int gqp_mala_stats(const float *grad, const float *energy, int n_obj, int batch_each, int D, float *grad2_mean,
+                   float *z, float *scratch, void *stream);
+int gqp_mala_propose(const GqpMalaParams *p_host, const float *pose, const float *grad, const float *grad2_mean,
+                     float *ema, int32_t *step, const int32_t *idx, int Bt, int D, int n_c, int n_cand,
+                     const float *u_switch, const int32_t *idx_rand, uint64_t seed, uint64_t iteration, float *pose_new,
+                     int32_t *idx_new, float *step_size_out, void *stream);
+int gqp_mala_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n_terms, const float *weights_host,
+                    const float *losses_new /* (n_terms,Bt) */, const float *z, const uint8_t *reset_mask,
+                    const float *u_accept, uint64_t seed, uint64_t iteration, const int32_t *step,
+                    const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose, int32_t *idx,
+                    float *grad, float *energy, float *losses /* (n_terms,Bt) */, float *new_energy_out,
+                    uint8_t *accept_out, float *temperature_out, void *stream);
+
+/* FP32 FMA micro-benchmark (roofline denominator for the SIMT stages): runs `iters` dependent-chain FMAs on every
+ * lane of a full-chip grid; returns the FMA count in *n_fma_host.  Timed by the caller with CUDA events. */
+int gqp_fma_peak_probe(int iters, float *sink, uint64_t *n_fma_host, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
