@@ -41,15 +41,17 @@ SIGNATURES = {
     "gqp_mesh_destroy": (None, [c_void_p]),
     "gqp_mesh_num_faces": (c_int, [c_void_p]),
     "gqp_mesh_sdf_forward": (c_int, [c_void_p, P, c_int, P, P, P, P, P, P]),
-    "gqp_object_distance_forward": (c_int, [P, c_int, c_int, c_int, P, c_float, P, P, P, P, P]),
+    "gqp_objset_create": (c_int, [P, c_int, POINTER(c_void_p)]),
+    "gqp_objset_destroy": (None, [c_void_p]),
+    "gqp_object_distance_forward": (c_int, [c_void_p, c_int, c_int, P, c_float, P, P, P, P, P]),
     "gqp_object_distance_backward": (c_int, [P, P, P, P, c_int, c_float, P, P]),
     "gqp_hand_create": (c_int, [POINTER(GqpHandDesc), POINTER(c_void_p)]),
     "gqp_hand_destroy": (None, [c_void_p]),
     "gqp_fk_forward": (c_int, [c_void_p, P, c_int, P, P]),
-    "gqp_fk_backward": (c_int, [c_void_p, P, P, c_int, P, P]),
+    "gqp_fk_backward": (c_int, [c_void_p, P, P, P, c_int, P, P]),
     "gqp_contacts_forward": (c_int, [c_void_p, P, P, c_int, c_int, P, P, P]),
     "gqp_contacts_backward": (c_int, [c_void_p, P, P, P, c_int, c_int, P, P]),
-    "gqp_hand_distance": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, c_float, P, P]),
+    "gqp_hand_distance": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, c_float, P, P]),
     "gqp_self_pen_joints": (c_int, [c_void_p, P, P, c_int, P, P, c_float, c_float, P, P, P]),
     "gqp_fc_dis_energy": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P, P, P, P, P]),
     "gqp_fc_stop_iter": (c_int, [P, c_int, c_int, c_float, P, P]),

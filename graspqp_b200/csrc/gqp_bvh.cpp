@@ -1,0 +1,216 @@
+// Host-side builders: BVH over a triangle mesh and the far-field sign grids (see gqp_hand.h).  Runs once per mesh at
+// *_create time; nothing here is on the per-iteration path.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "gqp_hand.h"
+
+namespace {
+struct D3 {
+    double x, y, z;
+};
+inline D3 operator-(D3 a, D3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline D3 operator+(D3 a, D3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline D3 operator*(D3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+inline double dot(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline D3 cross(D3 a, D3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline D3 ldv(const float *p) { return {p[0], p[1], p[2]}; }
+
+// exact (double) distance point -> triangle, Ericson's region walk
+double tri_dist(D3 p, D3 a, D3 b, D3 c) {
+    D3 ab = b - a, ac = c - a, ap = p - a;
+    double d1 = dot(ab, ap), d2 = dot(ac, ap);
+    D3 q;
+    if (d1 <= 0 && d2 <= 0) q = a;
+    else {
+        D3 bp = p - b;
+        double d3 = dot(ab, bp), d4 = dot(ac, bp);
+        if (d3 >= 0 && d4 <= d3) q = b;
+        else {
+            double vc = d1 * d4 - d3 * d2;
+            if (vc <= 0 && d1 >= 0 && d3 <= 0) q = a + ab * (d1 / (d1 - d3));
+            else {
+                D3 cp = p - c;
+                double d5 = dot(ab, cp), d6 = dot(ac, cp);
+                if (d6 >= 0 && d5 <= d6) q = c;
+                else {
+                    double vb = d5 * d2 - d1 * d6;
+                    if (vb <= 0 && d2 >= 0 && d6 <= 0) q = a + ac * (d2 / (d2 - d6));
+                    else {
+                        double va = d3 * d6 - d5 * d4;
+                        if (va <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0)
+                            q = b + (c - b) * ((d4 - d3) / ((d4 - d3) + (d5 - d6)));
+                        else {
+                            double den = 1.0 / (va + vb + vc);
+                            q = a + ab * (vb * den) + ac * (vc * den);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    D3 d = p - q;
+    return std::sqrt(dot(d, d));
+}
+
+double box_dist(const GqpBvhNode &n, D3 p) {
+    double dx = std::max({0.0, (double)n.lo[0] - p.x, p.x - (double)n.hi[0]});
+    double dy = std::max({0.0, (double)n.lo[1] - p.y, p.y - (double)n.hi[1]});
+    double dz = std::max({0.0, (double)n.lo[2] - p.z, p.z - (double)n.hi[2]});
+    return std::sqrt(dx * dx + dy * dy + dz * dz);
+}
+
+struct Builder {
+    const float *fv;
+    int leaf_size;
+    std::vector<int> order;
+    std::vector<float> cen;  // (F,3)
+    GqpBvhHost *out;
+    float pad;
+
+    int build(int lo, int hi, int depth) {
+        int id = (int)out->nodes.size();
+        out->nodes.push_back(GqpBvhNode());
+        out->max_depth = std::max(out->max_depth, depth);
+        float bl[3] = {1e30f, 1e30f, 1e30f}, bh[3] = {-1e30f, -1e30f, -1e30f};
+        float cl[3] = {1e30f, 1e30f, 1e30f}, ch[3] = {-1e30f, -1e30f, -1e30f};
+        for (int i = lo; i < hi; ++i) {
+            const float *t = fv + 9 * (size_t)order[i];
+            for (int v = 0; v < 3; ++v)
+                for (int k = 0; k < 3; ++k) {
+                    bl[k] = std::min(bl[k], t[3 * v + k]);
+                    bh[k] = std::max(bh[k], t[3 * v + k]);
+                }
+            for (int k = 0; k < 3; ++k) {
+                cl[k] = std::min(cl[k], cen[3 * order[i] + k]);
+                ch[k] = std::max(ch[k], cen[3 * order[i] + k]);
+            }
+        }
+        GqpBvhNode n;
+        for (int k = 0; k < 3; ++k) {
+            n.lo[k] = bl[k] - pad - 4e-7f * std::fabs(bl[k]);
+            n.hi[k] = bh[k] + pad + 4e-7f * std::fabs(bh[k]);
+        }
+        if (hi - lo <= leaf_size) {
+            n.a = lo;
+            n.b = -(hi - lo);
+            out->nodes[id] = n;
+            return id;
+        }
+        int ax = 0;
+        if (ch[1] - cl[1] > ch[ax] - cl[ax]) ax = 1;
+        if (ch[2] - cl[2] > ch[ax] - cl[ax]) ax = 2;
+        int mid = (lo + hi) / 2;
+        std::nth_element(order.begin() + lo, order.begin() + mid, order.begin() + hi,
+                         [&](int a, int b) { return cen[3 * a + ax] < cen[3 * b + ax]; });
+        int l = build(lo, mid, depth + 1);
+        int r = build(mid, hi, depth + 1);
+        n.a = l;
+        n.b = r;
+        out->nodes[id] = n;
+        return id;
+    }
+};
+}  // namespace
+
+void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &out) {
+    out.nodes.clear();
+    out.max_depth = 0;
+    Builder b;
+    b.fv = face_verts;
+    b.leaf_size = std::max(1, leaf_size);
+    b.out = &out;
+    b.pad = 1e-6f;
+    b.order.resize(F);
+    std::iota(b.order.begin(), b.order.end(), 0);
+    b.cen.resize(3 * (size_t)F);
+    for (int f = 0; f < F; ++f)
+        for (int k = 0; k < 3; ++k)
+            b.cen[3 * f + k] = (face_verts[9 * f + k] + face_verts[9 * f + 3 + k] + face_verts[9 * f + 6 + k]) / 3.f;
+    if (F > 0) b.build(0, F, 1);
+    // inside a leaf keep the original face order (first-minimum rule is then free of tie handling inside a leaf)
+    for (auto &n : out.nodes)
+        if (n.b < 0) std::sort(b.order.begin() + n.a, b.order.begin() + n.a - n.b);
+    out.tris.resize(9 * (size_t)F);
+    out.face_id.resize(F);
+    for (int i = 0; i < F; ++i) {
+        out.face_id[i] = b.order[i];
+        std::memcpy(&out.tris[9 * (size_t)i], face_verts + 9 * (size_t)b.order[i], 36);
+    }
+}
+
+// ---- far-field sign grid ----------------------------------------------------------------------------------------------
+// The reference's sign is sign(dot(p - c, n_f)) for the WINNING face f (.cu:236); c lies in f's plane, so this is the
+// side of f's plane p is on.  A cell is flagged when, for every face that can win anywhere in the cell
+// (dist(centre,f) <= d* + 2r, r = cell circumradius, d* = distance of the centre to the mesh), the whole cell is on the
+// positive side of f's plane by a safety margin that dominates fp32 rounding of the runtime test.
+namespace {
+void nearest(const GqpBvhHost &bvh, D3 p, double &best) {
+    int stack[128], sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        const GqpBvhNode &n = bvh.nodes[stack[--sp]];
+        if (box_dist(n, p) > best) continue;
+        if (n.b < 0) {
+            for (int i = n.a; i < n.a - n.b; ++i) {
+                const float *t = &bvh.tris[9 * (size_t)i];
+                best = std::min(best, tri_dist(p, ldv(t), ldv(t + 3), ldv(t + 6)));
+            }
+        } else {
+            double dl = box_dist(bvh.nodes[n.a], p), dr = box_dist(bvh.nodes[n.b], p);
+            if (dl < dr) { stack[sp++] = n.b; stack[sp++] = n.a; }
+            else { stack[sp++] = n.a; stack[sp++] = n.b; }
+        }
+    }
+}
+// all faces within `radius` of p are on whose positive side the ball (p, r) lies entirely?
+bool all_positive(const GqpBvhHost &bvh, D3 p, double radius, double r) {
+    int stack[128], sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        const GqpBvhNode &n = bvh.nodes[stack[--sp]];
+        if (box_dist(n, p) > radius) continue;
+        if (n.b < 0) {
+            for (int i = n.a; i < n.a - n.b; ++i) {
+                const float *t = &bvh.tris[9 * (size_t)i];
+                D3 a = ldv(t), b = ldv(t + 3), c = ldv(t + 6);
+                double d = tri_dist(p, a, b, c);
+                if (d > radius) continue;
+                D3 nrm = cross(b - a, c - a);
+                double nl = std::sqrt(dot(nrm, nrm));
+                double e = std::max({std::sqrt(dot(b - a, b - a)), std::sqrt(dot(c - a, c - a)), std::sqrt(dot(c - b, c - b))});
+                if (!(nl > 1e-6 * e * e) || !(nl > 0)) return false;  // sliver: the fp32 normal is unreliable
+                double h = dot(p - a, nrm) / nl;                       // signed plane distance of the centre
+                if (h - r < 1e-5 + 1e-3 * (d + r)) return false;
+            }
+        } else {
+            stack[sp++] = n.a;
+            stack[sp++] = n.b;
+        }
+    }
+    return true;
+}
+}  // namespace
+
+void gqp_sign_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
+                         std::vector<uint32_t> &bits) {
+    size_t ncell = (size_t)dim[0] * dim[1] * dim[2];
+    bits.assign((ncell + 31) / 32, 0u);
+    if (bvh.nodes.empty()) return;
+    const double r = 0.5 * std::sqrt(3.0) * cell * 1.0001 + 1e-7;  // + slack for the fp32 cell index computation
+    for (int z = 0; z < dim[2]; ++z)
+        for (int y = 0; y < dim[1]; ++y)
+            for (int x = 0; x < dim[0]; ++x) {
+                D3 c = {origin[0] + (x + 0.5) * (double)cell, origin[1] + (y + 0.5) * (double)cell,
+                        origin[2] + (z + 0.5) * (double)cell};
+                double best = 1e30;
+                nearest(bvh, c, best);
+                if (best <= 2 * r) continue;  // the mesh may cross or touch the cell's neighbourhood
+                if (all_positive(bvh, c, best + 2 * r + 1e-7, r)) {
+                    size_t i = ((size_t)z * dim[1] + y) * dim[0] + x;
+                    bits[i >> 5] |= 1u << (i & 31);
+                }
+            }
+}

@@ -102,3 +102,30 @@ void gqp_count_launch(int n = 1);
 #else
 #define GQP_CHECK_LAUNCH(name) gqp_count_launch()
 #endif
+
+// ---- "device" memory for the immutable tables behind the handles (host heap under the emulator) ----
+#include <cstdlib>
+#include <cstring>
+static inline void *gqp_dev_alloc_upload(const void *src, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    void *d = nullptr;
+#ifndef GQP_EMU
+    if (cudaMalloc(&d, bytes) != cudaSuccess) return nullptr;
+    if (src && cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaFree(d);
+        return nullptr;
+    }
+#else
+    d = std::aligned_alloc(256, (bytes + 255) / 256 * 256);
+    if (d && src) std::memcpy(d, src, bytes);
+#endif
+    return d;
+}
+static inline void gqp_dev_free(void *d) {
+    if (!d) return;
+#ifndef GQP_EMU
+    cudaFree(d);
+#else
+    std::free(d);
+#endif
+}

@@ -1,0 +1,357 @@
+// H1/H2/H3 — hand kinematics: forward kinematics over the URDF chain, analytic Jacobian-transpose backward, contact
+// candidate gather.  Replaces HandModel.set_parameters / fk / _set_contact_idxs (core/hand_model.py:762-873,
+// 1220-1267), pytorch_kinematics' recursive FK (chain.py:146-168, frame.py:98-114, rotation_conversions.py:43-71) and
+// the autograd walk through them (scripts/fit.py:440).
+//
+// Layout: pose (Bt, 9+dof) row-major as in the reference; link_tf (Bt, n_links, 12) world transforms, one candidate's
+// links contiguous (the consumers assign one candidate to a warp or block).  A thread owns a candidate: the chain is
+// short (19 frames for Allegro), the tables sit in shared memory, per-frame transforms in thread-local arrays.
+// FK is < 0.1 % of a grasp-step's work; it is bound by nothing but launch latency.
+#include "gqp_common.cuh"
+#include "gqp_hand.h"
+#include "graspqp_b200.h"
+
+#define FK_THREADS 128
+
+__device__ __forceinline__ void load_hand_tables(GqpHandDev *dst, const GqpHandDev *src) {
+    const int n = sizeof(GqpHandDev) / 4;
+    const int32_t *s = reinterpret_cast<const int32_t *>(src);
+    int32_t *d = reinterpret_cast<int32_t *>(dst);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) d[i] = s[i];
+}
+
+// utils/transforms.py:5-13 -> roma.special_gramschmidt: columns (x^, y^, x^ x y^)
+struct GramSchmidt {
+    V3 xh, yh, z;
+    float nx, ny, d;  // |x|, |y'|, x^.y
+    V3 y;
+};
+__device__ __forceinline__ GramSchmidt gram_schmidt(V3 x, V3 y) {
+    GramSchmidt g;
+    g.y = y;
+    g.nx = sqrtf(dot3(x, x));
+    g.xh = x * (1.0f / g.nx);
+    g.d = dot3(g.xh, y);
+    V3 yp = y - g.xh * g.d;
+    g.ny = sqrtf(dot3(yp, yp));
+    g.yh = yp * (1.0f / g.ny);
+    g.z = cross3(g.xh, g.yh);
+    return g;
+}
+__device__ __forceinline__ T34 global_tf(const float *pose, GramSchmidt &gs) {
+    gs = gram_schmidt(ld3(pose + 3), ld3(pose + 6));
+    T34 G;
+    G.m[0] = gs.xh.x; G.m[1] = gs.yh.x; G.m[2] = gs.z.x; G.m[3] = pose[0];
+    G.m[4] = gs.xh.y; G.m[5] = gs.yh.y; G.m[6] = gs.z.y; G.m[7] = pose[1];
+    G.m[8] = gs.xh.z; G.m[9] = gs.yh.z; G.m[10] = gs.z.z; G.m[11] = pose[2];
+    return G;
+}
+
+// joint transform of frame f for parameter theta (frame.py:98-114, rotation_conversions.py:43-71)
+__device__ __forceinline__ T34 joint_tf(const GqpHandDev &H, int f, const float *theta) {
+    T34 J = t34_identity();
+    int jt = H.frame_jtype[f], d = H.frame_dof[f];
+    if (jt == 1) {
+        float th = d >= 0 ? theta[d] : 0.0f;
+        th = th + 2.0f * ((th > 0.0f ? 1.0f : 0.0f) - 0.5f) * 1e-2f;
+        float s, c;
+        sincosf(th * 0.5f, &s, &c);
+        float r = c, i = s * H.frame_axis[f][0], j = s * H.frame_axis[f][1], k = s * H.frame_axis[f][2];
+        float two_s = 2.0f / (r * r + i * i + j * j + k * k);
+        J.m[0] = 1 - two_s * (j * j + k * k); J.m[1] = two_s * (i * j - k * r); J.m[2] = two_s * (i * k + j * r);
+        J.m[4] = two_s * (i * j + k * r); J.m[5] = 1 - two_s * (i * i + k * k); J.m[6] = two_s * (j * k - i * r);
+        J.m[8] = two_s * (i * k - j * r); J.m[9] = two_s * (j * k + i * r); J.m[10] = 1 - two_s * (i * i + j * j);
+    } else if (jt == 2 && d >= 0) {
+        float th = theta[d];
+        J.m[3] = th * H.frame_axis[f][0]; J.m[7] = th * H.frame_axis[f][1]; J.m[11] = th * H.frame_axis[f][2];
+    }
+    return J;
+}
+
+// world transform of every frame BEFORE its link offset (children hang on it): A[f] = A[parent] * (joff * jt);
+// B[f] = A[parent] * joff is the joint frame (axis / origin for the backward), returned only when wanted.
+template <bool WANT_JOINT_FRAME>
+__device__ __forceinline__ void fk_frames(const GqpHandDev &H, const float *pose, const T34 &G, T34 *A, T34 *Bj) {
+    const float *theta = pose + 9;
+    for (int f = 0; f < H.n_frames; ++f) {
+        int par = H.frame_parent[f];
+        T34 joff = t34_load(H.frame_joff[f]);
+        T34 J = joint_tf(H, f, theta);
+        const T34 &Ap = par < 0 ? G : A[par];
+        A[f] = t34_mul(Ap, t34_mul(joff, J));
+        if (WANT_JOINT_FRAME) Bj[f] = t34_mul(Ap, joff);
+    }
+}
+
+__global__ void __launch_bounds__(FK_THREADS)
+fk_forward_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict__ pose, int Bt,
+                  float *__restrict__ link_tf) {
+    __shared__ GqpHandDev H;
+    load_hand_tables(&H, hand);
+    __syncthreads();
+    int b = blockIdx.x * FK_THREADS + threadIdx.x;
+    if (b >= Bt) return;
+    const int D = 9 + H.n_dofs;
+    float prow[9 + GQP_MAX_DOFS];
+    for (int i = 0; i < D; ++i) prow[i] = pose[(size_t)b * D + i];
+    GramSchmidt gs;
+    T34 G = global_tf(prow, gs);
+    T34 A[GQP_MAX_FRAMES];
+    fk_frames<false>(H, prow, G, A, nullptr);
+    for (int l = 0; l < H.n_links; ++l) {
+        int f = H.link_frame[l];
+        T34 W = t34_mul(A[f], t34_load(H.frame_loff[f]));
+        float *o = link_tf + ((size_t)b * H.n_links + l) * 12;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) o[i] = W.m[i];
+    }
+}
+
+__global__ void __launch_bounds__(FK_THREADS)
+fk_backward_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict__ pose,
+                   const float *__restrict__ grad_link_tf, const float *__restrict__ grad_pose_extra, int Bt,
+                   float *__restrict__ grad_pose) {
+    __shared__ GqpHandDev H;
+    load_hand_tables(&H, hand);
+    __syncthreads();
+    int b = blockIdx.x * FK_THREADS + threadIdx.x;
+    if (b >= Bt) return;
+    const int D = 9 + H.n_dofs;
+    float prow[9 + GQP_MAX_DOFS], gp[9 + GQP_MAX_DOFS];
+    for (int i = 0; i < D; ++i) {
+        prow[i] = pose[(size_t)b * D + i];
+        gp[i] = 0.f;
+    }
+    GramSchmidt gs;
+    T34 G = global_tf(prow, gs);
+    T34 A[GQP_MAX_FRAMES], Bj[GQP_MAX_FRAMES];
+    fk_frames<true>(H, prow, G, A, Bj);
+    // wrench (torque about the world origin, force) that the loss exerts on every frame
+    float accM[GQP_MAX_FRAMES][3], accF[GQP_MAX_FRAMES][3];
+    for (int f = 0; f < H.n_frames; ++f)
+        for (int k = 0; k < 3; ++k) accM[f][k] = accF[f][k] = 0.f;
+    float S[9];  // sum_l gW.R W.R^T + gW.t (W.t - t_g)^T
+    for (int i = 0; i < 9; ++i) S[i] = 0.f;
+    V3 tg = V3{prow[0], prow[1], prow[2]};
+    for (int l = 0; l < H.n_links; ++l) {
+        int f = H.link_frame[l];
+        T34 W = t34_mul(A[f], t34_load(H.frame_loff[f]));
+        T34 g = t34_load(grad_link_tf + ((size_t)b * H.n_links + l) * 12);
+        V3 gt = V3{g.m[3], g.m[7], g.m[11]}, wt = V3{W.m[3], W.m[7], W.m[11]};
+        V3 M = cross3(wt, gt);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            V3 rk = V3{W.m[k], W.m[4 + k], W.m[8 + k]}, gk = V3{g.m[k], g.m[4 + k], g.m[8 + k]};
+            M = M + cross3(rk, gk);
+        }
+        accM[f][0] += M.x; accM[f][1] += M.y; accM[f][2] += M.z;
+        accF[f][0] += gt.x; accF[f][1] += gt.y; accF[f][2] += gt.z;
+        V3 dt = wt - tg;
+        float dtv[3] = {dt.x, dt.y, dt.z}, gtv[3] = {gt.x, gt.y, gt.z};
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                S[3 * i + j] += g.m[4 * i] * W.m[4 * j] + g.m[4 * i + 1] * W.m[4 * j + 1] +
+                                g.m[4 * i + 2] * W.m[4 * j + 2] + gtv[i] * dtv[j];
+    }
+    V3 Ftot = V3{0, 0, 0};
+    for (int f = H.n_frames - 1; f >= 0; --f) {
+        V3 M = V3{accM[f][0], accM[f][1], accM[f][2]}, F = V3{accF[f][0], accF[f][1], accF[f][2]};
+        int jt = H.frame_jtype[f], d = H.frame_dof[f];
+        if (jt != 0 && d >= 0) {
+            V3 a = t34_vec(Bj[f], V3{H.frame_axis[f][0], H.frame_axis[f][1], H.frame_axis[f][2]});
+            if (jt == 1) {
+                V3 o = V3{Bj[f].m[3], Bj[f].m[7], Bj[f].m[11]};
+                gp[9 + d] += dot3(a, M - cross3(o, F));
+            } else {
+                gp[9 + d] += dot3(a, F);
+            }
+        }
+        int par = H.frame_parent[f];
+        if (par >= 0) {
+            accM[par][0] += M.x; accM[par][1] += M.y; accM[par][2] += M.z;
+            accF[par][0] += F.x; accF[par][1] += F.y; accF[par][2] += F.z;
+        } else {
+            Ftot = Ftot + F;
+        }
+    }
+    gp[0] = Ftot.x; gp[1] = Ftot.y; gp[2] = Ftot.z;
+    // dL/dR_g = S R_g, columns -> (x^, y^, z); then back through the Gram-Schmidt
+    float Rg[9] = {G.m[0], G.m[1], G.m[2], G.m[4], G.m[5], G.m[6], G.m[8], G.m[9], G.m[10]};
+    float gR[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) gR[3 * i + j] = S[3 * i] * Rg[j] + S[3 * i + 1] * Rg[3 + j] + S[3 * i + 2] * Rg[6 + j];
+    V3 gxh = V3{gR[0], gR[3], gR[6]}, gyh = V3{gR[1], gR[4], gR[7]}, gz = V3{gR[2], gR[5], gR[8]};
+    gxh = gxh + cross3(gs.yh, gz);
+    gyh = gyh + cross3(gz, gs.xh);
+    V3 gyp = (gyh - gs.yh * dot3(gs.yh, gyh)) * (1.0f / gs.ny);
+    V3 gy = gyp;
+    float gd = -dot3(gs.xh, gyp);
+    gxh = gxh - gyp * gs.d;
+    gxh = gxh + gs.y * gd;
+    gy = gy + gs.xh * gd;
+    V3 gx = (gxh - gs.xh * dot3(gs.xh, gxh)) * (1.0f / gs.nx);
+    gp[3] = gx.x; gp[4] = gx.y; gp[5] = gx.z;
+    gp[6] = gy.x; gp[7] = gy.y; gp[8] = gy.z;
+    for (int i = 0; i < D; ++i)
+        grad_pose[(size_t)b * D + i] = gp[i] + (grad_pose_extra ? grad_pose_extra[(size_t)b * D + i] : 0.f);
+}
+
+// ---- H3: contact candidates -> world contact points / normals (hand_model.py:787-831, 1220-1267) -------------------
+// forward: a thread per (candidate, contact).  The reference transforms all C candidates and gathers n_c of them.
+__global__ void contacts_forward_kernel(const float *__restrict__ cand, const float *__restrict__ cand_normal,
+                                        const int32_t *__restrict__ cand_link, int n_cand, int n_links,
+                                        const float *__restrict__ link_tf, const int32_t *__restrict__ idx, int n,
+                                        int n_c, float *__restrict__ cpts, float *__restrict__ cnrm) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int b = i / n_c;
+    int k = idx[i];
+    k = k < 0 ? 0 : (k >= n_cand ? n_cand - 1 : k);
+    int l = cand_link[k];
+    T34 W = t34_load(link_tf + ((size_t)b * n_links + l) * 12);
+    st3(cpts + 3 * (size_t)i, t34_point(W, ld3(cand + 3 * k)));
+    st3(cnrm + 3 * (size_t)i, t34_vec(W, ld3(cand_normal + 3 * k)));
+}
+// backward: a thread per candidate walks its n_c contacts (no atomics, deterministic); accumulates into grad_link_tf.
+__global__ void contacts_backward_kernel(const float *__restrict__ cand, const float *__restrict__ cand_normal,
+                                         const int32_t *__restrict__ cand_link, int n_cand, int n_links,
+                                         const int32_t *__restrict__ idx, const float *__restrict__ grad_cpts,
+                                         const float *__restrict__ grad_cnrm, int Bt, int n_c,
+                                         float *__restrict__ grad_link_tf) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    for (int c = 0; c < n_c; ++c) {
+        size_t i = (size_t)b * n_c + c;
+        int k = idx[i];
+        k = k < 0 ? 0 : (k >= n_cand ? n_cand - 1 : k);
+        int l = cand_link[k];
+        V3 p = ld3(cand + 3 * k), nn = ld3(cand_normal + 3 * k);
+        V3 gpnt = grad_cpts ? ld3(grad_cpts + 3 * i) : V3{0, 0, 0};
+        V3 gn = grad_cnrm ? ld3(grad_cnrm + 3 * i) : V3{0, 0, 0};
+        float *g = grad_link_tf + ((size_t)b * n_links + l) * 12;
+        float gpv[3] = {gpnt.x, gpnt.y, gpnt.z}, gnv[3] = {gn.x, gn.y, gn.z};
+        float pv[3] = {p.x, p.y, p.z}, nv[3] = {nn.x, nn.y, nn.z};
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q) g[4 * r + q] += gpv[r] * pv[q] + gnv[r] * nv[q];
+            g[4 * r + 3] += gpv[r];
+        }
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
+    if (!d || !out) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: null argument");
+    if (d->n_frames <= 0 || d->n_frames > GQP_MAX_FRAMES || d->n_links <= 0 || d->n_links > GQP_MAX_LINKS ||
+        d->n_dofs < 0 || d->n_dofs > GQP_MAX_DOFS || d->n_cand <= 0 || d->n_spheres < 0)
+        return gqp_set_error(GQP_ERR_LIMIT, "gqp_hand_create: sizes out of range (frames %d/%d links %d/%d dofs %d/%d)",
+                             d->n_frames, GQP_MAX_FRAMES, d->n_links, GQP_MAX_LINKS, d->n_dofs, GQP_MAX_DOFS);
+    GqpHand *h = new GqpHand();
+    GqpHandDev &H = h->host;
+    std::memset(&H, 0, sizeof(H));
+    H.n_frames = d->n_frames; H.n_dofs = d->n_dofs; H.n_links = d->n_links; H.n_cand = d->n_cand;
+    H.n_spheres = d->n_spheres;
+    for (int f = 0; f < d->n_frames; ++f) {
+        H.frame_parent[f] = d->frame_parent_host[f];
+        H.frame_jtype[f] = d->frame_jtype_host[f];
+        H.frame_dof[f] = d->frame_dof_host[f];
+        H.frame_link[f] = -1;
+        if (H.frame_parent[f] >= f || H.frame_dof[f] >= d->n_dofs) {
+            delete h;
+            return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: frame %d: parent must precede it, dof < n_dofs", f);
+        }
+        for (int k = 0; k < 3; ++k) H.frame_axis[f][k] = d->frame_axis_host[3 * f + k];
+        for (int k = 0; k < 12; ++k) {
+            H.frame_joff[f][k] = d->frame_joff_host[12 * f + k];
+            H.frame_loff[f][k] = d->frame_loff_host[12 * f + k];
+        }
+    }
+    for (int l = 0; l < d->n_links; ++l) {
+        H.link_frame[l] = d->link_frame_host[l];
+        H.frame_link[H.link_frame[l]] = l;
+    }
+    for (int j = 0; j < d->n_dofs; ++j) {
+        H.joints_lower[j] = d->joints_lower_host[j];
+        H.joints_upper[j] = d->joints_upper_host[j];
+    }
+    for (int k = 0; k < d->n_cand; ++k)
+        if (d->cand_link_host[k] < 0 || d->cand_link_host[k] >= d->n_links) {
+            delete h;
+            return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: cand_link[%d] out of range", k);
+        }
+    h->d_dev = (GqpHandDev *)gqp_dev_alloc_upload(&H, sizeof(H));
+    h->d_cand = (float *)gqp_dev_alloc_upload(d->cand_host, sizeof(float) * 3 * d->n_cand);
+    h->d_cand_normal = (float *)gqp_dev_alloc_upload(d->cand_normal_host, sizeof(float) * 3 * d->n_cand);
+    h->d_cand_link = (int32_t *)gqp_dev_alloc_upload(d->cand_link_host, sizeof(int32_t) * d->n_cand);
+    h->d_spheres = (float *)gqp_dev_alloc_upload(d->spheres_host, sizeof(float) * 4 * d->n_spheres);
+    h->d_sphere_link = (int32_t *)gqp_dev_alloc_upload(d->sphere_link_host, sizeof(int32_t) * d->n_spheres);
+    h->face_offset.assign(d->face_offset_host, d->face_offset_host + d->n_links + 1);
+    if (!h->d_dev || !h->d_cand || !h->d_cand_normal || !h->d_cand_link || !h->d_spheres || !h->d_sphere_link) {
+        gqp_hand_destroy(h);
+        return gqp_set_error(GQP_ERR_CUDA, "gqp_hand_create: device allocation failed");
+    }
+    int rc = gqp_pen_tables_create(h, d->face_verts_host);
+    if (rc != GQP_OK) {
+        gqp_hand_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return GQP_OK;
+}
+
+extern "C" void gqp_hand_destroy(GqpHand *h) {
+    if (!h) return;
+    gqp_pen_tables_destroy(h);
+    gqp_dev_free(h->d_dev); gqp_dev_free(h->d_cand); gqp_dev_free(h->d_cand_normal); gqp_dev_free(h->d_cand_link);
+    gqp_dev_free(h->d_spheres); gqp_dev_free(h->d_sphere_link);
+    delete h;
+}
+
+extern "C" int gqp_fk_forward(const GqpHand *h, const float *pose, int Bt, float *link_tf, void *stream) {
+    if (!h || Bt < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_forward: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!pose || !link_tf) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_forward: null pointer");
+    GQP_LAUNCH(fk_forward_kernel, (Bt + FK_THREADS - 1) / FK_THREADS, FK_THREADS, 0, (cudaStream_t)stream, h->d_dev,
+               pose, Bt, link_tf);
+    GQP_CHECK_LAUNCH("gqp_fk_forward");
+    return GQP_OK;
+}
+
+extern "C" int gqp_fk_backward(const GqpHand *h, const float *pose, const float *grad_link_tf,
+                               const float *grad_pose_extra, int Bt, float *grad_pose, void *stream) {
+    if (!h || Bt < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_backward: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!pose || !grad_link_tf || !grad_pose) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_backward: null pointer");
+    GQP_LAUNCH(fk_backward_kernel, (Bt + FK_THREADS - 1) / FK_THREADS, FK_THREADS, 0, (cudaStream_t)stream, h->d_dev,
+               pose, grad_link_tf, grad_pose_extra, Bt, grad_pose);
+    GQP_CHECK_LAUNCH("gqp_fk_backward");
+    return GQP_OK;
+}
+
+extern "C" int gqp_contacts_forward(const GqpHand *h, const float *link_tf, const int32_t *idx, int Bt, int n_c,
+                                    float *cpts, float *cnrm, void *stream) {
+    if (!h || Bt < 0 || n_c <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_contacts_forward: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!link_tf || !idx || !cpts || !cnrm) return gqp_set_error(GQP_ERR_ARG, "gqp_contacts_forward: null pointer");
+    int n = Bt * n_c;
+    GQP_LAUNCH(contacts_forward_kernel, (n + 255) / 256, 256, 0, (cudaStream_t)stream, h->d_cand, h->d_cand_normal,
+               h->d_cand_link, h->host.n_cand, h->host.n_links, link_tf, idx, n, n_c, cpts, cnrm);
+    GQP_CHECK_LAUNCH("gqp_contacts_forward");
+    return GQP_OK;
+}
+
+extern "C" int gqp_contacts_backward(const GqpHand *h, const int32_t *idx, const float *grad_cpts,
+                                     const float *grad_cnrm, int Bt, int n_c, float *grad_link_tf, void *stream) {
+    if (!h || Bt < 0 || n_c <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_contacts_backward: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!idx || !grad_link_tf) return gqp_set_error(GQP_ERR_ARG, "gqp_contacts_backward: null pointer");
+    GQP_LAUNCH(contacts_backward_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, h->d_cand, h->d_cand_normal,
+               h->d_cand_link, h->host.n_cand, h->host.n_links, idx, grad_cpts, grad_cnrm, Bt, n_c, grad_link_tf);
+    GQP_CHECK_LAUNCH("gqp_contacts_backward");
+    return GQP_OK;
+}

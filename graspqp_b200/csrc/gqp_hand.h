@@ -1,0 +1,73 @@
+// Internal layout of the opaque handles of include/graspqp_b200.h.
+#pragma once
+#include <stdint.h>
+
+#include <vector>
+
+#define GQP_MAX_FRAMES 48
+#define GQP_MAX_LINKS 32
+#define GQP_MAX_DOFS 32
+
+// ---- BVH over a triangle mesh (built on the host, gqp_bvh.cpp) ----------------------------------------------------
+// Node = 32 bytes: box min (3 floats), `a`, box max (3 floats), `b`.
+//   inner node: a = index of left child, b = index of right child (both > 0), count == 0 is encoded as b >= 0
+//   leaf      : a = first slot in the reordered triangle array, b = -(count)  (count >= 1)
+// Boxes are inflated by a few ulps so that a box's fp32 lower bound never exceeds the fp32 distance of a face inside.
+struct GqpBvhNode {
+    float lo[3];
+    int32_t a;
+    float hi[3];
+    int32_t b;
+};
+
+struct GqpBvhHost {
+    std::vector<GqpBvhNode> nodes;   // nodes[0] = root
+    std::vector<float> tris;         // (F,9) vertices in leaf order
+    std::vector<int32_t> face_id;    // (F) original face index of slot i
+    int max_depth = 0;
+};
+// leaf_size: max faces per leaf
+void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &out);
+
+// Far-field sign grid of one mesh (gqp_bvh.cpp): bit = 1 when EVERY point of the cell is provably on the positive
+// side of the plane of every face that can be its nearest face, i.e. the reference's sign heuristic returns +1 there.
+// Cell (x,y,z) -> bit ((z*dim[1]+y)*dim[0]+x).
+void gqp_sign_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
+                         std::vector<uint32_t> &bits);
+
+struct GqpMesh {
+    int F = 0;
+    int n_nodes = 0;
+    int max_depth = 0;
+    GqpBvhNode *d_nodes = nullptr;  // device
+    float *d_tris = nullptr;        // device (F,9) leaf order
+    int32_t *d_face_id = nullptr;   // device (F)
+};
+
+// Device-side view of the hand tables (one contiguous blob, see gqp_hand.cu)
+struct GqpHandDev {
+    int32_t n_frames, n_dofs, n_links, n_cand, n_spheres;
+    int32_t frame_parent[GQP_MAX_FRAMES], frame_jtype[GQP_MAX_FRAMES], frame_dof[GQP_MAX_FRAMES];
+    int32_t frame_link[GQP_MAX_FRAMES];  // mesh-link id hanging on the frame, or -1
+    float frame_axis[GQP_MAX_FRAMES][3];
+    float frame_joff[GQP_MAX_FRAMES][12];
+    float frame_loff[GQP_MAX_FRAMES][12];
+    int32_t link_frame[GQP_MAX_LINKS];
+    float joints_lower[GQP_MAX_DOFS], joints_upper[GQP_MAX_DOFS];
+};
+
+struct GqpPenTables;  // gqp_pen.cu
+
+struct GqpHand {
+    GqpHandDev host;              // host copy
+    GqpHandDev *d_dev = nullptr;  // device copy
+    float *d_cand = nullptr, *d_cand_normal = nullptr;  // (n_cand,3)
+    int32_t *d_cand_link = nullptr;                      // (n_cand)
+    float *d_spheres = nullptr;                          // (n_spheres,4)
+    int32_t *d_sphere_link = nullptr;                    // (n_spheres)
+    std::vector<int32_t> face_offset;                    // host (n_links+1)
+    GqpPenTables *pen = nullptr;                         // per-link BVHs + sign grids (device blob)
+};
+
+int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host);
+void gqp_pen_tables_destroy(GqpHand *h);

@@ -1,0 +1,171 @@
+// Meshes with a BVH: the exact-winner accelerated form of K1, and O1 = ObjectModel.cal_distance
+// (core/object_model.py:186-255, TORCHSDF branch) for all objects of a device in one launch.
+// A thread owns a query point and walks the BVH (nodes 32 B, read as two float4 through L1/L2; a 50k-face object mesh is
+// 1.8 MB of faces + 0.8 MB of nodes, L2 resident).  Arithmetic per (point, face) is the non-contracted reference order,
+// so distances, signs and closest points are bit-identical to gqp_sdf_forward and to the host-compiled reference.
+#include "gqp_bvh.cuh"
+#include "graspqp_b200.h"
+
+struct GqpObjSet {
+    int n_obj = 0;
+    std::vector<const GqpMesh *> meshes;
+    const GqpBvhNode **d_nodes = nullptr;
+    const float **d_tris = nullptr;
+    const int32_t **d_face_id = nullptr;
+};
+
+__global__ void __launch_bounds__(128)
+mesh_sdf_kernel(const GqpBvhNode *__restrict__ nodes, const float *__restrict__ tris,
+                const int32_t *__restrict__ face_id, const float *__restrict__ points, int P,
+                float *__restrict__ dist2, int32_t *__restrict__ sign, float *__restrict__ normals,
+                float *__restrict__ clst, int32_t *__restrict__ face_out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    V3 p = ld3(points + 3 * (size_t)i);
+    SdfBest best;
+    sdf_best_init(best);
+    bvh_query<true>(nodes, tris, face_id, p, best);
+    int sg;
+    V3 un;
+    sdf_finish<true>(p, best, sg, un);
+    dist2[i] = best.d2;
+    sign[i] = sg;
+    st3(normals + 3 * (size_t)i, un);
+    st3(clst + 3 * (size_t)i, best.c);
+    if (face_out) face_out[i] = best.face;
+}
+
+// O1 forward: query i belongs to object i / (batch_each * n_pts)
+__global__ void __launch_bounds__(128)
+object_distance_kernel(const GqpBvhNode *const *__restrict__ nodes, const float *const *__restrict__ tris,
+                       const int32_t *const *__restrict__ face_id, int per_obj, int n, const float *__restrict__ x,
+                       float scale, float *__restrict__ distance, float *__restrict__ normals,
+                       float *__restrict__ clst, int32_t *__restrict__ sign) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int o = i / per_obj;
+    V3 p = ld3(x + 3 * (size_t)i);
+    p = V3{p.x / scale, p.y / scale, p.z / scale};  // object_model.py:215-216
+    SdfBest best;
+    sdf_best_init(best);
+    bvh_query<true>(nodes[o], tris[o], face_id[o], p, best);
+    int sg;
+    V3 un;
+    sdf_finish<true>(p, best, sg, un);
+    float d = sqrtf(best.d2 + 1e-8f) * (float)(-sg);  // :243
+    distance[i] = d * scale;                          // :249
+    st3(normals + 3 * (size_t)i, un * (float)sg);     // :246
+    st3(clst + 3 * (size_t)i, best.c);
+    sign[i] = sg;
+}
+
+// O1 backward: TorchSDF backward (2 g' (p-c), sdf.py:60-66) chained through sqrt(d2+1e-8)*(-sign)*scale and p = x/scale
+__global__ void object_distance_backward_kernel(const float *__restrict__ grad_distance, const float *__restrict__ x,
+                                                const float *__restrict__ clst, const int32_t *__restrict__ sign,
+                                                int n, float scale, float *__restrict__ grad_x) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V3 p = ld3(x + 3 * (size_t)i);
+    p = V3{p.x / scale, p.y / scale, p.z / scale};
+    V3 dv = p - ld3(clst + 3 * (size_t)i);
+    float d2 = dot3(dv, dv);
+    float g = grad_distance[i] * (float)(-sign[i]) / sqrtf(d2 + 1e-8f);
+    st3(grad_x + 3 * (size_t)i, dv * g);
+}
+
+extern "C" int gqp_mesh_create(const float *face_verts_host, int F, GqpMesh **out) {
+    if (!face_verts_host || F <= 0 || !out) return gqp_set_error(GQP_ERR_ARG, "gqp_mesh_create: need F > 0");
+    GqpBvhHost bvh;
+    gqp_bvh_build(face_verts_host, F, 4, bvh);
+    if (bvh.max_depth > GQP_BVH_STACK - 2)
+        return gqp_set_error(GQP_ERR_LIMIT, "gqp_mesh_create: BVH depth %d exceeds the traversal stack", bvh.max_depth);
+    GqpMesh *m = new GqpMesh();
+    m->F = F;
+    m->n_nodes = (int)bvh.nodes.size();
+    m->max_depth = bvh.max_depth;
+    m->d_nodes = (GqpBvhNode *)gqp_dev_alloc_upload(bvh.nodes.data(), bvh.nodes.size() * sizeof(GqpBvhNode));
+    m->d_tris = (float *)gqp_dev_alloc_upload(bvh.tris.data(), bvh.tris.size() * sizeof(float));
+    m->d_face_id = (int32_t *)gqp_dev_alloc_upload(bvh.face_id.data(), bvh.face_id.size() * sizeof(int32_t));
+    if (!m->d_nodes || !m->d_tris || !m->d_face_id) {
+        gqp_mesh_destroy(m);
+        return gqp_set_error(GQP_ERR_CUDA, "gqp_mesh_create: device allocation failed");
+    }
+    *out = m;
+    return GQP_OK;
+}
+extern "C" void gqp_mesh_destroy(GqpMesh *m) {
+    if (!m) return;
+    gqp_dev_free(m->d_nodes); gqp_dev_free(m->d_tris); gqp_dev_free(m->d_face_id);
+    delete m;
+}
+extern "C" int gqp_mesh_num_faces(const GqpMesh *m) { return m ? m->F : 0; }
+
+extern "C" int gqp_mesh_sdf_forward(const GqpMesh *m, const float *points, int P, float *dist2, int32_t *sign,
+                                    float *normals, float *clst, int32_t *face, void *stream) {
+    if (!m || P < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_mesh_sdf_forward: bad argument");
+    if (P == 0) return GQP_OK;
+    if (!points || !dist2 || !sign || !normals || !clst) return gqp_set_error(GQP_ERR_ARG, "gqp_mesh_sdf_forward: null pointer");
+    GQP_LAUNCH(mesh_sdf_kernel, (P + 127) / 128, 128, 0, (cudaStream_t)stream, m->d_nodes, m->d_tris, m->d_face_id,
+               points, P, dist2, sign, normals, clst, face);
+    GQP_CHECK_LAUNCH("gqp_mesh_sdf_forward");
+    return GQP_OK;
+}
+
+extern "C" int gqp_objset_create(const GqpMesh *const *meshes_host, int n_obj, GqpObjSet **out) {
+    if (!meshes_host || n_obj <= 0 || !out) return gqp_set_error(GQP_ERR_ARG, "gqp_objset_create: bad argument");
+    GqpObjSet *s = new GqpObjSet();
+    s->n_obj = n_obj;
+    std::vector<const GqpBvhNode *> n(n_obj);
+    std::vector<const float *> t(n_obj);
+    std::vector<const int32_t *> f(n_obj);
+    for (int o = 0; o < n_obj; ++o) {
+        if (!meshes_host[o]) {
+            delete s;
+            return gqp_set_error(GQP_ERR_ARG, "gqp_objset_create: mesh %d is null", o);
+        }
+        s->meshes.push_back(meshes_host[o]);
+        n[o] = meshes_host[o]->d_nodes; t[o] = meshes_host[o]->d_tris; f[o] = meshes_host[o]->d_face_id;
+    }
+    s->d_nodes = (const GqpBvhNode **)gqp_dev_alloc_upload(n.data(), n_obj * sizeof(void *));
+    s->d_tris = (const float **)gqp_dev_alloc_upload(t.data(), n_obj * sizeof(void *));
+    s->d_face_id = (const int32_t **)gqp_dev_alloc_upload(f.data(), n_obj * sizeof(void *));
+    if (!s->d_nodes || !s->d_tris || !s->d_face_id) {
+        gqp_objset_destroy(s);
+        return gqp_set_error(GQP_ERR_CUDA, "gqp_objset_create: device allocation failed");
+    }
+    *out = s;
+    return GQP_OK;
+}
+extern "C" void gqp_objset_destroy(GqpObjSet *s) {
+    if (!s) return;
+    gqp_dev_free((void *)s->d_nodes); gqp_dev_free((void *)s->d_tris); gqp_dev_free((void *)s->d_face_id);
+    delete s;
+}
+
+extern "C" int gqp_object_distance_forward(const GqpObjSet *s, int batch_each, int n_pts, const float *x, float scale,
+                                           float *distance, float *normals, float *clst, int32_t *sign,
+                                           void *stream) {
+    if (!s || batch_each < 0 || n_pts < 0 || !(scale > 0.f))
+        return gqp_set_error(GQP_ERR_ARG, "gqp_object_distance_forward: bad argument");
+    long long n = (long long)s->n_obj * batch_each * n_pts;
+    if (n == 0) return GQP_OK;
+    if (n > 0x7fffffffLL) return gqp_set_error(GQP_ERR_LIMIT, "gqp_object_distance_forward: too many queries");
+    if (!x || !distance || !normals || !clst || !sign)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_object_distance_forward: null pointer");
+    GQP_LAUNCH(object_distance_kernel, (int)((n + 127) / 128), 128, 0, (cudaStream_t)stream, s->d_nodes, s->d_tris,
+               s->d_face_id, batch_each * n_pts, (int)n, x, scale, distance, normals, clst, sign);
+    GQP_CHECK_LAUNCH("gqp_object_distance_forward");
+    return GQP_OK;
+}
+
+extern "C" int gqp_object_distance_backward(const float *grad_distance, const float *x, const float *clst,
+                                            const int32_t *sign, int n, float scale, float *grad_x, void *stream) {
+    if (n < 0 || !(scale > 0.f)) return gqp_set_error(GQP_ERR_ARG, "gqp_object_distance_backward: bad argument");
+    if (n == 0) return GQP_OK;
+    if (!grad_distance || !x || !clst || !sign || !grad_x)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_object_distance_backward: null pointer");
+    GQP_LAUNCH(object_distance_backward_kernel, (n + 255) / 256, 256, 0, (cudaStream_t)stream, grad_distance, x, clst,
+               sign, n, scale, grad_x);
+    GQP_CHECK_LAUNCH("gqp_object_distance_backward");
+    return GQP_OK;
+}

@@ -1,0 +1,381 @@
+// H4 — HandModel.cal_distance / E_pen (core/hand_model.py:875-987, core/energy.py:57-62): signed penetration depth of
+// the object's surface samples into the hand's link meshes, max over links, and H5/E_joints (hand_model.py:989-1040,
+// energy.py:47-54).
+//
+// This is the dominant stage of a grasp-step: the reference runs n_links brute-force TorchSDF launches over
+// Bt*n_pts points (2500 x 3540 point-face tests per candidate for Allegro).  Here:
+//   * one persistent-style grid; every CTA first pulls the hand's "penetration blob" — link headers, far-field sign
+//     grids and the BVH nodes of ALL links — into shared memory with one TMA bulk copy (cp.async.bulk + mbarrier);
+//   * a warp owns 32 consecutive surface samples of one candidate and walks the links in lockstep;
+//   * per (point, link): world->link transform, then a sign-grid lookup (1 shared-memory word).  A set bit proves
+//     that the reference's sign heuristic yields +1 everywhere in that cell, i.e. the link cannot contribute to
+//     relu(max_l d_l): skip.  Otherwise an exact BVH nearest-face search (same winner as brute force).
+//   * energy partials are written per warp-task and summed in a fixed order (deterministic); the gradient w.r.t. the
+//     link transform is accumulated with atomics only for the few penetrating samples.
+// Bound: FP32/ALU issue + shared-memory latency.  Algorithmic HBM bytes per grasp-step: n_links*48 B of transforms
+// + 4 B of energy; the surface samples (30 KB per object) and triangles stay in L2/L1.
+#include "gqp_bvh.cuh"
+#include "gqp_stage.cuh"
+#include "graspqp_b200.h"
+
+struct PenHdr {
+    int32_t n_links, n_grids, links_off, grids_off, nodes_off, bits_off, total_bytes, pad;
+};
+struct PenLink {
+    int32_t node_first, n_nodes, tri_first, n_faces, grid_first, n_grids, pad0, pad1;
+};
+struct PenGrid {
+    float org[3];
+    float inv_cell;
+    int32_t dim[3];
+    int32_t bit_first;  // first 32-bit word
+};
+struct GqpPenTables {
+    std::vector<unsigned char> blob_host;
+    unsigned char *d_blob = nullptr;
+    float *d_tris = nullptr;       // (F_total, 9) leaf order, links concatenated
+    int32_t *d_face_id = nullptr;  // (F_total) index inside the link's original face list
+    int total_bytes = 0;
+};
+
+#define PEN_THREADS 256
+#define PEN_MAX_SMEM (200 * 1024)
+
+// sign-grid lookup; returns true when the cell containing q is proven positive
+__device__ __forceinline__ bool pen_grid_positive(const PenGrid *grids, int first, int n, const uint32_t *bits, V3 q) {
+    for (int g = first; g < first + n; ++g) {
+        const PenGrid &G = grids[g];
+        float fx = (q.x - G.org[0]) * G.inv_cell, fy = (q.y - G.org[1]) * G.inv_cell, fz = (q.z - G.org[2]) * G.inv_cell;
+        if (fx >= 0.f && fy >= 0.f && fz >= 0.f) {
+            int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+            if (ix < G.dim[0] && iy < G.dim[1] && iz < G.dim[2]) {
+                int i = (iz * G.dim[1] + iy) * G.dim[0] + ix;
+                return (bits[G.bit_first + (i >> 5)] >> (i & 31)) & 1u;
+            }
+        }
+    }
+    return false;
+}
+
+template <bool CULL>
+__global__ void __launch_bounds__(PEN_THREADS)
+hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
+                const int32_t *__restrict__ face_id, const float *__restrict__ link_tf, const float *__restrict__ x,
+                int Bt, int batch_each, int n_pts, int per_candidate_points, float *__restrict__ dist_out,
+                float *__restrict__ partial, float w_pen, float *__restrict__ grad_link_tf) {
+    GQP_DYN_SMEM(unsigned char, sm);
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) mbar_init(&bar);
+    __syncthreads();
+    if (threadIdx.x == 0) bulk_load(sm, blob, (uint32_t)blob_bytes, &bar);
+    mbar_wait(&bar, 0);
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(sm);
+    const PenLink *links = reinterpret_cast<const PenLink *>(sm + hdr->links_off);
+    const PenGrid *grids = reinterpret_cast<const PenGrid *>(sm + hdr->grids_off);
+    const GqpBvhNode *nodes = reinterpret_cast<const GqpBvhNode *>(sm + hdr->nodes_off);
+    const uint32_t *bits = reinterpret_cast<const uint32_t *>(sm + hdr->bits_off);
+    const int L = hdr->n_links;
+
+    const int lane = threadIdx.x & 31;
+    const int warps_per_block = PEN_THREADS / 32;
+    const int n_chunks = (n_pts + 31) / 32;
+    const long long n_tasks = (long long)Bt * n_chunks;
+    for (long long task = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;
+         task += (long long)gridDim.x * warps_per_block) {
+        const int b = (int)(task / n_chunks);
+        const int pi = (int)(task % n_chunks) * 32 + lane;
+        const bool valid = pi < n_pts;
+        const int pj = valid ? pi : n_pts - 1;
+        const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
+        const V3 p = ld3(x + (row * n_pts + pj) * 3);
+        float best_d = -__int_as_float(0x7f800000);
+        int best_l = -1;
+        V3 best_g = V3{0, 0, 0};
+        const float *Wb = link_tf + (size_t)b * L * 12;
+        for (int l = 0; l < L; ++l) {
+            const PenLink &K = links[l];
+            if (K.n_faces == 0) continue;  // hand_model.py:919-921: links without a mesh are skipped
+            T34 W;
+#pragma unroll
+            for (int i = 0; i < 12; ++i) W.m[i] = __ldg(Wb + l * 12 + i);
+            V3 q = t34_inv_point(W, p);
+            if (CULL && pen_grid_positive(grids, K.grid_first, K.n_grids, bits, q)) continue;
+            SdfBest best;
+            sdf_best_init(best);
+            bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first, q, best);
+            V3 dv = q - best.c;
+            float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
+            float r = sqrtf(best.d2 + 1e-8f);
+            float d = r * (-sgn);  // hand_model.py:975-976
+            if (d > best_d) {      // :986 max over links (first maximum)
+                best_d = d;
+                best_l = l;
+                best_g = dv * (1.0f / r);
+            }
+        }
+        if (dist_out && valid) dist_out[(size_t)b * n_pts + pi] = best_d;
+        float e = (valid && best_d > 0.f) ? best_d : 0.f;  // energy.py:60-61
+        if (grad_link_tf && e > 0.f) {
+            // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
+            T34 W = t34_load(Wb + best_l * 12);
+            V3 g = best_g * w_pen;
+            float *G = grad_link_tf + ((size_t)b * L + best_l) * 12;
+            float pt[3] = {p.x - W.m[3], p.y - W.m[7], p.z - W.m[11]}, gv[3] = {g.x, g.y, g.z};
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+#pragma unroll
+                for (int i = 0; i < 3; ++i) atomicAdd(G + 4 * j + i, pt[j] * gv[i]);
+                atomicAdd(G + 4 * j + 3, -(W.m[4 * j] * gv[0] + W.m[4 * j + 1] * gv[1] + W.m[4 * j + 2] * gv[2]));
+            }
+        }
+        if (partial) {
+            float s = warp_sum(e);
+            if (lane == 0) partial[task] = s;
+        }
+    }
+}
+
+__global__ void pen_reduce_kernel(const float *__restrict__ partial, int Bt, int n_chunks, float *__restrict__ e_pen) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    float s = 0.f;
+    for (int c = 0; c < n_chunks; ++c) s += partial[(size_t)b * n_chunks + c];
+    e_pen[b] = s;
+}
+
+// ---- H5 + E_joints: a thread per candidate --------------------------------------------------------------------------
+#define GQP_MAX_SPHERES 64
+__global__ void __launch_bounds__(128)
+self_pen_joints_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict__ spheres,
+                       const int32_t *__restrict__ sphere_link, const float *__restrict__ link_tf,
+                       const float *__restrict__ pose, int Bt, float *__restrict__ e_spen, float *__restrict__ e_joints,
+                       float w_spen, float w_joints, float *__restrict__ grad_link_tf,
+                       float *__restrict__ grad_pose_joints) {
+    __shared__ float s_sph[GQP_MAX_SPHERES * 4];
+    __shared__ int32_t s_link[GQP_MAX_SPHERES];
+    __shared__ float s_lo[GQP_MAX_DOFS], s_hi[GQP_MAX_DOFS];
+    const int S = hand->n_spheres, L = hand->n_links, dof = hand->n_dofs;
+    for (int i = threadIdx.x; i < S * 4; i += blockDim.x) s_sph[i] = spheres[i];
+    for (int i = threadIdx.x; i < S; i += blockDim.x) s_link[i] = sphere_link[i];
+    for (int i = threadIdx.x; i < dof; i += blockDim.x) {
+        s_lo[i] = hand->joints_lower[i];
+        s_hi[i] = hand->joints_upper[i];
+    }
+    __syncthreads();
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    const int D = 9 + dof;
+    // E_joints (energy.py:47-54)
+    float ej = 0.f;
+    for (int j = 0; j < dof; ++j) {
+        float th = pose[(size_t)b * D + 9 + j];
+        float g = 0.f;
+        if (th > s_hi[j]) { ej += th - s_hi[j]; g = 1.f; }
+        if (th < s_lo[j]) { ej += s_lo[j] - th; g = -1.f; }
+        if (grad_pose_joints) grad_pose_joints[(size_t)b * D + 9 + j] = g * w_joints;
+    }
+    if (grad_pose_joints)
+        for (int j = 0; j < 9; ++j) grad_pose_joints[(size_t)b * D + j] = 0.f;
+    if (e_joints) e_joints[b] = ej;
+    // self penetration (hand_model.py:989-1040)
+    float wp[GQP_MAX_SPHERES][3];
+    for (int i = 0; i < S; ++i) {
+        T34 W = t34_load(link_tf + ((size_t)b * L + s_link[i]) * 12);
+        V3 c = t34_point(W, V3{s_sph[4 * i], s_sph[4 * i + 1], s_sph[4 * i + 2]});
+        wp[i][0] = c.x; wp[i][1] = c.y; wp[i][2] = c.z;
+    }
+    float es = 0.f;
+    int i0 = 0;
+    while (i0 < S) {
+        int i1 = i0;
+        while (i1 < S && s_link[i1] == s_link[i0]) ++i1;  // spheres of one link: [i0, i1)
+        if (i1 >= S) break;                               // the last link has nothing after it (:1013)
+        float mn = __int_as_float(0x7f800000);
+        int ma = -1, mb = -1;
+        for (int a = i0; a < i1; ++a)
+            for (int c = i1; c < S; ++c) {
+                float dx = wp[a][0] - wp[c][0] + 1e-13f, dy = wp[a][1] - wp[c][1] + 1e-13f,
+                      dz = wp[a][2] - wp[c][2] + 1e-13f;
+                float pen = sqrtf(dx * dx + dy * dy + dz * dz) - (s_sph[4 * a + 3] + s_sph[4 * c + 3]);
+                if (pen < mn) { mn = pen; ma = a; mb = c; }
+            }
+        if (mn < 0.f) {
+            es += -mn;
+            if (grad_link_tf) {
+                float dx = wp[ma][0] - wp[mb][0] + 1e-13f, dy = wp[ma][1] - wp[mb][1] + 1e-13f,
+                      dz = wp[ma][2] - wp[mb][2] + 1e-13f;
+                float inv = -w_spen / sqrtf(dx * dx + dy * dy + dz * dz);  // d(-dis)/da = -(a-b)/dis
+                float g[3] = {dx * inv, dy * inv, dz * inv};
+                for (int side = 0; side < 2; ++side) {
+                    int k = side == 0 ? ma : mb;
+                    float sg = side == 0 ? 1.f : -1.f;
+                    float *G = grad_link_tf + ((size_t)b * L + s_link[k]) * 12;
+                    for (int r = 0; r < 3; ++r) {
+                        for (int q = 0; q < 3; ++q) G[4 * r + q] += sg * g[r] * s_sph[4 * k + q];
+                        G[4 * r + 3] += sg * g[r];
+                    }
+                }
+            }
+        }
+        i0 = i1;
+    }
+    if (e_spen) e_spen[b] = es;
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+static void pad16(std::vector<unsigned char> &v) { v.resize((v.size() + 15) / 16 * 16, 0); }
+
+int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
+    const int L = h->host.n_links;
+    GqpPenTables *T = new GqpPenTables();
+    h->pen = T;
+    std::vector<PenLink> links(L);
+    std::vector<PenGrid> grids;
+    std::vector<GqpBvhNode> nodes;
+    std::vector<uint32_t> bits;
+    std::vector<float> tris;
+    std::vector<int32_t> fid;
+    const float cells[3] = {0.002f, 0.008f, 0.04f}, margins[3] = {0.01f, 0.06f, 0.40f};
+    for (int l = 0; l < L; ++l) {
+        int f0 = h->face_offset[l], F = h->face_offset[l + 1] - f0;
+        PenLink K{};
+        K.node_first = (int)nodes.size();
+        K.tri_first = (int)(tris.size() / 9);
+        K.n_faces = F;
+        K.grid_first = (int)grids.size();
+        if (F > 0) {
+            GqpBvhHost bvh;
+            gqp_bvh_build(face_verts_host + 9 * (size_t)f0, F, 4, bvh);
+            if (bvh.max_depth > GQP_BVH_STACK - 2)
+                return gqp_set_error(GQP_ERR_LIMIT, "hand link %d: BVH too deep (%d)", l, bvh.max_depth);
+            K.n_nodes = (int)bvh.nodes.size();
+            nodes.insert(nodes.end(), bvh.nodes.begin(), bvh.nodes.end());
+            tris.insert(tris.end(), bvh.tris.begin(), bvh.tris.end());
+            fid.insert(fid.end(), bvh.face_id.begin(), bvh.face_id.end());
+            const GqpBvhNode &root = bvh.nodes[0];
+            for (int lev = 0; lev < 3; ++lev) {
+                PenGrid G{};
+                float cell = cells[lev];
+                int dim[3];
+                for (;;) {
+                    bool ok = true;
+                    for (int k = 0; k < 3; ++k) {
+                        dim[k] = (int)std::ceil((root.hi[k] - root.lo[k] + 2 * margins[lev]) / cell);
+                        if (dim[k] > 64) ok = false;
+                    }
+                    if (ok) break;
+                    cell *= 1.25f;
+                }
+                for (int k = 0; k < 3; ++k) {
+                    G.dim[k] = dim[k];
+                    G.org[k] = 0.5f * (root.lo[k] + root.hi[k]) - 0.5f * dim[k] * cell;
+                }
+                G.inv_cell = 1.0f / cell;
+                // the device computes (q - org) * inv_cell; build with the cell size that product implies
+                std::vector<uint32_t> gb;
+                gqp_sign_grid_build(bvh, G.org, 1.0f / G.inv_cell, G.dim, gb);
+                G.bit_first = (int)bits.size();
+                bits.insert(bits.end(), gb.begin(), gb.end());
+                grids.push_back(G);
+            }
+        }
+        K.n_grids = (int)grids.size() - K.grid_first;
+        links[l] = K;
+    }
+    PenHdr hdr{};
+    hdr.n_links = L;
+    hdr.n_grids = (int)grids.size();
+    std::vector<unsigned char> &B = T->blob_host;
+    B.resize(sizeof(PenHdr));
+    auto append = [&](const void *p, size_t n) {
+        pad16(B);
+        int off = (int)B.size();
+        B.insert(B.end(), (const unsigned char *)p, (const unsigned char *)p + n);
+        return off;
+    };
+    hdr.links_off = append(links.data(), links.size() * sizeof(PenLink));
+    hdr.grids_off = append(grids.data(), grids.size() * sizeof(PenGrid));
+    hdr.nodes_off = append(nodes.data(), nodes.size() * sizeof(GqpBvhNode));
+    hdr.bits_off = append(bits.data(), bits.size() * sizeof(uint32_t));
+    pad16(B);
+    hdr.total_bytes = (int)B.size();
+    std::memcpy(B.data(), &hdr, sizeof(hdr));
+    if (hdr.total_bytes > PEN_MAX_SMEM)
+        return gqp_set_error(GQP_ERR_LIMIT, "hand penetration tables need %d B of shared memory (limit %d)",
+                             hdr.total_bytes, PEN_MAX_SMEM);
+    T->total_bytes = hdr.total_bytes;
+    T->d_blob = (unsigned char *)gqp_dev_alloc_upload(B.data(), B.size());
+    T->d_tris = (float *)gqp_dev_alloc_upload(tris.data(), tris.size() * sizeof(float));
+    T->d_face_id = (int32_t *)gqp_dev_alloc_upload(fid.data(), fid.size() * sizeof(int32_t));
+    if (!T->d_blob || !T->d_tris || !T->d_face_id) return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
+#ifndef GQP_EMU
+    cudaFuncSetAttribute(hand_pen_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM);
+    cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM);
+#endif
+    return GQP_OK;
+}
+
+void gqp_pen_tables_destroy(GqpHand *h) {
+    if (!h || !h->pen) return;
+    gqp_dev_free(h->pen->d_blob); gqp_dev_free(h->pen->d_tris); gqp_dev_free(h->pen->d_face_id);
+    delete h->pen;
+    h->pen = nullptr;
+}
+
+static int pen_grid_size(int blob_bytes, long long n_tasks) {
+#ifndef GQP_EMU
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int per_sm = (int)std::max(1, std::min(8, (int)((220 * 1024) / (blob_bytes + 1024))));
+    long long want = (n_tasks + PEN_THREADS / 32 - 1) / (PEN_THREADS / 32);
+    return (int)std::max(1LL, std::min<long long>(want, (long long)sms * per_sm));
+#else
+    (void)blob_bytes;
+    return (int)std::max(1LL, std::min<long long>(2, n_tasks));
+#endif
+}
+
+extern "C" int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
+                                 int n_pts, int per_candidate_points, float *dist, float *e_pen, float *scratch,
+                                 float w_pen, float *grad_link_tf, void *stream) {
+    if (!h || n_obj < 0 || batch_each < 0 || n_pts <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: bad argument");
+    const int Bt = n_obj * batch_each;
+    if (Bt == 0) return GQP_OK;
+    if (!link_tf || !x) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: null pointer");
+    if (e_pen && !scratch) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: e_pen needs scratch (Bt*ceil(n_pts/32) floats)");
+    const int n_chunks = (n_pts + 31) / 32;
+    const long long n_tasks = (long long)Bt * n_chunks;
+    const GqpPenTables *T = h->pen;
+    int grid = pen_grid_size(T->total_bytes, n_tasks);
+    float *partial = e_pen ? scratch : nullptr;
+    if (dist) {  // every link's true distance is needed: no culling
+        GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, (size_t)T->total_bytes, (cudaStream_t)stream, T->d_blob,
+                   T->total_bytes, T->d_tris, T->d_face_id, link_tf, x, Bt, batch_each, n_pts, per_candidate_points,
+                   dist, partial, w_pen, grad_link_tf);
+    } else {
+        GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, (size_t)T->total_bytes, (cudaStream_t)stream, T->d_blob,
+                   T->total_bytes, T->d_tris, T->d_face_id, link_tf, x, Bt, batch_each, n_pts, per_candidate_points,
+                   dist, partial, w_pen, grad_link_tf);
+    }
+    GQP_CHECK_LAUNCH("gqp_hand_distance");
+    if (e_pen) {
+        GQP_LAUNCH(pen_reduce_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, partial, Bt, n_chunks, e_pen);
+        GQP_CHECK_LAUNCH("gqp_hand_distance/reduce");
+    }
+    return GQP_OK;
+}
+
+extern "C" int gqp_self_pen_joints(const GqpHand *h, const float *link_tf, const float *pose, int Bt, float *e_spen,
+                                   float *e_joints, float w_spen, float w_joints, float *grad_link_tf,
+                                   float *grad_pose_joints, void *stream) {
+    if (!h || Bt < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_self_pen_joints: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!link_tf || !pose) return gqp_set_error(GQP_ERR_ARG, "gqp_self_pen_joints: null pointer");
+    if (h->host.n_spheres > GQP_MAX_SPHERES) return gqp_set_error(GQP_ERR_LIMIT, "too many penetration spheres");
+    GQP_LAUNCH(self_pen_joints_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, h->d_dev, h->d_spheres,
+               h->d_sphere_link, link_tf, pose, Bt, e_spen, e_joints, w_spen, w_joints, grad_link_tf,
+               grad_pose_joints);
+    GQP_CHECK_LAUNCH("gqp_self_pen_joints");
+    return GQP_OK;
+}

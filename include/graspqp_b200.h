@@ -25,6 +25,7 @@ extern "C" {
 #define GQP_ERR_LIMIT (-3)
 
 typedef struct GqpMesh GqpMesh; /* triangle mesh + BVH + far-field sign grid, device resident */
+typedef struct GqpObjSet GqpObjSet; /* the objects of one device: table of mesh handles for single-launch queries */
 typedef struct GqpHand GqpHand; /* kinematic tree, contact candidates, penetration spheres, link meshes */
 
 int gqp_abi_version(void);
@@ -56,12 +57,15 @@ int gqp_mesh_sdf_forward(const GqpMesh *m, const float *points, int P, float *di
                          float *clst, int32_t *face, void *stream);
 
 /* ---- O1: ObjectModel.cal_distance (object_model.py:186-255, TORCHSDF branch) -----------------------------------------
- * x (n_obj*batch_each, n_pts, 3); object o owns rows [o*batch_each, (o+1)*batch_each).  meshes_host = array of n_obj
- * handles (host array of pointers).  distance = sqrt(d2+1e-8)*(-sign)*scale, normals = unit(p-c)*sign; clst kept for the
- * backward:  grad_x = grad_distance * (-sign) * (p-c)/sqrt(d2+1e-8)  (sdf.py:60-66 chained with :243-249). */
-int gqp_object_distance_forward(const GqpMesh *const *meshes_host, int n_obj, int batch_each, int n_pts,
-                                const float *x, float scale, float *distance, float *normals, float *clst,
-                                int32_t *sign, void *stream);
+ * An object set is the list of meshes of the objects a device optimises (ObjectModel.initialize, object_model.py:70-184);
+ * the meshes must outlive the set.  x (n_obj*batch_each, n_pts, 3); object o owns rows [o*batch_each, (o+1)*batch_each).
+ * distance = sqrt(d2+1e-8)*(-sign)*scale, normals = unit(p-c)*sign (outward object normal); clst and sign are kept for
+ * the backward:  grad_x = grad_distance * (-sign) * (p-c)/sqrt(d2+1e-8)  (sdf.py:60-66 chained with :243-249).
+ * All objects are answered by ONE launch (the reference launches TorchSDF once per object, :217-220). */
+int gqp_objset_create(const GqpMesh *const *meshes_host, int n_obj, GqpObjSet **out);
+void gqp_objset_destroy(GqpObjSet *s);
+int gqp_object_distance_forward(const GqpObjSet *s, int batch_each, int n_pts, const float *x, float scale,
+                                float *distance, float *normals, float *clst, int32_t *sign, void *stream);
 int gqp_object_distance_backward(const float *grad_distance, const float *x, const float *clst, const int32_t *sign,
                                  int n, float scale, float *grad_x, void *stream);
 
@@ -97,10 +101,10 @@ void gqp_hand_destroy(GqpHand *h);
  * pose (Bt, 9+n_dofs): translation, ortho6d, joint angles.  link_tf (Bt, n_links, 12): WORLD transform of every mesh
  * link, row-major 3x4, i.e. [R_g R_l | R_g t_l + t_g].  Includes the reference's +-0.01 rad revolute perturbation.
  * gqp_fk_backward maps d(loss)/d(link_tf) to d(loss)/d(pose) (replaces autograd through the chain, fit.py:440);
- * grad_pose is OVERWRITTEN. */
+ * grad_pose is OVERWRITTEN with that plus grad_pose_extra (Bt, 9+n_dofs; may be NULL, e.g. the joint-limit term). */
 int gqp_fk_forward(const GqpHand *h, const float *pose, int Bt, float *link_tf, void *stream);
-int gqp_fk_backward(const GqpHand *h, const float *pose, const float *grad_link_tf, int Bt, float *grad_pose,
-                    void *stream);
+int gqp_fk_backward(const GqpHand *h, const float *pose, const float *grad_link_tf, const float *grad_pose_extra,
+                    int Bt, float *grad_pose, void *stream);
 
 /* ---- H3: contact gather (hand_model.py:787-831, 1220-1267) ---------------------------------------------------------
  * idx (Bt,n_c) int32 indices into the candidate table; cpts/cnrm (Bt,n_c,3) world position / normal.
@@ -115,10 +119,13 @@ int gqp_contacts_backward(const GqpHand *h, const int32_t *idx, const float *gra
  * repeat, object_model.py:181-184; x_stride_candidates != 0 selects a per-candidate (Bt,n_pts,3) set instead).
  * dist (Bt,n_pts) = max over links of sqrt(d2+1e-8)*(-sign)   [positive inside], may be NULL;
  * e_pen (Bt) = sum_p relu(dist) (energy.py:57-62), may be NULL;
- * grad_link_tf (Bt,n_links,12), may be NULL: ACCUMULATES w_pen * d(e_pen)/d(link_tf). */
+ * scratch: Bt*ceil(n_pts/32) floats of workspace, required when e_pen is wanted (deterministic two-stage sum);
+ * grad_link_tf (Bt,n_links,12), may be NULL: ACCUMULATES w_pen * d(e_pen)/d(link_tf).
+ * With dist == NULL, (point, link) pairs whose sign is provably +1 (far-field sign grid built at gqp_hand_create) are
+ * skipped: they cannot contribute to relu(max).  With dist != NULL every pair is searched. */
 int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each, int n_pts,
-                      int per_candidate_points, float *dist, float *e_pen, float w_pen, float *grad_link_tf,
-                      void *stream);
+                      int per_candidate_points, float *dist, float *e_pen, float *scratch, float w_pen,
+                      float *grad_link_tf, void *stream);
 
 /* ---- H5 + E_joints: self_penetration (hand_model.py:989-1040) and joint limits (energy.py:47-54) ------------------
  * e_spen (Bt), e_joints (Bt); ACCUMULATES w_spen*d(e_spen) into grad_link_tf and OVERWRITES grad_pose_joints
