@@ -141,13 +141,18 @@ void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &ou
     }
 }
 
-// ---- far-field sign grid ----------------------------------------------------------------------------------------------
-// The reference's sign is sign(dot(p - c, n_f)) for the WINNING face f (.cu:236); c lies in f's plane, so this is the
-// side of f's plane p is on.  A cell is flagged when, for every face that can win anywhere in the cell
-// (dist(centre,f) <= d* + 2r, r = cell circumradius, d* = distance of the centre to the mesh), the whole cell is on the
-// positive side of f's plane by a safety margin that dominates fp32 rounding of the runtime test.
+// ---- exact culling of "outside" queries ------------------------------------------------------------------------------
+// The reference's sign is sign(dot(p - c, n_f)) for the WINNING face f (.cu:236); c lies in f's plane, so it is the side
+// of f's plane p is on.  For a closed, consistently outward-oriented manifold mesh and a point p OUTSIDE it, p - c lies
+// in the cone spanned by the normals of the faces incident to the nearest feature; if all faces sharing a vertex have
+// pairwise non-negative normal products ("nice" mesh: no crease sharper than 90 degrees), that cone has a non-negative
+// product with every incident normal, so the reference returns +1 for EVERY outside point, whichever tying face wins.
+// Hence for a nice mesh a query can be skipped as soon as the point is known to be outside: outside the bounding box,
+// or inside a grid cell that lies entirely outside the mesh.
+#include <map>
+#include <array>
 namespace {
-void nearest(const GqpBvhHost &bvh, D3 p, double &best) {
+void nearest(const GqpBvhHost &bvh, D3 p, double &best, int &slot) {
     int stack[128], sp = 0;
     stack[sp++] = 0;
     while (sp) {
@@ -156,7 +161,8 @@ void nearest(const GqpBvhHost &bvh, D3 p, double &best) {
         if (n.b < 0) {
             for (int i = n.a; i < n.a - n.b; ++i) {
                 const float *t = &bvh.tris[9 * (size_t)i];
-                best = std::min(best, tri_dist(p, ldv(t), ldv(t + 3), ldv(t + 6)));
+                double d = tri_dist(p, ldv(t), ldv(t + 3), ldv(t + 6));
+                if (d < best) { best = d; slot = i; }
             }
         } else {
             double dl = box_dist(bvh.nodes[n.a], p), dr = box_dist(bvh.nodes[n.b], p);
@@ -165,52 +171,72 @@ void nearest(const GqpBvhHost &bvh, D3 p, double &best) {
         }
     }
 }
-// all faces within `radius` of p are on whose positive side the ball (p, r) lies entirely?
-bool all_positive(const GqpBvhHost &bvh, D3 p, double radius, double r) {
-    int stack[128], sp = 0;
-    stack[sp++] = 0;
-    while (sp) {
-        const GqpBvhNode &n = bvh.nodes[stack[--sp]];
-        if (box_dist(n, p) > radius) continue;
-        if (n.b < 0) {
-            for (int i = n.a; i < n.a - n.b; ++i) {
-                const float *t = &bvh.tris[9 * (size_t)i];
-                D3 a = ldv(t), b = ldv(t + 3), c = ldv(t + 6);
-                double d = tri_dist(p, a, b, c);
-                if (d > radius) continue;
-                D3 nrm = cross(b - a, c - a);
-                double nl = std::sqrt(dot(nrm, nrm));
-                double e = std::max({std::sqrt(dot(b - a, b - a)), std::sqrt(dot(c - a, c - a)), std::sqrt(dot(c - b, c - b))});
-                if (!(nl > 1e-6 * e * e) || !(nl > 0)) return false;  // sliver: the fp32 normal is unreliable
-                double h = dot(p - a, nrm) / nl;                       // signed plane distance of the centre
-                if (h - r < 1e-5 + 1e-3 * (d + r)) return false;
-            }
-        } else {
-            stack[sp++] = n.a;
-            stack[sp++] = n.b;
-        }
-    }
-    return true;
-}
 }  // namespace
 
-void gqp_sign_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
-                         std::vector<uint32_t> &bits) {
+bool gqp_mesh_is_nice(const float *fv, int F) {
+    if (F < 4) return false;
+    std::map<std::array<float, 3>, int> vid;
+    std::vector<int> idx(3 * (size_t)F);
+    for (int i = 0; i < 3 * F; ++i) {
+        std::array<float, 3> k = {fv[3 * i], fv[3 * i + 1], fv[3 * i + 2]};
+        auto it = vid.find(k);
+        if (it == vid.end()) it = vid.emplace(k, (int)vid.size()).first;
+        idx[i] = it->second;
+    }
+    // closed + consistently oriented: every directed edge appears once and its reverse appears once
+    std::map<std::pair<int, int>, int> edges;
+    for (int f = 0; f < F; ++f)
+        for (int k = 0; k < 3; ++k) {
+            int u = idx[3 * f + k], v = idx[3 * f + (k + 1) % 3];
+            if (u == v) return false;
+            if (++edges[{u, v}] > 1) return false;
+        }
+    for (auto &e : edges)
+        if (!edges.count({e.first.second, e.first.first})) return false;
+    // unit normals; no slivers
+    std::vector<D3> nh(F);
+    for (int f = 0; f < F; ++f) {
+        D3 a = ldv(fv + 9 * f), b = ldv(fv + 9 * f + 3), c = ldv(fv + 9 * f + 6);
+        D3 n = cross(b - a, c - a);
+        double l = std::sqrt(dot(n, n));
+        double e = std::max({dot(b - a, b - a), dot(c - a, c - a), dot(c - b, c - b)});
+        if (!(l > 1e-6 * e)) return false;
+        nh[f] = n * (1.0 / l);
+    }
+    std::vector<std::vector<int>> inc(vid.size());
+    for (int f = 0; f < F; ++f)
+        for (int k = 0; k < 3; ++k) inc[idx[3 * f + k]].push_back(f);
+    for (auto &fs : inc)
+        for (size_t i = 0; i < fs.size(); ++i)
+            for (size_t j = i + 1; j < fs.size(); ++j)
+                if (dot(nh[fs[i]], nh[fs[j]]) < -1e-6) return false;
+    // outward orientation: signed volume > 0
+    double vol = 0;
+    for (int f = 0; f < F; ++f) vol += dot(ldv(fv + 9 * f), cross(ldv(fv + 9 * f + 3), ldv(fv + 9 * f + 6)));
+    return vol > 0;
+}
+
+// bit = 1 when the whole cell is outside the (nice) mesh with a 10 micron margin.  Cell (x,y,z) -> bit
+// ((z*dim[1]+y)*dim[0]+x).
+void gqp_outside_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
+                            std::vector<uint32_t> &bits) {
     size_t ncell = (size_t)dim[0] * dim[1] * dim[2];
     bits.assign((ncell + 31) / 32, 0u);
     if (bvh.nodes.empty()) return;
-    const double r = 0.5 * std::sqrt(3.0) * cell * 1.0001 + 1e-7;  // + slack for the fp32 cell index computation
+    const double r = 0.5 * std::sqrt(3.0) * cell * 1.001 + 1e-5;  // circumradius + slack for the fp32 cell index + margin
     for (int z = 0; z < dim[2]; ++z)
         for (int y = 0; y < dim[1]; ++y)
             for (int x = 0; x < dim[0]; ++x) {
                 D3 c = {origin[0] + (x + 0.5) * (double)cell, origin[1] + (y + 0.5) * (double)cell,
                         origin[2] + (z + 0.5) * (double)cell};
                 double best = 1e30;
-                nearest(bvh, c, best);
-                if (best <= 2 * r) continue;  // the mesh may cross or touch the cell's neighbourhood
-                if (all_positive(bvh, c, best + 2 * r + 1e-7, r)) {
-                    size_t i = ((size_t)z * dim[1] + y) * dim[0] + x;
-                    bits[i >> 5] |= 1u << (i & 31);
-                }
+                int slot = -1;
+                nearest(bvh, c, best, slot);
+                if (slot < 0 || best <= r) continue;
+                const float *t = &bvh.tris[9 * (size_t)slot];
+                D3 a = ldv(t), b = ldv(t + 3), cc = ldv(t + 6);
+                if (dot(c - a, cross(b - a, cc - a)) <= 0) continue;  // centre is inside
+                size_t i = ((size_t)z * dim[1] + y) * dim[0] + x;
+                bits[i >> 5] |= 1u << (i & 31);
             }
 }

@@ -29,11 +29,11 @@ struct GqpBvhHost {
 // leaf_size: max faces per leaf
 void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &out);
 
-// Far-field sign grid of one mesh (gqp_bvh.cpp): bit = 1 when EVERY point of the cell is provably on the positive
-// side of the plane of every face that can be its nearest face, i.e. the reference's sign heuristic returns +1 there.
-// Cell (x,y,z) -> bit ((z*dim[1]+y)*dim[0]+x).
-void gqp_sign_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
-                         std::vector<uint32_t> &bits);
+// Exact culling support (gqp_bvh.cpp): a "nice" mesh is a closed, outward-oriented manifold without creases sharper
+// than 90 degrees; the reference's sign heuristic returns +1 for every point outside such a mesh.
+bool gqp_mesh_is_nice(const float *face_verts, int F);
+void gqp_outside_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
+                            std::vector<uint32_t> &bits);
 
 struct GqpMesh {
     int F = 0;

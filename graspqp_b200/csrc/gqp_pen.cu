@@ -22,7 +22,11 @@ struct PenHdr {
     int32_t n_links, n_grids, links_off, grids_off, nodes_off, bits_off, total_bytes, pad;
 };
 struct PenLink {
-    int32_t node_first, n_nodes, tri_first, n_faces, grid_first, n_grids, pad0, pad1;
+    int32_t node_first, n_nodes, tri_first, n_faces;
+    int32_t grid;  // index of the link's outside-grid, or -1 when the mesh is not "nice" (no culling)
+    int32_t pad;
+    float lo[3], hi[3];  // bounding box, slightly inflated
+    int32_t pad2[4];
 };
 struct PenGrid {
     float org[3];
@@ -38,23 +42,19 @@ struct GqpPenTables {
     int total_bytes = 0;
 };
 
-#define PEN_THREADS 256
+#define PEN_THREADS 768
 #define PEN_MAX_SMEM (200 * 1024)
 
-// sign-grid lookup; returns true when the cell containing q is proven positive
-__device__ __forceinline__ bool pen_grid_positive(const PenGrid *grids, int first, int n, const uint32_t *bits, V3 q) {
-    for (int g = first; g < first + n; ++g) {
-        const PenGrid &G = grids[g];
-        float fx = (q.x - G.org[0]) * G.inv_cell, fy = (q.y - G.org[1]) * G.inv_cell, fz = (q.z - G.org[2]) * G.inv_cell;
-        if (fx >= 0.f && fy >= 0.f && fz >= 0.f) {
-            int ix = (int)fx, iy = (int)fy, iz = (int)fz;
-            if (ix < G.dim[0] && iy < G.dim[1] && iz < G.dim[2]) {
-                int i = (iz * G.dim[1] + iy) * G.dim[0] + ix;
-                return (bits[G.bit_first + (i >> 5)] >> (i & 31)) & 1u;
-            }
-        }
-    }
-    return false;
+// true when q is provably outside the (nice) link mesh: outside its box, or in a grid cell entirely outside it
+__device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *grids, const uint32_t *bits, V3 q) {
+    if (K.grid < 0) return false;
+    if (q.x < K.lo[0] || q.y < K.lo[1] || q.z < K.lo[2] || q.x > K.hi[0] || q.y > K.hi[1] || q.z > K.hi[2]) return true;
+    const PenGrid &G = grids[K.grid];
+    float fx = (q.x - G.org[0]) * G.inv_cell, fy = (q.y - G.org[1]) * G.inv_cell, fz = (q.z - G.org[2]) * G.inv_cell;
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    if (fx < 0.f || fy < 0.f || fz < 0.f || ix >= G.dim[0] || iy >= G.dim[1] || iz >= G.dim[2]) return false;
+    int i = (iz * G.dim[1] + iy) * G.dim[0] + ix;
+    return (bits[G.bit_first + (i >> 5)] >> (i & 31)) & 1u;
 }
 
 template <bool CULL>
@@ -99,7 +99,7 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
 #pragma unroll
             for (int i = 0; i < 12; ++i) W.m[i] = __ldg(Wb + l * 12 + i);
             V3 q = t34_inv_point(W, p);
-            if (CULL && pen_grid_positive(grids, K.grid_first, K.n_grids, bits, q)) continue;
+            if (CULL && pen_outside(K, grids, bits, q)) continue;
             SdfBest best;
             sdf_best_init(best);
             bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first, q, best);
@@ -235,14 +235,13 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     std::vector<uint32_t> bits;
     std::vector<float> tris;
     std::vector<int32_t> fid;
-    const float cells[3] = {0.002f, 0.008f, 0.04f}, margins[3] = {0.01f, 0.06f, 0.40f};
     for (int l = 0; l < L; ++l) {
         int f0 = h->face_offset[l], F = h->face_offset[l + 1] - f0;
         PenLink K{};
         K.node_first = (int)nodes.size();
         K.tri_first = (int)(tris.size() / 9);
         K.n_faces = F;
-        K.grid_first = (int)grids.size();
+        K.grid = -1;
         if (F > 0) {
             GqpBvhHost bvh;
             gqp_bvh_build(face_verts_host + 9 * (size_t)f0, F, 4, bvh);
@@ -253,33 +252,36 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
             tris.insert(tris.end(), bvh.tris.begin(), bvh.tris.end());
             fid.insert(fid.end(), bvh.face_id.begin(), bvh.face_id.end());
             const GqpBvhNode &root = bvh.nodes[0];
-            for (int lev = 0; lev < 3; ++lev) {
+            for (int k = 0; k < 3; ++k) {
+                K.lo[k] = root.lo[k] - 2e-5f;
+                K.hi[k] = root.hi[k] + 2e-5f;
+            }
+            if (gqp_mesh_is_nice(face_verts_host + 9 * (size_t)f0, F)) {
                 PenGrid G{};
-                float cell = cells[lev];
+                float cell = 0.002f;
                 int dim[3];
                 for (;;) {
                     bool ok = true;
                     for (int k = 0; k < 3; ++k) {
-                        dim[k] = (int)std::ceil((root.hi[k] - root.lo[k] + 2 * margins[lev]) / cell);
-                        if (dim[k] > 64) ok = false;
+                        dim[k] = (int)std::ceil((K.hi[k] - K.lo[k]) / cell) + 1;
+                        if (dim[k] > 48) ok = false;
                     }
                     if (ok) break;
-                    cell *= 1.25f;
-                }
-                for (int k = 0; k < 3; ++k) {
-                    G.dim[k] = dim[k];
-                    G.org[k] = 0.5f * (root.lo[k] + root.hi[k]) - 0.5f * dim[k] * cell;
+                    cell *= 1.1f;
                 }
                 G.inv_cell = 1.0f / cell;
-                // the device computes (q - org) * inv_cell; build with the cell size that product implies
+                for (int k = 0; k < 3; ++k) {
+                    G.dim[k] = dim[k];
+                    G.org[k] = 0.5f * (K.lo[k] + K.hi[k]) - 0.5f * dim[k] * (1.0f / G.inv_cell);
+                }
                 std::vector<uint32_t> gb;
-                gqp_sign_grid_build(bvh, G.org, 1.0f / G.inv_cell, G.dim, gb);
+                gqp_outside_grid_build(bvh, G.org, 1.0f / G.inv_cell, G.dim, gb);
                 G.bit_first = (int)bits.size();
                 bits.insert(bits.end(), gb.begin(), gb.end());
+                K.grid = (int)grids.size();
                 grids.push_back(G);
             }
         }
-        K.n_grids = (int)grids.size() - K.grid_first;
         links[l] = K;
     }
     PenHdr hdr{};
@@ -377,5 +379,27 @@ extern "C" int gqp_self_pen_joints(const GqpHand *h, const float *link_tf, const
                h->d_sphere_link, link_tf, pose, Bt, e_spen, e_joints, w_spen, w_joints, grad_link_tf,
                grad_pose_joints);
     GQP_CHECK_LAUNCH("gqp_self_pen_joints");
+    return GQP_OK;
+}
+
+// diagnostics for DESIGN.md / tests: {blob bytes, BVH nodes, grid cells, cells proven positive, faces, grids}
+extern "C" int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host) {
+    if (!h || !h->pen || !info_host) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_pen_info: bad argument");
+    const std::vector<unsigned char> &B = h->pen->blob_host;
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(B.data());
+    const PenGrid *grids = reinterpret_cast<const PenGrid *>(B.data() + hdr->grids_off);
+    const uint32_t *bits = reinterpret_cast<const uint32_t *>(B.data() + hdr->bits_off);
+    long long cells = 0, set = 0;
+    for (int g = 0; g < hdr->n_grids; ++g) {
+        long long n = (long long)grids[g].dim[0] * grids[g].dim[1] * grids[g].dim[2];
+        cells += n;
+        for (long long i = 0; i < n; ++i) set += (bits[grids[g].bit_first + (i >> 5)] >> (i & 31)) & 1u;
+    }
+    info_host[0] = hdr->total_bytes;
+    info_host[1] = (hdr->bits_off - hdr->nodes_off) / (int)sizeof(GqpBvhNode);
+    info_host[2] = (int32_t)cells;
+    info_host[3] = (int32_t)set;
+    info_host[4] = h->face_offset.back();
+    info_host[5] = hdr->n_grids;
     return GQP_OK;
 }

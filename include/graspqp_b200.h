@@ -127,6 +127,9 @@ int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, in
                       int per_candidate_points, float *dist, float *e_pen, float *scratch, float w_pen,
                       float *grad_link_tf, void *stream);
 
+/* diagnostics: info_host[6] = {shared-memory blob bytes, BVH nodes, sign-grid cells, cells proven positive, faces, grids} */
+int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host);
+
 /* ---- H5 + E_joints: self_penetration (hand_model.py:989-1040) and joint limits (energy.py:47-54) ------------------
  * e_spen (Bt), e_joints (Bt); ACCUMULATES w_spen*d(e_spen) into grad_link_tf and OVERWRITES grad_pose_joints
  * (Bt, 9+n_dofs) with w_joints*d(e_joints)/d(pose) (both may be NULL). */

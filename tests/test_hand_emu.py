@@ -86,3 +86,69 @@ def test_contacts(emu, pack, hand):
     gp = np.zeros_like(pose)
     assert emu.gqp_fk_backward(hand, ptr(pose), ptr(gtf), None, B, ptr(gp), None) == 0
     np.testing.assert_allclose(gp, p64.grad.numpy(), rtol=2e-4, atol=2e-5)
+
+
+def _object(seed=2, n=96):
+    v, f = synth.make_mesh("sphere", 300, seed)
+    return v, f, synth.sample_surface(v, f, n, seed=seed)
+
+
+def test_hand_distance_and_pen(emu, pack, hand):
+    """H4: full distances vs the oracle, culled E_pen == un-culled E_pen, gradient vs autograd."""
+    B, n_pts = 3, 96
+    v, f, sp = _object()
+    pose, idx = synth.random_grasp_init(pack, [v], B, 12, 5)
+    pose[:, :3] *= 0.55  # push the hand into the object so that some samples penetrate
+    idx = idx.astype(np.int32)
+    L = len(pack["mesh_frame"])
+    tf = np.zeros((B, L, 12), np.float32)
+    emu.gqp_fk_forward(hand, ptr(pose), B, ptr(tf), None)
+    x = np.ascontiguousarray(sp[None], np.float32)  # (n_obj=1, n_pts, 3)
+    dist = np.zeros((B, n_pts), np.float32)
+    e_full, e_cull = np.zeros(B, np.float32), np.zeros(B, np.float32)
+    scratch = np.zeros(B * ((n_pts + 31) // 32), np.float32)
+    g_full, g_cull = np.zeros((B, L, 12), np.float32), np.zeros((B, L, 12), np.float32)
+    assert emu.gqp_hand_distance(hand, ptr(tf), ptr(x), 1, B, n_pts, 0, ptr(dist), ptr(e_full), ptr(scratch), 100.0,
+                                 ptr(g_full), None) == 0, emu.gqp_last_error()
+    assert emu.gqp_hand_distance(hand, ptr(tf), ptr(x), 1, B, n_pts, 0, None, ptr(e_cull), ptr(scratch), 100.0,
+                                 ptr(g_cull), None) == 0
+    o = HandOracle(pack, torch.float32)
+    p32 = torch.tensor(pose, requires_grad=True)
+    o.set_parameters(p32, torch.tensor(idx).long())
+    xs = torch.tensor(sp).unsqueeze(0).repeat(B, 1, 1)
+    want = o.cal_distance(xs)
+    np.testing.assert_allclose(dist, want.detach().numpy(), atol=1e-5)
+    e_want = torch.relu(want).sum(-1)
+    assert (e_want > 0).any(), "test pose does not penetrate"
+    np.testing.assert_allclose(e_full, e_want.detach().numpy(), rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(e_cull, e_full, rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(g_cull, g_full, rtol=1e-5, atol=1e-6)
+    (100.0 * e_want.sum()).backward()
+    gp = np.zeros_like(pose)
+    assert emu.gqp_fk_backward(hand, ptr(pose), ptr(g_cull), None, B, ptr(gp), None) == 0
+    np.testing.assert_allclose(gp, p32.grad.numpy(), rtol=2e-3, atol=2e-3)
+
+
+def test_self_pen_joints(emu, pack, hand):
+    B = 6
+    pose, idx = _poses(pack, B, 7)
+    pose[:, 9:] += np.random.default_rng(0).normal(size=pose[:, 9:].shape).astype(np.float32) * 0.6  # curl + exceed limits
+    L = len(pack["mesh_frame"])
+    tf = np.zeros((B, L, 12), np.float32)
+    emu.gqp_fk_forward(hand, ptr(pose), B, ptr(tf), None)
+    es, ej = np.zeros(B, np.float32), np.zeros(B, np.float32)
+    gtf, gj = np.zeros((B, L, 12), np.float32), np.zeros_like(pose)
+    assert emu.gqp_self_pen_joints(hand, ptr(tf), ptr(pose), B, ptr(es), ptr(ej), 10.0, 1.0, ptr(gtf), ptr(gj), None) == 0
+    o = HandOracle(pack, torch.float64)
+    p64 = torch.tensor(pose, dtype=torch.float64, requires_grad=True)
+    o.set_parameters(p64, torch.tensor(idx.astype(np.int64)))
+    want_s = o.self_penetration()
+    th = o.hand_pose[:, 9:]
+    want_j = ((th > o.joints_upper) * (th - o.joints_upper)).sum(-1) + ((th < o.joints_lower) * (o.joints_lower - th)).sum(-1)
+    assert (want_s > 0).any() and (want_j > 0).any()
+    np.testing.assert_allclose(es, want_s.detach().numpy(), rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(ej, want_j.detach().numpy(), rtol=1e-5, atol=1e-6)
+    (10.0 * want_s.sum() + want_j.sum()).backward()
+    gp = np.zeros_like(pose)
+    assert emu.gqp_fk_backward(hand, ptr(pose), ptr(gtf), ptr(gj), B, ptr(gp), None) == 0
+    np.testing.assert_allclose(gp, p64.grad.numpy(), rtol=1e-3, atol=1e-4)
