@@ -1,0 +1,495 @@
+// Q1-Q4 + E_dis — the force-closure metric of energy_type=graspqp and the contact-distance term, forward and analytic
+// backward in ONE launch, a warp per candidate.
+//   friction cone  : metrics/ops/span.py:263-295            grasp matrix F (6 x n): span.py:341-346
+//   QP             : metrics/solver/qp_solver.py:60-134 -> qpth.qp.QPFunction(maxIter=12, eps=5e-2) (qpth 0.0.18)
+//   E_fc           : metrics/ops/registry.py:82-87, svd term span.py:402        E_dis: core/energy.py:25-28
+//
+// The QP is  min 1/2 x'(F'F + ridge I)x  s.t.  lower <= x <= upper  (n = 4 n_c <= 64 variables, 2n inequalities).
+// qpth runs a primal-dual interior point method whose Newton systems it solves through a 2n x 2n Schur complement in
+// fp32 LU.  The same Newton steps are computed here in reduced form:  (F'F + M) dx = r  with M = ridge + d_u + d_l
+// diagonal, i.e. by the Woodbury identity  dx = M^-1 r - M^-1 F'(I6 + F M^-1 F')^-1 F M^-1 r : one 6x6 SPD system per
+// solve.  Every lane owns <= 2 variables (its F columns, x, slacks, duals: registers); the 6x6 matrix is reduced across
+// the warp through shared memory and factorised redundantly by every lane.  All QP arithmetic is fp64 (B200 runs fp64
+// at half the fp32 rate; the stage is < 1 % of a grasp-step), so the iterates are the exact-arithmetic iterates of
+// qpth's algorithm rather than one fp32 realisation of them.
+// Implicit differentiation (qpth QPFunction.backward): one more solve with d = clamp(lam)/clamp(slack).
+#include "gqp_common.cuh"
+#include "graspqp_b200.h"
+
+#define FC_WARPS 4
+#define FC_RED_K 29  // widest reduction (odd: conflict-free column sums)
+#define FC_SM_PER_WARP (32 * FC_RED_K + 32 + 64 * 3)
+
+struct FcParamsDev {
+    double mu_f, c0, tw, lo, hi, ridge, svd_gain, values_gain, values_offset;
+    int max_iter;
+    double w_fc, w_dis;
+};
+
+// all-reduce K doubles across the warp through shared memory: v[k] <- op over lanes
+template <int K, bool IS_MIN>
+__device__ __forceinline__ void warp_allreduce(double *sm, double (&v)[K], int lane) {
+    const int S = K | 1;
+#pragma unroll
+    for (int k = 0; k < K; ++k) sm[lane * S + k] = v[k];
+    __syncwarp();
+    if (lane < K) {
+        double a = sm[lane];
+        for (int r = 1; r < 32; ++r) {
+            double t = sm[r * S + lane];
+            a = IS_MIN ? (t < a ? t : a) : a + t;
+        }
+        sm[32 * FC_RED_K + lane] = a;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < K; ++k) v[k] = sm[32 * FC_RED_K + k];
+    __syncwarp();
+}
+
+// packed lower-triangular index
+__device__ __forceinline__ int tri_ix(int i, int j) { return i * (i + 1) / 2 + j; }
+
+// in-place Cholesky of a packed 6x6 SPD matrix (lower), A = L L'
+__device__ __forceinline__ void chol6(double *A) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        double s = A[tri_ix(j, j)];
+#pragma unroll
+        for (int k = 0; k < j; ++k) s -= A[tri_ix(j, k)] * A[tri_ix(j, k)];
+        double l = sqrt(s);
+        A[tri_ix(j, j)] = l;
+        double inv = 1.0 / l;
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) {
+            double t = A[tri_ix(i, j)];
+#pragma unroll
+            for (int k = 0; k < j; ++k) t -= A[tri_ix(i, k)] * A[tri_ix(j, k)];
+            A[tri_ix(i, j)] = t * inv;
+        }
+    }
+}
+__device__ __forceinline__ void chol6_solve(const double *L, double *y) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        double t = y[i];
+#pragma unroll
+        for (int k = 0; k < i; ++k) t -= L[tri_ix(i, k)] * y[k];
+        y[i] = t / L[tri_ix(i, i)];
+    }
+#pragma unroll
+    for (int i = 5; i >= 0; --i) {
+        double t = y[i];
+#pragma unroll
+        for (int k = i + 1; k < 6; ++k) t -= L[tri_ix(k, i)] * y[k];
+        y[i] = t / L[tri_ix(i, i)];
+    }
+}
+
+struct Dir {
+    double dx[2], dsu[2], dsl[2], dzu[2], dzl[2];
+};
+
+// step length to the boundary (qpth get_step): min over entries with dv < 0 of -v/dv, +inf otherwise
+__device__ __forceinline__ double step_len(double v, double dv) { return dv < 0.0 ? -v / dv : 1e300; }
+
+__global__ void __launch_bounds__(FC_WARPS * 32)
+fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
+              const float *__restrict__ obj_dist, const float *__restrict__ obj_nrm,
+              const float *__restrict__ obj_dgrad, const float *__restrict__ cog, int Bt, int batch_each, int n_c,
+              float *__restrict__ e_fc, float *__restrict__ e_dis, float *__restrict__ lam_out,
+              float *__restrict__ grad_cpts, float *__restrict__ grad_cnrm, const int32_t *__restrict__ stop_iter,
+              float *__restrict__ trace) {
+    __shared__ double smem[FC_WARPS][FC_SM_PER_WARP + 64];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *sm = smem[warp];
+    double *sm4 = sm + 32 * FC_RED_K + 32;  // (64,4) per-variable scratch
+    const int n = 4 * n_c, m = 2 * n;
+    const int stop = stop_iter ? *stop_iter : P.max_iter;
+    const double INF = 1e300;
+
+    for (int b = blockIdx.x * FC_WARPS + warp; b < Bt; b += gridDim.x * FC_WARPS) {
+        const int o = b / batch_each;
+        // ---- Q1/Q2: friction-cone edges and grasp-matrix columns of this lane's variables ----
+        double F[2][6];
+        bool valid[2];
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+            const int j = lane + 32 * v;
+            valid[v] = j < n;
+#pragma unroll
+            for (int i = 0; i < 6; ++i) F[v][i] = 0.0;
+            if (valid[v]) {
+                const int c = j >> 2, k = j & 3;
+                const size_t q = ((size_t)b * n_c + c) * 3;
+                double nx = obj_nrm[q], ny = obj_nrm[q + 1], nz = obj_nrm[q + 2];
+                double b1x = 0.57735026918962576, b1y = b1x, b1z = b1x;
+                double dp = (b1x * nx + b1y * ny + b1z * nz) * 1.0 / (sqrt(nx * nx + ny * ny + nz * nz) + 1e-6);
+                if (dp > 0.9) b1y -= 2.0;
+                double t1x = ny * b1z - nz * b1y, t1y = nz * b1x - nx * b1z, t1z = nx * b1y - ny * b1x;
+                double tx = t1x, ty = t1y, tz = t1z;
+                if (k & 1) {  // t2 = n x t1
+                    tx = ny * t1z - nz * t1y; ty = nz * t1x - nx * t1z; tz = nx * t1y - ny * t1x;
+                }
+                double sg = (k & 2) ? -P.mu_f : P.mu_f;
+                double fx = (sg * tx + P.c0 * nx) * 0.25, fy = (sg * ty + P.c0 * ny) * 0.25,
+                       fz = (sg * tz + P.c0 * nz) * 0.25;
+                double rx = (double)cpts[q] - cog[3 * o], ry = (double)cpts[q + 1] - cog[3 * o + 1],
+                       rz = (double)cpts[q + 2] - cog[3 * o + 2];
+                F[v][0] = fx; F[v][1] = fy; F[v][2] = fz;
+                F[v][3] = (ry * fz - rz * fy) * P.tw;
+                F[v][4] = (rz * fx - rx * fz) * P.tw;
+                F[v][5] = (rx * fy - ry * fx) * P.tw;
+            }
+        }
+        // ---- Q3: qpth's PDIPM, Newton systems in Woodbury form ----
+        double Minv[2], L6[21];
+        auto factor = [&](const double *du, const double *dl) {
+            double a[21];
+#pragma unroll
+            for (int i = 0; i < 21; ++i) a[i] = 0.0;
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                Minv[v] = valid[v] ? 1.0 / (P.ridge + du[v] + dl[v]) : 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; ++i)
+#pragma unroll
+                    for (int j2 = 0; j2 <= i; ++j2) a[tri_ix(i, j2)] += Minv[v] * F[v][i] * F[v][j2];
+            }
+            warp_allreduce<21, false>(sm, a, lane);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) a[tri_ix(i, i)] += 1.0;
+            chol6(a);
+#pragma unroll
+            for (int i = 0; i < 21; ++i) L6[i] = a[i];
+        };
+        auto solve = [&](const double *du, const double *dl, const double *rx, const double *rsu, const double *rsl,
+                         const double *rzu, const double *rzl, Dir &d) {
+            double r[2], t[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) t[i] = 0.0;
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                r[v] = -rx[v] + (rsu[v] - du[v] * rzu[v]) - (rsl[v] - dl[v] * rzl[v]);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) t[i] += F[v][i] * r[v] * Minv[v];
+            }
+            warp_allreduce<6, false>(sm, t, lane);
+            chol6_solve(L6, t);
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                double fty = 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) fty += F[v][i] * t[i];
+                double dx = Minv[v] * (r[v] - fty);
+                d.dx[v] = dx;
+                d.dzu[v] = -rsu[v] + du[v] * rzu[v] + du[v] * dx;
+                d.dzl[v] = -rsl[v] + dl[v] * rzl[v] - dl[v] * dx;
+                d.dsu[v] = -rzu[v] - dx;
+                d.dsl[v] = -rzl[v] + dx;
+            }
+        };
+        double x[2], su[2], sl[2], zu[2], zl[2];
+        double bx[2] = {0, 0}, bsu[2] = {1, 1}, bsl[2] = {1, 1}, bzu[2] = {1, 1}, bzl[2] = {1, 1};
+        const double zero2[2] = {0.0, 0.0};
+        {   // starting point: KKT solve with d = 1, then shift slacks / duals to >= 1 (qpth pdipm forward)
+            const double one2[2] = {1.0, 1.0};
+            double rzu[2] = {-P.hi, -P.hi}, rzl[2] = {P.lo, P.lo};
+            factor(one2, one2);
+            Dir d;
+            solve(one2, one2, zero2, zero2, zero2, rzu, rzl, d);
+            double mn[2] = {INF, INF};
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                x[v] = d.dx[v]; su[v] = d.dsu[v]; sl[v] = d.dsl[v]; zu[v] = d.dzu[v]; zl[v] = d.dzl[v];
+                if (valid[v]) {
+                    mn[0] = fmin(mn[0], fmin(su[v], sl[v]));
+                    mn[1] = fmin(mn[1], fmin(zu[v], zl[v]));
+                }
+            }
+            warp_allreduce<2, true>(sm, mn, lane);
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                if (mn[0] < 0.0) { su[v] -= mn[0] - 1.0; sl[v] -= mn[0] - 1.0; }
+                if (mn[1] < 0.0) { zu[v] -= mn[1] - 1.0; zl[v] -= mn[1] - 1.0; }
+            }
+        }
+        double best_res = INF;
+        for (int it = 0; it < P.max_iter; ++it) {
+            double fxv[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) fxv[i] = 0.0;
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+                if (valid[v])
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) fxv[i] += F[v][i] * x[v];
+            warp_allreduce<6, false>(sm, fxv, lane);
+            double rx[2], rzu[2], rzl[2], du[2], dl[2], acc[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                double ftfx = 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) ftfx += F[v][i] * fxv[i];
+                rx[v] = zu[v] - zl[v] + ftfx + P.ridge * x[v];
+                rzu[v] = x[v] + su[v] - P.hi;
+                rzl[v] = -x[v] + sl[v] + P.lo;
+                du[v] = zu[v] / su[v];
+                dl[v] = zl[v] / sl[v];
+                if (valid[v]) {
+                    acc[0] += su[v] * zu[v] + sl[v] * zl[v];
+                    acc[1] += rzu[v] * rzu[v] + rzl[v] * rzl[v];
+                    acc[2] += rx[v] * rx[v];
+                } else {
+                    rx[v] = rzu[v] = rzl[v] = 0.0;
+                    du[v] = dl[v] = 1.0;
+                }
+            }
+            warp_allreduce<3, false>(sm, acc, lane);
+            const double mu = fabs(acc[0] / m);
+            const double res = sqrt(acc[1]) + sqrt(acc[2]) + m * mu;
+            if (trace && lane == 0) trace[(size_t)b * P.max_iter + it] = (float)res;
+            if (it == 0 || res < best_res) {
+                best_res = res;
+#pragma unroll
+                for (int v = 0; v < 2; ++v) { bx[v] = x[v]; bsu[v] = su[v]; bsl[v] = sl[v]; bzu[v] = zu[v]; bzl[v] = zl[v]; }
+            }
+            if (it >= stop) break;
+            factor(du, dl);
+            Dir aff;
+            solve(du, dl, rx, zu, zl, rzu, rzl, aff);  // rs = z
+            double al[1] = {INF};
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+                if (valid[v])
+                    al[0] = fmin(al[0], fmin(fmin(step_len(zu[v], aff.dzu[v]), step_len(zl[v], aff.dzl[v])),
+                                             fmin(step_len(su[v], aff.dsu[v]), step_len(sl[v], aff.dsl[v]))));
+            warp_allreduce<1, true>(sm, al, lane);
+            const double a1 = fmin(al[0], 1.0);
+            double t3[1] = {0.0};
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+                if (valid[v])
+                    t3[0] += (su[v] + a1 * aff.dsu[v]) * (zu[v] + a1 * aff.dzu[v]) +
+                             (sl[v] + a1 * aff.dsl[v]) * (zl[v] + a1 * aff.dzl[v]);
+            warp_allreduce<1, false>(sm, t3, lane);
+            const double ratio = t3[0] / acc[0];
+            const double sig = ratio * ratio * ratio;
+            double rs2u[2], rs2l[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                rs2u[v] = valid[v] ? (-mu * sig + aff.dsu[v] * aff.dzu[v]) / su[v] : 0.0;
+                rs2l[v] = valid[v] ? (-mu * sig + aff.dsl[v] * aff.dzl[v]) / sl[v] : 0.0;
+            }
+            Dir cor;
+            solve(du, dl, zero2, rs2u, rs2l, zero2, zero2, cor);
+            al[0] = INF;
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                aff.dx[v] += cor.dx[v]; aff.dsu[v] += cor.dsu[v]; aff.dsl[v] += cor.dsl[v];
+                aff.dzu[v] += cor.dzu[v]; aff.dzl[v] += cor.dzl[v];
+                if (valid[v])
+                    al[0] = fmin(al[0], fmin(fmin(step_len(zu[v], aff.dzu[v]), step_len(zl[v], aff.dzl[v])),
+                                             fmin(step_len(su[v], aff.dsu[v]), step_len(sl[v], aff.dsl[v]))));
+            }
+            warp_allreduce<1, true>(sm, al, lane);
+            const double a2 = fmin(0.999 * al[0], 1.0);
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                x[v] += a2 * aff.dx[v]; su[v] += a2 * aff.dsu[v]; sl[v] += a2 * aff.dsl[v];
+                zu[v] += a2 * aff.dzu[v]; zl[v] += a2 * aff.dzl[v];
+            }
+        }
+        // ---- value, svd term, E_fc (qp_solver.py:126, span.py:402, registry.py:82-87) ----
+        double red[27];
+#pragma unroll
+        for (int i = 0; i < 27; ++i) red[i] = 0.0;
+#pragma unroll
+        for (int v = 0; v < 2; ++v)
+            if (valid[v]) {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    red[i] += F[v][i] * bx[v];
+#pragma unroll
+                    for (int j2 = 0; j2 <= i; ++j2) red[6 + tri_ix(i, j2)] += F[v][i] * F[v][j2];
+                }
+            }
+        warp_allreduce<27, false>(sm, red, lane);
+        double Fx[6], Lg[21];
+        double value = 0.0;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { Fx[i] = red[i]; value += 0.5 * red[i] * red[i]; }
+#pragma unroll
+        for (int i = 0; i < 21; ++i) Lg[i] = red[6 + i];
+        chol6(Lg);  // F F' = Lg Lg'  ->  prod(svdvals(F)) = prod(diag Lg)
+        double logdet = 0.0;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) logdet += log(Lg[tri_ix(i, i)]);
+        const bool rank_ok = logdet == logdet;  // NaN when F F' is numerically singular
+        const double svd = rank_ok ? exp(logdet / 6.0) : 0.0;
+        const double ex = exp(-P.svd_gain * svd);
+        const double Efc = P.values_gain * (value + P.values_offset) * ex;
+        // ---- E_dis (energy.py:25-28) on lanes < n_c ----
+        double edis = 0.0, gpd[3] = {0.0, 0.0, 0.0};
+        if (lane < n_c) {
+            const size_t q = ((size_t)b * n_c + lane) * 3;
+            double ox = obj_nrm[q], oy = obj_nrm[q + 1], oz = obj_nrm[q + 2];
+            double a = 1.0 + (ox * cnrm_hand[q] + oy * cnrm_hand[q + 1] + oz * cnrm_hand[q + 2]);
+            double dd = obj_dist[(size_t)b * n_c + lane];
+            double ea = exp(a);
+            edis = ea * fabs(dd);
+            if (grad_cnrm) {
+                double g = P.w_dis * edis;
+                grad_cnrm[q] = (float)(g * ox); grad_cnrm[q + 1] = (float)(g * oy); grad_cnrm[q + 2] = (float)(g * oz);
+            }
+            double gd = P.w_dis * ea * (dd > 0.0 ? 1.0 : (dd < 0.0 ? -1.0 : 0.0));
+            if (obj_dgrad) {
+                gpd[0] = gd * obj_dgrad[q]; gpd[1] = gd * obj_dgrad[q + 1]; gpd[2] = gd * obj_dgrad[q + 2];
+            }
+        }
+        double es[1] = {edis};
+        warp_allreduce<1, false>(sm, es, lane);
+        if (lane == 0) {
+            if (e_fc) e_fc[b] = (float)Efc;
+            if (e_dis) e_dis[b] = (float)es[0];
+        }
+        // ---- backward: d(w_fc E_fc)/dF, implicit differentiation of the QP (qpth QPFunction.backward) ----
+        double gF[2][6];
+#pragma unroll
+        for (int v = 0; v < 2; ++v)
+#pragma unroll
+            for (int i = 0; i < 6; ++i) gF[v][i] = 0.0;
+        if (grad_cpts) {
+            const double gv = P.w_fc * P.values_gain * ex;         // dE/dvalue
+            const double gs = -P.w_fc * P.svd_gain * Efc;          // dE/dsvd
+            double du[2], dl[2], rxb[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                double ftfx = 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) ftfx += F[v][i] * Fx[i];
+                rxb[v] = valid[v] ? gv * ftfx : 0.0;  // dl/dx
+                du[v] = fmax(bzu[v], 1e-8) / fmax(bsu[v], 1e-8);
+                dl[v] = fmax(bzl[v], 1e-8) / fmax(bsl[v], 1e-8);
+            }
+            factor(du, dl);
+            Dir bd;
+            solve(du, dl, rxb, zero2, zero2, zero2, zero2, bd);
+            double fdx[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) fdx[i] = 0.0;
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+                if (valid[v])
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) fdx[i] += F[v][i] * bd.dx[v];
+            warp_allreduce<6, false>(sm, fdx, lane);
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                if (!valid[v]) continue;
+                double pin[6];  // (F F')^-1 F_j
+#pragma unroll
+                for (int i = 0; i < 6; ++i) pin[i] = F[v][i];
+                if (rank_ok) chol6_solve(Lg, pin);
+#pragma unroll
+                for (int i = 0; i < 6; ++i)
+                    gF[v][i] = (gv * Fx[i] + fdx[i]) * bx[v] + Fx[i] * bd.dx[v] +
+                               (rank_ok ? gs * (svd / 6.0) * pin[i] : 0.0);
+            }
+        }
+        // ---- per-contact sums: force solution (span.py:414) and d/d(contact point) through tau = tw (r x f) ----
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+            const int j = lane + 32 * v;
+            if (j < 64) {
+                double fx = F[v][0], fy = F[v][1], fz = F[v][2], gx = gF[v][3], gy = gF[v][4], gz = gF[v][5];
+                sm4[4 * j + 0] = valid[v] ? P.tw * (fy * gz - fz * gy) : 0.0;
+                sm4[4 * j + 1] = valid[v] ? P.tw * (fz * gx - fx * gz) : 0.0;
+                sm4[4 * j + 2] = valid[v] ? P.tw * (fx * gy - fy * gx) : 0.0;
+                sm4[4 * j + 3] = valid[v] ? bx[v] : 0.0;
+            }
+        }
+        __syncwarp();
+        if (lane < n_c) {
+            double s[4] = {0.0, 0.0, 0.0, 0.0};
+            for (int k = 0; k < 4; ++k)
+                for (int i = 0; i < 4; ++i) s[i] += sm4[4 * (4 * lane + k) + i];
+            const size_t q = ((size_t)b * n_c + lane) * 3;
+            if (grad_cpts) {
+                grad_cpts[q] = (float)(s[0] + gpd[0]);
+                grad_cpts[q + 1] = (float)(s[1] + gpd[1]);
+                grad_cpts[q + 2] = (float)(s[2] + gpd[2]);
+            }
+            if (lam_out) lam_out[(size_t)b * n_c + lane] = (float)s[3];
+        }
+        __syncwarp();
+    }
+}
+
+// batch-wide exit test of qpth's loop, replayed from the residual trace (one block of 256 threads)
+__global__ void fc_stop_iter_kernel(const float *__restrict__ trace, int Bt, int max_iter, float eps,
+                                    int32_t *__restrict__ stop_iter) {
+    __shared__ int s_improved;
+    __shared__ float s_max[256];
+    __shared__ int s_stop;
+    int not_improved = 0;
+    if (threadIdx.x == 0) s_stop = max_iter;
+    for (int it = 0; it < max_iter; ++it) {
+        if (threadIdx.x == 0) s_improved = 0;
+        __syncthreads();
+        float mx = -1e30f;
+        int imp = 0;
+        for (int b = threadIdx.x; b < Bt; b += blockDim.x) {
+            float best = trace[(size_t)b * max_iter];
+            for (int k = 1; k < it; ++k) best = fminf(best, trace[(size_t)b * max_iter + k]);
+            float r = trace[(size_t)b * max_iter + it];
+            if (it > 0 && r < best) imp = 1;
+            mx = fmaxf(mx, it > 0 ? fminf(best, r) : r);
+        }
+        s_max[threadIdx.x] = mx;
+        if (imp) atomicAdd(&s_improved, 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float m2 = -1e30f;
+            for (int i = 0; i < (int)blockDim.x; ++i) m2 = fmaxf(m2, s_max[i]);
+            if (it > 0) not_improved = s_improved > 0 ? 0 : not_improved + 1;
+            if ((not_improved == 3 || m2 < eps) && s_stop == max_iter) s_stop = it;
+        }
+        __syncthreads();
+        if (s_stop != max_iter) break;
+    }
+    if (threadIdx.x == 0) *stop_iter = s_stop;
+}
+
+extern "C" int gqp_fc_dis_energy(const GqpFcParams *p, const float *cpts, const float *cnrm_hand,
+                                 const float *obj_dist, const float *obj_nrm, const float *obj_dgrad, const float *cog,
+                                 int n_obj, int batch_each, int n_c, float *e_fc, float *e_dis, float *lam,
+                                 float *grad_cpts, float *grad_cnrm, const int32_t *qp_stop_iter, float *qp_trace,
+                                 void *stream) {
+    if (!p || n_obj < 0 || batch_each < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_dis_energy: bad argument");
+    if (n_c < 2 || n_c > 16) return gqp_set_error(GQP_ERR_LIMIT, "gqp_fc_dis_energy: n_c must be in [2,16], got %d", n_c);
+    if (p->max_iter < 1 || p->max_iter > 64) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_dis_energy: max_iter out of range");
+    const int Bt = n_obj * batch_each;
+    if (Bt == 0) return GQP_OK;
+    if (!cpts || !cnrm_hand || !obj_dist || !obj_nrm || !cog)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_fc_dis_energy: null pointer");
+    FcParamsDev P;
+    P.mu_f = p->friction;
+    P.c0 = sqrt(1.0 - (double)p->friction * (double)p->friction);
+    P.tw = p->torque_weight; P.lo = p->lower; P.hi = p->upper; P.ridge = p->ridge; P.svd_gain = p->svd_gain;
+    P.values_gain = p->values_gain; P.values_offset = p->values_offset; P.max_iter = p->max_iter;
+    P.w_fc = p->w_fc; P.w_dis = p->w_dis;
+    int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
+    GQP_LAUNCH(fc_dis_kernel, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist, obj_nrm,
+               obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm, qp_stop_iter, qp_trace);
+    GQP_CHECK_LAUNCH("gqp_fc_dis_energy");
+    return GQP_OK;
+}
+
+extern "C" int gqp_fc_stop_iter(const float *qp_trace, int Bt, int max_iter, float eps, int32_t *stop_iter,
+                                void *stream) {
+    if (!qp_trace || !stop_iter || Bt <= 0 || max_iter < 1) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_stop_iter: bad argument");
+    GQP_LAUNCH(fc_stop_iter_kernel, 1, 256, 0, (cudaStream_t)stream, qp_trace, Bt, max_iter, eps, stop_iter);
+    GQP_CHECK_LAUNCH("gqp_fc_stop_iter");
+    return GQP_OK;
+}

@@ -1,0 +1,87 @@
+"""Q1-Q4 + E_dis kernel (csrc/gqp_fc.cu) run by the host emulator vs the fp64 torch oracle (oracle/qp.py)."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ptr
+from graspqp_b200 import _lib
+from oracle import qp as oqp
+
+
+def fc_params(**kw):
+    p = _lib.GqpFcParams(friction=0.2, torque_weight=5.0, lower=1.0, upper=21.0, ridge=1e-4, svd_gain=0.1,
+                         values_gain=2.0, values_offset=1e-2, eps=5e-2, max_iter=12, w_fc=1.0, w_dis=100.0)
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def _inputs(B, n_c, seed):
+    rng = np.random.default_rng(seed)
+    nrm = rng.normal(size=(B, n_c, 3)); nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
+    nrm[0, 0] = np.array([1.0, 1.0, 1.0]) / np.sqrt(3)  # triggers the b1 switch (span.py:271-277)
+    cp = (-nrm * 0.08 + rng.normal(size=(B, n_c, 3)) * 0.01).astype(np.float32)
+    nrm = nrm.astype(np.float32)
+    hn = -nrm + rng.normal(size=nrm.shape).astype(np.float32) * 0.2
+    hn = (hn / np.linalg.norm(hn, axis=-1, keepdims=True)).astype(np.float32)
+    dist = (rng.normal(size=(B, n_c)) * 0.01).astype(np.float32)
+    dgrad = rng.normal(size=(B, n_c, 3)).astype(np.float32)
+    cog = (rng.normal(size=(1, 3)) * 0.005).astype(np.float32)
+    return cp, hn, dist, nrm, dgrad, cog
+
+
+def run_kernel(lib, P, cp, hn, dist, nrm, dgrad, cog, n_obj, two_pass=True):
+    B, n_c = dist.shape
+    e_fc, e_dis = np.zeros(B, np.float32), np.zeros(B, np.float32)
+    lam = np.zeros((B, n_c), np.float32)
+    g_cp, g_hn = np.zeros_like(cp), np.zeros_like(cp)
+    trace = np.zeros((B, P.max_iter), np.float32)
+    stop = np.full(1, -1, np.int32)
+    args = lambda st, tr: (ctypes.byref(P), ptr(cp), ptr(hn), ptr(dist), ptr(nrm), ptr(dgrad), ptr(cog), n_obj,
+                           B // n_obj, n_c, ptr(e_fc), ptr(e_dis), ptr(lam), ptr(g_cp), ptr(g_hn), st, tr, None)
+    assert lib.gqp_fc_dis_energy(*args(None, ptr(trace))) == 0, lib.gqp_last_error()
+    if two_pass:
+        assert lib.gqp_fc_stop_iter(ptr(trace), B, P.max_iter, P.eps, ptr(stop), None) == 0
+        assert lib.gqp_fc_dis_energy(*args(ptr(stop), None)) == 0
+    return e_fc, e_dis, lam, g_cp, g_hn, trace, int(stop[0])
+
+
+def oracle(cp, hn, dist, nrm, dgrad, cog, w_fc=1.0, w_dis=100.0):
+    t = lambda a: torch.tensor(a, dtype=torch.float64)
+    cpt = t(cp).requires_grad_(True)
+    hnt = t(hn).requires_grad_(True)
+    B = cp.shape[0]
+    E, lam, info = oqp.graspqp_energy(cpt, t(nrm), t(cog).expand(B, 3))
+    # E_dis with the object distance linearised around cp: d = dist + dgrad.(p - p0)
+    d = t(dist) + (t(dgrad) * (cpt - t(cp))).sum(-1)
+    E_dis = ((1 - ((-t(nrm)) * hnt).sum(-1)).exp() * d.abs()).sum(-1)
+    (w_fc * E + w_dis * E_dis).sum().backward()
+    return E.detach().numpy(), E_dis.detach().numpy(), lam.detach().numpy(), cpt.grad.numpy(), hnt.grad.numpy(), info
+
+
+@pytest.mark.parametrize("B,n_c", [(3, 12), (2, 16), (2, 4)])
+def test_fc_dis_vs_oracle(emu, B, n_c):
+    inp = _inputs(B, n_c, 10 + n_c)
+    P = fc_params()
+    e_fc, e_dis, lam, g_cp, g_hn, trace, stop = run_kernel(emu, P, *inp, n_obj=1)
+    tr = []
+    import oracle.qp as q
+    F = q.grasp_matrix(torch.tensor(inp[0], dtype=torch.float64), torch.tensor(inp[3], dtype=torch.float64),
+                       torch.tensor(inp[5], dtype=torch.float64).expand(B, 3))
+    n = F.shape[-1]
+    Q = F.mT @ F + torch.eye(n, dtype=torch.float64) * 1e-4
+    G = torch.cat([torch.eye(n), -torch.eye(n)], 0).double().unsqueeze(0).expand(B, -1, -1).contiguous()
+    h = torch.cat([torch.full((B, n), 21.0), torch.full((B, n), -1.0)], -1).double()
+    q.pdipm_forward(Q, torch.zeros(B, n, dtype=torch.float64), G, h, trace=tr)
+    want_trace = torch.stack(tr, 1).numpy()
+    k = want_trace.shape[1]
+    assert stop == (k - 1 if k <= 12 and stop < 12 else stop)
+    np.testing.assert_allclose(trace[:, :k], want_trace, rtol=2e-5, atol=1e-8)
+    E, Ed, lam_w, gcp_w, ghn_w, info = oracle(*inp)
+    np.testing.assert_allclose(e_fc, E, rtol=1e-5)
+    np.testing.assert_allclose(e_dis, Ed, rtol=1e-5)
+    np.testing.assert_allclose(lam, lam_w, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(g_hn, ghn_w, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(g_cp, gcp_w, rtol=1e-4, atol=1e-4 * np.abs(gcp_w).max())
