@@ -56,11 +56,12 @@ SIGNATURES = {
     "gqp_self_pen_joints": (c_int, [c_void_p, P, P, c_int, P, P, c_float, c_float, P, P, P]),
     "gqp_fc_dis_energy": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P, P, P, P, P]),
     "gqp_fc_stop_iter": (c_int, [P, c_int, c_int, c_float, P, P]),
-    "gqp_mala_stats": (c_int, [P, P, c_int, c_int, c_int, P, P, P, P]),
+    "gqp_mala_stats": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P]),
     "gqp_mala_propose": (c_int, [POINTER(GqpMalaParams), P, P, P, P, P, P, c_int, c_int, c_int, c_int, P, P, c_uint64,
                                  c_uint64, P, P, P, P]),
     "gqp_mala_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, P, P, c_uint64, c_uint64,
                                 P, P, P, P, P, P, P, P, P, P, P, P, P]),
+    "gqp_memset_zero": (c_int, [P, c_uint64, P]),
     "gqp_fma_peak_probe": (c_int, [c_int, P, POINTER(c_uint64), P]),
 }
 

@@ -48,3 +48,15 @@ extern "C" int gqp_fma_peak_probe(int iters, float *sink, uint64_t *n_fma_host, 
 #else
 extern "C" int gqp_fma_peak_probe(int, float *, uint64_t *, void *) { return gqp_set_error(GQP_ERR_ARG, "emu"); }
 #endif
+
+// zero a device buffer on the stream (the per-step reset of the link-transform gradient)
+extern "C" int gqp_memset_zero(void *ptr, uint64_t bytes, void *stream) {
+    if (!ptr && bytes) return gqp_set_error(GQP_ERR_ARG, "gqp_memset_zero: null pointer");
+#ifndef GQP_EMU
+    cudaError_t e = cudaMemsetAsync(ptr, 0, bytes, (cudaStream_t)stream);
+    if (e != cudaSuccess) return gqp_set_error(GQP_ERR_CUDA, "gqp_memset_zero: %s", cudaGetErrorString(e));
+#else
+    std::memset(ptr, 0, bytes);
+#endif
+    return GQP_OK;
+}

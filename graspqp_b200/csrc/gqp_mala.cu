@@ -1,0 +1,219 @@
+// M1/M2/M4 — MALA* proposal, accept/reject and the caller's bookkeeping.
+//   MalaStar.try_step    core/optimizer.py:199-273      MalaStar.accept_step  core/optimizer.py:289-340
+//   z-score, weighted sum, masked commit                scripts/fit.py:403-406, 434-458
+// The reference runs ~15 element-wise launches and three host syncs per iteration here; these are three launches, no
+// sync.  State rows are candidates; everything is HBM-streaming over a few KB per candidate (bound: launch latency).
+// Randomness: injected arrays (parity runs) or Philox4x32-10 keyed by (seed, iteration, row) (production runs).
+#include "gqp_common.cuh"
+#include "graspqp_b200.h"
+
+// ---- Philox4x32-10 (Salmon et al. 2011), counter = (row, slot, iteration lo, iteration hi), key = seed ----
+struct Philox {
+    uint32_t c[4];
+};
+__device__ __forceinline__ Philox philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                             uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0, hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += W0; k1 += W1;
+    }
+    Philox p;
+    p.c[0] = c0; p.c[1] = c1; p.c[2] = c2; p.c[3] = c3;
+    return p;
+}
+__device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }  // [0,1)
+
+#define STATS_ROWS 64
+
+// blocks [0, n_gblk): partial sums of grad^2 over 64 rows; blocks [n_gblk, n_gblk + n_obj): z-score of one object
+__global__ void __launch_bounds__(256)
+mala_stats_kernel(const float *__restrict__ grad, const float *__restrict__ energy, int n_obj, int batch_each, int D,
+                  int n_gblk, int clip_grad, float *__restrict__ partial, float *__restrict__ z) {
+    const int Bt = n_obj * batch_each;
+    if ((int)blockIdx.x < n_gblk) {
+        const int r0 = blockIdx.x * STATS_ROWS, r1 = min(Bt, r0 + STATS_ROWS);
+        for (int d = threadIdx.x; d < D; d += blockDim.x) {
+            float s = 0.f;
+            for (int r = r0; r < r1; ++r) {
+                float g = grad[(size_t)r * D + d];
+                if (clip_grad) {
+                    g = fminf(fmaxf(g, -100.f), 100.f);
+                    if (g != g) g = 0.f;
+                }
+                s += g * g;
+            }
+            partial[(size_t)blockIdx.x * D + d] = s;
+        }
+        return;
+    }
+    // z-score (fit.py:403-406): mean and UNBIASED std over the object's candidates, fixed-order tree reduction
+    __shared__ float red[256];
+    const int o = blockIdx.x - n_gblk;
+    const float *e = energy + (size_t)o * batch_each;
+    float s = 0.f;
+    for (int i = threadIdx.x; i < batch_each; i += blockDim.x) s += e[i];
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+        __syncthreads();
+    }
+    const float mean = red[0] / (float)batch_each;
+    __syncthreads();
+    s = 0.f;
+    for (int i = threadIdx.x; i < batch_each; i += blockDim.x) {
+        float dlt = e[i] - mean;
+        s += dlt * dlt;
+    }
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+        __syncthreads();
+    }
+    const float sd = sqrtf(red[0] / (float)(batch_each - 1));
+    for (int i = threadIdx.x; i < batch_each; i += blockDim.x) z[(size_t)o * batch_each + i] = (e[i] - mean) / sd;
+}
+
+__global__ void mala_stats_final_kernel(const float *__restrict__ partial, int n_gblk, int D, int Bt,
+                                        float *__restrict__ grad2_mean) {
+    int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= D) return;
+    float s = 0.f;
+    for (int k = 0; k < n_gblk; ++k) s += partial[(size_t)k * D + d];
+    grad2_mean[d] = s / (float)Bt;
+}
+
+// optimizer.py:199-273
+__global__ void __launch_bounds__(128)
+mala_propose_kernel(GqpMalaParams P, const float *__restrict__ pose, const float *__restrict__ grad,
+                    const float *__restrict__ grad2_mean, float *__restrict__ ema, int32_t *__restrict__ step,
+                    const int32_t *__restrict__ idx, int Bt, int D, int n_c, int n_cand,
+                    const float *__restrict__ u_switch, const int32_t *__restrict__ idx_rand, uint64_t seed,
+                    uint64_t iteration, float *__restrict__ pose_new, int32_t *__restrict__ idx_new,
+                    float *__restrict__ step_size_out) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    const int st = step[b];
+    const float s = P.step_size * powf(P.temperature_decay, (float)(st / P.stepsize_period));  // :209
+    for (int d = 0; d < D; ++d) {
+        const size_t i = (size_t)b * D + d;
+        float g = grad[i];
+        if (P.clip_grad) {
+            g = fminf(fmaxf(g, -100.f), 100.f);
+            if (g != g) g = 0.f;
+        }
+        float e = P.mu * grad2_mean[d] + (1.0f - P.mu) * ema[i];  // :233
+        if (e != e) e = 0.f;                                       // :235-236
+        ema[i] = e;
+        pose_new[i] = pose[i] - s * g / (sqrtf(e) + 1e-6f);  // :240
+    }
+    for (int c = 0; c < n_c; ++c) {  // :252-257
+        const size_t i = (size_t)b * n_c + c;
+        float u;
+        int32_t r;
+        if (u_switch) {
+            u = u_switch[i];
+            r = idx_rand[i];
+        } else {
+            Philox p = philox4x32((uint32_t)b, (uint32_t)c, (uint32_t)iteration, (uint32_t)(iteration >> 32),
+                                  (uint32_t)seed, (uint32_t)(seed >> 32));
+            u = u01(p.c[0]);
+            r = (int32_t)(((uint64_t)p.c[1] * (uint64_t)n_cand) >> 32);
+        }
+        idx_new[i] = (u < P.switch_possibility) ? r : idx[i];
+    }
+    step[b] = st + 1;  // :271
+    if (step_size_out) step_size_out[b] = s;
+}
+
+// optimizer.py:289-340 + fit.py:434-458.  Accepted rows adopt the proposal; rejected rows keep pose / idx / grad.
+__global__ void __launch_bounds__(128)
+mala_accept_kernel(GqpMalaParams P, int Bt, int D, int n_c, int n_terms, const float *__restrict__ weights,
+                   const float *__restrict__ losses_new, const float *__restrict__ z,
+                   const uint8_t *__restrict__ reset_mask, const float *__restrict__ u_accept, uint64_t seed,
+                   uint64_t iteration, const int32_t *__restrict__ step, const float *__restrict__ pose_new,
+                   const int32_t *__restrict__ idx_new, const float *__restrict__ grad_new, float *__restrict__ pose,
+                   int32_t *__restrict__ idx, float *__restrict__ grad, float *__restrict__ energy,
+                   float *__restrict__ losses, float *__restrict__ new_energy_out, uint8_t *__restrict__ accept_out,
+                   float *__restrict__ temperature_out) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    float en = 0.f;
+    for (int k = 0; k < n_terms; ++k) en += weights[k] * losses_new[(size_t)k * Bt + b];  // fit.py:434-438
+    float T = P.starting_temperature * powf(P.temperature_decay, (float)(step[b] / P.annealing_period));  // :301-303
+    if (z) T = T * (1.0f + 0.5f * (1.0f + erff(z[b] * 0.70710678118654752f)));                            // :307-309
+    float u;
+    if (u_accept) u = u_accept[b];
+    else {
+        Philox p = philox4x32((uint32_t)b, 0xffffffffu, (uint32_t)iteration, (uint32_t)(iteration >> 32),
+                              (uint32_t)seed, (uint32_t)(seed >> 32));
+        u = u01(p.c[0]);
+    }
+    bool acc = u < expf((energy[b] - en) / T);  // :313
+    if (reset_mask && reset_mask[b]) acc = true;  // :315-316
+    if (acc) {
+        for (int d = 0; d < D; ++d) {
+            pose[(size_t)b * D + d] = pose_new[(size_t)b * D + d];
+            grad[(size_t)b * D + d] = grad_new[(size_t)b * D + d];
+        }
+        for (int c = 0; c < n_c; ++c) idx[(size_t)b * n_c + c] = idx_new[(size_t)b * n_c + c];
+        energy[b] = en;  // fit.py:454-458
+        for (int k = 0; k < n_terms; ++k) losses[(size_t)k * Bt + b] = losses_new[(size_t)k * Bt + b];
+    }
+    if (new_energy_out) new_energy_out[b] = en;
+    if (accept_out) accept_out[b] = acc ? 1 : 0;
+    if (temperature_out) temperature_out[b] = T;
+}
+
+extern "C" int gqp_mala_stats(const float *grad, const float *energy, int n_obj, int batch_each, int D, int clip_grad,
+                              float *grad2_mean, float *z, float *scratch, void *stream) {
+    if (n_obj <= 0 || batch_each <= 0 || D <= 0 || !grad || !energy || !grad2_mean || !z || !scratch)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_mala_stats: bad argument");
+    const int Bt = n_obj * batch_each, n_gblk = (Bt + STATS_ROWS - 1) / STATS_ROWS;
+    GQP_LAUNCH(mala_stats_kernel, n_gblk + n_obj, 256, 0, (cudaStream_t)stream, grad, energy, n_obj, batch_each, D,
+               n_gblk, clip_grad, scratch, z);
+    GQP_CHECK_LAUNCH("gqp_mala_stats");
+    GQP_LAUNCH(mala_stats_final_kernel, (D + 63) / 64, 64, 0, (cudaStream_t)stream, scratch, n_gblk, D, Bt,
+               grad2_mean);
+    GQP_CHECK_LAUNCH("gqp_mala_stats/final");
+    return GQP_OK;
+}
+
+extern "C" int gqp_mala_propose(const GqpMalaParams *p, const float *pose, const float *grad,
+                                const float *grad2_mean, float *ema, int32_t *step, const int32_t *idx, int Bt, int D,
+                                int n_c, int n_cand, const float *u_switch, const int32_t *idx_rand, uint64_t seed,
+                                uint64_t iteration, float *pose_new, int32_t *idx_new, float *step_size_out,
+                                void *stream) {
+    if (!p || Bt < 0 || D <= 0 || n_c <= 0 || n_cand <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_mala_propose: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!pose || !grad || !grad2_mean || !ema || !step || !idx || !pose_new || !idx_new)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_mala_propose: null pointer");
+    if ((u_switch == nullptr) != (idx_rand == nullptr))
+        return gqp_set_error(GQP_ERR_ARG, "gqp_mala_propose: u_switch and idx_rand must be injected together");
+    GQP_LAUNCH(mala_propose_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, *p, pose, grad, grad2_mean, ema,
+               step, idx, Bt, D, n_c, n_cand, u_switch, idx_rand, seed, iteration, pose_new, idx_new, step_size_out);
+    GQP_CHECK_LAUNCH("gqp_mala_propose");
+    return GQP_OK;
+}
+
+extern "C" int gqp_mala_accept(const GqpMalaParams *p, int Bt, int D, int n_c, int n_terms, const float *weights,
+                               const float *losses_new, const float *z, const uint8_t *reset_mask,
+                               const float *u_accept, uint64_t seed, uint64_t iteration, const int32_t *step,
+                               const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose,
+                               int32_t *idx, float *grad, float *energy, float *losses, float *new_energy_out,
+                               uint8_t *accept_out, float *temperature_out, void *stream) {
+    if (!p || Bt < 0 || D <= 0 || n_c <= 0 || n_terms <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_mala_accept: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!weights || !losses_new || !step || !pose_new || !idx_new || !grad_new || !pose || !idx || !grad || !energy ||
+        !losses)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_mala_accept: null pointer");
+    GQP_LAUNCH(mala_accept_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, *p, Bt, D, n_c, n_terms, weights,
+               losses_new, z, reset_mask, u_accept, seed, iteration, step, pose_new, idx_new, grad_new, pose, idx,
+               grad, energy, losses, new_energy_out, accept_out, temperature_out);
+    GQP_CHECK_LAUNCH("gqp_mala_accept");
+    return GQP_OK;
+}

@@ -42,7 +42,11 @@ struct GqpPenTables {
     int total_bytes = 0;
 };
 
+#ifdef GQP_EMU
+#define PEN_THREADS 64
+#else
 #define PEN_THREADS 768
+#endif
 #define PEN_MAX_SMEM (200 * 1024)
 
 // true when q is provably outside the (nice) link mesh: outside its box, or in a grid cell entirely outside it
@@ -77,7 +81,7 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
     const int L = hdr->n_links;
 
     const int lane = threadIdx.x & 31;
-    const int warps_per_block = PEN_THREADS / 32;
+    const int warps_per_block = blockDim.x / 32;
     const int n_chunks = (n_pts + 31) / 32;
     const long long n_tasks = (long long)Bt * n_chunks;
     for (long long task = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;

@@ -1,0 +1,230 @@
+"""FitEngine — the loop body of the reference's scripts/fit.py:399-458 as a sequence of C-ABI kernel launches.
+
+One engine = one device = one group of objects (the reference's job-level sharding, scripts/fit_all.sh:154-248), with
+`batch_each` grasp candidates per object.  All state lives in device buffers; an iteration enqueues ~14 launches on the
+given stream and never synchronises, so it can be captured in a CUDA graph (see `FitEngine.capture`).
+
+The engine is written against two tiny adapters so that the SAME host code drives
+  * the product: libgraspqp_b200.so + torch CUDA tensors (`TorchBackend`), and
+  * the tests:   the kernel sources run by the host SIMT emulator + numpy buffers (`NumpyBackend`, tests only).
+There is no CPU implementation of any stage here: without one of those two libraries nothing computes.
+
+Order of the energy terms (= the reference's dict order, core/energy.py:29-66): E_dis, E_fc, E_joints, E_pen, E_spen.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib, hand_pack
+
+TERMS = ("E_dis", "E_fc", "E_joints", "E_pen", "E_spen")
+DEFAULT_WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_joints=1.0, E_pen=100.0, E_spen=10.0)  # scripts/fit.py:90-112
+
+
+class NumpyBackend:
+    """Host buffers for the emulator library (tests/_emu).  Test infrastructure."""
+    stream = None
+
+    def empty(self, shape, dtype):
+        return np.zeros(shape, dtype)
+
+    def from_host(self, a, dtype=None):
+        return np.ascontiguousarray(a, dtype)
+
+    def to_host(self, a):
+        return np.array(a, copy=True)
+
+    def ptr(self, a):
+        return None if a is None else a.ctypes.data
+
+    def copy_(self, dst, src):
+        dst[...] = src
+
+
+class TorchBackend:
+    """torch CUDA tensors; launches go to torch's current stream."""
+
+    def __init__(self, device="cuda"):
+        import torch
+        self.torch = torch
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("graspqp_b200 computes on CUDA devices only (no CPU fallback)")
+
+    _np2t = {np.float32: "float32", np.int32: "int32", np.uint8: "uint8", np.float64: "float64", np.int64: "int64"}
+
+    @property
+    def stream(self):
+        return ctypes.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def empty(self, shape, dtype):
+        return self.torch.zeros(shape, dtype=getattr(self.torch, self._np2t[dtype]), device=self.device)
+
+    def from_host(self, a, dtype=None):
+        t = self.torch.as_tensor(np.ascontiguousarray(a, dtype))
+        return t.to(self.device).contiguous()
+
+    def to_host(self, a):
+        return a.detach().cpu().numpy()
+
+    def ptr(self, a):
+        return None if a is None else a.data_ptr()
+
+    def copy_(self, dst, src):
+        dst.copy_(src)
+
+
+class FitEngine:
+    def __init__(self, cdll, backend, pack, face_verts_list, surface_points, batch_each, hand_pose, contact_idx,
+                 weights=None, friction=0.2, max_limit=20.0, svd_gain=0.1, torque_weight=5.0, switch_possibility=0.4,
+                 starting_temperature=18.0, temperature_decay=0.95, annealing_period=30, step_size=0.005,
+                 stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1):
+        self.lib, self.be = cdll, backend
+        self.pack = pack
+        self.n_obj = len(face_verts_list)
+        self.batch_each = int(batch_each)
+        self.Bt = self.n_obj * self.batch_each
+        self.dof = len(pack["joints_lower"])
+        self.D = 9 + self.dof
+        self.L = len(pack["mesh_frame"])
+        self.n_cand = len(pack["cand"])
+        self.n_c = int(np.asarray(contact_idx).shape[1])
+        self.seed = int(seed)
+        self.iteration = 0
+        self.qp_batch_stop = bool(qp_batch_stop)
+        be, Bt, D, n_c, L = backend, self.Bt, self.D, self.n_c, self.L
+        surface_points = np.ascontiguousarray(surface_points, np.float32)
+        assert surface_points.shape[0] == self.n_obj and surface_points.shape[2] == 3
+        self.n_pts = surface_points.shape[1]
+        # ---- handles ----
+        self.hand = hand_pack.create_hand(cdll, pack)
+        self.meshes = []
+        for fv in face_verts_list:
+            fv = np.ascontiguousarray(fv, np.float32).reshape(-1, 9)
+            m = ctypes.c_void_p()
+            _lib.check(cdll.gqp_mesh_create(fv.ctypes.data, len(fv), ctypes.byref(m)), cdll)
+            self.meshes.append(m)
+        arr = (ctypes.c_void_p * self.n_obj)(*[m.value for m in self.meshes])
+        self.objset = ctypes.c_void_p()
+        _lib.check(cdll.gqp_objset_create(ctypes.cast(arr, ctypes.c_void_p), self.n_obj, ctypes.byref(self.objset)), cdll)
+        # ---- parameters ----
+        w = dict(DEFAULT_WEIGHTS)
+        w.update(weights or {})
+        self.weights = w
+        self.fc = _lib.GqpFcParams(friction=friction, torque_weight=torque_weight, lower=1.0, upper=max_limit + 1.0,
+                                   ridge=1e-4, svd_gain=svd_gain, values_gain=2.0, values_offset=1e-2, eps=5e-2,
+                                   max_iter=12, w_fc=w["E_fc"], w_dis=w["E_dis"])
+        self.mala = _lib.GqpMalaParams(switch_possibility=switch_possibility, starting_temperature=starting_temperature,
+                                       temperature_decay=temperature_decay, step_size=step_size, mu=mu,
+                                       annealing_period=annealing_period, stepsize_period=stepsize_period,
+                                       clip_grad=int(clip_grad))
+        # ---- device state ----
+        f32, i32, u8 = np.float32, np.int32, np.uint8
+        self.surf = be.from_host(surface_points, f32)
+        self.cog = be.from_host(surface_points.mean(1, dtype=np.float32), f32)  # object_model.py:64-68
+        self.w_dev = be.from_host(np.array([w[k] for k in TERMS], f32))
+        self.pose = be.from_host(hand_pose, f32)
+        self.idx = be.from_host(contact_idx, i32)
+        assert tuple(self.pose.shape) == (Bt, D) and tuple(self.idx.shape) == (Bt, n_c)
+        self.grad, self.ema = be.empty((Bt, D), f32), be.empty((Bt, D), f32)
+        self.step_count = be.empty((Bt,), i32)
+        self.energy, self.losses = be.empty((Bt,), f32), be.empty((len(TERMS), Bt), f32)
+        self.pose_new, self.idx_new = be.empty((Bt, D), f32), be.empty((Bt, n_c), i32)
+        self.grad_new, self.losses_new = be.empty((Bt, D), f32), be.empty((len(TERMS), Bt), f32)
+        self.new_energy, self.accept = be.empty((Bt,), f32), be.empty((Bt,), u8)
+        self.temperature, self.step_size_out = be.empty((Bt,), f32), be.empty((Bt,), f32)
+        self.z, self.grad2_mean = be.empty((Bt,), f32), be.empty((D,), f32)
+        self.stats_scratch = be.empty(((Bt + 63) // 64 * D,), f32)
+        self.link_tf, self.g_link_tf = be.empty((Bt, L, 12), f32), be.empty((Bt, L, 12), f32)
+        self.cpts, self.cnrm = be.empty((Bt, n_c, 3), f32), be.empty((Bt, n_c, 3), f32)
+        self.g_cpts, self.g_cnrm = be.empty((Bt, n_c, 3), f32), be.empty((Bt, n_c, 3), f32)
+        self.obj_dist, self.obj_nrm = be.empty((Bt, n_c), f32), be.empty((Bt, n_c, 3), f32)
+        self.obj_clst, self.obj_sign = be.empty((Bt, n_c, 3), f32), be.empty((Bt, n_c), i32)
+        self.obj_dgrad = be.empty((Bt, n_c, 3), f32)
+        self.ones = be.from_host(np.ones((Bt, n_c), f32))
+        self.lam = be.empty((Bt, n_c), f32)
+        self.g_pose_joints = be.empty((Bt, D), f32)
+        self.pen_scratch = be.empty((Bt * ((self.n_pts + 31) // 32),), f32)
+        self.qp_trace = be.empty((Bt, self.fc.max_iter), f32)
+        self.qp_stop = be.empty((1,), i32)
+        self.reset_all = be.from_host(np.ones(Bt, u8))
+        self._init_energy()
+
+    # ------------------------------------------------------------------------------------------------------------
+    def _ck(self, rc):
+        _lib.check(rc, self.lib)
+
+    def evaluate(self, pose, idx, losses_out, grad_out):
+        """calculate_energy (core/energy.py:6-66) + backward (fit.py:440) at (pose, idx): 5 terms and d(sum w E)/d pose."""
+        lib, be, p, st = self.lib, self.be, self.be.ptr, self.be.stream
+        Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
+        row = lambda k: p(losses_out) + 4 * Bt * TERMS.index(k)
+        self._ck(lib.gqp_fk_forward(self.hand, p(pose), Bt, p(self.link_tf), st))
+        self._ck(lib.gqp_contacts_forward(self.hand, p(self.link_tf), p(idx), Bt, n_c, p(self.cpts), p(self.cnrm), st))
+        self._ck(lib.gqp_object_distance_forward(self.objset, B, n_c, p(self.cpts), 1.0, p(self.obj_dist),
+                                                 p(self.obj_nrm), p(self.obj_clst), p(self.obj_sign), st))
+        self._ck(lib.gqp_object_distance_backward(p(self.ones), p(self.cpts), p(self.obj_clst), p(self.obj_sign),
+                                                  Bt * n_c, 1.0, p(self.obj_dgrad), st))
+        self._ck(lib.gqp_memset_zero(p(self.g_link_tf), 4 * Bt * self.L * 12, st))
+        fc_args = lambda stop, trace: (ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist),
+                                       p(self.obj_nrm), p(self.obj_dgrad), p(self.cog), O, B, n_c, row("E_fc"),
+                                       row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm), stop, trace, st)
+        if self.qp_batch_stop:  # replay qpth's batch-wide exit test: trace pass, exit iteration, final pass
+            self._ck(lib.gqp_fc_dis_energy(*fc_args(None, p(self.qp_trace))))
+            self._ck(lib.gqp_fc_stop_iter(p(self.qp_trace), Bt, self.fc.max_iter, self.fc.eps, p(self.qp_stop), st))
+            self._ck(lib.gqp_fc_dis_energy(*fc_args(p(self.qp_stop), None)))
+        else:
+            self._ck(lib.gqp_fc_dis_energy(*fc_args(None, None)))
+        self._ck(lib.gqp_contacts_backward(self.hand, p(idx), p(self.g_cpts), p(self.g_cnrm), Bt, n_c,
+                                           p(self.g_link_tf), st))
+        self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
+                                       row("E_pen"), p(self.pen_scratch), self.weights["E_pen"], p(self.g_link_tf), st))
+        self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
+                                         self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
+                                         p(self.g_pose_joints), st))
+        self._ck(lib.gqp_fk_backward(self.hand, p(pose), p(self.g_link_tf), p(self.g_pose_joints), Bt, p(grad_out), st))
+
+    def _accept(self, z, reset, u_accept):
+        lib, p, st = self.lib, self.be.ptr, self.be.stream
+        self._ck(lib.gqp_mala_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(TERMS), p(self.w_dev),
+                                     p(self.losses_new), p(z), p(reset), p(u_accept), self.seed, self.iteration,
+                                     p(self.step_count), p(self.pose_new), p(self.idx_new), p(self.grad_new),
+                                     p(self.pose), p(self.idx), p(self.grad), p(self.energy), p(self.losses),
+                                     p(self.new_energy), p(self.accept), p(self.temperature), st))
+
+    def _init_energy(self):
+        """fit.py:381-396: first energy + backward, then optimizer.zero_grad()."""
+        self.be.copy_(self.pose_new, self.pose)
+        self.be.copy_(self.idx_new, self.idx)
+        self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
+        self._accept(None, self.reset_all, None)
+        self.first_grad = self.be.to_host(self.grad)
+        self._ck(self.lib.gqp_memset_zero(self.be.ptr(self.grad), 4 * self.Bt * self.D, self.be.stream))
+
+    def step(self, u_switch=None, idx_rand=None, u_accept=None, reset_mask=None):
+        """One iteration of fit.py:399-458.  Noise arrays (device buffers) are injected, or drawn by Philox if None."""
+        lib, p, st = self.lib, self.be.ptr, self.be.stream
+        self.iteration += 1
+        self._ck(lib.gqp_mala_stats(p(self.grad), p(self.energy), self.n_obj, self.batch_each, self.D,
+                                    self.mala.clip_grad, p(self.grad2_mean), p(self.z), p(self.stats_scratch), st))
+        self._ck(lib.gqp_mala_propose(ctypes.byref(self.mala), p(self.pose), p(self.grad), p(self.grad2_mean),
+                                      p(self.ema), p(self.step_count), p(self.idx), self.Bt, self.D, self.n_c,
+                                      self.n_cand, p(u_switch), p(idx_rand), self.seed, self.iteration,
+                                      p(self.pose_new), p(self.idx_new), p(self.step_size_out), st))
+        self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
+        self._accept(self.z, reset_mask, u_accept)
+
+    def launches_per_step(self):
+        return 14 if self.qp_batch_stop else 12
+
+    def close(self):
+        lib = self.lib
+        if getattr(self, "objset", None):
+            lib.gqp_objset_destroy(self.objset)
+            self.objset = None
+        for m in getattr(self, "meshes", []):
+            lib.gqp_mesh_destroy(m)
+        self.meshes = []
+        if getattr(self, "hand", None):
+            lib.gqp_hand_destroy(self.hand)
+            self.hand = None

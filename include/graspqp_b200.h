@@ -171,18 +171,21 @@ typedef struct GqpMalaParams {
     int32_t annealing_period, stepsize_period;
     int32_t clip_grad;
 } GqpMalaParams;
-int gqp_mala_stats(const float *grad, const float *energy, int n_obj, int batch_each, int D, float *grad2_mean,
-                   float *z, float *scratch, void *stream);
+int gqp_mala_stats(const float *grad, const float *energy, int n_obj, int batch_each, int D, int clip_grad,
+                   float *grad2_mean, float *z, float *scratch /* ceil(Bt/64)*D floats */, void *stream);
 int gqp_mala_propose(const GqpMalaParams *p_host, const float *pose, const float *grad, const float *grad2_mean,
                      float *ema, int32_t *step, const int32_t *idx, int Bt, int D, int n_c, int n_cand,
                      const float *u_switch, const int32_t *idx_rand, uint64_t seed, uint64_t iteration, float *pose_new,
                      int32_t *idx_new, float *step_size_out, void *stream);
-int gqp_mala_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n_terms, const float *weights_host,
+int gqp_mala_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n_terms, const float *weights /* device (n_terms) */,
                     const float *losses_new /* (n_terms,Bt) */, const float *z, const uint8_t *reset_mask,
                     const float *u_accept, uint64_t seed, uint64_t iteration, const int32_t *step,
                     const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose, int32_t *idx,
                     float *grad, float *energy, float *losses /* (n_terms,Bt) */, float *new_energy_out,
                     uint8_t *accept_out, float *temperature_out, void *stream);
+
+/* cudaMemsetAsync(ptr, 0, bytes) on the stream: the per-step reset of grad_link_tf. */
+int gqp_memset_zero(void *ptr, uint64_t bytes, void *stream);
 
 /* FP32 FMA micro-benchmark (roofline denominator for the SIMT stages): runs `iters` dependent-chain FMAs on every
  * lane of a full-chip grid; returns the FMA count in *n_fma_host.  Timed by the caller with CUDA events. */

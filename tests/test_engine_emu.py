@@ -1,0 +1,52 @@
+"""The whole iteration (FitEngine over the C-ABI, kernels run by the host emulator) vs the torch oracle of
+scripts/fit.py:399-458 with injected noise — CPU only, tiny sizes."""
+import numpy as np
+import pytest
+import torch
+
+from graspqp_b200 import engine, hand_pack, synth
+from oracle.pipeline import FitLoopOracle
+
+
+def make_case(B=4, n_pts=64, n_c=12, seed=3):
+    pack = hand_pack.load_pack("allegro")
+    v, f = synth.make_mesh("sphere", 200, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.7  # closer to the object: penetration and contact terms are active
+    return pack, fv, sp, pose, idx
+
+
+def noise(T, B, n_c, n_cand, seed=0):
+    rng = np.random.default_rng(seed)
+    return (rng.random((T, B, n_c), dtype=np.float32), rng.integers(0, n_cand, (T, B, n_c)).astype(np.int32),
+            rng.random((T, B), dtype=np.float32))
+
+
+def test_iteration_vs_oracle(emu):
+    B, n_c, T = 4, 12, 3
+    pack, fv, sp, pose, idx = make_case(B=B, n_c=n_c)
+    eng = engine.FitEngine(emu, engine.NumpyBackend(), pack, [fv], sp[None], B, pose, idx.astype(np.int32))
+    orc = FitLoopOracle(pack, [fv], [sp], B, pose, idx, dtype=torch.float64)
+    np.testing.assert_allclose(eng.energy, orc.energy.numpy(), rtol=1e-4)
+    for k, name in enumerate(engine.TERMS):
+        np.testing.assert_allclose(eng.losses[k], orc.losses[name].numpy(), rtol=1e-4, atol=1e-6, err_msg=name)
+    g0 = orc.first_grad.numpy()
+    np.testing.assert_allclose(eng.first_grad, g0, rtol=2e-3, atol=2e-3 * np.abs(g0).max())
+    us, ir, ua = noise(T, B, n_c, len(pack["cand"]))
+    for t in range(T):
+        eng.step(us[t], ir[t], ua[t])
+        out = orc.iterate(torch.tensor(us[t], dtype=torch.float64), torch.tensor(ir[t]).long(),
+                          torch.tensor(ua[t], dtype=torch.float64))
+        np.testing.assert_array_equal(eng.idx_new, out["idx_prop"].numpy())
+        np.testing.assert_allclose(eng.pose_new, out["proposal"].numpy(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(eng.new_energy, out["new_energy"].numpy(), rtol=2e-4)
+        g = out["new_grad"].numpy()
+        np.testing.assert_allclose(eng.grad_new, g, rtol=2e-3, atol=2e-3 * np.abs(g).max())
+        np.testing.assert_allclose(eng.z, out["z"].numpy(), rtol=1e-3, atol=1e-4)
+        np.testing.assert_array_equal(eng.accept.astype(bool), out["accept"].numpy())
+        np.testing.assert_allclose(eng.temperature, out["temperature"].numpy(), rtol=1e-4)
+        np.testing.assert_allclose(eng.energy, orc.energy.numpy(), rtol=2e-4)
+        np.testing.assert_allclose(eng.pose, orc.hand.hand_pose.detach().numpy(), rtol=1e-4, atol=1e-5)
+    eng.close()
