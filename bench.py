@@ -1,0 +1,283 @@
+#!/usr/bin/env python
+"""bench.py — grasp-steps/s of the GraspQP hot path (per-iteration energy + MALA* update), BASELINE.json's metric.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload config2] [--impl reference]
+
+A step = one iteration of scripts/fit.py:399-458 over the whole batch of this rank (N=1 workload: config 2 = Allegro,
+8 synthetic 10k-triangle meshes, 1024 candidates per object, n_contact 12, 2500 surface samples).  N>1: one process per
+GPU (torchrun), every rank optimises its own 8 objects (weak scaling, no data-path collective; NCCL only for the
+barrier, the max-over-ranks time and the final all-gather of energies).
+`--impl reference` times the CPU restatement of the reference path (oracle/, torch CPU + host-compiled TorchSDF math) on
+a bounded sample of the same workload; rank 0 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "grasp-steps/sec"
+UNIT = "grasp-steps/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="config2")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=None, help="override candidates per object")
+    ap.add_argument("--objects", type=int, default=None, help="override objects per GPU")
+    ap.add_argument("--no-qp-batch-stop", action="store_true")
+    ap.add_argument("--cpu-sample-batch", type=int, default=16)
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md's clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(args, steps, warmup, sample_batch):
+    """The CPU restatement of the reference path (oracle/) on a bounded sample: 1 object of the workload,
+    `sample_batch` candidates, all host threads."""
+    import torch
+    from graspqp_b200 import workload
+    from oracle.pipeline import FitLoopOracle
+    subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
+    w = workload.build(args.workload, batch_each=sample_batch, n_objects=1)
+    B, n_c = sample_batch, w["n_contact"]
+    orc = FitLoopOracle(w["pack"], w["face_verts"], [w["surface"][0]], B, w["pose"], w["idx"].astype(np.int64),
+                        dtype=torch.float32)
+    rng = np.random.default_rng(0)
+    n_cand = len(w["pack"]["cand"])
+
+    def one():
+        orc.iterate(torch.tensor(rng.random((B, n_c), dtype=np.float32)),
+                    torch.tensor(rng.integers(0, n_cand, (B, n_c))).long(), torch.tensor(rng.random(B, dtype=np.float32)))
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    cores = torch.get_num_threads()
+    return dict(value=B * steps / dt, unit=UNIT, cores=cores, kind="port", seconds=dt,
+                sample=f"{args.workload}: 1 object ({w['kinds'][0]}, {w['faces_per_mesh']} tris) x {B} candidates x "
+                       f"{steps} iterations, 2500 surface samples, torch-CPU fp32 + OpenMP TorchSDF math "
+                       f"({os.cpu_count()} host cpus)"), dt / steps
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # bounded: the oracle does ~1 s per iteration of 16 candidates on 8 cores
+    steps, warmup = min(steps, 10), min(warmup, 2)
+    cb, sec_per_step = cpu_reference_run(args, steps, warmup, args.cpu_sample_batch)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * sec_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "sample": cb["sample"]}, "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from graspqp_b200 import _lib, engine, workload
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.lib()
+    be = engine.TorchBackend(dev)
+    w = workload.build(args.workload, rank=rank, batch_each=args.batch, n_objects=args.objects)
+    B, n_c, O = w["batch_each"], w["n_contact"], len(w["face_verts"])
+    Bt = B * O
+    t_setup = time.perf_counter()
+    eng = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], B, w["pose"], w["idx"],
+                           qp_batch_stop=not args.no_qp_batch_stop, seed=1 + rank)
+    torch.cuda.synchronize()
+    t_setup = time.perf_counter() - t_setup
+    K, W = max(1, args.steps), max(3, args.warmup)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (Philox noise drawn on the device) ----
+    for _ in range(W):
+        eng.step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    n0 = lib.gqp_launch_count()
+    evs = []
+    for _ in range(K):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.step()
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    launches = int(lib.gqp_launch_count() - n0)
+    clocks = sampler.stop()
+    ms_total = sum(a.elapsed_time(b) for a, b in evs)
+    # ---- end-to-end: host noise in pinned memory -> device, step, energy + accept back to the host, every step ----
+    n_cand = len(w["pack"]["cand"])
+    rng = np.random.default_rng(rank)
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    h_us = [pin(rng.random((Bt, n_c), dtype=np.float32)) for _ in range(K)]
+    h_ir = [pin(rng.integers(0, n_cand, (Bt, n_c)).astype(np.int32)) for _ in range(K)]
+    h_ua = [pin(rng.random(Bt, dtype=np.float32)) for _ in range(K)]
+    d_us, d_ir, d_ua = be.empty((Bt, n_c), np.float32), be.empty((Bt, n_c), np.int32), be.empty((Bt,), np.float32)
+    h_energy, h_accept = torch.empty(Bt, dtype=torch.float32).pin_memory(), torch.empty(Bt, dtype=torch.uint8).pin_memory()
+    barrier()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for k in range(K):
+        d_us.copy_(h_us[k], non_blocking=True); d_ir.copy_(h_ir[k], non_blocking=True); d_ua.copy_(h_ua[k], non_blocking=True)
+        eng.step(d_us, d_ir, d_ua)
+        h_energy.copy_(eng.energy, non_blocking=True); h_accept.copy_(eng.accept, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller reads the energies every iteration
+    s1.record()
+    barrier()
+    ms_e2e = s0.elapsed_time(s1)
+    h2d = Bt * n_c * 8 + Bt * 4
+    d2h = Bt * 5
+    # ---- dominant kernel alone: hand penetration (H4) on the current state ----
+    p = be.ptr
+    reps = max(5, K)
+    for _ in range(2):
+        lib.gqp_hand_distance(eng.hand, p(eng.link_tf), p(eng.surf), O, B, eng.n_pts, 0, None, p(eng.new_energy),
+                              p(eng.pen_scratch), 100.0, p(eng.g_link_tf), be.stream)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    k0.record()
+    for _ in range(reps):
+        lib.gqp_hand_distance(eng.hand, p(eng.link_tf), p(eng.surf), O, B, eng.n_pts, 0, None, p(eng.new_energy),
+                              p(eng.pen_scratch), 100.0, p(eng.g_link_tf), be.stream)
+    k1.record()
+    torch.cuda.synchronize()
+    ms_pen = k0.elapsed_time(k1) / reps
+    # FP32 FMA peak, measured live
+    sink = be.empty((4,), np.float32)
+    import ctypes
+    nf = ctypes.c_uint64(0)
+    lib.gqp_fma_peak_probe(2000, p(sink), ctypes.byref(nf), be.stream)
+    torch.cuda.synchronize()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    lib.gqp_fma_peak_probe(20000, p(sink), ctypes.byref(nf), be.stream)
+    f1.record()
+    torch.cuda.synchronize()
+    fp32_peak_tflops = 2.0 * nf.value / (f0.elapsed_time(f1) * 1e-3) / 1e12
+    # ---- max over ranks, gather ----
+    t = torch.tensor([ms_total, ms_e2e, ms_pen], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gathered = [torch.empty_like(eng.energy) for _ in range(world)]
+        dist.all_gather(gathered, eng.energy)  # final energies of all ranks (the only data exchange of the path)
+    ms_total, ms_e2e, ms_pen = [float(v) for v in t.tolist()]
+    final_energy = float(eng.energy.float().mean().item())
+    if rank == 0:
+        f_hand = int(w["pack"]["face_offset"][-1])
+        pen_flops = 80.0 * eng.n_pts * f_hand * Bt  # brute-force-equivalent point-face tests x 80 flop
+        achieved = pen_flops / (ms_pen * 1e-3) / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        alg_bytes = Bt * (eng.L * 48 + 4 + 4 * ((eng.n_pts + 31) // 32)) + O * eng.n_pts * 12
+        line = {
+            "metric": METRIC, "value": Bt * world * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
+                                   f"{w['faces_per_mesh']} tris), batch {B}/object, n_contact {n_c}, 2500 surface samples",
+                       "candidates_per_gpu": Bt, "l2": "flushed between timed steps (256 MiB write)",
+                       "qp_batch_stop": eng.qp_batch_stop, "noise": "philox on device (value) / injected from host (e2e)",
+                       "setup_s": round(t_setup, 2), "final_mean_energy": final_energy},
+            "e2e": {"value": Bt * world * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h},
+            "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"bound": "fp32", "kernel": "hand_pen_kernel<true> (H4, hand penetration)", "achieved": achieved,
+                         "peak": fp32_peak_tflops, "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops,
+                         "traffic": None, "ms_per_launch": ms_pen,
+                         "note": "achieved = brute-force-equivalent flops (80 x n_pts x F_hand x candidates) / launch "
+                                 "time; exact culling skips most pairs, so frac may exceed 1 (SURVEY 8d). peak = FP32 "
+                                 "FMA probe measured live in this run",
+                         "hbm": {"achieved": alg_bytes / (ms_pen * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": alg_bytes / (ms_pen * 1e-3) / 1e9 / hbm_peak,
+                                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}},
+        }
+        if world == 1 and not args.skip_cpu_baseline:
+            cb, _ = cpu_reference_run(args, 10, 1, args.cpu_sample_batch)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -1,0 +1,128 @@
+"""Parity cases shared by the GPU tests (libgraspqp_b200.so + torch CUDA tensors).  Each takes (lib, be)."""
+import ctypes
+
+import numpy as np
+import torch
+
+from graspqp_b200 import _lib, engine, hand_pack, synth
+from oracle import qp as oqp
+from oracle import sdf as osdf
+from oracle.hand import HandOracle
+from oracle.pipeline import FitLoopOracle
+
+
+def sdf_forward(lib, be, pts, fv):
+    P = len(pts)
+    dp, df = be.from_host(pts, np.float32), be.from_host(fv.reshape(-1, 9), np.float32)
+    d2, sg = be.empty((P,), np.float32), be.empty((P,), np.int32)
+    nr, cl = be.empty((P, 3), np.float32), be.empty((P, 3), np.float32)
+    _lib.check(lib.gqp_sdf_forward(be.ptr(dp), be.ptr(df), P, len(fv), be.ptr(d2), be.ptr(sg), be.ptr(nr), be.ptr(cl),
+                                   be.stream), lib)
+    return [be.to_host(a) for a in (d2, sg, nr, cl)]
+
+
+def mesh_sdf_forward(lib, be, pts, fv):
+    P = len(pts)
+    fvh = np.ascontiguousarray(fv.reshape(-1, 9), np.float32)
+    m = ctypes.c_void_p()
+    _lib.check(lib.gqp_mesh_create(fvh.ctypes.data, len(fvh), ctypes.byref(m)), lib)
+    dp = be.from_host(pts, np.float32)
+    d2, sg, fi = be.empty((P,), np.float32), be.empty((P,), np.int32), be.empty((P,), np.int32)
+    nr, cl = be.empty((P, 3), np.float32), be.empty((P, 3), np.float32)
+    _lib.check(lib.gqp_mesh_sdf_forward(m, be.ptr(dp), P, be.ptr(d2), be.ptr(sg), be.ptr(nr), be.ptr(cl), be.ptr(fi),
+                                        be.stream), lib)
+    out = [be.to_host(a) for a in (d2, sg, nr, cl, fi)]
+    lib.gqp_mesh_destroy(m)
+    return out
+
+
+def query_points(fv, P, seed=0, spread=0.15):
+    rng = np.random.default_rng(seed)
+    pts = rng.uniform(-spread, spread, (P, 3)).astype(np.float32)
+    k = P // 4
+    pts[:k] = (fv.reshape(-1, 3)[rng.integers(0, len(fv) * 3, k)] * (1 + rng.normal(size=(k, 1)) * 0.02)).astype(np.float32)
+    return pts
+
+
+def check_sdf_bit_exact(lib, be, kind, nf, P, seed=0):
+    v, f = synth.make_mesh(kind, nf, seed + 1)
+    fv = synth.face_vertices(v, f)
+    pts = query_points(fv, P, seed)
+    want = osdf.compute_sdf_port(pts, fv, with_face=True)
+    got = sdf_forward(lib, be, pts, fv)
+    for g, w in zip(got, want[:4]):
+        np.testing.assert_array_equal(g, w)
+    got = mesh_sdf_forward(lib, be, pts, fv)
+    for g, w in zip(got, want):
+        np.testing.assert_array_equal(g, w)
+
+
+def fk_state(lib, be, hand, pack, pose):
+    B, L = len(pose), len(pack["mesh_frame"])
+    dpose = be.from_host(pose, np.float32)
+    tf = be.empty((B, L, 12), np.float32)
+    _lib.check(lib.gqp_fk_forward(hand, be.ptr(dpose), B, be.ptr(tf), be.stream), lib)
+    return dpose, tf
+
+
+def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5):
+    """culled E_pen / gradient == un-culled at the reference's sample count; distances vs the oracle on a subset."""
+    pack = hand_pack.load_pack("allegro")
+    hand = hand_pack.create_hand(lib, pack)
+    v, f = synth.make_mesh("hull", 2000, seed)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed, oversample=2)
+    pose, idx = synth.random_grasp_init(pack, [v], B, 12, seed)
+    pose[:, :3] *= np.linspace(0.4, 1.0, B, dtype=np.float32)[:, None]
+    dpose, tf = fk_state(lib, be, hand, pack, pose)
+    L = len(pack["mesh_frame"])
+    x = be.from_host(sp[None], np.float32)
+    dist = be.empty((B, n_pts), np.float32)
+    e1, e2 = be.empty((B,), np.float32), be.empty((B,), np.float32)
+    sc = be.empty((B * ((n_pts + 31) // 32),), np.float32)
+    g1, g2 = be.empty((B, L, 12), np.float32), be.empty((B, L, 12), np.float32)
+    _lib.check(lib.gqp_hand_distance(hand, be.ptr(tf), be.ptr(x), 1, B, n_pts, 0, be.ptr(dist), be.ptr(e1), be.ptr(sc),
+                                     100.0, be.ptr(g1), be.stream), lib)
+    _lib.check(lib.gqp_hand_distance(hand, be.ptr(tf), be.ptr(x), 1, B, n_pts, 0, None, be.ptr(e2), be.ptr(sc), 100.0,
+                                     be.ptr(g2), be.stream), lib)
+    e1h, e2h, g1h, g2h, dh = [be.to_host(a) for a in (e1, e2, g1, g2, dist)]
+    assert (e1h > 0).sum() >= B // 4, "poses do not penetrate"
+    np.testing.assert_array_equal(e2h, e1h)  # same winners, same fixed-order sums
+    np.testing.assert_allclose(g2h, g1h, rtol=1e-4, atol=1e-4)  # atomics: order differs
+    nb = min(B, 6)
+    o = HandOracle(pack, torch.float32)
+    o.set_parameters(torch.tensor(pose[:nb]), torch.tensor(idx[:nb]).long())
+    want = o.cal_distance(torch.tensor(sp).unsqueeze(0).repeat(nb, 1, 1)).numpy()
+    np.testing.assert_allclose(dh[:nb], want, atol=1e-5)
+    np.testing.assert_allclose(e1h[:nb], np.maximum(want, 0).sum(-1), rtol=1e-4, atol=1e-5)
+    lib.gqp_hand_destroy(hand)
+
+
+def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=False):
+    pack = hand_pack.load_pack("allegro")
+    v, f = synth.make_mesh("hull" if hull else "sphere", 400, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.7
+    eng = engine.FitEngine(lib, be, pack, [fv], sp[None], B, pose, idx.astype(np.int32))
+    orc = FitLoopOracle(pack, [fv], [sp], B, pose, idx, dtype=torch.float64)
+    H = be.to_host
+    np.testing.assert_allclose(H(eng.energy), orc.energy.numpy(), rtol=1e-4)
+    g0 = orc.first_grad.numpy()
+    np.testing.assert_allclose(eng.first_grad, g0, rtol=2e-3, atol=2e-3 * np.abs(g0).max())
+    rng = np.random.default_rng(0)
+    n_acc = 0
+    for t in range(T):
+        us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, len(pack["cand"]), (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+        eng.step(be.from_host(us), be.from_host(ir), be.from_host(ua))
+        out = orc.iterate(torch.tensor(us, dtype=torch.float64), torch.tensor(ir).long(), torch.tensor(ua, dtype=torch.float64))
+        np.testing.assert_array_equal(H(eng.idx_new), out["idx_prop"].numpy())
+        np.testing.assert_allclose(H(eng.new_energy), out["new_energy"].numpy(), rtol=2e-4)
+        g = out["new_grad"].numpy()
+        np.testing.assert_allclose(H(eng.grad_new), g, rtol=2e-3, atol=2e-3 * np.abs(g).max())
+        np.testing.assert_array_equal(H(eng.accept).astype(bool), out["accept"].numpy())
+        np.testing.assert_allclose(H(eng.energy), orc.energy.numpy(), rtol=2e-4)
+        np.testing.assert_allclose(H(eng.pose), orc.hand.hand_pose.detach().numpy(), rtol=1e-4, atol=1e-5)
+        n_acc += int(out["accept"].sum())
+    eng.close()
+    return n_acc

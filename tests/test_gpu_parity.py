@@ -1,0 +1,73 @@
+"""Parity tests proper: the CUDA path through the C-ABI (libgraspqp_b200.so) vs the oracle.  Run with -m gpu on a B200."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu(oracle_built):
+    from graspqp_b200 import _lib, engine
+    assert torch.cuda.is_available()
+    return _lib.lib(), engine.TorchBackend("cuda:0")
+
+
+@pytest.mark.parametrize("kind,nf,P", [("sphere", 80, 1000), ("box", 2000, 20000), ("torus", 10000, 30011),
+                                       ("hull", 10000, 4096), ("cylinder", 2051, 777)])
+def test_sdf_bit_exact(gpu, kind, nf, P):
+    cases.check_sdf_bit_exact(*gpu, kind, nf, P)
+
+
+def test_sdf_self_consistency_full_size(gpu):
+    """thirdparty/TorchSDF/tests/normal.py:36-39 law at 50k faces x 200k points: normal * 2 sqrt(d2) == backward(1);
+    BVH and brute force agree bit for bit (winner included)."""
+    lib, be = gpu
+    from graspqp_b200 import synth
+    v, f = synth.make_mesh("hull", 50000, 7)
+    fv = synth.face_vertices(v, f)
+    pts = cases.query_points(fv, 200000, 1)
+    d2, sg, nr, cl = cases.sdf_forward(lib, be, pts, fv)
+    d2b, sgb, nrb, clb, fi = cases.mesh_sdf_forward(lib, be, pts, fv)
+    np.testing.assert_array_equal(d2, d2b); np.testing.assert_array_equal(sg, sgb)
+    np.testing.assert_array_equal(cl, clb); np.testing.assert_array_equal(nr, nrb)
+    np.testing.assert_allclose(nr * 2 * np.sqrt(d2)[:, None], 2 * (pts - cl), atol=5e-7)
+    np.testing.assert_allclose(((pts - cl) ** 2).sum(-1), d2, rtol=1e-5, atol=1e-12)
+    assert set(np.unique(sg)) <= {-1, 1}
+
+
+def test_hand_distance(gpu):
+    cases.check_hand_distance(*gpu)
+
+
+def test_engine_vs_oracle(gpu):
+    n_acc = cases.check_engine_vs_oracle(*gpu, B=8, n_pts=256, T=4)
+    assert n_acc > 0
+
+
+def test_engine_vs_oracle_hull_nc16(gpu):
+    cases.check_engine_vs_oracle(*gpu, B=6, n_pts=200, n_c=16, T=3, seed=11, hull=True)
+
+
+def test_philox_run_is_deterministic(gpu):
+    lib, be = gpu
+    from graspqp_b200 import engine, hand_pack, synth
+    pack = hand_pack.load_pack("allegro")
+    v, f = synth.make_mesh("box", 1000, 2)
+    fv, sp = synth.face_vertices(v, f), synth.sample_surface(v, f, 512, seed=2)
+    pose, idx = synth.random_grasp_init(pack, [v, v], 64, 12, 2)
+    runs = []
+    for _ in range(2):
+        eng = engine.FitEngine(lib, be, pack, [fv, fv], np.stack([sp, sp]), 64, pose, idx.astype(np.int32), seed=5)
+        for _ in range(10):
+            eng.step()
+        runs.append((be.to_host(eng.energy), be.to_host(eng.idx), be.to_host(eng.accept)))
+        eng.close()
+    np.testing.assert_array_equal(runs[0][1], runs[1][1])
+    np.testing.assert_array_equal(runs[0][2], runs[1][2])
+    np.testing.assert_allclose(runs[0][0], runs[1][0], rtol=1e-4)
+    assert np.isfinite(runs[0][0]).all()
