@@ -14,6 +14,7 @@ if [ -f "$SRC" ]; then
       > _ref/torchsdf_kernel_body.inc
   echo "}  // namespace kaolin" >> _ref/torchsdf_kernel_body.inc
   g++ -O2 -ffp-contract=off -fopenmp -fPIC -shared -I. -I_ref ref_wrap.cpp -o _ref/libtorchsdf_ref.so
+  rm -f _ref/torchsdf_kernel_body.inc  # the extracted kernel text is a build intermediate, never kept
   echo "built oracle/_ref/libtorchsdf_ref.so"
 else
   echo "reference not present; keeping prebuilt oracle/_ref if any"
