@@ -50,16 +50,15 @@ __device__ __forceinline__ void warp_allreduce(double *sm, double (&v)[K], int l
 // packed lower-triangular index
 __device__ __forceinline__ int tri_ix(int i, int j) { return i * (i + 1) / 2 + j; }
 
-// in-place Cholesky of a packed 6x6 SPD matrix (lower), A = L L'
+// in-place Cholesky of a packed 6x6 SPD matrix (lower), A = L L'; diagonal entries are stored INVERTED
 __device__ __forceinline__ void chol6(double *A) {
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
         double s = A[tri_ix(j, j)];
 #pragma unroll
         for (int k = 0; k < j; ++k) s -= A[tri_ix(j, k)] * A[tri_ix(j, k)];
-        double l = sqrt(s);
-        A[tri_ix(j, j)] = l;
-        double inv = 1.0 / l;
+        double inv = rsqrt(s);  // the diagonal holds 1/L_jj: the solves multiply instead of dividing
+        A[tri_ix(j, j)] = inv;
 #pragma unroll
         for (int i = j + 1; i < 6; ++i) {
             double t = A[tri_ix(i, j)];
@@ -75,14 +74,14 @@ __device__ __forceinline__ void chol6_solve(const double *L, double *y) {
         double t = y[i];
 #pragma unroll
         for (int k = 0; k < i; ++k) t -= L[tri_ix(i, k)] * y[k];
-        y[i] = t / L[tri_ix(i, i)];
+        y[i] = t * L[tri_ix(i, i)];
     }
 #pragma unroll
     for (int i = 5; i >= 0; --i) {
         double t = y[i];
 #pragma unroll
         for (int k = i + 1; k < 6; ++k) t -= L[tri_ix(k, i)] * y[k];
-        y[i] = t / L[tri_ix(i, i)];
+        y[i] = t * L[tri_ix(i, i)];
     }
 }
 
@@ -93,7 +92,7 @@ struct Dir {
 // step length to the boundary (qpth get_step): min over entries with dv < 0 of -v/dv, +inf otherwise
 __device__ __forceinline__ double step_len(double v, double dv) { return dv < 0.0 ? -v / dv : 1e300; }
 
-__global__ void __launch_bounds__(FC_WARPS * 32)
+__global__ void __launch_bounds__(FC_WARPS * 32, 3)
 fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
               const float *__restrict__ obj_dist, const float *__restrict__ obj_nrm,
               const float *__restrict__ obj_dgrad, const float *__restrict__ cog, int Bt, int batch_each, int n_c,
@@ -300,6 +299,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 zu[v] += a2 * aff.dzu[v]; zl[v] += a2 * aff.dzl[v];
             }
         }
+        if (!e_fc && !e_dis && !lam_out && !grad_cpts && !grad_cnrm) continue;  // trace-only pass
         // ---- value, svd term, E_fc (qp_solver.py:126, span.py:402, registry.py:82-87) ----
         double red[27];
 #pragma unroll
@@ -324,7 +324,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         chol6(Lg);  // F F' = Lg Lg'  ->  prod(svdvals(F)) = prod(diag Lg)
         double logdet = 0.0;
 #pragma unroll
-        for (int i = 0; i < 6; ++i) logdet += log(Lg[tri_ix(i, i)]);
+        for (int i = 0; i < 6; ++i) logdet -= log(Lg[tri_ix(i, i)]);  // diagonal is stored inverted
         const bool rank_ok = logdet == logdet;  // NaN when F F' is numerically singular
         const double svd = rank_ok ? exp(logdet / 6.0) : 0.0;
         const double ex = exp(-P.svd_gain * svd);

@@ -45,8 +45,9 @@ struct GqpPenTables {
 #ifdef GQP_EMU
 #define PEN_THREADS 64
 #else
-#define PEN_THREADS 768
+#define PEN_THREADS 512
 #endif
+#define PEN_MIN_BLOCKS 2
 #define PEN_MAX_SMEM (200 * 1024)
 
 // true when q is provably outside the (nice) link mesh: outside its box, or in a grid cell entirely outside it
@@ -62,7 +63,7 @@ __device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *gri
 }
 
 template <bool CULL>
-__global__ void __launch_bounds__(PEN_THREADS)
+__global__ void __launch_bounds__(PEN_THREADS, PEN_MIN_BLOCKS)
 hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
                 const int32_t *__restrict__ face_id, const float *__restrict__ link_tf, const float *__restrict__ x,
                 int Bt, int batch_each, int n_pts, int per_candidate_points, float *__restrict__ dist_out,
@@ -82,6 +83,8 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
 
     const int lane = threadIdx.x & 31;
     const int warps_per_block = blockDim.x / 32;
+    // per-warp staging of the candidate's link transforms (L x 12 floats), behind the blob
+    float *sW = reinterpret_cast<float *>(sm + blob_bytes) + (size_t)(threadIdx.x >> 5) * L * 12;
     const int n_chunks = (n_pts + 31) / 32;
     const long long n_tasks = (long long)Bt * n_chunks;
     for (long long task = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;
@@ -92,16 +95,42 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
         const int pj = valid ? pi : n_pts - 1;
         const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
         const V3 p = ld3(x + (row * n_pts + pj) * 3);
+        const float *Wb = link_tf + (size_t)b * L * 12;
+        // bounding sphere of the warp's 32 samples (callers order samples spatially, so it is small)
+        V3 cen = V3{warp_sum(p.x) * (1.f / 32.f), warp_sum(p.y) * (1.f / 32.f), warp_sum(p.z) * (1.f / 32.f)};
+        V3 dc = p - cen;
+        const float rad = sqrtf(warp_max(dot3(dc, dc))) * 1.0001f + 1e-5f;
+        // lane l: stage link l's transform and test the sphere against the link's box (exact for "nice" links:
+        // every sample outside the box is outside the mesh, where the reference's sign is +1)
+        bool keep = false;
+        for (int l0 = 0; l0 < L; l0 += 32) {  // L <= 32: one round
+            const int l = l0 + lane;
+            if (l < L) {
+                T34 W = t34_load(Wb + l * 12);
+#pragma unroll
+                for (int i = 0; i < 12; ++i) sW[l * 12 + i] = W.m[i];
+                const PenLink &K = links[l];
+                keep = K.n_faces > 0;  // hand_model.py:919-921: links without a mesh are skipped
+                if (CULL && keep && K.grid >= 0) {
+                    V3 q = t34_inv_point(W, cen);
+                    if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
+                        q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
+                        keep = false;
+                }
+            }
+        }
+        unsigned todo = __ballot_sync(GQP_FULL, keep);
+        __syncwarp();
         float best_d = -__int_as_float(0x7f800000);
         int best_l = -1;
         V3 best_g = V3{0, 0, 0};
-        const float *Wb = link_tf + (size_t)b * L * 12;
-        for (int l = 0; l < L; ++l) {
+        while (todo) {
+            const int l = __ffs((int)todo) - 1;
+            todo &= todo - 1;
             const PenLink &K = links[l];
-            if (K.n_faces == 0) continue;  // hand_model.py:919-921: links without a mesh are skipped
             T34 W;
 #pragma unroll
-            for (int i = 0; i < 12; ++i) W.m[i] = __ldg(Wb + l * 12 + i);
+            for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
             V3 q = t34_inv_point(W, p);
             if (CULL && pen_outside(K, grids, bits, q)) continue;
             SdfBest best;
@@ -121,21 +150,22 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
         float e = (valid && best_d > 0.f) ? best_d : 0.f;  // energy.py:60-61
         if (grad_link_tf && e > 0.f) {
             // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
-            T34 W = t34_load(Wb + best_l * 12);
+            const float *W = sW + best_l * 12;
             V3 g = best_g * w_pen;
             float *G = grad_link_tf + ((size_t)b * L + best_l) * 12;
-            float pt[3] = {p.x - W.m[3], p.y - W.m[7], p.z - W.m[11]}, gv[3] = {g.x, g.y, g.z};
+            float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {g.x, g.y, g.z};
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
 #pragma unroll
                 for (int i = 0; i < 3; ++i) atomicAdd(G + 4 * j + i, pt[j] * gv[i]);
-                atomicAdd(G + 4 * j + 3, -(W.m[4 * j] * gv[0] + W.m[4 * j + 1] * gv[1] + W.m[4 * j + 2] * gv[2]));
+                atomicAdd(G + 4 * j + 3, -(W[4 * j] * gv[0] + W[4 * j + 1] * gv[1] + W[4 * j + 2] * gv[2]));
             }
         }
         if (partial) {
             float s = warp_sum(e);
             if (lane == 0) partial[task] = s;
         }
+        __syncwarp();  // sW is rewritten by the next task
     }
 }
 
@@ -315,8 +345,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     T->d_face_id = (int32_t *)gqp_dev_alloc_upload(fid.data(), fid.size() * sizeof(int32_t));
     if (!T->d_blob || !T->d_tris || !T->d_face_id) return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
 #ifndef GQP_EMU
-    cudaFuncSetAttribute(hand_pen_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM);
-    cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM);
+    cudaFuncSetAttribute(hand_pen_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
+    cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
 #endif
     return GQP_OK;
 }
@@ -333,7 +363,7 @@ static int pen_grid_size(int blob_bytes, long long n_tasks) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int per_sm = (int)std::max(1, std::min(8, (int)((220 * 1024) / (blob_bytes + 1024))));
+    int per_sm = (int)std::max(1, std::min(PEN_MIN_BLOCKS, (int)((226 * 1024) / (blob_bytes + 1024))));
     long long want = (n_tasks + PEN_THREADS / 32 - 1) / (PEN_THREADS / 32);
     return (int)std::max(1LL, std::min<long long>(want, (long long)sms * per_sm));
 #else
@@ -353,14 +383,15 @@ extern "C" int gqp_hand_distance(const GqpHand *h, const float *link_tf, const f
     const int n_chunks = (n_pts + 31) / 32;
     const long long n_tasks = (long long)Bt * n_chunks;
     const GqpPenTables *T = h->pen;
-    int grid = pen_grid_size(T->total_bytes, n_tasks);
+    const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * h->host.n_links * 48;
+    int grid = pen_grid_size((int)smem, n_tasks);
     float *partial = e_pen ? scratch : nullptr;
     if (dist) {  // every link's true distance is needed: no culling
-        GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, (size_t)T->total_bytes, (cudaStream_t)stream, T->d_blob,
+        GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, (cudaStream_t)stream, T->d_blob,
                    T->total_bytes, T->d_tris, T->d_face_id, link_tf, x, Bt, batch_each, n_pts, per_candidate_points,
                    dist, partial, w_pen, grad_link_tf);
     } else {
-        GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, (size_t)T->total_bytes, (cudaStream_t)stream, T->d_blob,
+        GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, (cudaStream_t)stream, T->d_blob,
                    T->total_bytes, T->d_tris, T->d_face_id, link_tf, x, Bt, batch_each, n_pts, per_candidate_points,
                    dist, partial, w_pen, grad_link_tf);
     }

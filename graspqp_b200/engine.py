@@ -21,6 +21,18 @@ TERMS = ("E_dis", "E_fc", "E_joints", "E_pen", "E_spen")
 DEFAULT_WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_joints=1.0, E_pen=100.0, E_spen=10.0)  # scripts/fit.py:90-112
 
 
+def morton_order(pts, bits=10):
+    """permutation sorting (N,3) points along a Z-order curve"""
+    p = np.asarray(pts, np.float64)
+    lo, hi = p.min(0), p.max(0)
+    q = np.minimum(((p - lo) / np.maximum(hi - lo, 1e-12) * (1 << bits)).astype(np.int64), (1 << bits) - 1)
+    code = np.zeros(len(p), np.int64)
+    for b in range(bits):
+        for k in range(3):
+            code |= ((q[:, k] >> b) & 1) << (3 * b + k)
+    return np.argsort(code, kind="stable")
+
+
 class NumpyBackend:
     """Host buffers for the emulator library (tests/_emu).  Test infrastructure."""
     stream = None
@@ -96,6 +108,8 @@ class FitEngine:
         surface_points = np.ascontiguousarray(surface_points, np.float32)
         assert surface_points.shape[0] == self.n_obj and surface_points.shape[2] == 3
         self.n_pts = surface_points.shape[1]
+        # spatial (Morton) order: the penetration kernel culls whole 32-sample chunks against each link's box
+        surface_points_sorted = np.stack([sp[morton_order(sp)] for sp in surface_points])
         # ---- handles ----
         self.hand = hand_pack.create_hand(cdll, pack)
         self.meshes = []
@@ -120,7 +134,7 @@ class FitEngine:
                                        clip_grad=int(clip_grad))
         # ---- device state ----
         f32, i32, u8 = np.float32, np.int32, np.uint8
-        self.surf = be.from_host(surface_points, f32)
+        self.surf = be.from_host(surface_points_sorted, f32)
         self.cog = be.from_host(surface_points.mean(1, dtype=np.float32), f32)  # object_model.py:64-68
         self.w_dev = be.from_host(np.array([w[k] for k in TERMS], f32))
         self.pose = be.from_host(hand_pose, f32)
@@ -170,7 +184,9 @@ class FitEngine:
                                        p(self.obj_nrm), p(self.obj_dgrad), p(self.cog), O, B, n_c, row("E_fc"),
                                        row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm), stop, trace, st)
         if self.qp_batch_stop:  # replay qpth's batch-wide exit test: trace pass, exit iteration, final pass
-            self._ck(lib.gqp_fc_dis_energy(*fc_args(None, p(self.qp_trace))))
+            self._ck(lib.gqp_fc_dis_energy(ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist),
+                                           p(self.obj_nrm), p(self.obj_dgrad), p(self.cog), O, B, n_c, None, None, None,
+                                           None, None, None, p(self.qp_trace), st))
             self._ck(lib.gqp_fc_stop_iter(p(self.qp_trace), Bt, self.fc.max_iter, self.fc.eps, p(self.qp_stop), st))
             self._ck(lib.gqp_fc_dis_energy(*fc_args(p(self.qp_stop), None)))
         else:
