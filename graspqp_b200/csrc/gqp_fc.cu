@@ -26,19 +26,38 @@ struct FcParamsDev {
     double w_fc, w_dis;
 };
 
-// all-reduce K doubles across the warp through shared memory: v[k] <- op over lanes
+// all-reduce K doubles across the warp: v[k] <- op over lanes.  Narrow reductions (K <= 6) are shuffle butterflies;
+// wide ones go through shared memory, each of K lanes summing one column in 4 independent chains.
 template <int K, bool IS_MIN>
 __device__ __forceinline__ void warp_allreduce(double *sm, double (&v)[K], int lane) {
+    if (K <= 6) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                double t = __shfl_xor_sync(GQP_FULL, v[k], o);
+                v[k] = IS_MIN ? (t < v[k] ? t : v[k]) : v[k] + t;
+            }
+        }
+        return;
+    }
     const int S = K | 1;
 #pragma unroll
     for (int k = 0; k < K; ++k) sm[lane * S + k] = v[k];
     __syncwarp();
     if (lane < K) {
-        double a = sm[lane];
-        for (int r = 1; r < 32; ++r) {
-            double t = sm[r * S + lane];
-            a = IS_MIN ? (t < a ? t : a) : a + t;
+        double a0 = sm[lane], a1 = sm[S + lane], a2 = sm[2 * S + lane], a3 = sm[3 * S + lane];
+#pragma unroll
+        for (int r = 4; r < 32; r += 4) {
+            double t0 = sm[r * S + lane], t1 = sm[(r + 1) * S + lane], t2 = sm[(r + 2) * S + lane],
+                   t3 = sm[(r + 3) * S + lane];
+            if (IS_MIN) {
+                a0 = t0 < a0 ? t0 : a0; a1 = t1 < a1 ? t1 : a1; a2 = t2 < a2 ? t2 : a2; a3 = t3 < a3 ? t3 : a3;
+            } else {
+                a0 += t0; a1 += t1; a2 += t2; a3 += t3;
+            }
         }
+        double a = IS_MIN ? fmin(fmin(a0, a1), fmin(a2, a3)) : (a0 + a1) + (a2 + a3);
         sm[32 * FC_RED_K + lane] = a;
     }
     __syncwarp();
@@ -89,8 +108,28 @@ struct Dir {
     double dx[2], dsu[2], dsl[2], dzu[2], dzl[2];
 };
 
-// step length to the boundary (qpth get_step): min over entries with dv < 0 of -v/dv, +inf otherwise
-__device__ __forceinline__ double step_len(double v, double dv) { return dv < 0.0 ? -v / dv : 1e300; }
+// step length to the boundary (qpth get_step): min over entries with dv < 0 of -v/dv, +inf otherwise.  The running
+// minimum is kept as a fraction num/den (den > 0) and compared by cross-multiplication: one division per lane.
+struct Frac {
+    double num, den;
+};
+__device__ __forceinline__ void step_min(Frac &f, double v, double dv) {
+    if (dv < 0.0 && v * f.den < f.num * (-dv)) {
+        f.num = v;
+        f.den = -dv;
+    }
+}
+__device__ __forceinline__ double step_lane(const double *zu, const double *zl, const double *su, const double *sl,
+                                            const Dir &d, const bool *valid) {
+    Frac f = {1e300, 1.0};
+#pragma unroll
+    for (int v = 0; v < 2; ++v)
+        if (valid[v]) {
+            step_min(f, zu[v], d.dzu[v]); step_min(f, zl[v], d.dzl[v]);
+            step_min(f, su[v], d.dsu[v]); step_min(f, sl[v], d.dsl[v]);
+        }
+    return f.num / f.den;
+}
 
 __global__ void __launch_bounds__(FC_WARPS * 32, 3)
 fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
@@ -257,12 +296,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             factor(du, dl);
             Dir aff;
             solve(du, dl, rx, zu, zl, rzu, rzl, aff);  // rs = z
-            double al[1] = {INF};
-#pragma unroll
-            for (int v = 0; v < 2; ++v)
-                if (valid[v])
-                    al[0] = fmin(al[0], fmin(fmin(step_len(zu[v], aff.dzu[v]), step_len(zl[v], aff.dzl[v])),
-                                             fmin(step_len(su[v], aff.dsu[v]), step_len(sl[v], aff.dsl[v]))));
+            double al[1] = {step_lane(zu, zl, su, sl, aff, valid)};
             warp_allreduce<1, true>(sm, al, lane);
             const double a1 = fmin(al[0], 1.0);
             double t3[1] = {0.0};
@@ -282,15 +316,12 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             }
             Dir cor;
             solve(du, dl, zero2, rs2u, rs2l, zero2, zero2, cor);
-            al[0] = INF;
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
                 aff.dx[v] += cor.dx[v]; aff.dsu[v] += cor.dsu[v]; aff.dsl[v] += cor.dsl[v];
                 aff.dzu[v] += cor.dzu[v]; aff.dzl[v] += cor.dzl[v];
-                if (valid[v])
-                    al[0] = fmin(al[0], fmin(fmin(step_len(zu[v], aff.dzu[v]), step_len(zl[v], aff.dzl[v])),
-                                             fmin(step_len(su[v], aff.dsu[v]), step_len(sl[v], aff.dsl[v]))));
             }
+            al[0] = step_lane(zu, zl, su, sl, aff, valid);
             warp_allreduce<1, true>(sm, al, lane);
             const double a2 = fmin(0.999 * al[0], 1.0);
 #pragma unroll

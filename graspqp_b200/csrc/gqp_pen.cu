@@ -62,12 +62,84 @@ __device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *gri
     return (bits[G.bit_first + (i >> 5)] >> (i & 31)) & 1u;
 }
 
+#define PEN_CB 8  // candidates per warp-task: amortises the sample loads and index arithmetic
+
+// Bounding spheres of every 32-sample chunk of a point row, and of the whole row (slot n_chunks).  One block per row.
+__global__ void __launch_bounds__(256)
+pen_bounds_kernel(const float *__restrict__ x, int n_pts, int n_chunks, float *__restrict__ bounds) {
+    __shared__ float red[8][4];
+    const int row = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float *xr = x + (size_t)row * n_pts * 3;
+    float *br = bounds + (size_t)row * (n_chunks + 1) * 4;
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    for (int c = warp; c < n_chunks; c += 8) {
+        const int pi = min(c * 32 + lane, n_pts - 1);
+        V3 p = ld3(xr + 3 * pi);
+        V3 cen = V3{warp_sum(p.x) * (1.f / 32.f), warp_sum(p.y) * (1.f / 32.f), warp_sum(p.z) * (1.f / 32.f)};
+        V3 d = p - cen;
+        float r = sqrtf(warp_max(dot3(d, d))) * 1.0001f + 1e-5f;
+        if (lane == 0) { br[4 * c] = cen.x; br[4 * c + 1] = cen.y; br[4 * c + 2] = cen.z; br[4 * c + 3] = r; }
+        if (c * 32 + lane < n_pts) { sx += p.x; sy += p.y; sz += p.z; }
+    }
+    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+    if (lane == 0) { red[warp][0] = sx; red[warp][1] = sy; red[warp][2] = sz; }
+    __syncthreads();
+    V3 cen = V3{0, 0, 0};
+    for (int w = 0; w < 8; ++w) cen = cen + V3{red[w][0], red[w][1], red[w][2]};
+    cen = cen * (1.0f / n_pts);
+    __syncthreads();
+    float r2 = 0.f;
+    for (int i = threadIdx.x; i < n_pts; i += 256) {
+        V3 d = ld3(xr + 3 * i) - cen;
+        r2 = fmaxf(r2, dot3(d, d));
+    }
+    r2 = warp_max(r2);
+    if (lane == 0) red[warp][3] = r2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = 0.f;
+        for (int w = 0; w < 8; ++w) m = fmaxf(m, red[w][3]);
+        br[4 * n_chunks] = cen.x; br[4 * n_chunks + 1] = cen.y; br[4 * n_chunks + 2] = cen.z;
+        br[4 * n_chunks + 3] = sqrtf(m) * 1.0001f + 1e-5f;
+    }
+}
+
+// Per candidate: bit l set when link l can matter for this candidate's point row, i.e. it has faces and (when culling)
+// the row's bounding sphere reaches the link's box.  Exact for "nice" links (see gqp_bvh.cpp); others are always kept.
+__global__ void pen_mask_kernel(const unsigned char *__restrict__ blob, const float *__restrict__ link_tf,
+                                const float *__restrict__ bounds, int Bt, int batch_each, int n_chunks,
+                                int per_candidate_points, int cull, uint32_t *__restrict__ masks) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(blob);
+    const PenLink *links = reinterpret_cast<const PenLink *>(blob + hdr->links_off);
+    const int L = hdr->n_links;
+    const int row = per_candidate_points ? b : b / batch_each;
+    const float *s = bounds + ((size_t)row * (n_chunks + 1) + n_chunks) * 4;
+    const V3 cen = V3{s[0], s[1], s[2]};
+    const float rad = s[3];
+    uint32_t m = 0;
+    for (int l = 0; l < L; ++l) {
+        const PenLink &K = links[l];
+        if (K.n_faces == 0) continue;  // hand_model.py:919-921: links without a mesh are skipped
+        bool keep = true;
+        if (cull && K.grid >= 0) {
+            V3 q = t34_inv_point(t34_load(link_tf + ((size_t)b * L + l) * 12), cen);
+            keep = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
+                     q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
+        }
+        if (keep) m |= 1u << l;
+    }
+    masks[b] = m;
+}
+
 template <bool CULL>
 __global__ void __launch_bounds__(PEN_THREADS, PEN_MIN_BLOCKS)
 hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
                 const int32_t *__restrict__ face_id, const float *__restrict__ link_tf, const float *__restrict__ x,
-                int Bt, int batch_each, int n_pts, int per_candidate_points, float *__restrict__ dist_out,
-                float *__restrict__ partial, float w_pen, float *__restrict__ grad_link_tf) {
+                const float *__restrict__ bounds, const uint32_t *__restrict__ masks, int n_rows, int cands_per_row,
+                int n_pts, float *__restrict__ dist_out, float *__restrict__ partial, float w_pen,
+                float *__restrict__ grad_link_tf) {
     GQP_DYN_SMEM(unsigned char, sm);
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) mbar_init(&bar);
@@ -86,86 +158,87 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
     // per-warp staging of the candidate's link transforms (L x 12 floats), behind the blob
     float *sW = reinterpret_cast<float *>(sm + blob_bytes) + (size_t)(threadIdx.x >> 5) * L * 12;
     const int n_chunks = (n_pts + 31) / 32;
-    const long long n_tasks = (long long)Bt * n_chunks;
-    for (long long task = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;
-         task += (long long)gridDim.x * warps_per_block) {
-        const int b = (int)(task / n_chunks);
-        const int pi = (int)(task % n_chunks) * 32 + lane;
+    const int n_cblk = (cands_per_row + PEN_CB - 1) / PEN_CB;
+    const int n_tasks = n_rows * n_chunks * n_cblk;
+    for (int task = blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;
+         task += gridDim.x * warps_per_block) {
+        const int cb = task % n_cblk, rc = task / n_cblk;
+        const int chunk = rc % n_chunks, row = rc / n_chunks;
+        const int pi = chunk * 32 + lane;
         const bool valid = pi < n_pts;
-        const int pj = valid ? pi : n_pts - 1;
-        const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
-        const V3 p = ld3(x + (row * n_pts + pj) * 3);
-        const float *Wb = link_tf + (size_t)b * L * 12;
-        // bounding sphere of the warp's 32 samples (callers order samples spatially, so it is small)
-        V3 cen = V3{warp_sum(p.x) * (1.f / 32.f), warp_sum(p.y) * (1.f / 32.f), warp_sum(p.z) * (1.f / 32.f)};
-        V3 dc = p - cen;
-        const float rad = sqrtf(warp_max(dot3(dc, dc))) * 1.0001f + 1e-5f;
-        // lane l: stage link l's transform and test the sphere against the link's box (exact for "nice" links:
-        // every sample outside the box is outside the mesh, where the reference's sign is +1)
-        bool keep = false;
-        for (int l0 = 0; l0 < L; l0 += 32) {  // L <= 32: one round
-            const int l = l0 + lane;
-            if (l < L) {
-                T34 W = t34_load(Wb + l * 12);
+        const V3 p = ld3(x + ((size_t)row * n_pts + (valid ? pi : n_pts - 1)) * 3);
+        const float *sph = bounds + ((size_t)row * (n_chunks + 1) + chunk) * 4;
+        const V3 cen = V3{sph[0], sph[1], sph[2]};
+        const float rad = sph[3];
+        const int b_end = row * cands_per_row + min(cands_per_row, (cb + 1) * PEN_CB);
+        for (int b = row * cands_per_row + cb * PEN_CB; b < b_end; ++b) {
+            const uint32_t mask = masks[b];
+            if (mask == 0) continue;  // the whole row is outside every link of this candidate
+            const float *Wb = link_tf + (size_t)b * L * 12;
+            // lane l: stage link l's transform and test the chunk's sphere against the link's box
+            bool keep = false;
+            if ((mask >> lane) & 1u) {
+                T34 W = t34_load(Wb + lane * 12);
 #pragma unroll
-                for (int i = 0; i < 12; ++i) sW[l * 12 + i] = W.m[i];
-                const PenLink &K = links[l];
-                keep = K.n_faces > 0;  // hand_model.py:919-921: links without a mesh are skipped
-                if (CULL && keep && K.grid >= 0) {
+                for (int i = 0; i < 12; ++i) sW[lane * 12 + i] = W.m[i];
+                const PenLink &K = links[lane];
+                keep = true;
+                if (CULL && K.grid >= 0) {
                     V3 q = t34_inv_point(W, cen);
                     if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
                         q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
                         keep = false;
                 }
             }
-        }
-        unsigned todo = __ballot_sync(GQP_FULL, keep);
-        __syncwarp();
-        float best_d = -__int_as_float(0x7f800000);
-        int best_l = -1;
-        V3 best_g = V3{0, 0, 0};
-        while (todo) {
-            const int l = __ffs((int)todo) - 1;
-            todo &= todo - 1;
-            const PenLink &K = links[l];
-            T34 W;
+            unsigned todo = __ballot_sync(GQP_FULL, keep);
+            if (todo == 0) continue;
+            __syncwarp();
+            float best_d = -__int_as_float(0x7f800000);
+            int best_l = -1;
+            V3 best_g = V3{0, 0, 0};
+            while (todo) {
+                const int l = __ffs((int)todo) - 1;
+                todo &= todo - 1;
+                const PenLink &K = links[l];
+                T34 W;
 #pragma unroll
-            for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
-            V3 q = t34_inv_point(W, p);
-            if (CULL && pen_outside(K, grids, bits, q)) continue;
-            SdfBest best;
-            sdf_best_init(best);
-            bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first, q, best);
-            V3 dv = q - best.c;
-            float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
-            float r = sqrtf(best.d2 + 1e-8f);
-            float d = r * (-sgn);  // hand_model.py:975-976
-            if (d > best_d) {      // :986 max over links (first maximum)
-                best_d = d;
-                best_l = l;
-                best_g = dv * (1.0f / r);
+                for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
+                V3 q = t34_inv_point(W, p);
+                if (CULL && pen_outside(K, grids, bits, q)) continue;
+                SdfBest best;
+                sdf_best_init(best);
+                bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first, q, best);
+                V3 dv = q - best.c;
+                float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
+                float r = sqrtf(best.d2 + 1e-8f);
+                float d = r * (-sgn);  // hand_model.py:975-976
+                if (d > best_d) {      // :986 max over links (first maximum)
+                    best_d = d;
+                    best_l = l;
+                    best_g = dv * (1.0f / r);
+                }
             }
-        }
-        if (dist_out && valid) dist_out[(size_t)b * n_pts + pi] = best_d;
-        float e = (valid && best_d > 0.f) ? best_d : 0.f;  // energy.py:60-61
-        if (grad_link_tf && e > 0.f) {
-            // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
-            const float *W = sW + best_l * 12;
-            V3 g = best_g * w_pen;
-            float *G = grad_link_tf + ((size_t)b * L + best_l) * 12;
-            float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {g.x, g.y, g.z};
+            if (dist_out && valid) dist_out[(size_t)b * n_pts + pi] = best_d;
+            float e = (valid && best_d > 0.f) ? best_d : 0.f;  // energy.py:60-61
+            if (grad_link_tf && e > 0.f) {
+                // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
+                const float *W = sW + best_l * 12;
+                V3 g = best_g * w_pen;
+                float *G = grad_link_tf + ((size_t)b * L + best_l) * 12;
+                float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {g.x, g.y, g.z};
 #pragma unroll
-            for (int j = 0; j < 3; ++j) {
+                for (int j = 0; j < 3; ++j) {
 #pragma unroll
-                for (int i = 0; i < 3; ++i) atomicAdd(G + 4 * j + i, pt[j] * gv[i]);
-                atomicAdd(G + 4 * j + 3, -(W[4 * j] * gv[0] + W[4 * j + 1] * gv[1] + W[4 * j + 2] * gv[2]));
+                    for (int i = 0; i < 3; ++i) atomicAdd(G + 4 * j + i, pt[j] * gv[i]);
+                    atomicAdd(G + 4 * j + 3, -(W[4 * j] * gv[0] + W[4 * j + 1] * gv[1] + W[4 * j + 2] * gv[2]));
+                }
             }
+            if (partial && __any_sync(GQP_FULL, e > 0.f)) {  // partial was zeroed by the host wrapper
+                float s = warp_sum(e);
+                if (lane == 0) partial[(size_t)b * n_chunks + chunk] = s;
+            }
+            __syncwarp();  // sW is rewritten for the next candidate
         }
-        if (partial) {
-            float s = warp_sum(e);
-            if (lane == 0) partial[task] = s;
-        }
-        __syncwarp();  // sW is rewritten by the next task
     }
 }
 
@@ -378,26 +451,39 @@ extern "C" int gqp_hand_distance(const GqpHand *h, const float *link_tf, const f
     if (!h || n_obj < 0 || batch_each < 0 || n_pts <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: bad argument");
     const int Bt = n_obj * batch_each;
     if (Bt == 0) return GQP_OK;
-    if (!link_tf || !x) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: null pointer");
-    if (e_pen && !scratch) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: e_pen needs scratch (Bt*ceil(n_pts/32) floats)");
+    if (!link_tf || !x || !scratch) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: null pointer (scratch is required)");
+    cudaStream_t st = (cudaStream_t)stream;
     const int n_chunks = (n_pts + 31) / 32;
-    const long long n_tasks = (long long)Bt * n_chunks;
+    const int n_rows = per_candidate_points ? Bt : n_obj, cands_per_row = per_candidate_points ? 1 : batch_each;
+    const long long n_tasks = (long long)n_rows * n_chunks * ((cands_per_row + PEN_CB - 1) / PEN_CB);
+    if (n_tasks > 0x7fffffffLL) return gqp_set_error(GQP_ERR_LIMIT, "gqp_hand_distance: too many point chunks");
     const GqpPenTables *T = h->pen;
+    // scratch: [Bt*n_chunks partial sums][n_rows*(n_chunks+1)*4 bounding spheres][Bt link masks]
+    float *partial = scratch;
+    float *bounds = scratch + (size_t)Bt * n_chunks;
+    uint32_t *masks = reinterpret_cast<uint32_t *>(bounds + (size_t)n_rows * (n_chunks + 1) * 4);
+    const int cull = dist ? 0 : 1;  // with dist wanted, every link's true distance is needed
+    int rc = gqp_memset_zero(partial, sizeof(float) * (size_t)Bt * n_chunks, stream);
+    if (rc != GQP_OK) return rc;
+    GQP_LAUNCH(pen_bounds_kernel, n_rows, 256, 0, st, x, n_pts, n_chunks, bounds);
+    GQP_CHECK_LAUNCH("gqp_hand_distance/bounds");
+    GQP_LAUNCH(pen_mask_kernel, (Bt + 127) / 128, 128, 0, st, T->d_blob, link_tf, bounds, Bt, batch_each, n_chunks,
+               per_candidate_points, cull, masks);
+    GQP_CHECK_LAUNCH("gqp_hand_distance/mask");
     const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * h->host.n_links * 48;
     int grid = pen_grid_size((int)smem, n_tasks);
-    float *partial = e_pen ? scratch : nullptr;
-    if (dist) {  // every link's true distance is needed: no culling
-        GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, (cudaStream_t)stream, T->d_blob,
-                   T->total_bytes, T->d_tris, T->d_face_id, link_tf, x, Bt, batch_each, n_pts, per_candidate_points,
-                   dist, partial, w_pen, grad_link_tf);
+    if (cull) {
+        GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
+                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, partial, w_pen,
+                   grad_link_tf);
     } else {
-        GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, (cudaStream_t)stream, T->d_blob,
-                   T->total_bytes, T->d_tris, T->d_face_id, link_tf, x, Bt, batch_each, n_pts, per_candidate_points,
-                   dist, partial, w_pen, grad_link_tf);
+        GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
+                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, partial, w_pen,
+                   grad_link_tf);
     }
     GQP_CHECK_LAUNCH("gqp_hand_distance");
     if (e_pen) {
-        GQP_LAUNCH(pen_reduce_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, partial, Bt, n_chunks, e_pen);
+        GQP_LAUNCH(pen_reduce_kernel, (Bt + 127) / 128, 128, 0, st, partial, Bt, n_chunks, e_pen);
         GQP_CHECK_LAUNCH("gqp_hand_distance/reduce");
     }
     return GQP_OK;
@@ -437,4 +523,10 @@ extern "C" int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host) {
     info_host[4] = h->face_offset.back();
     info_host[5] = hdr->n_grids;
     return GQP_OK;
+}
+
+extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {
+    const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
+    const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;
+    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16;
 }

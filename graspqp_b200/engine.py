@@ -158,7 +158,7 @@ class FitEngine:
         self.ones = be.from_host(np.ones((Bt, n_c), f32))
         self.lam = be.empty((Bt, n_c), f32)
         self.g_pose_joints = be.empty((Bt, D), f32)
-        self.pen_scratch = be.empty((Bt * ((self.n_pts + 31) // 32),), f32)
+        self.pen_scratch = be.empty((int(cdll.gqp_hand_distance_scratch_floats(self.n_obj, self.batch_each, self.n_pts, 0)),), f32)
         self.qp_trace = be.empty((Bt, self.fc.max_iter), f32)
         self.qp_stop = be.empty((1,), i32)
         self.reset_all = be.from_host(np.ones(Bt, u8))

@@ -119,13 +119,16 @@ int gqp_contacts_backward(const GqpHand *h, const int32_t *idx, const float *gra
  * repeat, object_model.py:181-184; x_stride_candidates != 0 selects a per-candidate (Bt,n_pts,3) set instead).
  * dist (Bt,n_pts) = max over links of sqrt(d2+1e-8)*(-sign)   [positive inside], may be NULL;
  * e_pen (Bt) = sum_p relu(dist) (energy.py:57-62), may be NULL;
- * scratch: Bt*ceil(n_pts/32) floats of workspace, required when e_pen is wanted (deterministic two-stage sum);
+ * scratch (required): workspace of gqp_hand_distance_scratch_floats(...) floats — per-chunk partial sums (deterministic
+ *   two-stage sum), bounding spheres of the 32-sample chunks, per-candidate link masks;
  * grad_link_tf (Bt,n_links,12), may be NULL: ACCUMULATES w_pen * d(e_pen)/d(link_tf).
  * With dist == NULL, (point, link) pairs whose sign is provably +1 (far-field sign grid built at gqp_hand_create) are
  * skipped: they cannot contribute to relu(max).  With dist != NULL every pair is searched. */
 int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each, int n_pts,
                       int per_candidate_points, float *dist, float *e_pen, float *scratch, float w_pen,
                       float *grad_link_tf, void *stream);
+
+uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points);
 
 /* diagnostics: info_host[6] = {shared-memory blob bytes, BVH nodes, sign-grid cells, cells proven positive, faces, grids} */
 int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host);

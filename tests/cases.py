@@ -78,7 +78,7 @@ def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5):
     x = be.from_host(sp[None], np.float32)
     dist = be.empty((B, n_pts), np.float32)
     e1, e2 = be.empty((B,), np.float32), be.empty((B,), np.float32)
-    sc = be.empty((B * ((n_pts + 31) // 32),), np.float32)
+    sc = be.empty((int(lib.gqp_hand_distance_scratch_floats(1, B, n_pts, 0)),), np.float32)
     g1, g2 = be.empty((B, L, 12), np.float32), be.empty((B, L, 12), np.float32)
     _lib.check(lib.gqp_hand_distance(hand, be.ptr(tf), be.ptr(x), 1, B, n_pts, 0, be.ptr(dist), be.ptr(e1), be.ptr(sc),
                                      100.0, be.ptr(g1), be.stream), lib)

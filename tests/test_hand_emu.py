@@ -106,7 +106,7 @@ def test_hand_distance_and_pen(emu, pack, hand):
     x = np.ascontiguousarray(sp[None], np.float32)  # (n_obj=1, n_pts, 3)
     dist = np.zeros((B, n_pts), np.float32)
     e_full, e_cull = np.zeros(B, np.float32), np.zeros(B, np.float32)
-    scratch = np.zeros(B * ((n_pts + 31) // 32), np.float32)
+    scratch = np.zeros(int(emu.gqp_hand_distance_scratch_floats(1, B, n_pts, 0)), np.float32)
     g_full, g_cull = np.zeros((B, L, 12), np.float32), np.zeros((B, L, 12), np.float32)
     assert emu.gqp_hand_distance(hand, ptr(tf), ptr(x), 1, B, n_pts, 0, ptr(dist), ptr(e_full), ptr(scratch), 100.0,
                                  ptr(g_full), None) == 0, emu.gqp_last_error()
