@@ -52,6 +52,8 @@ SIGNATURES = {
     "gqp_contacts_forward": (c_int, [c_void_p, P, P, c_int, c_int, P, P, P]),
     "gqp_contacts_backward": (c_int, [c_void_p, P, P, P, c_int, c_int, P, P]),
     "gqp_hand_distance": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, c_float, P, P]),
+    "gqp_hand_distance_full": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
+    "gqp_hand_distance_backward": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_hand_distance_scratch_floats": (c_uint64, [c_int, c_int, c_int, c_int]),
     "gqp_hand_pen_info": (c_int, [c_void_p, P]),
     "gqp_self_pen_joints": (c_int, [c_void_p, P, P, c_int, P, P, c_float, c_float, P, P, P]),

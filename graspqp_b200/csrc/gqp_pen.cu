@@ -138,7 +138,8 @@ __global__ void __launch_bounds__(PEN_THREADS, PEN_MIN_BLOCKS)
 hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
                 const int32_t *__restrict__ face_id, const float *__restrict__ link_tf, const float *__restrict__ x,
                 const float *__restrict__ bounds, const uint32_t *__restrict__ masks, int n_rows, int cands_per_row,
-                int n_pts, float *__restrict__ dist_out, float *__restrict__ partial, float w_pen,
+                int n_pts, float *__restrict__ dist_out, int32_t *__restrict__ arg_link_out,
+                float *__restrict__ dgrad_out, float *__restrict__ partial, float w_pen,
                 float *__restrict__ grad_link_tf) {
     GQP_DYN_SMEM(unsigned char, sm);
     __shared__ __align__(8) uint64_t bar;
@@ -219,6 +220,12 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
                 }
             }
             if (dist_out && valid) dist_out[(size_t)b * n_pts + pi] = best_d;
+            if (arg_link_out && valid) {  // saved for gqp_hand_distance_backward: argmax link and d(dist)/d(q)
+                const size_t o = (size_t)b * n_pts + pi;
+                const float sg = best_d > 0.f ? 1.f : -1.f;  // dist = r * (-sign): d(dist)/dq = (-sign) (q-c)/r
+                arg_link_out[o] = best_l;
+                st3(dgrad_out + 3 * o, best_g * sg);
+            }
             float e = (valid && best_d > 0.f) ? best_d : 0.f;  // energy.py:60-61
             if (grad_link_tf && e > 0.f) {
                 // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
@@ -445,9 +452,9 @@ static int pen_grid_size(int blob_bytes, long long n_tasks) {
 #endif
 }
 
-extern "C" int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
-                                 int n_pts, int per_candidate_points, float *dist, float *e_pen, float *scratch,
-                                 float w_pen, float *grad_link_tf, void *stream) {
+static int hand_distance_impl(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
+                              int n_pts, int per_candidate_points, float *dist, int32_t *arg_link, float *dgrad,
+                              float *e_pen, float *scratch, float w_pen, float *grad_link_tf, void *stream) {
     if (!h || n_obj < 0 || batch_each < 0 || n_pts <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: bad argument");
     const int Bt = n_obj * batch_each;
     if (Bt == 0) return GQP_OK;
@@ -474,18 +481,72 @@ extern "C" int gqp_hand_distance(const GqpHand *h, const float *link_tf, const f
     int grid = pen_grid_size((int)smem, n_tasks);
     if (cull) {
         GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
-                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, partial, w_pen,
-                   grad_link_tf);
+                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
+                   partial, w_pen, grad_link_tf);
     } else {
         GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
-                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, partial, w_pen,
-                   grad_link_tf);
+                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
+                   partial, w_pen, grad_link_tf);
     }
     GQP_CHECK_LAUNCH("gqp_hand_distance");
     if (e_pen) {
         GQP_LAUNCH(pen_reduce_kernel, (Bt + 127) / 128, 128, 0, st, partial, Bt, n_chunks, e_pen);
         GQP_CHECK_LAUNCH("gqp_hand_distance/reduce");
     }
+    return GQP_OK;
+}
+
+extern "C" int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
+                                 int n_pts, int per_candidate_points, float *dist, float *e_pen, float *scratch,
+                                 float w_pen, float *grad_link_tf, void *stream) {
+    return hand_distance_impl(h, link_tf, x, n_obj, batch_each, n_pts, per_candidate_points, dist, nullptr, nullptr,
+                              e_pen, scratch, w_pen, grad_link_tf, stream);
+}
+
+// cal_distance with what its backward needs: argmax link and d(dist)/d(link-frame point) per sample
+extern "C" int gqp_hand_distance_full(const GqpHand *h, const float *link_tf, const float *x, int n_obj,
+                                      int batch_each, int n_pts, int per_candidate_points, float *dist,
+                                      int32_t *arg_link, float *dgrad, float *scratch, void *stream) {
+    if (!dist || !arg_link || !dgrad) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance_full: null output");
+    return hand_distance_impl(h, link_tf, x, n_obj, batch_each, n_pts, per_candidate_points, dist, arg_link, dgrad,
+                              nullptr, scratch, 0.f, nullptr, stream);
+}
+
+// d(loss)/d(link_tf) += sum_p grad_dist[b,p] * d(dist[b,p])/d(link_tf[b, arg_link])   (q = R^T (x - t))
+__global__ void hand_distance_backward_kernel(const float *__restrict__ link_tf, const float *__restrict__ x,
+                                              const float *__restrict__ grad_dist, const int32_t *__restrict__ arg_link,
+                                              const float *__restrict__ dgrad, int Bt, int batch_each, int n_pts,
+                                              int per_candidate_points, int L, float *__restrict__ grad_link_tf) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)Bt * n_pts) return;
+    const float g0 = grad_dist[i];
+    const int l = arg_link[i];
+    if (g0 == 0.f || l < 0) return;
+    const int b = (int)(i / n_pts), pi = (int)(i % n_pts);
+    const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
+    const V3 p = ld3(x + (row * n_pts + pi) * 3);
+    const float *W = link_tf + ((size_t)b * L + l) * 12;
+    float *G = grad_link_tf + ((size_t)b * L + l) * 12;
+    const float gv[3] = {dgrad[3 * i] * g0, dgrad[3 * i + 1] * g0, dgrad[3 * i + 2] * g0};
+    const float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]};
+    for (int j = 0; j < 3; ++j) {
+        for (int k = 0; k < 3; ++k) atomicAdd(G + 4 * j + k, pt[j] * gv[k]);
+        atomicAdd(G + 4 * j + 3, -(W[4 * j] * gv[0] + W[4 * j + 1] * gv[1] + W[4 * j + 2] * gv[2]));
+    }
+}
+extern "C" int gqp_hand_distance_backward(const GqpHand *h, const float *link_tf, const float *x, int n_obj,
+                                          int batch_each, int n_pts, int per_candidate_points, const float *grad_dist,
+                                          const int32_t *arg_link, const float *dgrad, float *grad_link_tf,
+                                          void *stream) {
+    if (!h || n_obj < 0 || batch_each < 0 || n_pts <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance_backward: bad argument");
+    const long long n = (long long)n_obj * batch_each * n_pts;
+    if (n == 0) return GQP_OK;
+    if (!link_tf || !x || !grad_dist || !arg_link || !dgrad || !grad_link_tf)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance_backward: null pointer");
+    GQP_LAUNCH(hand_distance_backward_kernel, (unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream, link_tf, x,
+               grad_dist, arg_link, dgrad, n_obj * batch_each, batch_each, n_pts, per_candidate_points,
+               h->host.n_links, grad_link_tf);
+    GQP_CHECK_LAUNCH("gqp_hand_distance_backward");
     return GQP_OK;
 }
 

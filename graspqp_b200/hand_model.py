@@ -1,0 +1,104 @@
+"""HandModel — the reference's class (graspqp/src/graspqp/core/hand_model.py:395-1267) for the hot path, over the
+sm_100a kernels.  Same attribute and method names, so scripts/fit.py's loop, MalaStar and calculate_energy run unchanged:
+
+    set_parameters(hand_pose, contact_point_indices)   hand_model.py:833-873
+    cal_distance(x)                                     :875-987   (SDF_BACKEND TORCHSDF semantics)
+    self_penetration()                                  :989-1040
+    fk(joint_angles)                                    :762-766   (returns world link transforms here)
+    attributes: n_dofs, n_contact_candidates, joints_lower/upper, hand_pose, contact_points, contact_normals,
+                contact_point_indices, global_rotation, global_translation, current_status, device
+
+What is NOT here (out of the hot path's scope): URDF/mesh parsing at construction (done once by
+tools/build_hand_pack.py into assets/<hand>.npz), plotting, retargeting helpers.
+"""
+import numpy as np
+import torch
+
+from . import _lib, hand_pack, ops
+
+
+class HandModel:
+    def __init__(self, hand="allegro", device="cuda", pack=None):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("graspqp_b200.HandModel runs on CUDA devices only (no CPU fallback)")
+        self.pack = pack if pack is not None else hand_pack.load_pack(hand)
+        self.name = str(self.pack["name"])
+        with torch.cuda.device(self.device):
+            self.handle = hand_pack.create_hand(_lib.lib(), self.pack)
+        t = lambda k, dt=torch.float32: torch.as_tensor(np.asarray(self.pack[k]), dtype=dt, device=self.device)
+        self.n_dofs = len(self.pack["joints_lower"])
+        self.n_links = len(self.pack["mesh_frame"])
+        self.n_contact_candidates = len(self.pack["cand"])
+        self.joints_lower, self.joints_upper = t("joints_lower"), t("joints_upper")
+        self.default_state = t("default_state")
+        self.contact_candidates, self.normal_candidates = t("cand"), t("cand_normal")
+        self.global_index_to_link_index = t("cand_link", torch.long)
+        self.penetration_keypoints = t("spheres")
+        self._actuated_joints_names = [str(s) for s in self.pack["joint_names"]]
+        self._contact_links = [str(s) for s in self.pack["mesh_names"]]
+        self.mesh_names = self._contact_links
+        self.hand_pose = None
+        self.contact_point_indices = None
+        self.contact_points = self.contact_normals = None
+        self.global_translation = self.global_rotation = None
+        self.current_status = None  # (Bt, n_links, 12) world transforms [R|t] of the mesh links
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _lib.lib().gqp_hand_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    # ---- kinematics --------------------------------------------------------------------------------------------
+    def fk(self, joint_angles=None):
+        """hand_model.py:762-766.  Returns the WORLD transforms of the mesh links for the current global pose
+        (the reference returns hand-frame Transform3d objects; its consumers compose the global pose afterwards)."""
+        pose = self.hand_pose if joint_angles is None else torch.cat([self.hand_pose[:, :9], joint_angles], 1)
+        return ops.FkFn.apply(pose, self)
+
+    def set_parameters(self, hand_pose, contact_point_indices=None, env_mask=None):
+        if env_mask is not None:  # hand_model.py:846-850
+            with torch.no_grad():
+                hp = torch.where(env_mask.unsqueeze(-1), hand_pose, self.hand_pose)
+            self.hand_pose = hp.detach().requires_grad_(True)
+        else:
+            self.hand_pose = hand_pose.clone()
+        if self.hand_pose.requires_grad:
+            self.hand_pose.retain_grad()
+        if torch.isnan(self.hand_pose).any():
+            raise ValueError("nan in hand_pose")
+        self.global_translation = self.hand_pose[:, 0:3]
+        self.current_status = ops.FkFn.apply(self.hand_pose, self)
+        with torch.no_grad():  # attribute only; the kernels carry R_g inside current_status
+            x, y = self.hand_pose[:, 3:6], self.hand_pose[:, 6:9]
+            x = x / x.norm(dim=-1, keepdim=True)
+            y = y - (x * y).sum(-1, keepdim=True) * x
+            y = y / y.norm(dim=-1, keepdim=True)
+            self.global_rotation = torch.stack((x, y, torch.cross(x, y, dim=-1)), dim=-1)
+        if contact_point_indices is not None:
+            if env_mask is not None and self.contact_point_indices is not None:
+                contact_point_indices = torch.where(env_mask.unsqueeze(-1), contact_point_indices,
+                                                    self.contact_point_indices)
+            self.contact_point_indices = contact_point_indices.clone()
+        if self.contact_point_indices is not None:
+            self.contact_points, self.contact_normals = ops.ContactsFn.apply(self.current_status,
+                                                                             self.contact_point_indices, self)
+
+    # ---- distances ---------------------------------------------------------------------------------------------
+    def cal_distance(self, x):
+        """hand_model.py:875-987: signed depth of world points x (Bt,P,3) w.r.t. the hand, max over links, positive
+        inside.  Differentiable w.r.t. hand_pose."""
+        return ops.HandDistanceFn.apply(self.current_status, x, self)
+
+    def self_penetration(self):
+        """hand_model.py:989-1040."""
+        return ops.SelfPenFn.apply(self.current_status, self.hand_pose, self)
+
+    def get_contact_candidates(self):
+        """hand_model.py:1220-1267: world positions of ALL contact candidates (Bt, C, 3)."""
+        B = self.hand_pose.shape[0]
+        idx = torch.arange(self.n_contact_candidates, device=self.device, dtype=torch.int32).repeat(B, 1)
+        return ops.ContactsFn.apply(self.current_status, idx, self)[0]

@@ -128,6 +128,16 @@ int gqp_hand_distance(const GqpHand *h, const float *link_tf, const float *x, in
                       int per_candidate_points, float *dist, float *e_pen, float *scratch, float w_pen,
                       float *grad_link_tf, void *stream);
 
+/* cal_distance for autograd callers (HandModel.cal_distance, hand_model.py:875-987): dist plus what the backward needs,
+ * arg_link (Bt,n_pts) int32 = the max link, dgrad (Bt,n_pts,3) = d(dist)/d(link-frame point).  The backward
+ * ACCUMULATES d(loss)/d(link_tf) for a cotangent grad_dist (Bt,n_pts); the points themselves get no gradient (the
+ * reference passes constant surface samples, energy.py:57-59). */
+int gqp_hand_distance_full(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each, int n_pts,
+                           int per_candidate_points, float *dist, int32_t *arg_link, float *dgrad, float *scratch,
+                           void *stream);
+int gqp_hand_distance_backward(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
+                               int n_pts, int per_candidate_points, const float *grad_dist, const int32_t *arg_link,
+                               const float *dgrad, float *grad_link_tf, void *stream);
 uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points);
 
 /* diagnostics: info_host[6] = {shared-memory blob bytes, BVH nodes, sign-grid cells, cells proven positive, faces, grids} */
