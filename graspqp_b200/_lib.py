@@ -59,6 +59,9 @@ SIGNATURES = {
     "gqp_self_pen_joints": (c_int, [c_void_p, P, P, c_int, P, P, c_float, c_float, P, P, P]),
     "gqp_fc_dis_energy": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P, P, P, P, P]),
     "gqp_fc_stop_iter": (c_int, [P, c_int, c_int, c_float, P, P]),
+    "gqp_fc_workspace_bytes": (c_uint64, [c_int, c_int, c_int]),
+    "gqp_fc_solve": (c_int, [POINTER(GqpFcParams), P, P, P, c_int, c_int, c_int, P, P]),
+    "gqp_fc_finish": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, c_int, P, P, P, P, P, P, P]),
     "gqp_mala_stats": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P]),
     "gqp_mala_propose": (c_int, [POINTER(GqpMalaParams), P, P, P, P, P, P, c_int, c_int, c_int, c_int, P, P, c_uint64,
                                  c_uint64, P, P, P, P]),

@@ -139,6 +139,28 @@ void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &ou
         out.face_id[i] = b.order[i];
         std::memcpy(&out.tris[9 * (size_t)i], face_verts + 9 * (size_t)b.order[i], 36);
     }
+    // pre-test records (gqp_bvh.cuh: tri_lower_bound): the face's plane (unit normal through the centroid) and the
+    // radius of the circle around the centroid that holds the face, both from double arithmetic, radius rounded up
+    out.pre.assign(8 * (size_t)F, 0.f);
+    out.extent = 0.f;
+    for (int i = 0; i < F; ++i) {
+        const float *t = &out.tris[9 * (size_t)i];
+        D3 a = ldv(t), bb = ldv(t + 3), c = ldv(t + 6);
+        D3 cen = (a + bb + c) * (1.0 / 3.0);
+        D3 n = cross(bb - a, c - a);
+        double l = std::sqrt(dot(n, n));
+        float *q = &out.pre[8 * (size_t)i];
+        float cf[3] = {(float)cen.x, (float)cen.y, (float)cen.z};
+        D3 cr = {cf[0], cf[1], cf[2]};  // the ROUNDED centre is what the kernel uses: measure the radius from it
+        double r = 0;
+        for (D3 v : {a, bb, c}) r = std::max(r, std::sqrt(dot(v - cr, v - cr)));
+        // a degenerate face gets a zero normal: the bound degrades to the sphere bound, still valid
+        bool ok = l > 1e-30 && l > 1e-9 * std::max({dot(bb - a, bb - a), dot(c - a, c - a)});
+        q[0] = ok ? (float)(n.x / l) : 0.f; q[1] = ok ? (float)(n.y / l) : 0.f; q[2] = ok ? (float)(n.z / l) : 0.f;
+        q[3] = (float)(r * 1.0001 + 1e-7 * (std::fabs(cen.x) + std::fabs(cen.y) + std::fabs(cen.z)) + 1e-30);
+        q[4] = cf[0]; q[5] = cf[1]; q[6] = cf[2]; q[7] = 0.f;
+        for (int k = 0; k < 9; ++k) out.extent = std::max(out.extent, std::fabs(t[k]));
+    }
 }
 
 // ---- exact culling of "outside" queries ------------------------------------------------------------------------------

@@ -123,6 +123,16 @@ inline unsigned atomicAdd(unsigned *p, unsigned v) {
     std::atomic_ref<unsigned> a(*p);
     return a.fetch_add(v, std::memory_order_relaxed);
 }
+inline unsigned atomicMax(unsigned *p, unsigned v) {
+    std::atomic_ref<unsigned> a(*p);
+    unsigned old = a.load(std::memory_order_relaxed);
+    while (old < v && !a.compare_exchange_weak(old, v, std::memory_order_relaxed)) {}
+    return old;
+}
+inline unsigned atomicOr(unsigned *p, unsigned v) {
+    std::atomic_ref<unsigned> a(*p);
+    return a.fetch_or(v, std::memory_order_relaxed);
+}
 template <class T>
 inline T __ldg(const T *p) { return *p; }
 inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }

@@ -24,6 +24,7 @@ struct FcParamsDev {
     double mu_f, c0, tw, lo, hi, ridge, svd_gain, values_gain, values_offset;
     int max_iter;
     double w_fc, w_dis;
+    float eps;
 };
 
 // all-reduce K doubles across the warp: v[k] <- op over lanes.  Narrow reductions (K <= 6) are shuffle butterflies;
@@ -131,19 +132,63 @@ __device__ __forceinline__ double step_lane(const double *zu, const double *zl, 
     return f.num / f.den;
 }
 
+// Workspace of the split form (gqp_fc_solve -> gqp_fc_finish).  The interior-point pass keeps, per candidate, every
+// iterate that improved its best residual (x and the backward's d = clamp(z)/clamp(s) per bound: 3n doubles) and which
+// iterate was best as of each iteration; batch-wide it keeps, per iteration, the maximum best residual and whether
+// any candidate improved — exactly what qpth's exit test reads.  The finish pass derives the exit iteration from those
+// 2 x max_iter words and completes every candidate from its stored iterate: one IPM pass instead of two.
+struct FcWorkspace {
+    unsigned *gmax;     // (FC_MAX_ITER) float bits of max_b best_res_b after iteration it
+    unsigned *gimp;     // (FC_MAX_ITER) != 0 if any candidate improved at iteration it
+    uint8_t *best_idx;  // (Bt, FC_MAX_ITER) index of the candidate's best iterate as of iteration it
+    double *snap;       // (Bt, max_iter, 3, n)
+};
+#define FC_MAX_ITER 64
+#define FC_WS_HEADER 512
+__host__ __device__ static inline size_t fc_align256(size_t v) { return (v + 255) / 256 * 256; }
+static inline FcWorkspace fc_workspace_view(void *ws, int Bt) {
+    FcWorkspace w;
+    unsigned char *b = (unsigned char *)ws;
+    w.gmax = (unsigned *)b;
+    w.gimp = w.gmax + FC_MAX_ITER;
+    w.best_idx = b + FC_WS_HEADER;
+    w.snap = (double *)(b + FC_WS_HEADER + fc_align256((size_t)Bt * FC_MAX_ITER));
+    return w;
+}
+
+// qpth's exit test (pdipm/batch.py forward): leave at the first iteration where no candidate improved for 3 consecutive
+// iterations or the batch maximum of the best residuals is below eps
+__device__ __forceinline__ int fc_batch_stop(const unsigned *gmax, const unsigned *gimp, int max_iter, float eps) {
+    int not_improved = 0;
+    for (int it = 0; it < max_iter; ++it) {
+        const float m2 = __int_as_float((int)gmax[it]);
+        if (it > 0) not_improved = gimp[it] ? 0 : not_improved + 1;
+        if (not_improved == 3 || m2 < eps) return it;
+    }
+    return max_iter;
+}
+
+enum { FC_FUSED = 0, FC_SOLVE = 1, FC_FINISH = 2 };
+
+template <int MODE>
 __global__ void __launch_bounds__(FC_WARPS * 32, 3)
 fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
               const float *__restrict__ obj_dist, const float *__restrict__ obj_nrm,
               const float *__restrict__ obj_dgrad, const float *__restrict__ cog, int Bt, int batch_each, int n_c,
               float *__restrict__ e_fc, float *__restrict__ e_dis, float *__restrict__ lam_out,
               float *__restrict__ grad_cpts, float *__restrict__ grad_cnrm, const int32_t *__restrict__ stop_iter,
-              float *__restrict__ trace) {
+              float *__restrict__ trace, FcWorkspace ws, int batch_stop, int32_t *__restrict__ stop_out) {
     __shared__ double smem[FC_WARPS][FC_SM_PER_WARP + 64];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double *sm = smem[warp];
     double *sm4 = sm + 32 * FC_RED_K + 32;  // (64,4) per-variable scratch
     const int n = 4 * n_c, m = 2 * n;
-    const int stop = stop_iter ? *stop_iter : P.max_iter;
+    int stop = P.max_iter;
+    if (MODE == FC_FUSED && stop_iter) stop = *stop_iter;
+    if (MODE == FC_FINISH) {
+        if (batch_stop) stop = fc_batch_stop(ws.gmax, ws.gimp, P.max_iter, P.eps);
+        if (stop_out && blockIdx.x == 0 && threadIdx.x == 0) *stop_out = stop;
+    }
     const double INF = 1e300;
 
     for (int b = blockIdx.x * FC_WARPS + warp; b < Bt; b += gridDim.x * FC_WARPS) {
@@ -230,6 +275,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         double x[2], su[2], sl[2], zu[2], zl[2];
         double bx[2] = {0, 0}, bsu[2] = {1, 1}, bsl[2] = {1, 1}, bzu[2] = {1, 1}, bzl[2] = {1, 1};
         const double zero2[2] = {0.0, 0.0};
+        if (MODE != FC_FINISH) {
         {   // starting point: KKT solve with d = 1, then shift slacks / duals to >= 1 (qpth pdipm forward)
             const double one2[2] = {1.0, 1.0};
             double rzu[2] = {-P.hi, -P.hi}, rzl[2] = {P.lo, P.lo};
@@ -253,6 +299,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             }
         }
         double best_res = INF;
+        int best_it = 0;
         for (int it = 0; it < P.max_iter; ++it) {
             double fxv[6];
 #pragma unroll
@@ -287,12 +334,33 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             const double mu = fabs(acc[0] / m);
             const double res = sqrt(acc[1]) + sqrt(acc[2]) + m * mu;
             if (trace && lane == 0) trace[(size_t)b * P.max_iter + it] = (float)res;
-            if (it == 0 || res < best_res) {
+            const bool improved = it == 0 || res < best_res;
+            if (improved) {
                 best_res = res;
+                best_it = it;
+                if (MODE == FC_SOLVE) {
+                    double *sn = ws.snap + ((size_t)b * P.max_iter + it) * 3 * n;
 #pragma unroll
-                for (int v = 0; v < 2; ++v) { bx[v] = x[v]; bsu[v] = su[v]; bsl[v] = sl[v]; bzu[v] = zu[v]; bzl[v] = zl[v]; }
+                    for (int v = 0; v < 2; ++v)
+                        if (valid[v]) {
+                            const int j = lane + 32 * v;
+                            sn[j] = x[v];
+                            sn[n + j] = fmax(zu[v], 1e-8) / fmax(su[v], 1e-8);
+                            sn[2 * n + j] = fmax(zl[v], 1e-8) / fmax(sl[v], 1e-8);
+                        }
+                } else {
+#pragma unroll
+                    for (int v = 0; v < 2; ++v) { bx[v] = x[v]; bsu[v] = su[v]; bsl[v] = sl[v]; bzu[v] = zu[v]; bzl[v] = zl[v]; }
+                }
             }
-            if (it >= stop) break;
+            if (MODE == FC_SOLVE && lane == 0) {
+                ws.best_idx[(size_t)b * FC_MAX_ITER + it] = (uint8_t)best_it;
+                // batch statistics: the maximum only grows and the flag only sets, so a plain read filters most atomics
+                const unsigned bits = (unsigned)__float_as_int((float)best_res);
+                if (*(volatile unsigned *)(ws.gmax + it) < bits) atomicMax(ws.gmax + it, bits);
+                if (improved && it > 0 && *(volatile unsigned *)(ws.gimp + it) == 0u) atomicOr(ws.gimp + it, 1u);
+            }
+            if (it >= stop || it == P.max_iter - 1) break;  // the step after the last examined iterate is never used
             factor(du, dl);
             Dir aff;
             solve(du, dl, rx, zu, zl, rzu, rzl, aff);  // rs = z
@@ -330,7 +398,27 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 zu[v] += a2 * aff.dzu[v]; zl[v] += a2 * aff.dzl[v];
             }
         }
+        }  // MODE != FC_FINISH
+        if (MODE == FC_SOLVE) continue;
         if (!e_fc && !e_dis && !lam_out && !grad_cpts && !grad_cnrm) continue;  // trace-only pass
+        double bdu[2] = {1.0, 1.0}, bdl[2] = {1.0, 1.0};
+        if (MODE == FC_FINISH) {
+            const int kk = stop < P.max_iter ? stop : P.max_iter - 1;
+            const int bi = ws.best_idx[(size_t)b * FC_MAX_ITER + kk];
+            const double *sn = ws.snap + ((size_t)b * P.max_iter + bi) * 3 * n;
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+                if (valid[v]) {
+                    const int j = lane + 32 * v;
+                    bx[v] = sn[j]; bdu[v] = sn[n + j]; bdl[v] = sn[2 * n + j];
+                }
+        } else {
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                bdu[v] = fmax(bzu[v], 1e-8) / fmax(bsu[v], 1e-8);
+                bdl[v] = fmax(bzl[v], 1e-8) / fmax(bsl[v], 1e-8);
+            }
+        }
         // ---- value, svd term, E_fc (qp_solver.py:126, span.py:402, registry.py:82-87) ----
         double red[27];
 #pragma unroll
@@ -400,8 +488,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
 #pragma unroll
                 for (int i = 0; i < 6; ++i) ftfx += F[v][i] * Fx[i];
                 rxb[v] = valid[v] ? gv * ftfx : 0.0;  // dl/dx
-                du[v] = fmax(bzu[v], 1e-8) / fmax(bsu[v], 1e-8);
-                dl[v] = fmax(bzl[v], 1e-8) / fmax(bsl[v], 1e-8);
+                du[v] = bdu[v];
+                dl[v] = bdl[v];
             }
             factor(du, dl);
             Dir bd;
@@ -509,11 +597,73 @@ extern "C" int gqp_fc_dis_energy(const GqpFcParams *p, const float *cpts, const 
     P.c0 = sqrt(1.0 - (double)p->friction * (double)p->friction);
     P.tw = p->torque_weight; P.lo = p->lower; P.hi = p->upper; P.ridge = p->ridge; P.svd_gain = p->svd_gain;
     P.values_gain = p->values_gain; P.values_offset = p->values_offset; P.max_iter = p->max_iter;
-    P.w_fc = p->w_fc; P.w_dis = p->w_dis;
+    P.w_fc = p->w_fc; P.w_dis = p->w_dis; P.eps = p->eps;
     int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
-    GQP_LAUNCH(fc_dis_kernel, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist, obj_nrm,
-               obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm, qp_stop_iter, qp_trace);
+    GQP_LAUNCH(fc_dis_kernel<FC_FUSED>, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
+               obj_nrm, obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm, qp_stop_iter,
+               qp_trace, FcWorkspace{}, 0, (int32_t *)nullptr);
     GQP_CHECK_LAUNCH("gqp_fc_dis_energy");
+    return GQP_OK;
+}
+
+extern "C" uint64_t gqp_fc_workspace_bytes(int Bt, int n_c, int max_iter) {
+    if (Bt < 0 || n_c < 0 || max_iter < 0) return 0;
+    return FC_WS_HEADER + fc_align256((size_t)Bt * FC_MAX_ITER) + (size_t)Bt * max_iter * 3 * 4 * n_c * sizeof(double) + 256;
+}
+
+static int fc_check(const char *who, const GqpFcParams *p, int n_obj, int batch_each, int n_c, FcParamsDev &P) {
+    if (!p || n_obj < 0 || batch_each < 0) return gqp_set_error(GQP_ERR_ARG, "%s: bad argument", who);
+    if (n_c < 2 || n_c > 16) return gqp_set_error(GQP_ERR_LIMIT, "%s: n_c must be in [2,16], got %d", who, n_c);
+    if (p->max_iter < 1 || p->max_iter > FC_MAX_ITER) return gqp_set_error(GQP_ERR_ARG, "%s: max_iter out of range", who);
+    P.mu_f = p->friction;
+    P.c0 = sqrt(1.0 - (double)p->friction * (double)p->friction);
+    P.tw = p->torque_weight; P.lo = p->lower; P.hi = p->upper; P.ridge = p->ridge; P.svd_gain = p->svd_gain;
+    P.values_gain = p->values_gain; P.values_offset = p->values_offset; P.max_iter = p->max_iter;
+    P.w_fc = p->w_fc; P.w_dis = p->w_dis; P.eps = p->eps;
+    return GQP_OK;
+}
+
+extern "C" int gqp_fc_solve(const GqpFcParams *p, const float *cpts, const float *obj_nrm, const float *cog, int n_obj,
+                            int batch_each, int n_c, void *workspace, void *stream) {
+    FcParamsDev P;
+    if (int rc = fc_check("gqp_fc_solve", p, n_obj, batch_each, n_c, P)) return rc;
+    const int Bt = n_obj * batch_each;
+    if (Bt == 0) return GQP_OK;
+    if (!cpts || !obj_nrm || !cog || !workspace) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_solve: null pointer");
+    if (((uintptr_t)workspace & 7) != 0) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_solve: workspace must be 8-byte aligned");
+    FcWorkspace ws = fc_workspace_view(workspace, Bt);
+#ifndef GQP_EMU
+    if (cudaMemsetAsync(workspace, 0, FC_WS_HEADER, (cudaStream_t)stream) != cudaSuccess)
+        return gqp_set_error(GQP_ERR_CUDA, "gqp_fc_solve: memset failed");
+#else
+    memset(workspace, 0, FC_WS_HEADER);
+#endif
+    int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
+    GQP_LAUNCH(fc_dis_kernel<FC_SOLVE>, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, (const float *)nullptr,
+               (const float *)nullptr, obj_nrm, (const float *)nullptr, cog, Bt, batch_each, n_c, (float *)nullptr,
+               (float *)nullptr, (float *)nullptr, (float *)nullptr, (float *)nullptr, (const int32_t *)nullptr,
+               (float *)nullptr, ws, 0, (int32_t *)nullptr);
+    GQP_CHECK_LAUNCH("gqp_fc_solve");
+    return GQP_OK;
+}
+
+extern "C" int gqp_fc_finish(const GqpFcParams *p, const float *cpts, const float *cnrm_hand, const float *obj_dist,
+                             const float *obj_nrm, const float *obj_dgrad, const float *cog, int n_obj, int batch_each,
+                             int n_c, const void *workspace, int batch_stop, float *e_fc, float *e_dis, float *lam,
+                             float *grad_cpts, float *grad_cnrm, int32_t *stop_iter_out, void *stream) {
+    FcParamsDev P;
+    if (int rc = fc_check("gqp_fc_finish", p, n_obj, batch_each, n_c, P)) return rc;
+    const int Bt = n_obj * batch_each;
+    if (Bt == 0) return GQP_OK;
+    if (!cpts || !cnrm_hand || !obj_dist || !obj_nrm || !cog || !workspace)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_fc_finish: null pointer");
+    if (!e_fc && !e_dis && !lam && !grad_cpts && !grad_cnrm) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_finish: no output");
+    FcWorkspace ws = fc_workspace_view(const_cast<void *>(workspace), Bt);
+    int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
+    GQP_LAUNCH(fc_dis_kernel<FC_FINISH>, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
+               obj_nrm, obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm,
+               (const int32_t *)nullptr, (float *)nullptr, ws, batch_stop, stop_iter_out);
+    GQP_CHECK_LAUNCH("gqp_fc_finish");
     return GQP_OK;
 }
 

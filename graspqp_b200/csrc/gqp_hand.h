@@ -24,6 +24,8 @@ struct GqpBvhHost {
     std::vector<GqpBvhNode> nodes;   // nodes[0] = root
     std::vector<float> tris;         // (F,9) vertices in leaf order
     std::vector<int32_t> face_id;    // (F) original face index of slot i
+    std::vector<float> pre;          // (F,8) per slot: unit normal xyz, bounding-circle radius, centroid xyz, 0
+    float extent = 0.f;              // max |coordinate| of the mesh
     int max_depth = 0;
 };
 // leaf_size: max faces per leaf
@@ -42,6 +44,8 @@ struct GqpMesh {
     GqpBvhNode *d_nodes = nullptr;  // device
     float *d_tris = nullptr;        // device (F,9) leaf order
     int32_t *d_face_id = nullptr;   // device (F)
+    float *d_pre = nullptr;         // device (F,8) pre-test records in leaf order
+    float extent = 0.f;
 };
 
 // Device-side view of the hand tables (one contiguous blob, see gqp_hand.cu)

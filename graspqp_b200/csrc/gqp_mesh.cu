@@ -12,51 +12,76 @@ struct GqpObjSet {
     const GqpBvhNode **d_nodes = nullptr;
     const float **d_tris = nullptr;
     const int32_t **d_face_id = nullptr;
+    const float **d_pre = nullptr;
+    float *d_extent = nullptr;
 };
 
-__global__ void __launch_bounds__(128)
+static int mesh_qpw() {
+    static int v = 0;
+    if (!v) {
+        const char *e = getenv("GQP_MESH_QPW");
+        v = e ? atoi(e) : 64;
+        if (v < 32) v = 32;
+    }
+    return v;
+}
+#define MESH_WARPS 4
+
+__global__ void __launch_bounds__(MESH_WARPS * 32)
 mesh_sdf_kernel(const GqpBvhNode *__restrict__ nodes, const float *__restrict__ tris,
-                const int32_t *__restrict__ face_id, const float *__restrict__ points, int P,
+                const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
+                const float *__restrict__ points, int P, int qpw,
                 float *__restrict__ dist2, int32_t *__restrict__ sign, float *__restrict__ normals,
                 float *__restrict__ clst, int32_t *__restrict__ face_out) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    V3 p = ld3(points + 3 * (size_t)i);
-    SdfBest best;
-    sdf_best_init(best);
-    bvh_query<true>(nodes, tris, face_id, p, best);
-    int sg;
-    V3 un;
-    sdf_finish<true>(p, best, sg, un);
-    dist2[i] = best.d2;
-    sign[i] = sg;
-    st3(normals + 3 * (size_t)i, un);
-    st3(clst + 3 * (size_t)i, best.c);
-    if (face_out) face_out[i] = best.face;
+    const long long w = (long long)blockIdx.x * MESH_WARPS + (threadIdx.x >> 5);
+    const int q0 = (int)min((long long)P, w * qpw);
+    const int q1 = (int)min((long long)P, (w + 1) * qpw);
+    bvh_query_stream<true>(
+        q0, q1,
+        [&](int i, V3 &p, BvhTree &tr) {
+            p = ld3(points + 3 * (size_t)i);
+            tr = BvhTree{nodes, tris, face_id, pre, extent};
+        },
+        [&](int i, V3 p, const SdfBest &best) {
+            int sg;
+            V3 un;
+            sdf_finish<true>(p, best, sg, un);
+            dist2[i] = best.d2;
+            sign[i] = sg;
+            st3(normals + 3 * (size_t)i, un);
+            st3(clst + 3 * (size_t)i, best.c);
+            if (face_out) face_out[i] = best.face;
+        });
 }
 
 // O1 forward: query i belongs to object i / (batch_each * n_pts)
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(MESH_WARPS * 32)
 object_distance_kernel(const GqpBvhNode *const *__restrict__ nodes, const float *const *__restrict__ tris,
-                       const int32_t *const *__restrict__ face_id, int per_obj, int n, const float *__restrict__ x,
-                       float scale, float *__restrict__ distance, float *__restrict__ normals,
+                       const int32_t *const *__restrict__ face_id, const float *const *__restrict__ pre,
+                       const float *__restrict__ extent, int per_obj, int n, int qpw,
+                       const float *__restrict__ x, float scale, float *__restrict__ distance, float *__restrict__ normals,
                        float *__restrict__ clst, int32_t *__restrict__ sign) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int o = i / per_obj;
-    V3 p = ld3(x + 3 * (size_t)i);
-    p = V3{p.x / scale, p.y / scale, p.z / scale};  // object_model.py:215-216
-    SdfBest best;
-    sdf_best_init(best);
-    bvh_query<true>(nodes[o], tris[o], face_id[o], p, best);
-    int sg;
-    V3 un;
-    sdf_finish<true>(p, best, sg, un);
-    float d = sqrtf(best.d2 + 1e-8f) * (float)(-sg);  // :243
-    distance[i] = d * scale;                          // :249
-    st3(normals + 3 * (size_t)i, un * (float)sg);     // :246
-    st3(clst + 3 * (size_t)i, best.c);
-    sign[i] = sg;
+    const long long w = (long long)blockIdx.x * MESH_WARPS + (threadIdx.x >> 5);
+    const int q0 = (int)min((long long)n, w * qpw);
+    const int q1 = (int)min((long long)n, (w + 1) * qpw);
+    bvh_query_stream<true>(
+        q0, q1,
+        [&](int i, V3 &p, BvhTree &tr) {
+            const int o = i / per_obj;
+            p = ld3(x + 3 * (size_t)i);
+            p = V3{p.x / scale, p.y / scale, p.z / scale};  // object_model.py:215-216
+            tr = BvhTree{nodes[o], tris[o], face_id[o], pre[o], extent[o]};
+        },
+        [&](int i, V3 p, const SdfBest &best) {
+            int sg;
+            V3 un;
+            sdf_finish<true>(p, best, sg, un);
+            float d = sqrtf(best.d2 + 1e-8f) * (float)(-sg);  // :243
+            distance[i] = d * scale;                          // :249
+            st3(normals + 3 * (size_t)i, un * (float)sg);     // :246
+            st3(clst + 3 * (size_t)i, best.c);
+            sign[i] = sg;
+        });
 }
 
 // O1 backward: TorchSDF backward (2 g' (p-c), sdf.py:60-66) chained through sqrt(d2+1e-8)*(-sign)*scale and p = x/scale
@@ -76,7 +101,7 @@ __global__ void object_distance_backward_kernel(const float *__restrict__ grad_d
 extern "C" int gqp_mesh_create(const float *face_verts_host, int F, GqpMesh **out) {
     if (!face_verts_host || F <= 0 || !out) return gqp_set_error(GQP_ERR_ARG, "gqp_mesh_create: need F > 0");
     GqpBvhHost bvh;
-    gqp_bvh_build(face_verts_host, F, 4, bvh);
+    gqp_bvh_build(face_verts_host, F, 8, bvh);
     if (bvh.max_depth > GQP_BVH_STACK - 2)
         return gqp_set_error(GQP_ERR_LIMIT, "gqp_mesh_create: BVH depth %d exceeds the traversal stack", bvh.max_depth);
     GqpMesh *m = new GqpMesh();
@@ -86,7 +111,9 @@ extern "C" int gqp_mesh_create(const float *face_verts_host, int F, GqpMesh **ou
     m->d_nodes = (GqpBvhNode *)gqp_dev_alloc_upload(bvh.nodes.data(), bvh.nodes.size() * sizeof(GqpBvhNode));
     m->d_tris = (float *)gqp_dev_alloc_upload(bvh.tris.data(), bvh.tris.size() * sizeof(float));
     m->d_face_id = (int32_t *)gqp_dev_alloc_upload(bvh.face_id.data(), bvh.face_id.size() * sizeof(int32_t));
-    if (!m->d_nodes || !m->d_tris || !m->d_face_id) {
+    m->d_pre = (float *)gqp_dev_alloc_upload(bvh.pre.data(), bvh.pre.size() * sizeof(float));
+    m->extent = bvh.extent;
+    if (!m->d_nodes || !m->d_tris || !m->d_face_id || !m->d_pre) {
         gqp_mesh_destroy(m);
         return gqp_set_error(GQP_ERR_CUDA, "gqp_mesh_create: device allocation failed");
     }
@@ -95,7 +122,7 @@ extern "C" int gqp_mesh_create(const float *face_verts_host, int F, GqpMesh **ou
 }
 extern "C" void gqp_mesh_destroy(GqpMesh *m) {
     if (!m) return;
-    gqp_dev_free(m->d_nodes); gqp_dev_free(m->d_tris); gqp_dev_free(m->d_face_id);
+    gqp_dev_free(m->d_nodes); gqp_dev_free(m->d_tris); gqp_dev_free(m->d_face_id); gqp_dev_free(m->d_pre);
     delete m;
 }
 extern "C" int gqp_mesh_num_faces(const GqpMesh *m) { return m ? m->F : 0; }
@@ -105,8 +132,10 @@ extern "C" int gqp_mesh_sdf_forward(const GqpMesh *m, const float *points, int P
     if (!m || P < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_mesh_sdf_forward: bad argument");
     if (P == 0) return GQP_OK;
     if (!points || !dist2 || !sign || !normals || !clst) return gqp_set_error(GQP_ERR_ARG, "gqp_mesh_sdf_forward: null pointer");
-    GQP_LAUNCH(mesh_sdf_kernel, (P + 127) / 128, 128, 0, (cudaStream_t)stream, m->d_nodes, m->d_tris, m->d_face_id,
-               points, P, dist2, sign, normals, clst, face);
+    const int qpw = mesh_qpw();
+    GQP_LAUNCH(mesh_sdf_kernel, (P + MESH_WARPS * qpw - 1) / (MESH_WARPS * qpw),
+               MESH_WARPS * 32, 0, (cudaStream_t)stream, m->d_nodes, m->d_tris, m->d_face_id,
+               m->d_pre, m->extent, points, P, qpw, dist2, sign, normals, clst, face);
     GQP_CHECK_LAUNCH("gqp_mesh_sdf_forward");
     return GQP_OK;
 }
@@ -118,6 +147,8 @@ extern "C" int gqp_objset_create(const GqpMesh *const *meshes_host, int n_obj, G
     std::vector<const GqpBvhNode *> n(n_obj);
     std::vector<const float *> t(n_obj);
     std::vector<const int32_t *> f(n_obj);
+    std::vector<const float *> pr(n_obj);
+    std::vector<float> ex(n_obj);
     for (int o = 0; o < n_obj; ++o) {
         if (!meshes_host[o]) {
             delete s;
@@ -125,11 +156,14 @@ extern "C" int gqp_objset_create(const GqpMesh *const *meshes_host, int n_obj, G
         }
         s->meshes.push_back(meshes_host[o]);
         n[o] = meshes_host[o]->d_nodes; t[o] = meshes_host[o]->d_tris; f[o] = meshes_host[o]->d_face_id;
+        pr[o] = meshes_host[o]->d_pre; ex[o] = meshes_host[o]->extent;
     }
     s->d_nodes = (const GqpBvhNode **)gqp_dev_alloc_upload(n.data(), n_obj * sizeof(void *));
     s->d_tris = (const float **)gqp_dev_alloc_upload(t.data(), n_obj * sizeof(void *));
     s->d_face_id = (const int32_t **)gqp_dev_alloc_upload(f.data(), n_obj * sizeof(void *));
-    if (!s->d_nodes || !s->d_tris || !s->d_face_id) {
+    s->d_pre = (const float **)gqp_dev_alloc_upload(pr.data(), n_obj * sizeof(void *));
+    s->d_extent = (float *)gqp_dev_alloc_upload(ex.data(), n_obj * sizeof(float));
+    if (!s->d_nodes || !s->d_tris || !s->d_face_id || !s->d_pre || !s->d_extent) {
         gqp_objset_destroy(s);
         return gqp_set_error(GQP_ERR_CUDA, "gqp_objset_create: device allocation failed");
     }
@@ -139,6 +173,7 @@ extern "C" int gqp_objset_create(const GqpMesh *const *meshes_host, int n_obj, G
 extern "C" void gqp_objset_destroy(GqpObjSet *s) {
     if (!s) return;
     gqp_dev_free((void *)s->d_nodes); gqp_dev_free((void *)s->d_tris); gqp_dev_free((void *)s->d_face_id);
+    gqp_dev_free((void *)s->d_pre); gqp_dev_free((void *)s->d_extent);
     delete s;
 }
 
@@ -152,8 +187,10 @@ extern "C" int gqp_object_distance_forward(const GqpObjSet *s, int batch_each, i
     if (n > 0x7fffffffLL) return gqp_set_error(GQP_ERR_LIMIT, "gqp_object_distance_forward: too many queries");
     if (!x || !distance || !normals || !clst || !sign)
         return gqp_set_error(GQP_ERR_ARG, "gqp_object_distance_forward: null pointer");
-    GQP_LAUNCH(object_distance_kernel, (int)((n + 127) / 128), 128, 0, (cudaStream_t)stream, s->d_nodes, s->d_tris,
-               s->d_face_id, batch_each * n_pts, (int)n, x, scale, distance, normals, clst, sign);
+    const int qpw = mesh_qpw();
+    GQP_LAUNCH(object_distance_kernel, (int)((n + MESH_WARPS * qpw - 1) / (MESH_WARPS * qpw)),
+               MESH_WARPS * 32, 0, (cudaStream_t)stream, s->d_nodes, s->d_tris,
+               s->d_face_id, s->d_pre, s->d_extent, batch_each * n_pts, (int)n, qpw, x, scale, distance, normals, clst, sign);
     GQP_CHECK_LAUNCH("gqp_object_distance_forward");
     return GQP_OK;
 }

@@ -39,6 +39,8 @@ struct GqpPenTables {
     unsigned char *d_blob = nullptr;
     float *d_tris = nullptr;       // (F_total, 9) leaf order, links concatenated
     int32_t *d_face_id = nullptr;  // (F_total) index inside the link's original face list
+    float *d_pre = nullptr;        // (F_total, 8) pre-test records, leaf order
+    float extent = 0.f;            // max |coordinate| over all link meshes
     int total_bytes = 0;
 };
 
@@ -136,8 +138,8 @@ __global__ void pen_mask_kernel(const unsigned char *__restrict__ blob, const fl
 template <bool CULL>
 __global__ void __launch_bounds__(PEN_THREADS, PEN_MIN_BLOCKS)
 hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
-                const int32_t *__restrict__ face_id, const float *__restrict__ link_tf, const float *__restrict__ x,
-                const float *__restrict__ bounds, const uint32_t *__restrict__ masks, int n_rows, int cands_per_row,
+                const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
+                const float *__restrict__ link_tf, const float *__restrict__ x, const float *__restrict__ bounds, const uint32_t *__restrict__ masks, int n_rows, int cands_per_row,
                 int n_pts, float *__restrict__ dist_out, int32_t *__restrict__ arg_link_out,
                 float *__restrict__ dgrad_out, float *__restrict__ partial, float w_pen,
                 float *__restrict__ grad_link_tf) {
@@ -208,7 +210,8 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
                 if (CULL && pen_outside(K, grids, bits, q)) continue;
                 SdfBest best;
                 sdf_best_init(best);
-                bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first, q, best);
+                bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first,
+                                 pre + (size_t)K.tri_first * 8, extent, q, best);
                 V3 dv = q - best.c;
                 float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
                 float r = sqrtf(best.d2 + 1e-8f);
@@ -349,6 +352,7 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     std::vector<uint32_t> bits;
     std::vector<float> tris;
     std::vector<int32_t> fid;
+    std::vector<float> pre;
     for (int l = 0; l < L; ++l) {
         int f0 = h->face_offset[l], F = h->face_offset[l + 1] - f0;
         PenLink K{};
@@ -365,6 +369,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
             nodes.insert(nodes.end(), bvh.nodes.begin(), bvh.nodes.end());
             tris.insert(tris.end(), bvh.tris.begin(), bvh.tris.end());
             fid.insert(fid.end(), bvh.face_id.begin(), bvh.face_id.end());
+            pre.insert(pre.end(), bvh.pre.begin(), bvh.pre.end());
+            T->extent = std::max(T->extent, bvh.extent);
             const GqpBvhNode &root = bvh.nodes[0];
             for (int k = 0; k < 3; ++k) {
                 K.lo[k] = root.lo[k] - 2e-5f;
@@ -423,7 +429,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     T->d_blob = (unsigned char *)gqp_dev_alloc_upload(B.data(), B.size());
     T->d_tris = (float *)gqp_dev_alloc_upload(tris.data(), tris.size() * sizeof(float));
     T->d_face_id = (int32_t *)gqp_dev_alloc_upload(fid.data(), fid.size() * sizeof(int32_t));
-    if (!T->d_blob || !T->d_tris || !T->d_face_id) return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
+    T->d_pre = (float *)gqp_dev_alloc_upload(pre.data(), pre.size() * sizeof(float));
+    if (!T->d_blob || !T->d_tris || !T->d_face_id || !T->d_pre) return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
 #ifndef GQP_EMU
     cudaFuncSetAttribute(hand_pen_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
     cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
@@ -434,6 +441,7 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
 void gqp_pen_tables_destroy(GqpHand *h) {
     if (!h || !h->pen) return;
     gqp_dev_free(h->pen->d_blob); gqp_dev_free(h->pen->d_tris); gqp_dev_free(h->pen->d_face_id);
+    gqp_dev_free(h->pen->d_pre);
     delete h->pen;
     h->pen = nullptr;
 }
@@ -481,11 +489,11 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
     int grid = pen_grid_size((int)smem, n_tasks);
     if (cull) {
         GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
-                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
+                   T->d_face_id, T->d_pre, T->extent, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
                    partial, w_pen, grad_link_tf);
     } else {
         GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
-                   T->d_face_id, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
+                   T->d_face_id, T->d_pre, T->extent, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
                    partial, w_pen, grad_link_tf);
     }
     GQP_CHECK_LAUNCH("gqp_hand_distance");

@@ -159,7 +159,7 @@ class FitEngine:
         self.lam = be.empty((Bt, n_c), f32)
         self.g_pose_joints = be.empty((Bt, D), f32)
         self.pen_scratch = be.empty((int(cdll.gqp_hand_distance_scratch_floats(self.n_obj, self.batch_each, self.n_pts, 0)),), f32)
-        self.qp_trace = be.empty((Bt, self.fc.max_iter), f32)
+        self.qp_ws = be.empty(((int(cdll.gqp_fc_workspace_bytes(Bt, n_c, self.fc.max_iter)) + 7) // 8,), np.float64)
         self.qp_stop = be.empty((1,), i32)
         self.reset_all = be.from_host(np.ones(Bt, u8))
         self._init_energy()
@@ -180,17 +180,14 @@ class FitEngine:
         self._ck(lib.gqp_object_distance_backward(p(self.ones), p(self.cpts), p(self.obj_clst), p(self.obj_sign),
                                                   Bt * n_c, 1.0, p(self.obj_dgrad), st))
         self._ck(lib.gqp_memset_zero(p(self.g_link_tf), 4 * Bt * self.L * 12, st))
-        fc_args = lambda stop, trace: (ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist),
-                                       p(self.obj_nrm), p(self.obj_dgrad), p(self.cog), O, B, n_c, row("E_fc"),
-                                       row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm), stop, trace, st)
-        if self.qp_batch_stop:  # replay qpth's batch-wide exit test: trace pass, exit iteration, final pass
-            self._ck(lib.gqp_fc_dis_energy(ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist),
-                                           p(self.obj_nrm), p(self.obj_dgrad), p(self.cog), O, B, n_c, None, None, None,
-                                           None, None, None, p(self.qp_trace), st))
-            self._ck(lib.gqp_fc_stop_iter(p(self.qp_trace), Bt, self.fc.max_iter, self.fc.eps, p(self.qp_stop), st))
-            self._ck(lib.gqp_fc_dis_energy(*fc_args(p(self.qp_stop), None)))
-        else:
-            self._ck(lib.gqp_fc_dis_energy(*fc_args(None, None)))
+        # Q1-Q4 + E_dis: one interior-point pass that records the batch statistics of qpth's exit test, then the
+        # finish pass (value, svd term, energies, analytic backward) from every candidate's best iterate as of the exit
+        self._ck(lib.gqp_fc_solve(ctypes.byref(self.fc), p(self.cpts), p(self.obj_nrm), p(self.cog), O, B, n_c,
+                                  p(self.qp_ws), st))
+        self._ck(lib.gqp_fc_finish(ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist), p(self.obj_nrm),
+                                   p(self.obj_dgrad), p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop),
+                                   row("E_fc"), row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm),
+                                   p(self.qp_stop), st))
         self._ck(lib.gqp_contacts_backward(self.hand, p(idx), p(self.g_cpts), p(self.g_cnrm), Bt, n_c,
                                            p(self.g_link_tf), st))
         self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
@@ -231,7 +228,7 @@ class FitEngine:
         self._accept(self.z, reset_mask, u_accept)
 
     def launches_per_step(self):
-        return 14 if self.qp_batch_stop else 12
+        return 13
 
     def close(self):
         lib = self.lib

@@ -177,14 +177,14 @@ class ForceClosureFn(torch.autograd.Function):
         e, lam = torch.empty(B, device=cp.device), torch.empty(B, n_c, device=cp.device)
         g = torch.empty_like(cp)
         zeros = torch.zeros(B, n_c, device=cp.device)
-        fc = lambda stop, trace, outs: lib.gqp_fc_dis_energy(
-            ctypes.byref(params), cp.data_ptr(), cn.data_ptr(), zeros.data_ptr(), cn.data_ptr(), None, cg.data_ptr(), B, 1,
-            n_c, *outs, stop, trace, _st(cp))
-        trace = torch.empty(B, params.max_iter, device=cp.device)
-        stop = torch.empty(1, dtype=torch.int32, device=cp.device)
-        _chk(fc(None, trace.data_ptr(), (None, None, None, None, None)))
-        _chk(lib.gqp_fc_stop_iter(trace.data_ptr(), B, params.max_iter, params.eps, stop.data_ptr(), _st(cp)))
-        _chk(fc(stop.data_ptr(), None, (e.data_ptr(), None, lam.data_ptr(), g.data_ptr(), None)))
+        ws = torch.empty((int(lib.gqp_fc_workspace_bytes(B, n_c, params.max_iter)) + 7) // 8, dtype=torch.float64,
+                         device=cp.device)
+        # cog is per candidate here (energy.py:35-42 passes (Bt,3)): n_obj = B "objects" of one candidate each
+        _chk(lib.gqp_fc_solve(ctypes.byref(params), cp.data_ptr(), cn.data_ptr(), cg.data_ptr(), B, 1, n_c,
+                              ws.data_ptr(), _st(cp)))
+        _chk(lib.gqp_fc_finish(ctypes.byref(params), cp.data_ptr(), cn.data_ptr(), zeros.data_ptr(), cn.data_ptr(), None,
+                               cg.data_ptr(), B, 1, n_c, ws.data_ptr(), 1, e.data_ptr(), None, lam.data_ptr(),
+                               g.data_ptr(), None, None, _st(cp)))
         ctx.save_for_backward(g)
         ctx.mark_non_differentiable(lam)
         return e, lam

@@ -170,6 +170,23 @@ int gqp_fc_dis_energy(const GqpFcParams *p_host, const float *cpts, const float 
 /* batch-wide exit iteration of qpth's loop from the trace (one block): writes *stop_iter. */
 int gqp_fc_stop_iter(const float *qp_trace, int Bt, int max_iter, float eps, int32_t *stop_iter, void *stream);
 
+/* The same computation split so that qpth's batch-wide exit test costs ONE interior-point pass instead of two (what
+ * the engine launches every iteration):
+ *   gqp_fc_solve  runs max_iter iterations per candidate; into `workspace` (gqp_fc_workspace_bytes bytes, 8-byte
+ *     aligned, caller-owned) it stores every iterate that improved the candidate's best residual, which iterate was the
+ *     best as of each iteration, and per iteration the batch maximum of the best residuals and an any-improved flag;
+ *   gqp_fc_finish derives the exit iteration from those flags (batch_stop != 0; else every candidate keeps its best
+ *     of all max_iter iterates), then computes value, svd term, E_fc, E_dis, lam and the analytic backward from each
+ *     candidate's stored best iterate as of the exit iteration.  *stop_iter_out (device, may be NULL) gets the exit
+ *     iteration.  Outputs as gqp_fc_dis_energy. */
+uint64_t gqp_fc_workspace_bytes(int Bt, int n_c, int max_iter);
+int gqp_fc_solve(const GqpFcParams *p_host, const float *cpts, const float *obj_nrm, const float *cog, int n_obj,
+                 int batch_each, int n_c, void *workspace, void *stream);
+int gqp_fc_finish(const GqpFcParams *p_host, const float *cpts, const float *cnrm_hand, const float *obj_dist,
+                  const float *obj_nrm, const float *obj_dgrad, const float *cog, int n_obj, int batch_each, int n_c,
+                  const void *workspace, int batch_stop, float *e_fc, float *e_dis, float *lam, float *grad_cpts,
+                  float *grad_cnrm, int32_t *stop_iter_out, void *stream);
+
 /* ---- M1/M2/M4: MALA* (optimizer.py:199-340) and the caller's bookkeeping (fit.py:403-406, 434-458) -----------------
  * State rows are candidates.  u_switch (Bt,n_c), idx_rand (Bt,n_c) int32, u_accept (Bt): injected noise, or all NULL
  * to draw them from Philox4x32-10 keyed (seed, iteration, row).

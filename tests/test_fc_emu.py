@@ -45,6 +45,18 @@ def run_kernel(lib, P, cp, hn, dist, nrm, dgrad, cog, n_obj, two_pass=True):
     if two_pass:
         assert lib.gqp_fc_stop_iter(ptr(trace), B, P.max_iter, P.eps, ptr(stop), None) == 0
         assert lib.gqp_fc_dis_energy(*args(ptr(stop), None)) == 0
+    # the split form the engine launches (one interior-point pass + finish) must reproduce the two-pass form exactly
+    ws = np.zeros((int(lib.gqp_fc_workspace_bytes(B, n_c, P.max_iter)) + 7) // 8, np.float64)
+    o2 = [np.zeros_like(a) for a in (e_fc, e_dis, lam, g_cp, g_hn)]
+    stop2 = np.full(1, -1, np.int32)
+    assert lib.gqp_fc_solve(ctypes.byref(P), ptr(cp), ptr(nrm), ptr(cog), n_obj, B // n_obj, n_c, ptr(ws), None) == 0
+    assert lib.gqp_fc_finish(ctypes.byref(P), ptr(cp), ptr(hn), ptr(dist), ptr(nrm), ptr(dgrad), ptr(cog), n_obj,
+                             B // n_obj, n_c, ptr(ws), int(two_pass), *[ptr(a) for a in o2], ptr(stop2), None) == 0, \
+        lib.gqp_last_error()
+    if two_pass:
+        assert int(stop2[0]) == int(stop[0])
+    for a, b in zip((e_fc, e_dis, lam, g_cp, g_hn), o2):
+        np.testing.assert_array_equal(a, b)
     return e_fc, e_dis, lam, g_cp, g_hn, trace, int(stop[0])
 
 
