@@ -20,7 +20,7 @@ static int mesh_qpw() {
     static int v = 0;
     if (!v) {
         const char *e = getenv("GQP_MESH_QPW");
-        v = e ? atoi(e) : 64;
+        v = e ? atoi(e) : 32;
         if (v < 32) v = 32;
     }
     return v;

@@ -1,0 +1,175 @@
+#!/usr/bin/env python
+"""TEST INFRASTRUCTURE.  Generates tests/golden/*.npz by running the REFERENCE's own code in the build container:
+
+  python tests/golden/make_golden.py          (needs /root/reference; see ref_harness.py for what is real and what is stubbed)
+
+  sdf_ref.npz        thirdparty/TorchSDF forward kernel body, host-compiled from the reference source (oracle/_ref), on two
+                     of TorchSDF's own test models (tests/models/cube.obj, sphere-42.obj) and seeded points
+  fk_ref.npz         pytorch_kinematics Chain.forward_kinematics (+-0.01 rad perturbation included) and
+                     Transform3d.transform_points / transform_normals on the Allegro tree
+  metric_ref.npz     GraspSpanMetricFactory.create(GRASPQP) callable (span.py, registry.py, qp_solver.py) forward and
+                     autograd backward; qpth replaced by oracle.qp (PARITY UNPINNED for the QP iterate)
+  solver_kat.npz     graspqp/tests/metrics/test_solver.py's known-answer problem through SQPLsqSolver
+  fit_ref_f32.npz    4 iterations of scripts/fit.py:381-458 with the reference MalaStar + calculate_energy, injected noise,
+  fit_ref_f64.npz    run in fp32 (as the reference does) and in fp64 (the rounding-free target the kernels are held to)
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+import ref_harness as rh  # noqa: E402
+from graspqp_b200 import hand_pack, synth  # noqa: E402
+from oracle import sdf as osdf  # noqa: E402
+
+
+def load_obj(path):
+    v, f = [], []
+    for line in open(path):
+        t = line.split()
+        if not t:
+            continue
+        if t[0] == "v":
+            v.append([float(x) for x in t[1:4]])
+        elif t[0] == "f":
+            f.append([int(x.split("/")[0]) - 1 for x in t[1:4]])
+    v, f = np.asarray(v, np.float32), np.asarray(f, np.int64)
+    return v[f]  # index_vertices_by_faces (torchsdf/sdf.py:5-31)
+
+
+def gen_sdf():
+    out = {}
+    rng = np.random.default_rng(7)
+    for name in ("cube", "sphere-42"):
+        fv = load_obj(os.path.join(rh.REF, "thirdparty/TorchSDF/tests/models", name + ".obj"))
+        pts = rng.uniform(-1, 1, (384, 3)).astype(np.float32)  # tests/value.py draws points in [-1,1]^3
+        k = 96  # on / near vertices, edges and faces: the tie-break cases
+        pts[:k] = fv.reshape(-1, 3)[rng.integers(0, len(fv) * 3, k)]
+        pts[k:2 * k] = (fv[rng.integers(0, len(fv), k)].mean(1) * (1 + rng.normal(size=(k, 1)) * 0.01)).astype(np.float32)
+        d2, sg, nr, cl = osdf.compute_sdf_ref(pts, fv)
+        key = name.replace("-", "_")
+        out.update({key + "_face_verts": fv, key + "_points": pts, key + "_dist2": d2, key + "_sign": sg,
+                    key + "_normals": nr, key + "_clst": cl})
+    np.savez_compressed(os.path.join(HERE, "sdf_ref.npz"), **out)
+    print("sdf_ref.npz", {k: v.shape for k, v in out.items() if k.endswith("dist2")})
+
+
+def gen_fk():
+    pack = hand_pack.load_pack("allegro")
+    chain, frames = rh.pk_chain_from_pack(pack)
+    rng = np.random.default_rng(3)
+    B = 6
+    lo, hi = pack["joints_lower"], pack["joints_upper"]
+    theta = (lo + (hi - lo) * rng.random((B, len(lo)))).astype(np.float32)
+    theta[0] = 0.0          # the perturbation's discontinuity: theta == 0 -> -0.01
+    theta[1, ::2] = -0.05   # negative angles
+    th = torch.tensor(theta)
+    th_dict = {f"j{f}": th[:, int(d)] for f, d in enumerate(pack["frame_dof"]) if d >= 0}
+    res = chain.forward_kinematics(th_dict)
+    link_m = np.stack([res[f"l{int(f)}"].get_matrix().expand(B, 4, 4).numpy() for f in pack["mesh_frame"]], 1)
+    # contact candidates through Transform3d.transform_points / transform_normals (hand_model.py:1233-1248)
+    cp, cn = [], []
+    for li, f in enumerate(pack["mesh_frame"]):
+        m = pack["cand_link"] == li
+        if m.sum() == 0:
+            continue
+        T = res[f"l{int(f)}"]
+        cp.append(T.transform_points(torch.tensor(pack["cand"][m])).expand(B, -1, -1))
+        cn.append(T.transform_normals(torch.tensor(pack["cand_normal"][m])).expand(B, -1, -1))
+    np.savez_compressed(os.path.join(HERE, "fk_ref.npz"), theta=theta, link_matrices=link_m.astype(np.float32),
+                        cand_points=torch.cat(cp, 1).numpy(), cand_normals=torch.cat(cn, 1).numpy())
+    print("fk_ref.npz", link_m.shape)
+
+
+def gen_metric():
+    ref = rh.load()
+    out = {}
+    for n_c in (12, 16, 4):
+        rng = np.random.default_rng(100 + n_c)
+        B = 5
+        nrm = rng.normal(size=(B, n_c, 3)); nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
+        nrm[0, 0] = np.array([1.0, 1.0, 1.0]) / np.sqrt(3)  # the b1 switch of span.py:271-277
+        cp = (-nrm * 0.08 + rng.normal(size=(B, n_c, 3)) * 0.01)
+        cog = rng.normal(size=(B, 3)) * 0.005
+        # the stored inputs are fp32: round first so that every run sees exactly the stored values
+        nrm, cp, cog = [a.astype(np.float32).astype(np.float64) for a in (nrm, cp, cog)]
+        for dt, tag in ((torch.float64, "f64"), (torch.float32, "f32")):
+            F = ref["registry"].GraspSpanMetricFactory
+            fn = F.create(F.MetricType.GRASPQP, solver_kwargs={"friction": 0.2, "max_limit": 20.0, "n_cone_vecs": 4})
+            cpt = torch.tensor(cp, dtype=dt, requires_grad=True)
+            nt = torch.tensor(nrm, dtype=dt)
+            if dt == torch.float64:
+                torch.set_default_dtype(torch.float64)  # the reference builds its eye()/ones() in the default dtype
+            try:
+                E, x = fn(contact_pts=cpt, contact_normals=nt, sdf=torch.zeros(B, n_c, dtype=dt),
+                          cog=torch.tensor(cog, dtype=dt), with_solution=True, svd_gain=0.1)
+                E.sum().backward()
+            finally:
+                torch.set_default_dtype(torch.float32)
+            out.update({f"nc{n_c}_{tag}_E_fc": E.detach().numpy(), f"nc{n_c}_{tag}_x": x.detach().numpy(),
+                        f"nc{n_c}_{tag}_grad_cpts": cpt.grad.numpy()})
+        out.update({f"nc{n_c}_cpts": cp.astype(np.float32), f"nc{n_c}_nrm": nrm.astype(np.float32),
+                    f"nc{n_c}_cog": cog.astype(np.float32)})
+    # friction cone + grasp matrix alone (no solver behind them)
+    m = ref["span"].OverallFrictionConeSpanMetric.from_dim(12, 6, batch_size=5, device="cpu", solver_cls=ref["qp_solver"].SQPLsqSolver,
+                                                            friction=0.2, n_cone_vecs=4)
+    cone = m.get_friction_cone(torch.tensor(out["nc12_nrm"]))
+    out["nc12_cone"] = cone.numpy()
+    np.savez_compressed(os.path.join(HERE, "metric_ref.npz"), **out)
+    print("metric_ref.npz", sorted(out)[:6], "...")
+
+
+def gen_solver_kat():
+    ref = rh.load()
+    A = torch.Tensor([[-0.0, 0.25819889, 0.25819889, -0.25819889, -0.25819889, -0.25819889],
+                      [0.31622777, -0.18257419, -0.18257419, -0.18257419, -0.18257419, -0.18257419],
+                      [0.02810913, -0.09128826, 0.10345754, 0.13997471, -0.05477109, -0.10345754]]).unsqueeze(0)
+    b = torch.Tensor([0.25819889, 0.18257419, 0.00608464]).unsqueeze(0)
+    S = ref["qp_solver"].SQPLsqSolver
+    solver = S.from_mat(A, b)
+    value, x = solver(A, b, min_bound=-10.0, max_bound=1e3, init=0.1, return_solution=True)
+    assert torch.allclose(value, torch.zeros_like(value), atol=1e-4), value  # graspqp/tests/metrics/test_solver.py:26
+    np.savez_compressed(os.path.join(HERE, "solver_kat.npz"), A=A.numpy(), b=b.numpy(), value=value.numpy(), x=x.numpy())
+    print("solver_kat.npz value", value.numpy())
+
+
+def gen_fit(dtype=torch.float32, name="fit_ref_f32.npz"):
+    pack = hand_pack.load_pack("allegro")
+    B, n_c, n_pts, T, seed = 6, 12, 192, 4, 3
+    v, f = synth.make_mesh("sphere", 400, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.7
+    if dtype == torch.float64:
+        torch.set_default_dtype(torch.float64)  # the reference builds eye()/ones() in the default dtype
+    st = rh.make_fit_state(pack, [fv], [sp], B, pose.astype(np.float32), idx, dtype=dtype)
+    out = dict(face_verts=fv, surface=sp.astype(np.float32), pose0=pose.astype(np.float32), idx0=idx.astype(np.int32),
+               energy0=st.energy.detach().numpy().copy(), first_grad=st.first_grad.numpy().copy())
+    for k, v_ in st.losses.items():
+        out["loss0_" + k] = v_.detach().numpy().copy()  # st.losses is updated in place later
+    rng = np.random.default_rng(0)
+    n_cand = len(pack["cand"])
+    for t in range(T):
+        us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, n_cand, (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+        o = rh.fit_iterate(st, torch.tensor(us), torch.tensor(ir).long(), torch.tensor(ua))
+        out.update({f"t{t}_u_switch": us, f"t{t}_idx_rand": ir, f"t{t}_u_accept": ua})
+        for k in ("s", "z", "proposal", "idx_prop", "new_energy", "new_grad", "accept", "temperature", "energy", "pose", "idx"):
+            out[f"t{t}_{k}"] = o[k].numpy()
+        for k, v_ in o["new_losses"].items():
+            out[f"t{t}_loss_{k}"] = v_.numpy()
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, "accepts", [out[f"t{t}_accept"].sum() for t in range(T)])
+
+
+if __name__ == "__main__":
+    assert rh.available(), "reference not present"
+    import subprocess
+    subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
+    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz")

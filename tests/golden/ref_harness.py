@@ -1,0 +1,219 @@
+"""TEST INFRASTRUCTURE — runs ONLY in the build container, where /root/reference exists.
+
+Loads the reference's OWN Python modules for the hot path from where they lie and executes them on the CPU:
+
+    graspqp/src/graspqp/core/optimizer.py      (MalaStar.try_step / accept_step / zero_grad)
+    graspqp/src/graspqp/core/energy.py         (calculate_energy)
+    graspqp/src/graspqp/metrics/ops/span.py    (friction cone, grasp matrix, OverallFrictionConeSpanMetric)
+    graspqp/src/graspqp/metrics/ops/registry.py (SpanMetricWrapper, GraspSpanMetricFactory)
+    graspqp/src/graspqp/metrics/solver/qp_solver.py (SQPLsqSolver: QP construction around qpth)
+    graspqp/src/graspqp/utils/transforms.py    (robust_compute_rotation_matrix_from_ortho6d)
+    thirdparty/pytorch_kinematics/pytorch_kinematics/{frame,chain,jacobian}.py + transforms/ (FK, Transform3d)
+
+The package __init__ files are bypassed (they import trimesh / pytorch3d / lxml, absent here) by pre-registering empty
+package modules whose __path__ points at the reference directories.  Third-party modules that are NOT vendored in the
+reference and not installed are replaced by stubs built from oracle/:
+
+    qpth.qp.QPFunction        -> oracle.qp.QPFunction  (restatement of qpth 0.0.18's batched PDIPM; PARITY UNPINNED)
+    roma.special_gramschmidt  -> oracle.hand.special_gramschmidt (restatement of roma 1.5.4;        PARITY UNPINNED)
+
+HandModel / ObjectModel themselves cannot be constructed here (trimesh, pytorch3d); the reference optimizer and energy
+code are therefore driven with oracle.hand.HandOracle / oracle.pipeline.ObjectOracle as duck-typed models.  What the
+golden vectors produced through this harness pin is the reference's own glue: MALA* update and accept rules, energy
+assembly, friction cone, grasp matrix, QP construction, E_fc wrapper, pk forward kinematics and transforms.
+"""
+import importlib
+import os
+import sys
+import types
+
+import torch
+
+REF = os.environ.get("GRASPQP_REFERENCE", "/root/reference")
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def available():
+    return os.path.isdir(os.path.join(REF, "graspqp", "src", "graspqp"))
+
+
+def _pkg(name, path):
+    m = types.ModuleType(name)
+    m.__path__ = [path]
+    m.__package__ = name
+    sys.modules[name] = m
+    return m
+
+
+_loaded = {}
+
+
+def load():
+    """-> dict of reference modules (optimizer, energy, span, registry, qp_solver, transforms, pk_chain, pk_frame, pk_tf)"""
+    if _loaded:
+        return _loaded
+    if not available():
+        raise RuntimeError("reference not present at " + REF)
+    from oracle import hand as ohand
+    from oracle import qp as oqp
+
+    # ---- stubs of the un-vendored third-party modules ----
+    class QPFunction:  # qpth.qp.QPFunction(verbose, maxIter, eps)(Q, p, G, h, A, b)
+        def __init__(self, eps=1e-12, verbose=0, notImprovedLim=3, maxIter=20, **kw):
+            self.eps, self.maxIter, self.notImprovedLim = eps, maxIter, notImprovedLim
+
+        def __call__(self, Q, p, G, h, A, b):
+            assert A.numel() == 0 and b.numel() == 0, "the hot path has no equality constraints"
+            assert (self.eps, self.maxIter) == (5e-2, 12), "oracle.qp is specialised to the reference's settings"
+            if G.ndim == 3:
+                G = G[0]
+            return oqp.QPFunction.apply(Q, p, G.to(Q.dtype), h)
+
+    qpth = types.ModuleType("qpth")
+    qpth.qp = types.ModuleType("qpth.qp")
+    qpth.qp.QPFunction = QPFunction
+    sys.modules.setdefault("qpth", qpth)
+    sys.modules.setdefault("qpth.qp", qpth.qp)
+    roma = types.ModuleType("roma")
+    roma.special_gramschmidt = ohand.special_gramschmidt
+    sys.modules.setdefault("roma", roma)
+
+    # ---- the reference's own packages, without their __init__ ----
+    g = os.path.join(REF, "graspqp", "src", "graspqp")
+    for name, path in [("graspqp", g), ("graspqp.core", g + "/core"), ("graspqp.metrics", g + "/metrics"),
+                       ("graspqp.metrics.ops", g + "/metrics/ops"), ("graspqp.metrics.solver", g + "/metrics/solver"),
+                       ("graspqp.utils", g + "/utils")]:
+        _pkg(name, path)
+    pk = os.path.join(REF, "thirdparty", "pytorch_kinematics", "pytorch_kinematics")
+    _pkg("pytorch_kinematics", pk)
+    imp = importlib.import_module
+    _loaded.update(
+        optimizer=imp("graspqp.core.optimizer"), energy=imp("graspqp.core.energy"),
+        span=imp("graspqp.metrics.ops.span"), registry=imp("graspqp.metrics.ops.registry"),
+        qp_solver=imp("graspqp.metrics.solver.qp_solver"), transforms=imp("graspqp.utils.transforms"),
+        pk_tf=imp("pytorch_kinematics.transforms"), pk_frame=imp("pytorch_kinematics.frame"),
+        pk_chain=imp("pytorch_kinematics.chain"))
+    return _loaded
+
+
+class _Noise:
+    """Replaces torch inside graspqp.core.optimizer: rand / randint return the injected draws (optimizer.py:252-257,
+    :311), everything else is the real torch."""
+
+    def __init__(self):
+        self.u_switch = self.idx_new = self.u_accept = self.mask_for_randint = None
+
+    def __getattr__(self, k):
+        return getattr(torch, k)
+
+    def rand(self, *shape, **kw):
+        if len(shape) == 2:
+            return self.u_switch.to(kw.get("dtype", torch.float))
+        return self.u_accept.to(kw.get("dtype", torch.float))
+
+    def randint(self, high, size, **kw):
+        # the reference draws exactly switch_mask.sum() values and scatters them in row-major mask order; the injected
+        # (B,n_c) table is read in that same order
+        assert self.idx_new.max() < high
+        return self.idx_new[self.mask_for_randint]
+
+
+def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_pose0, idx0, dtype=torch.float32,
+                   friction=0.2, max_limit=20.0, n_cone_vecs=4, svd_gain=0.1, **optim):
+    """The state scripts/fit.py holds between iterations, with the REFERENCE MalaStar / calculate_energy / metric."""
+    from oracle.hand import HandOracle
+    from oracle.pipeline import ObjectOracle, WEIGHTS
+    ref = load()
+    hand = HandOracle(pack, dtype)
+    obj = ObjectOracle(face_verts_list, surface_points_list, batch_each, dtype)
+    obj.device = torch.device("cpu")
+    obj.object_scale_tensor = torch.ones(len(face_verts_list), batch_each, dtype=dtype)
+    hand.set_parameters(torch.as_tensor(hand_pose0, dtype=dtype).clone().requires_grad_(True),
+                        torch.as_tensor(idx0).long())
+    cfg = dict(switch_possibility=0.4, starting_temperature=18.0, temperature_decay=0.95, annealing_period=30,
+               step_size=0.005, stepsize_period=50, mu=0.98)  # scripts/fit.py argparse defaults
+    cfg.update(optim)
+    opt = ref["optimizer"].MalaStar(hand, device="cpu", batch_size=batch_each, **cfg)
+    F = ref["registry"].GraspSpanMetricFactory
+    energy_fnc = F.create(F.MetricType.GRASPQP, solver_kwargs={"friction": friction, "max_limit": max_limit,
+                                                                "n_cone_vecs": n_cone_vecs})
+    st = types.SimpleNamespace(hand=hand, obj=obj, opt=opt, energy_fnc=energy_fnc, weights=dict(WEIGHTS), B=batch_each,
+                               svd_gain=svd_gain, ref=ref)
+
+    def energies():
+        losses = ref["energy"].calculate_energy(hand, obj, energy_fnc=energy_fnc,
+                                                energy_names=[k for k, v in st.weights.items() if v > 0],
+                                                method="gendexgrasp", svd_gain=svd_gain)
+        e = 0
+        for k, v in losses.items():
+            e = e + st.weights[k] * v
+        return losses, e
+
+    st.energies = energies
+    st.losses, st.energy = energies()          # fit.py:381-396
+    st.energy.sum().backward()
+    st.first_grad = hand.hand_pose.grad.clone()
+    opt.zero_grad()
+    return st
+
+
+def fit_iterate(st, u_switch, idx_new, u_accept):
+    """One pass of scripts/fit.py:399-458 with the reference optimizer and energy code and injected noise."""
+    ref, opt, hand = st.ref, st.opt, st.hand
+    noise = _Noise()
+    noise.u_switch, noise.idx_new, noise.u_accept = u_switch, idx_new, u_accept
+    noise.mask_for_randint = u_switch < opt.switch_possibility
+    mod = ref["optimizer"]
+    real = mod.torch
+    mod.torch = noise
+    try:
+        s = opt.try_step()
+        Eb = st.energy.view(-1, st.B)
+        z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        opt.zero_grad()
+        new_losses, new_energy = st.energies()
+        new_energy.sum().backward()
+        out = dict(s=s.clone(), z=z.detach().clone(), proposal=hand.hand_pose.detach().clone(),
+                   idx_prop=hand.contact_point_indices.clone(), new_energy=new_energy.detach().clone(),
+                   new_grad=hand.hand_pose.grad.clone(),
+                   new_losses={k: v.detach().clone() for k, v in new_losses.items()})
+        with torch.no_grad():
+            accept, t = opt.accept_step(st.energy, new_energy, None, z, 1.0)
+            st.energy[accept] = new_energy[accept]
+            for k, v in new_losses.items():
+                st.losses[k][accept] = v[accept]
+        out.update(accept=accept.clone(), temperature=t.clone(), energy=st.energy.detach().clone(),
+                   pose=hand.hand_pose.detach().clone(), idx=hand.contact_point_indices.clone())
+    finally:
+        mod.torch = real
+    return out
+
+
+def pk_chain_from_pack(pack, dtype=torch.float32):
+    """Rebuilds the reference's pk.Chain from the frame tables of a hand pack (the tables were extracted from the URDF
+    by tools/build_hand_pack.py; pk's own URDF loader needs lxml + transformations, absent here)."""
+    ref = load()
+    frame, tf = ref["pk_frame"], ref["pk_tf"]
+    n = len(pack["frame_parent"])
+    jt = {0: "fixed", 1: "revolute", 2: "prismatic"}
+
+    def t3d(m34):
+        m = torch.eye(4, dtype=dtype)
+        m[:3] = torch.as_tensor(m34, dtype=dtype)
+        return tf.Transform3d(matrix=m.unsqueeze(0), dtype=dtype)
+
+    frames = []
+    for f in range(n):
+        j = frame.Joint(name=f"j{f}", offset=t3d(pack["frame_joff"][f]), joint_type=jt[int(pack["frame_jtype"][f])],
+                        axis=[float(v) for v in pack["frame_axis"][f]])
+        l = frame.Link(name=f"l{f}", offset=t3d(pack["frame_loff"][f]))
+        frames.append(frame.Frame(name=f"f{f}", link=l, joint=j, children=[]))
+    for f in range(n):
+        p = int(pack["frame_parent"][f])
+        if p >= 0:
+            frames[p].children.append(frames[f])
+    roots = [f for f in range(n) if int(pack["frame_parent"][f]) < 0]
+    assert len(roots) == 1
+    return ref["pk_chain"].Chain(frames[roots[0]], dtype=dtype), frames

@@ -1,0 +1,113 @@
+"""CPU suite against the committed golden vectors (outputs of the reference's own code, tests/golden/make_golden.py):
+the oracle restatements, and the kernel sources run by the host emulator."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import golden_cases as gc
+from graspqp_b200 import engine, hand_pack
+from oracle import qp as oqp
+from oracle import sdf as osdf
+from oracle.hand import HandOracle
+from oracle.pipeline import FitLoopOracle
+
+
+def test_oracle_sdf_port_matches_reference_kernel(oracle_built):
+    g = gc.load("sdf_ref")
+    for key in ("cube", "sphere_42"):
+        got = osdf.compute_sdf_port(g[key + "_points"], g[key + "_face_verts"])
+        for a, name in zip(got, ("_dist2", "_sign", "_normals", "_clst")):
+            np.testing.assert_array_equal(a, g[key + name], err_msg=key + name)
+        # thirdparty/TorchSDF/tests/normal.py:36-39: normal * 2 sqrt(d2) == d(d2)/dp = 2 (p - c)
+        nr, d2, cl = g[key + "_normals"], g[key + "_dist2"], g[key + "_clst"]
+        np.testing.assert_allclose(nr * 2 * np.sqrt(d2)[:, None], 2 * (g[key + "_points"] - cl), atol=5e-7)
+
+
+def test_oracle_fk_matches_pytorch_kinematics():
+    g = gc.load("fk_ref")
+    pack = hand_pack.load_pack("allegro")
+    o = HandOracle(pack, torch.float32)
+    st = o.fk(torch.tensor(g["theta"]))
+    got = np.stack([st[int(f)].numpy() for f in pack["mesh_frame"]], 1)
+    np.testing.assert_allclose(got, g["link_matrices"], atol=1e-6)
+
+
+def test_oracle_solver_known_answer():
+    """graspqp/tests/metrics/test_solver.py:5-26 (residual ~ 0, atol 1e-4) and the converged optimum from scipy
+    (the reference's ScipyLsqSolver, metrics/solver/scipy_solver.py:64-125)."""
+    from scipy.optimize import lsq_linear
+    g = gc.load("solver_kat")
+    A, b = torch.tensor(g["A"]), torch.tensor(g["b"])
+    value, x = oqp.lsq_solve(A, b, -10.0, 1e3)
+    assert torch.allclose(value, torch.zeros_like(value), atol=1e-4)
+    np.testing.assert_allclose(value.numpy(), g["value"], atol=1e-6)
+    r = lsq_linear(g["A"][0].astype(np.float64), g["b"][0].astype(np.float64), bounds=(-10.0, 1e3))
+    assert 0.5 * np.sum((g["A"][0] @ r.x - g["b"][0]) ** 2) < 1e-4
+
+
+def test_oracle_metric_matches_reference_metric():
+    g = gc.load("metric_ref")
+    cone = oqp.friction_cone(torch.tensor(g["nc12_nrm"]))
+    np.testing.assert_allclose(cone.numpy(), g["nc12_cone"], rtol=1e-6, atol=1e-7)
+    for n_c in (12, 16, 4):
+        t = lambda k: torch.tensor(g[f"nc{n_c}_{k}"], dtype=torch.float64)
+        cp = t("cpts").requires_grad_(True)
+        E, lam, _ = oqp.graspqp_energy(cp, t("nrm"), t("cog"))
+        E.sum().backward()
+        np.testing.assert_allclose(E.detach().numpy(), g[f"nc{n_c}_f64_E_fc"], rtol=1e-9)
+        np.testing.assert_allclose(lam.detach().numpy(), g[f"nc{n_c}_f64_x"], rtol=1e-8, atol=1e-10)
+        np.testing.assert_allclose(cp.grad.numpy(), g[f"nc{n_c}_f64_grad_cpts"], rtol=1e-7, atol=1e-9)
+
+
+def test_oracle_loop_matches_reference_loop():
+    """oracle.pipeline (our restatement of optimizer.py / energy.py / fit.py glue) vs the reference's own MalaStar +
+    calculate_energy on the same injected noise, both fp32 on the CPU."""
+    g = gc.load("fit_ref_f32")
+    pack = hand_pack.load_pack("allegro")
+    B = len(g["pose0"])
+    orc = FitLoopOracle(pack, [g["face_verts"]], [g["surface"]], B, g["pose0"], g["idx0"].astype(np.int64), dtype=torch.float32)
+    np.testing.assert_allclose(orc.energy.numpy(), g["energy0"], rtol=1e-5)
+    np.testing.assert_allclose(orc.first_grad.numpy(), g["first_grad"], rtol=1e-3, atol=1e-3 * np.abs(g["first_grad"]).max())
+    for t in range(4):
+        out = orc.iterate(torch.tensor(g[f"t{t}_u_switch"]), torch.tensor(g[f"t{t}_idx_rand"]).long(),
+                          torch.tensor(g[f"t{t}_u_accept"]))
+        np.testing.assert_array_equal(out["idx_prop"].numpy(), g[f"t{t}_idx_prop"])
+        np.testing.assert_allclose(out["proposal"].numpy(), g[f"t{t}_proposal"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(out["new_energy"].numpy(), g[f"t{t}_new_energy"], rtol=1e-5)
+        np.testing.assert_array_equal(out["accept"].numpy(), g[f"t{t}_accept"])
+        np.testing.assert_allclose(out["temperature"].numpy(), g[f"t{t}_temperature"], rtol=1e-6)
+        np.testing.assert_allclose(orc.energy.numpy(), g[f"t{t}_energy"], rtol=1e-5)
+
+
+def test_emulated_kernels_sdf(emu):
+    gc.check_sdf(emu, engine.NumpyBackend())
+
+
+def test_emulated_kernels_fk(emu):
+    gc.check_fk(emu, engine.NumpyBackend())
+
+
+def test_emulated_kernels_metric(emu):
+    gc.check_metric(emu, engine.NumpyBackend())
+
+
+def test_emulated_kernels_fit_iteration(emu):
+    assert gc.check_fit(emu, engine.NumpyBackend(), T=2) > 0
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference is only present in the build container")
+def test_golden_vectors_are_reproducible(tmp_path, oracle_built):
+    """Re-run the reference through the harness and compare with the committed fixtures (build container only)."""
+    import sys
+    sys.path.insert(0, gc.GOLDEN)
+    import ref_harness as rh
+    g = gc.load("fit_ref_f32")
+    pack = hand_pack.load_pack("allegro")
+    B = len(g["pose0"])
+    st = rh.make_fit_state(pack, [g["face_verts"]], [g["surface"]], B, g["pose0"], g["idx0"].astype(np.int64))
+    np.testing.assert_allclose(st.energy.detach().numpy(), g["energy0"], rtol=1e-6)
+    o = rh.fit_iterate(st, torch.tensor(g["t0_u_switch"]), torch.tensor(g["t0_idx_rand"]).long(), torch.tensor(g["t0_u_accept"]))
+    np.testing.assert_allclose(o["new_energy"].numpy(), g["t0_new_energy"], rtol=1e-6)
+    np.testing.assert_array_equal(o["accept"].numpy(), g["t0_accept"])

@@ -71,3 +71,24 @@ def test_philox_run_is_deterministic(gpu):
     np.testing.assert_array_equal(runs[0][2], runs[1][2])
     np.testing.assert_allclose(runs[0][0], runs[1][0], rtol=1e-4)
     assert np.isfinite(runs[0][0]).all()
+
+
+# ---- against the committed golden vectors: outputs of the reference's own code (tests/golden/make_golden.py) ----
+def test_golden_sdf(gpu):
+    import golden_cases as gc
+    gc.check_sdf(*gpu)
+
+
+def test_golden_fk(gpu):
+    import golden_cases as gc
+    gc.check_fk(*gpu)
+
+
+def test_golden_metric(gpu):
+    import golden_cases as gc
+    gc.check_metric(*gpu)
+
+
+def test_golden_fit_iterations(gpu):
+    import golden_cases as gc
+    assert gc.check_fit(*gpu, T=4) > 0
