@@ -37,6 +37,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=None, help="override candidates per object")
     ap.add_argument("--objects", type=int, default=None, help="override objects per GPU")
     ap.add_argument("--no-qp-batch-stop", action="store_true")
+    ap.add_argument("--global-rms", action="store_true",
+                    help="N>1: all-reduce the batch-wide MALA*/qpth statistics every iteration (shard.GlobalStats); the "
+                         "default is the reference's practice of one independent process per object group")
     ap.add_argument("--cpu-sample-batch", type=int, default=16)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -132,7 +135,7 @@ def run_reference(args):
 def run_b200(args):
     import torch
     import torch.distributed as dist
-    from graspqp_b200 import _lib, engine, workload
+    from graspqp_b200 import _lib, engine, shard, workload
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -146,7 +149,8 @@ def run_b200(args):
     Bt = B * O
     t_setup = time.perf_counter()
     eng = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], B, w["pose"], w["idx"],
-                           qp_batch_stop=not args.no_qp_batch_stop, seed=1 + rank)
+                           qp_batch_stop=not args.no_qp_batch_stop, seed=1 + rank,
+                           collectives=shard.GlobalStats() if (world > 1 and args.global_rms) else None)
     torch.cuda.synchronize()
     t_setup = time.perf_counter() - t_setup
     K, W = max(1, args.steps), max(3, args.warmup)
@@ -229,8 +233,8 @@ def run_b200(args):
     t = torch.tensor([ms_total, ms_e2e, ms_pen], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        gathered = [torch.empty_like(eng.energy) for _ in range(world)]
-        dist.all_gather(gathered, eng.energy)  # final energies of all ranks (the only data exchange of the path)
+        # final grasps of all ranks in global object order (the only data exchange of the path by default)
+        shard.gather_results(eng.pose, eng.energy, eng.idx, O * world, B, rank, world)
     ms_total, ms_e2e, ms_pen = [float(v) for v in t.tolist()]
     final_energy = float(eng.energy.float().mean().item())
     if rank == 0:
@@ -251,7 +255,10 @@ def run_b200(args):
             "config": {"workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
                                    f"{w['faces_per_mesh']} tris), batch {B}/object, n_contact {n_c}, 2500 surface samples",
                        "candidates_per_gpu": Bt, "l2": "flushed between timed steps (256 MiB write)",
-                       "qp_batch_stop": eng.qp_batch_stop, "noise": "philox on device (value) / injected from host (e2e)",
+                       "qp_batch_stop": eng.qp_batch_stop,
+                       "collectives": ("global rms + qp exit words all-reduced per step" if eng.collectives else
+                                       "none on the data path; final all-gather of grasps") if world > 1 else "n/a",
+                       "noise": "philox on device (value) / injected from host (e2e)",
                        "setup_s": round(t_setup, 2), "final_mean_energy": final_energy},
             "e2e": {"value": Bt * world * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h},

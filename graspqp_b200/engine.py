@@ -90,7 +90,7 @@ class FitEngine:
     def __init__(self, cdll, backend, pack, face_verts_list, surface_points, batch_each, hand_pose, contact_idx,
                  weights=None, friction=0.2, max_limit=20.0, svd_gain=0.1, torque_weight=5.0, switch_possibility=0.4,
                  starting_temperature=18.0, temperature_decay=0.95, annealing_period=30, step_size=0.005,
-                 stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1):
+                 stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1, collectives=None):
         self.lib, self.be = cdll, backend
         self.pack = pack
         self.n_obj = len(face_verts_list)
@@ -104,6 +104,7 @@ class FitEngine:
         self.seed = int(seed)
         self.iteration = 0
         self.qp_batch_stop = bool(qp_batch_stop)
+        self.collectives = collectives  # shard.GlobalStats or None (no data-path collective: the default)
         be, Bt, D, n_c, L = backend, self.Bt, self.D, self.n_c, self.L
         surface_points = np.ascontiguousarray(surface_points, np.float32)
         assert surface_points.shape[0] == self.n_obj and surface_points.shape[2] == 3
@@ -184,6 +185,10 @@ class FitEngine:
         # finish pass (value, svd term, energies, analytic backward) from every candidate's best iterate as of the exit
         self._ck(lib.gqp_fc_solve(ctypes.byref(self.fc), p(self.cpts), p(self.obj_nrm), p(self.cog), O, B, n_c,
                                   p(self.qp_ws), st))
+        if self.collectives is not None and self.qp_batch_stop:  # qpth's exit test over the candidates of ALL ranks
+            hdr = self.qp_ws.view(np.int32)[:128] if isinstance(self.qp_ws, np.ndarray) else \
+                self.qp_ws.view(self.be.torch.int32)[:128]
+            self.collectives.reduce_qp_header(hdr)
         self._ck(lib.gqp_fc_finish(ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist), p(self.obj_nrm),
                                    p(self.obj_dgrad), p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop),
                                    row("E_fc"), row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm),
@@ -220,6 +225,8 @@ class FitEngine:
         self.iteration += 1
         self._ck(lib.gqp_mala_stats(p(self.grad), p(self.energy), self.n_obj, self.batch_each, self.D,
                                     self.mala.clip_grad, p(self.grad2_mean), p(self.z), p(self.stats_scratch), st))
+        if self.collectives is not None:  # (g**2).mean(0) over the rows of ALL ranks (optimizer.py:231)
+            self.collectives.reduce_rms(self.grad2_mean, self.Bt)
         self._ck(lib.gqp_mala_propose(ctypes.byref(self.mala), p(self.pose), p(self.grad), p(self.grad2_mean),
                                       p(self.ema), p(self.step_count), p(self.idx), self.Bt, self.D, self.n_c,
                                       self.n_cand, p(u_switch), p(idx_rand), self.seed, self.iteration,
