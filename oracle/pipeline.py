@@ -130,6 +130,15 @@ class FitLoopOracle:
         self.energy = self.energy.detach()
         self.losses = {k: v.detach().clone() for k, v in self.losses.items()}
 
+    def load_state(self, pose, idx, grad, energy, ema, step):
+        """Teacher forcing: take over the state between two iterations from another run of the same loop."""
+        dt = self.hand.dtype
+        self.hand.set_parameters(torch.as_tensor(pose, dtype=dt).clone().requires_grad_(True), torch.as_tensor(idx).long())
+        self.hand.hand_pose.grad = torch.as_tensor(grad, dtype=dt).clone()
+        self.energy = torch.as_tensor(energy, dtype=dt).clone()
+        self.opt.ema = torch.as_tensor(ema, dtype=dt).clone()
+        self.opt.step = torch.as_tensor(step).long().clone()
+
     def iterate(self, u_switch, idx_new, u_accept):
         s = self.opt.try_step(u_switch, idx_new)
         Eb = self.energy.view(-1, self.B)
@@ -137,7 +146,7 @@ class FitLoopOracle:
         new_losses, info = calculate_energy(self.hand, self.obj)
         new_energy = total_energy(new_losses)
         new_energy.sum().backward()
-        out = dict(new_energy=new_energy.detach().clone(), new_grad=self.hand.hand_pose.grad.clone(),
+        out = dict(energy_before=self.energy.detach().clone(), new_energy=new_energy.detach().clone(), new_grad=self.hand.hand_pose.grad.clone(),
                    new_losses={k: v.detach().clone() for k, v in new_losses.items()}, z=z, s=s,
                    proposal=self.hand.hand_pose.detach().clone(), idx_prop=self.hand.contact_point_indices.clone())
         with torch.no_grad():

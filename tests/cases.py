@@ -126,3 +126,63 @@ def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=Fa
         n_acc += int(out["accept"].sum())
     eng.close()
     return n_acc
+
+
+def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3):
+    """A T-step fixed-noise trajectory of the engine, every step checked against the fp64 oracle started from the
+    engine's own state (teacher forcing: two chaotic trajectories cannot be compared open-loop for 500 steps).
+    Stated tolerances: proposal 1e-5 abs, new energy 2e-4 relative, contact indices bit-exact, accept decisions
+    bit-exact except where the uniform draw lies within `tie` of the acceptance probability (must stay below 1 %).
+    -> (accepted, borderline)"""
+    pack = hand_pack.load_pack("allegro")
+    v, f = synth.make_mesh("hull", 400, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.75
+    eng = engine.FitEngine(lib, be, pack, [fv], sp[None], B, pose, idx.astype(np.int32))
+    orc = FitLoopOracle(pack, [fv], [sp], B, pose, idx, dtype=torch.float64)
+    H = be.to_host
+    rng = np.random.default_rng(seed)
+    n_acc = n_tie = 0
+    worst = 0.0
+    outliers = []
+    for t in range(T):
+        orc.load_state(H(eng.pose), H(eng.idx), H(eng.grad), H(eng.energy), H(eng.ema), H(eng.step_count))
+        us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, len(pack["cand"]), (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+        eng.step(be.from_host(us), be.from_host(ir), be.from_host(ua))
+        out = orc.iterate(torch.tensor(us, dtype=torch.float64), torch.tensor(ir).long(), torch.tensor(ua, dtype=torch.float64))
+        np.testing.assert_array_equal(H(eng.idx_new), out["idx_prop"].numpy(), err_msg=f"step {t}")
+        np.testing.assert_allclose(H(eng.pose_new), out["proposal"].numpy(), rtol=1e-5, atol=1e-5, err_msg=f"step {t}")
+        e_new, want = H(eng.new_energy), out["new_energy"].numpy()
+        rel = np.abs(e_new - want) / np.abs(want)
+        for b in np.nonzero(rel > 2e-4)[0]:  # discontinuity events, see the assertion below
+            terms = {k: float(H(eng.losses_new)[i][b] - out["new_losses"][k][b]) for i, k in enumerate(engine.TERMS)}
+            E_in, _, _ = oqp.graspqp_energy(torch.tensor(H(eng.cpts), dtype=torch.float64),
+                                            torch.tensor(H(eng.obj_nrm), dtype=torch.float64), orc.obj.cog)
+            e_fc = H(eng.losses_new)[engine.TERMS.index("E_fc")]
+            outliers.append((t, int(b), float(rel[b]), terms, abs(float(e_fc[b]) - E_in[b].item()) / abs(E_in[b].item())))
+        worst = max(worst, float(np.max(np.where(rel > 2e-4, 0.0, rel))))
+        p_acc = np.exp(np.minimum((orc_energy_before(out) - want) / out["temperature"].numpy(), 0.0))
+        got, exp = H(eng.accept).astype(bool), out["accept"].numpy()
+        border = (np.abs(ua - p_acc) < tie) | (rel > 2e-4)
+        assert np.array_equal(got[~border], exp[~border]), f"step {t}: accept mismatch away from a tie"
+        n_tie += int((got != exp).sum())
+        n_acc += int(got.sum())
+    eng.close()
+    assert n_tie <= max(1, T * B // 100), f"{n_tie} borderline accept mismatches"
+    # Conditioning events of the reference's own formulation (found with tools/debug_traj.py): the object normal at a
+    # contact is unit(p - c) * sign (object_model.py:246) and is not Lipschitz in p near nearest-face ties and on the
+    # surface itself; the contact points of the two runs differ by one fp32 ulp (fp32 FK here, fp64 FK in the oracle),
+    # which occasionally rotates ONE contact normal by 1e-4..1e-2 rad, and E_fc sees that.  Such steps are re-checked
+    # with the oracle's QP evaluated on the engine's own fp32 contacts/normals (must agree to 1e-5), and are allowed for
+    # at most 0.2 % of candidate-steps, each below 5e-3 relative.  Everything else is within 2e-4.
+    for o in outliers:
+        print("trajectory outlier (step, candidate, rel err, per-term diff, E_fc rel err on the engine's inputs):", o)
+    assert len(outliers) <= max(1, T * B // 500), outliers
+    assert all(o[2] < 5e-3 and o[4] < 1e-5 and abs(o[3]["E_pen"]) < 1e-5 for o in outliers), outliers
+    return n_acc, n_tie, worst
+
+
+def orc_energy_before(out):
+    return out["energy_before"].numpy()

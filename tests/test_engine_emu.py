@@ -50,3 +50,10 @@ def test_iteration_vs_oracle(emu):
         np.testing.assert_allclose(eng.energy, orc.energy.numpy(), rtol=2e-4)
         np.testing.assert_allclose(eng.pose, orc.hand.hand_pose.detach().numpy(), rtol=1e-4, atol=1e-5)
     eng.close()
+
+
+def test_short_trajectory_teacher_forced(emu):
+    """the 500-step GPU trajectory check (tests/cases.py:check_trajectory) at emulator size"""
+    import cases
+    n_acc, n_tie, worst = cases.check_trajectory(emu, engine.NumpyBackend(), T=3, B=3, n_pts=48)
+    assert n_tie == 0 and worst < 2e-4

@@ -92,3 +92,9 @@ def test_golden_metric(gpu):
 def test_golden_fit_iterations(gpu):
     import golden_cases as gc
     assert gc.check_fit(*gpu, T=4) > 0
+
+
+def test_trajectory_500_steps_teacher_forced(gpu):
+    n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=500)
+    print(f"500-step trajectory: {n_acc} accepted, {n_tie} borderline accept mismatches, worst energy error {worst:.2e}")
+    assert n_acc > 500
