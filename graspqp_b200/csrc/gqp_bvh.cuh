@@ -92,7 +92,7 @@ struct BvhTree {
     float extent;
 };
 template <bool EXACT, class Fetch, class Emit>
-__device__ __forceinline__ void bvh_query_stream(int q_begin, int q_end, Fetch fetch, Emit emit) {
+__device__ __forceinline__ void bvh_query_stream(int q_begin, int q_end, int max_steps, Fetch fetch, Emit emit) {
     const int lane = threadIdx.x & 31;
     int stack[GQP_BVH_STACK];
     int sp = 0, node = -1, qi = -1;
@@ -124,7 +124,7 @@ __device__ __forceinline__ void bvh_query_stream(int q_begin, int q_end, Fetch f
         int leaf_first = 0, leaf_count = 0;
         float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
         bool have_box = false;
-        while (node >= 0) {
+        for (int steps = 0; node >= 0 && steps < max_steps; ++steps) {
             if (!have_box) {
                 const float4 *n4 = reinterpret_cast<const float4 *>(tr.nodes + node);
                 lo = n4[0];

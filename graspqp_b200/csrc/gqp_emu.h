@@ -100,6 +100,11 @@ inline T __shfl_down_sync(unsigned, T v, int d) {
     int l = (threadIdx.x & 31) + d;
     return gqp_emu::shfl_any(v, l > 31 ? (int)(threadIdx.x & 31) : l);
 }
+template <class T>
+inline T __shfl_up_sync(unsigned, T v, int d) {
+    int l = (int)(threadIdx.x & 31) - d;
+    return gqp_emu::shfl_any(v, l < 0 ? (int)(threadIdx.x & 31) : l);
+}
 inline unsigned __ballot_sync(unsigned, int pred) {
     unsigned r = 0;
     for (int i = 0; i < 32; ++i) r |= (gqp_emu::shfl_any(pred ? 1 : 0, i) ? 1u : 0u) << i;

@@ -25,19 +25,28 @@ static int mesh_qpw() {
     }
     return v;
 }
+static int mesh_steps() {
+    static int v = 0;
+    if (!v) {
+        const char *e = getenv("GQP_MESH_STEPS");
+        v = e ? atoi(e) : 4;
+        if (v < 1) v = 1;
+    }
+    return v;
+}
 #define MESH_WARPS 4
 
 __global__ void __launch_bounds__(MESH_WARPS * 32)
 mesh_sdf_kernel(const GqpBvhNode *__restrict__ nodes, const float *__restrict__ tris,
                 const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
-                const float *__restrict__ points, int P, int qpw,
+                const float *__restrict__ points, int P, int qpw, int max_steps,
                 float *__restrict__ dist2, int32_t *__restrict__ sign, float *__restrict__ normals,
                 float *__restrict__ clst, int32_t *__restrict__ face_out) {
     const long long w = (long long)blockIdx.x * MESH_WARPS + (threadIdx.x >> 5);
     const int q0 = (int)min((long long)P, w * qpw);
     const int q1 = (int)min((long long)P, (w + 1) * qpw);
     bvh_query_stream<true>(
-        q0, q1,
+        q0, q1, max_steps,
         [&](int i, V3 &p, BvhTree &tr) {
             p = ld3(points + 3 * (size_t)i);
             tr = BvhTree{nodes, tris, face_id, pre, extent};
@@ -58,14 +67,14 @@ mesh_sdf_kernel(const GqpBvhNode *__restrict__ nodes, const float *__restrict__ 
 __global__ void __launch_bounds__(MESH_WARPS * 32)
 object_distance_kernel(const GqpBvhNode *const *__restrict__ nodes, const float *const *__restrict__ tris,
                        const int32_t *const *__restrict__ face_id, const float *const *__restrict__ pre,
-                       const float *__restrict__ extent, int per_obj, int n, int qpw,
+                       const float *__restrict__ extent, int per_obj, int n, int qpw, int max_steps,
                        const float *__restrict__ x, float scale, float *__restrict__ distance, float *__restrict__ normals,
                        float *__restrict__ clst, int32_t *__restrict__ sign) {
     const long long w = (long long)blockIdx.x * MESH_WARPS + (threadIdx.x >> 5);
     const int q0 = (int)min((long long)n, w * qpw);
     const int q1 = (int)min((long long)n, (w + 1) * qpw);
     bvh_query_stream<true>(
-        q0, q1,
+        q0, q1, max_steps,
         [&](int i, V3 &p, BvhTree &tr) {
             const int o = i / per_obj;
             p = ld3(x + 3 * (size_t)i);
@@ -135,7 +144,7 @@ extern "C" int gqp_mesh_sdf_forward(const GqpMesh *m, const float *points, int P
     const int qpw = mesh_qpw();
     GQP_LAUNCH(mesh_sdf_kernel, (P + MESH_WARPS * qpw - 1) / (MESH_WARPS * qpw),
                MESH_WARPS * 32, 0, (cudaStream_t)stream, m->d_nodes, m->d_tris, m->d_face_id,
-               m->d_pre, m->extent, points, P, qpw, dist2, sign, normals, clst, face);
+               m->d_pre, m->extent, points, P, qpw, mesh_steps(), dist2, sign, normals, clst, face);
     GQP_CHECK_LAUNCH("gqp_mesh_sdf_forward");
     return GQP_OK;
 }
@@ -190,7 +199,7 @@ extern "C" int gqp_object_distance_forward(const GqpObjSet *s, int batch_each, i
     const int qpw = mesh_qpw();
     GQP_LAUNCH(object_distance_kernel, (int)((n + MESH_WARPS * qpw - 1) / (MESH_WARPS * qpw)),
                MESH_WARPS * 32, 0, (cudaStream_t)stream, s->d_nodes, s->d_tris,
-               s->d_face_id, s->d_pre, s->d_extent, batch_each * n_pts, (int)n, qpw, x, scale, distance, normals, clst, sign);
+               s->d_face_id, s->d_pre, s->d_extent, batch_each * n_pts, (int)n, qpw, mesh_steps(), x, scale, distance, normals, clst, sign);
     GQP_CHECK_LAUNCH("gqp_object_distance_forward");
     return GQP_OK;
 }

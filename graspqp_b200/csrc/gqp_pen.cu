@@ -65,6 +65,8 @@ __device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *gri
 }
 
 #define PEN_CB 8  // candidates per warp-task: amortises the sample loads and index arithmetic
+// per warp, culled path: 8x32 need-masks (reused as energies), 32 result slots of 16 B, 32 pair descriptors of 2 B
+#define PEN_BATCH_BYTES (PEN_CB * 32 * 4 + 32 * 16 + 32 * 2)
 
 // Bounding spheres of every 32-sample chunk of a point row, and of the whole row (slot n_chunks).  One block per row.
 __global__ void __launch_bounds__(256)
@@ -160,6 +162,10 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
     const int warps_per_block = blockDim.x / 32;
     // per-warp staging of the candidate's link transforms (L x 12 floats), behind the blob
     float *sW = reinterpret_cast<float *>(sm + blob_bytes) + (size_t)(threadIdx.x >> 5) * L * 12;
+    unsigned char *wb = sm + blob_bytes + (size_t)(blockDim.x / 32) * L * 48 + (size_t)(threadIdx.x >> 5) * PEN_BATCH_BYTES;
+    uint32_t *sNeed = reinterpret_cast<uint32_t *>(wb);
+    float *sR = reinterpret_cast<float *>(wb + PEN_CB * 32 * 4);
+    uint16_t *sQ = reinterpret_cast<uint16_t *>(wb + PEN_CB * 32 * 4 + 32 * 16);
     const int n_chunks = (n_pts + 31) / 32;
     const int n_cblk = (cands_per_row + PEN_CB - 1) / PEN_CB;
     const int n_tasks = n_rows * n_chunks * n_cblk;
@@ -174,6 +180,153 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
         const V3 cen = V3{sph[0], sph[1], sph[2]};
         const float rad = sph[3];
         const int b_end = row * cands_per_row + min(cands_per_row, (cb + 1) * PEN_CB);
+        if (CULL) {
+            // ---- culled path (E_pen and its gradient only) ----------------------------------------------------------
+            // After the box / sphere / outside-grid tests only a couple of samples per chunk still need an exact search
+            // for any one (candidate, link): searching link by link left ~2 of 32 lanes busy.  So: phase 1 only
+            // COLLECTS, per lane, the links that survive for each of the task's 8 candidates; phase 2 compacts all
+            // surviving (candidate, sample, link) pairs of the warp and every lane runs one search per round.
+            const int b0 = row * cands_per_row + cb * PEN_CB, ncb = b_end - b0;
+            int c_total = 0;
+            for (int j = 0; j < ncb; ++j) {
+                const int b = b0 + j;
+                uint32_t need = 0;
+                const uint32_t mask = masks[b];
+                if (mask != 0) {
+                    const float *Wb = link_tf + (size_t)b * L * 12;
+                    bool keep = false;
+                    if ((mask >> lane) & 1u) {  // lane l: stage link l's transform, chunk sphere vs link box
+                        T34 W = t34_load(Wb + lane * 12);
+#pragma unroll
+                        for (int i = 0; i < 12; ++i) sW[lane * 12 + i] = W.m[i];
+                        const PenLink &K = links[lane];
+                        keep = true;
+                        if (K.grid >= 0) {
+                            V3 q = t34_inv_point(W, cen);
+                            if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad ||
+                                q.x > K.hi[0] + rad || q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
+                                keep = false;
+                        }
+                    }
+                    unsigned todo = __ballot_sync(GQP_FULL, keep);
+                    __syncwarp();
+                    while (todo) {
+                        const int l = __ffs((int)todo) - 1;
+                        todo &= todo - 1;
+                        T34 W;
+#pragma unroll
+                        for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
+                        if (!pen_outside(links[l], grids, bits, t34_inv_point(W, p))) need |= 1u << l;
+                    }
+                    __syncwarp();  // sW is rewritten for the next candidate
+                }
+                if (!valid) need = 0;  // padding lanes of the last chunk
+                sNeed[j * 32 + lane] = need;
+                c_total += __popc(need);
+            }
+            int incl = c_total;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int t = __shfl_up_sync(GQP_FULL, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const int total = __shfl_sync(GQP_FULL, incl, 31);
+            if (total == 0) continue;
+            // a lane's pairs are numbered [next, endi) in (candidate, link) order; (cj, cm) walks them
+            int next = incl - c_total;
+            const int endi = incl;
+            int cj = 0, fj = -1, best_l = -1;
+            uint32_t cm = sNeed[lane];
+            float best_d = 0.f;
+            V3 best_g = V3{0, 0, 0};
+            // a candidate of this lane is complete: energy.py:60-61 relu, gradient of the penetrating sample
+            auto finalize = [&]() {
+                if (fj < 0) return;
+                const bool pen = best_d > 0.f;
+                sNeed[fj * 32 + lane] = pen ? (uint32_t)__float_as_int(best_d) : 0u;  // the slot now holds the energy
+                if (pen && grad_link_tf) {
+                    const size_t wl = ((size_t)(b0 + fj) * L + best_l) * 12;
+                    const float *W = link_tf + wl;
+                    float *G = grad_link_tf + wl;
+                    V3 g = best_g * w_pen;
+                    float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {g.x, g.y, g.z};
+#pragma unroll
+                    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) atomicAdd(G + 4 * r + i, pt[r] * gv[i]);
+                        atomicAdd(G + 4 * r + 3, -(W[4 * r] * gv[0] + W[4 * r + 1] * gv[1] + W[4 * r + 2] * gv[2]));
+                    }
+                }
+            };
+            for (int base = 0; base < total; base += 32) {
+                {   // owners publish their pairs of this window: (owner lane, candidate, link)
+                    int pj = cj, pn = next;
+                    uint32_t pm = cm;
+                    while (pn < endi && pn < base + 32) {
+                        while (pm == 0) pm = sNeed[++pj * 32 + lane];
+                        const int l = __ffs((int)pm) - 1;
+                        pm &= pm - 1;
+                        sQ[pn - base] = (uint16_t)((lane << 8) | (pj << 5) | l);
+                        ++pn;
+                    }
+                }
+                __syncwarp();
+                const bool active = base + lane < total;
+                const int ent = active ? (int)sQ[lane] : (lane << 8);
+                const int own = ent >> 8;
+                const V3 po = V3{__shfl_sync(GQP_FULL, p.x, own), __shfl_sync(GQP_FULL, p.y, own),
+                                 __shfl_sync(GQP_FULL, p.z, own)};
+                if (active) {
+                    const int j = (ent >> 5) & 7, l = ent & 31;
+                    const PenLink &K = links[l];
+                    T34 W = t34_load(link_tf + ((size_t)(b0 + j) * L + l) * 12);
+                    V3 q = t34_inv_point(W, po);
+                    SdfBest best;
+                    sdf_best_init(best);
+                    bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first,
+                                     pre + (size_t)K.tri_first * 8, extent, q, best);
+                    V3 dv = q - best.c;
+                    float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
+                    float r = sqrtf(best.d2 + 1e-8f);
+                    V3 g = dv * (1.0f / r);
+                    sR[4 * lane] = r * (-sgn);  // hand_model.py:975-976
+                    sR[4 * lane + 1] = g.x; sR[4 * lane + 2] = g.y; sR[4 * lane + 3] = g.z;
+                }
+                __syncwarp();
+                while (next < endi && next < base + 32) {  // owners fold their pairs, ascending (candidate, link)
+                    while (cm == 0) cm = sNeed[++cj * 32 + lane];
+                    const int l = __ffs((int)cm) - 1;
+                    cm &= cm - 1;
+                    if (cj != fj) {
+                        finalize();
+                        fj = cj;
+                        best_d = -__int_as_float(0x7f800000);
+                        best_l = -1;
+                    }
+                    const int e = next - base;
+                    const float d = sR[4 * e];
+                    if (d > best_d) {  // hand_model.py:986 max over links (first maximum)
+                        best_d = d;
+                        best_l = l;
+                        best_g = V3{sR[4 * e + 1], sR[4 * e + 2], sR[4 * e + 3]};
+                    }
+                    ++next;
+                }
+                __syncwarp();
+            }
+            finalize();
+            if (partial) {  // partial was zeroed by the host wrapper; fixed-order sums keep E_pen deterministic
+                for (int j = 0; j < ncb; ++j) {
+                    const float e = __int_as_float((int)sNeed[j * 32 + lane]);
+                    if (__any_sync(GQP_FULL, e > 0.f)) {
+                        float s = warp_sum(e);
+                        if (lane == 0) partial[(size_t)(b0 + j) * n_chunks + chunk] = s;
+                    }
+                }
+            }
+            __syncwarp();
+            continue;
+        }
         for (int b = row * cands_per_row + cb * PEN_CB; b < b_end; ++b) {
             const uint32_t mask = masks[b];
             if (mask == 0) continue;  // the whole row is outside every link of this candidate
@@ -362,7 +515,7 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
         K.grid = -1;
         if (F > 0) {
             GqpBvhHost bvh;
-            gqp_bvh_build(face_verts_host + 9 * (size_t)f0, F, 4, bvh);
+            gqp_bvh_build(face_verts_host + 9 * (size_t)f0, F, 8, bvh);
             if (bvh.max_depth > GQP_BVH_STACK - 2)
                 return gqp_set_error(GQP_ERR_LIMIT, "hand link %d: BVH too deep (%d)", l, bvh.max_depth);
             K.n_nodes = (int)bvh.nodes.size();
@@ -485,7 +638,7 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
     GQP_LAUNCH(pen_mask_kernel, (Bt + 127) / 128, 128, 0, st, T->d_blob, link_tf, bounds, Bt, batch_each, n_chunks,
                per_candidate_points, cull, masks);
     GQP_CHECK_LAUNCH("gqp_hand_distance/mask");
-    const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * h->host.n_links * 48;
+    const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * (h->host.n_links * 48 + PEN_BATCH_BYTES);
     int grid = pen_grid_size((int)smem, n_tasks);
     if (cull) {
         GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
