@@ -128,6 +128,11 @@ inline unsigned atomicAdd(unsigned *p, unsigned v) {
     std::atomic_ref<unsigned> a(*p);
     return a.fetch_add(v, std::memory_order_relaxed);
 }
+inline unsigned long long atomicAdd(unsigned long long *p, unsigned long long v) {
+    std::atomic_ref<unsigned long long> a(*p);
+    return a.fetch_add(v, std::memory_order_relaxed);
+}
+inline long long __double2ll_rn(double a) { return std::llrint(a); }
 inline unsigned atomicMax(unsigned *p, unsigned v) {
     std::atomic_ref<unsigned> a(*p);
     unsigned old = a.load(std::memory_order_relaxed);

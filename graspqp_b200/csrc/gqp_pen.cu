@@ -65,8 +65,6 @@ __device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *gri
 }
 
 #define PEN_CB 8  // candidates per warp-task: amortises the sample loads and index arithmetic
-// per warp, culled path: 8x32 need-masks (reused as energies), 32 result slots of 16 B, 32 pair descriptors of 2 B
-#define PEN_BATCH_BYTES (PEN_CB * 32 * 4 + 32 * 16 + 32 * 2)
 
 // Bounding spheres of every 32-sample chunk of a point row, and of the whole row (slot n_chunks).  One block per row.
 __global__ void __launch_bounds__(256)
@@ -162,10 +160,6 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
     const int warps_per_block = blockDim.x / 32;
     // per-warp staging of the candidate's link transforms (L x 12 floats), behind the blob
     float *sW = reinterpret_cast<float *>(sm + blob_bytes) + (size_t)(threadIdx.x >> 5) * L * 12;
-    unsigned char *wb = sm + blob_bytes + (size_t)(blockDim.x / 32) * L * 48 + (size_t)(threadIdx.x >> 5) * PEN_BATCH_BYTES;
-    uint32_t *sNeed = reinterpret_cast<uint32_t *>(wb);
-    float *sR = reinterpret_cast<float *>(wb + PEN_CB * 32 * 4);
-    uint16_t *sQ = reinterpret_cast<uint16_t *>(wb + PEN_CB * 32 * 4 + 32 * 16);
     const int n_chunks = (n_pts + 31) / 32;
     const int n_cblk = (cands_per_row + PEN_CB - 1) / PEN_CB;
     const int n_tasks = n_rows * n_chunks * n_cblk;
@@ -180,153 +174,6 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
         const V3 cen = V3{sph[0], sph[1], sph[2]};
         const float rad = sph[3];
         const int b_end = row * cands_per_row + min(cands_per_row, (cb + 1) * PEN_CB);
-        if (CULL) {
-            // ---- culled path (E_pen and its gradient only) ----------------------------------------------------------
-            // After the box / sphere / outside-grid tests only a couple of samples per chunk still need an exact search
-            // for any one (candidate, link): searching link by link left ~2 of 32 lanes busy.  So: phase 1 only
-            // COLLECTS, per lane, the links that survive for each of the task's 8 candidates; phase 2 compacts all
-            // surviving (candidate, sample, link) pairs of the warp and every lane runs one search per round.
-            const int b0 = row * cands_per_row + cb * PEN_CB, ncb = b_end - b0;
-            int c_total = 0;
-            for (int j = 0; j < ncb; ++j) {
-                const int b = b0 + j;
-                uint32_t need = 0;
-                const uint32_t mask = masks[b];
-                if (mask != 0) {
-                    const float *Wb = link_tf + (size_t)b * L * 12;
-                    bool keep = false;
-                    if ((mask >> lane) & 1u) {  // lane l: stage link l's transform, chunk sphere vs link box
-                        T34 W = t34_load(Wb + lane * 12);
-#pragma unroll
-                        for (int i = 0; i < 12; ++i) sW[lane * 12 + i] = W.m[i];
-                        const PenLink &K = links[lane];
-                        keep = true;
-                        if (K.grid >= 0) {
-                            V3 q = t34_inv_point(W, cen);
-                            if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad ||
-                                q.x > K.hi[0] + rad || q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
-                                keep = false;
-                        }
-                    }
-                    unsigned todo = __ballot_sync(GQP_FULL, keep);
-                    __syncwarp();
-                    while (todo) {
-                        const int l = __ffs((int)todo) - 1;
-                        todo &= todo - 1;
-                        T34 W;
-#pragma unroll
-                        for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
-                        if (!pen_outside(links[l], grids, bits, t34_inv_point(W, p))) need |= 1u << l;
-                    }
-                    __syncwarp();  // sW is rewritten for the next candidate
-                }
-                if (!valid) need = 0;  // padding lanes of the last chunk
-                sNeed[j * 32 + lane] = need;
-                c_total += __popc(need);
-            }
-            int incl = c_total;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                int t = __shfl_up_sync(GQP_FULL, incl, o);
-                if (lane >= o) incl += t;
-            }
-            const int total = __shfl_sync(GQP_FULL, incl, 31);
-            if (total == 0) continue;
-            // a lane's pairs are numbered [next, endi) in (candidate, link) order; (cj, cm) walks them
-            int next = incl - c_total;
-            const int endi = incl;
-            int cj = 0, fj = -1, best_l = -1;
-            uint32_t cm = sNeed[lane];
-            float best_d = 0.f;
-            V3 best_g = V3{0, 0, 0};
-            // a candidate of this lane is complete: energy.py:60-61 relu, gradient of the penetrating sample
-            auto finalize = [&]() {
-                if (fj < 0) return;
-                const bool pen = best_d > 0.f;
-                sNeed[fj * 32 + lane] = pen ? (uint32_t)__float_as_int(best_d) : 0u;  // the slot now holds the energy
-                if (pen && grad_link_tf) {
-                    const size_t wl = ((size_t)(b0 + fj) * L + best_l) * 12;
-                    const float *W = link_tf + wl;
-                    float *G = grad_link_tf + wl;
-                    V3 g = best_g * w_pen;
-                    float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {g.x, g.y, g.z};
-#pragma unroll
-                    for (int r = 0; r < 3; ++r) {
-#pragma unroll
-                        for (int i = 0; i < 3; ++i) atomicAdd(G + 4 * r + i, pt[r] * gv[i]);
-                        atomicAdd(G + 4 * r + 3, -(W[4 * r] * gv[0] + W[4 * r + 1] * gv[1] + W[4 * r + 2] * gv[2]));
-                    }
-                }
-            };
-            for (int base = 0; base < total; base += 32) {
-                {   // owners publish their pairs of this window: (owner lane, candidate, link)
-                    int pj = cj, pn = next;
-                    uint32_t pm = cm;
-                    while (pn < endi && pn < base + 32) {
-                        while (pm == 0) pm = sNeed[++pj * 32 + lane];
-                        const int l = __ffs((int)pm) - 1;
-                        pm &= pm - 1;
-                        sQ[pn - base] = (uint16_t)((lane << 8) | (pj << 5) | l);
-                        ++pn;
-                    }
-                }
-                __syncwarp();
-                const bool active = base + lane < total;
-                const int ent = active ? (int)sQ[lane] : (lane << 8);
-                const int own = ent >> 8;
-                const V3 po = V3{__shfl_sync(GQP_FULL, p.x, own), __shfl_sync(GQP_FULL, p.y, own),
-                                 __shfl_sync(GQP_FULL, p.z, own)};
-                if (active) {
-                    const int j = (ent >> 5) & 7, l = ent & 31;
-                    const PenLink &K = links[l];
-                    T34 W = t34_load(link_tf + ((size_t)(b0 + j) * L + l) * 12);
-                    V3 q = t34_inv_point(W, po);
-                    SdfBest best;
-                    sdf_best_init(best);
-                    bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first,
-                                     pre + (size_t)K.tri_first * 8, extent, q, best);
-                    V3 dv = q - best.c;
-                    float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
-                    float r = sqrtf(best.d2 + 1e-8f);
-                    V3 g = dv * (1.0f / r);
-                    sR[4 * lane] = r * (-sgn);  // hand_model.py:975-976
-                    sR[4 * lane + 1] = g.x; sR[4 * lane + 2] = g.y; sR[4 * lane + 3] = g.z;
-                }
-                __syncwarp();
-                while (next < endi && next < base + 32) {  // owners fold their pairs, ascending (candidate, link)
-                    while (cm == 0) cm = sNeed[++cj * 32 + lane];
-                    const int l = __ffs((int)cm) - 1;
-                    cm &= cm - 1;
-                    if (cj != fj) {
-                        finalize();
-                        fj = cj;
-                        best_d = -__int_as_float(0x7f800000);
-                        best_l = -1;
-                    }
-                    const int e = next - base;
-                    const float d = sR[4 * e];
-                    if (d > best_d) {  // hand_model.py:986 max over links (first maximum)
-                        best_d = d;
-                        best_l = l;
-                        best_g = V3{sR[4 * e + 1], sR[4 * e + 2], sR[4 * e + 3]};
-                    }
-                    ++next;
-                }
-                __syncwarp();
-            }
-            finalize();
-            if (partial) {  // partial was zeroed by the host wrapper; fixed-order sums keep E_pen deterministic
-                for (int j = 0; j < ncb; ++j) {
-                    const float e = __int_as_float((int)sNeed[j * 32 + lane]);
-                    if (__any_sync(GQP_FULL, e > 0.f)) {
-                        float s = warp_sum(e);
-                        if (lane == 0) partial[(size_t)(b0 + j) * n_chunks + chunk] = s;
-                    }
-                }
-            }
-            __syncwarp();
-            continue;
-        }
         for (int b = row * cands_per_row + cb * PEN_CB; b < b_end; ++b) {
             const uint32_t mask = masks[b];
             if (mask == 0) continue;  // the whole row is outside every link of this candidate
@@ -403,6 +250,166 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
             __syncwarp();  // sW is rewritten for the next candidate
         }
     }
+}
+
+// ---- culled path (E_pen and its gradient only): collect -> search -> reduce --------------------------------------------
+// After the box / sphere / outside-grid tests only a handful of (candidate, sample) pairs per warp-task still need an
+// exact search; searching them where they are found left ~2 of 32 lanes busy in the expensive part.  So the culling
+// pass only EMITS the survivors — (sample id, mask of links to search) — into a global queue, and a second, dense
+// kernel searches them with every lane busy.  Penetration energies are accumulated in 2^-40 m fixed point (integer
+// atomics: deterministic whatever the queue order); gradients use float atomics as before.
+struct PenGroup {
+    uint32_t sample;  // b * n_pts + pi
+    uint32_t need;    // links whose exact distance is needed
+};
+#define PEN_FIX_SCALE 1099511627776.0  // 2^40
+
+__global__ void __launch_bounds__(PEN_THREADS)
+pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, const float *__restrict__ link_tf,
+                   const float *__restrict__ x, const float *__restrict__ bounds, const uint32_t *__restrict__ masks,
+                   int n_rows, int cands_per_row, int n_pts, uint32_t *__restrict__ counter,
+                   PenGroup *__restrict__ queue) {
+    GQP_DYN_SMEM(unsigned char, sm);
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) mbar_init(&bar);
+    __syncthreads();
+    if (threadIdx.x == 0) bulk_load(sm, blob, (uint32_t)prefix_bytes, &bar);  // header, links, grids, bits: no BVH nodes
+    mbar_wait(&bar, 0);
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(sm);
+    const PenLink *links = reinterpret_cast<const PenLink *>(sm + hdr->links_off);
+    const PenGrid *grids = reinterpret_cast<const PenGrid *>(sm + hdr->grids_off);
+    const uint32_t *bits = reinterpret_cast<const uint32_t *>(sm + hdr->bits_off);
+    const int L = hdr->n_links;
+    const int lane = threadIdx.x & 31, warps_per_block = blockDim.x / 32;
+    float *sW = reinterpret_cast<float *>(sm + prefix_bytes) + (size_t)(threadIdx.x >> 5) * L * 12;
+    const int n_chunks = (n_pts + 31) / 32;
+    const int n_cblk = (cands_per_row + PEN_CB - 1) / PEN_CB;
+    const int n_tasks = n_rows * n_chunks * n_cblk;
+    for (int task = blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;
+         task += gridDim.x * warps_per_block) {
+        const int cb = task % n_cblk, rc = task / n_cblk;
+        const int chunk = rc % n_chunks, row = rc / n_chunks;
+        const int pi = chunk * 32 + lane;
+        const bool valid = pi < n_pts;
+        const V3 p = ld3(x + ((size_t)row * n_pts + (valid ? pi : n_pts - 1)) * 3);
+        const float *sph = bounds + ((size_t)row * (n_chunks + 1) + chunk) * 4;
+        const V3 cen = V3{sph[0], sph[1], sph[2]};
+        const float rad = sph[3];
+        const int b_end = row * cands_per_row + min(cands_per_row, (cb + 1) * PEN_CB);
+        for (int b = row * cands_per_row + cb * PEN_CB; b < b_end; ++b) {
+            const uint32_t mask = masks[b];
+            if (mask == 0) continue;  // the whole row is outside every link of this candidate
+            const float *Wb = link_tf + (size_t)b * L * 12;
+            bool keep = false;
+            if ((mask >> lane) & 1u) {  // lane l: stage link l's transform, chunk sphere vs link box
+                T34 W = t34_load(Wb + lane * 12);
+#pragma unroll
+                for (int i = 0; i < 12; ++i) sW[lane * 12 + i] = W.m[i];
+                const PenLink &K = links[lane];
+                keep = true;
+                if (K.grid >= 0) {
+                    V3 q = t34_inv_point(W, cen);
+                    if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
+                        q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
+                        keep = false;
+                }
+            }
+            unsigned todo = __ballot_sync(GQP_FULL, keep);
+            if (todo == 0) continue;
+            __syncwarp();
+            uint32_t need = 0;
+            while (todo) {
+                const int l = __ffs((int)todo) - 1;
+                todo &= todo - 1;
+                T34 W;
+#pragma unroll
+                for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
+                if (!pen_outside(links[l], grids, bits, t34_inv_point(W, p))) need |= 1u << l;
+            }
+            if (!valid) need = 0;  // padding lanes of the last chunk
+            const unsigned em = __ballot_sync(GQP_FULL, need != 0);
+            if (em) {
+                int base = 0;
+                if (lane == 0) base = (int)atomicAdd(counter, (unsigned)__popc(em));
+                base = __shfl_sync(GQP_FULL, base, 0);
+                if (need) queue[base + __popc(em & ((1u << lane) - 1u))] = PenGroup{(uint32_t)(b * n_pts + pi), need};
+            }
+            __syncwarp();  // sW is rewritten for the next candidate
+        }
+    }
+}
+
+#define PEN_Q_THREADS 256
+__global__ void __launch_bounds__(PEN_Q_THREADS)
+pen_search_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
+                  const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
+                  const float *__restrict__ link_tf, const float *__restrict__ x, int batch_each, int n_pts,
+                  int per_candidate_points, const uint32_t *__restrict__ counter, const PenGroup *__restrict__ queue,
+                  unsigned long long *__restrict__ acc, float w_pen, float *__restrict__ grad_link_tf) {
+    GQP_DYN_SMEM(unsigned char, sm);
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) mbar_init(&bar);
+    __syncthreads();
+    if (threadIdx.x == 0) bulk_load(sm, blob, (uint32_t)blob_bytes, &bar);
+    mbar_wait(&bar, 0);
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(sm);
+    const PenLink *links = reinterpret_cast<const PenLink *>(sm + hdr->links_off);
+    const GqpBvhNode *nodes = reinterpret_cast<const GqpBvhNode *>(sm + hdr->nodes_off);
+    const int L = hdr->n_links;
+    const unsigned n_groups = *counter;
+    for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += gridDim.x * blockDim.x) {
+        const PenGroup G = queue[g];
+        const int b = (int)(G.sample / (unsigned)n_pts), pi = (int)(G.sample % (unsigned)n_pts);
+        const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
+        const V3 p = ld3(x + (row * n_pts + pi) * 3);
+        float best_d = -__int_as_float(0x7f800000);
+        int best_l = -1;
+        V3 best_g = V3{0, 0, 0};
+        uint32_t m = G.need;
+        while (m) {  // ascending link order: first maximum, hand_model.py:986
+            const int l = __ffs((int)m) - 1;
+            m &= m - 1;
+            const PenLink &K = links[l];
+            const T34 W = t34_load(link_tf + ((size_t)b * L + l) * 12);
+            const V3 q = t34_inv_point(W, p);
+            SdfBest best;
+            sdf_best_init(best);
+            bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first,
+                             pre + (size_t)K.tri_first * 8, extent, q, best);
+            const V3 dv = q - best.c;
+            const float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
+            const float r = sqrtf(best.d2 + 1e-8f);
+            const float d = r * (-sgn);  // hand_model.py:975-976
+            if (d > best_d) {
+                best_d = d;
+                best_l = l;
+                best_g = dv * (1.0f / r);
+            }
+        }
+        if (best_d > 0.f) {  // energy.py:60-61
+            if (acc) atomicAdd(acc + b, (unsigned long long)__double2ll_rn((double)best_d * PEN_FIX_SCALE));
+            if (grad_link_tf) {
+                // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
+                const size_t wl = ((size_t)b * L + best_l) * 12;
+                const float *W = link_tf + wl;
+                float *Gm = grad_link_tf + wl;
+                const V3 gg = best_g * w_pen;
+                const float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {gg.x, gg.y, gg.z};
+#pragma unroll
+                for (int r2 = 0; r2 < 3; ++r2) {
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) atomicAdd(Gm + 4 * r2 + i, pt[r2] * gv[i]);
+                    atomicAdd(Gm + 4 * r2 + 3, -(W[4 * r2] * gv[0] + W[4 * r2 + 1] * gv[1] + W[4 * r2 + 2] * gv[2]));
+                }
+            }
+        }
+    }
+}
+
+__global__ void pen_reduce_fixed_kernel(const unsigned long long *__restrict__ acc, int Bt, float *__restrict__ e_pen) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    e_pen[b] = (float)((double)acc[b] * (1.0 / PEN_FIX_SCALE));
 }
 
 __global__ void pen_reduce_kernel(const float *__restrict__ partial, int Bt, int n_chunks, float *__restrict__ e_pen) {
@@ -570,8 +577,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     };
     hdr.links_off = append(links.data(), links.size() * sizeof(PenLink));
     hdr.grids_off = append(grids.data(), grids.size() * sizeof(PenGrid));
-    hdr.nodes_off = append(nodes.data(), nodes.size() * sizeof(GqpBvhNode));
     hdr.bits_off = append(bits.data(), bits.size() * sizeof(uint32_t));
+    hdr.nodes_off = append(nodes.data(), nodes.size() * sizeof(GqpBvhNode));  // last: the collect kernel stops before it
     pad16(B);
     hdr.total_bytes = (int)B.size();
     std::memcpy(B.data(), &hdr, sizeof(hdr));
@@ -585,7 +592,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     T->d_pre = (float *)gqp_dev_alloc_upload(pre.data(), pre.size() * sizeof(float));
     if (!T->d_blob || !T->d_tris || !T->d_face_id || !T->d_pre) return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
 #ifndef GQP_EMU
-    cudaFuncSetAttribute(hand_pen_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
+    cudaFuncSetAttribute(pen_collect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
+    cudaFuncSetAttribute(pen_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
     cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
 #endif
     return GQP_OK;
@@ -599,16 +607,17 @@ void gqp_pen_tables_destroy(GqpHand *h) {
     h->pen = nullptr;
 }
 
-static int pen_grid_size(int blob_bytes, long long n_tasks) {
+static int pen_grid_size(int blob_bytes, long long n_tasks, int max_per_sm) {
 #ifndef GQP_EMU
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int per_sm = (int)std::max(1, std::min(PEN_MIN_BLOCKS, (int)((226 * 1024) / (blob_bytes + 1024))));
+    int per_sm = (int)std::max(1, std::min(max_per_sm, (int)((226 * 1024) / (blob_bytes + 1024))));
     long long want = (n_tasks + PEN_THREADS / 32 - 1) / (PEN_THREADS / 32);
     return (int)std::max(1LL, std::min<long long>(want, (long long)sms * per_sm));
 #else
     (void)blob_bytes;
+    (void)max_per_sm;
     return (int)std::max(1LL, std::min<long long>(2, n_tasks));
 #endif
 }
@@ -631,24 +640,46 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
     float *bounds = scratch + (size_t)Bt * n_chunks;
     uint32_t *masks = reinterpret_cast<uint32_t *>(bounds + (size_t)n_rows * (n_chunks + 1) * 4);
     const int cull = dist ? 0 : 1;  // with dist wanted, every link's true distance is needed
-    int rc = gqp_memset_zero(partial, sizeof(float) * (size_t)Bt * n_chunks, stream);
-    if (rc != GQP_OK) return rc;
+    int rc = GQP_OK;
     GQP_LAUNCH(pen_bounds_kernel, n_rows, 256, 0, st, x, n_pts, n_chunks, bounds);
     GQP_CHECK_LAUNCH("gqp_hand_distance/bounds");
     GQP_LAUNCH(pen_mask_kernel, (Bt + 127) / 128, 128, 0, st, T->d_blob, link_tf, bounds, Bt, batch_each, n_chunks,
                per_candidate_points, cull, masks);
     GQP_CHECK_LAUNCH("gqp_hand_distance/mask");
-    const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * (h->host.n_links * 48 + PEN_BATCH_BYTES);
-    int grid = pen_grid_size((int)smem, n_tasks);
     if (cull) {
-        GQP_LAUNCH(hand_pen_kernel<true>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
-                   T->d_face_id, T->d_pre, T->extent, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
-                   partial, w_pen, grad_link_tf);
-    } else {
-        GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris,
-                   T->d_face_id, T->d_pre, T->extent, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
-                   partial, w_pen, grad_link_tf);
+        // [counter 4 words][fixed-point energy accumulators Bt x u64][queue Bt*n_pts groups], 8-byte aligned
+        uint32_t *tail = masks + Bt;
+        tail += ((uintptr_t)tail & 7) ? 1 : 0;
+        uint32_t *counter = tail;
+        unsigned long long *acc = reinterpret_cast<unsigned long long *>(tail + 4);
+        PenGroup *queue = reinterpret_cast<PenGroup *>(acc + Bt);
+        rc = gqp_memset_zero(tail, 16 + sizeof(unsigned long long) * (size_t)Bt, stream);
+        if (rc != GQP_OK) return rc;
+        const PenHdr *hdr = reinterpret_cast<const PenHdr *>(T->blob_host.data());
+        const int prefix = hdr->nodes_off;  // header, links, grids, outside-grid bits
+        const size_t smem1 = (size_t)prefix + (size_t)(PEN_THREADS / 32) * h->host.n_links * 48;
+        int grid1 = pen_grid_size((int)smem1, n_tasks, 3);  // 39 registers x 512 threads: 3 CTAs per SM
+        GQP_LAUNCH(pen_collect_kernel, grid1, PEN_THREADS, smem1, st, T->d_blob, prefix, link_tf, x, bounds, masks,
+                   n_rows, cands_per_row, n_pts, counter, queue);
+        GQP_CHECK_LAUNCH("gqp_hand_distance/collect");
+        int grid2 = pen_grid_size(T->total_bytes, 1LL << 40, 3);
+        GQP_LAUNCH(pen_search_kernel, grid2, PEN_Q_THREADS, (size_t)T->total_bytes, st, T->d_blob, T->total_bytes,
+                   T->d_tris, T->d_face_id, T->d_pre, T->extent, link_tf, x, batch_each, n_pts, per_candidate_points,
+                   counter, queue, e_pen ? acc : nullptr, w_pen, grad_link_tf);
+        GQP_CHECK_LAUNCH("gqp_hand_distance/search");
+        if (e_pen) {
+            GQP_LAUNCH(pen_reduce_fixed_kernel, (Bt + 127) / 128, 128, 0, st, acc, Bt, e_pen);
+            GQP_CHECK_LAUNCH("gqp_hand_distance/reduce");
+        }
+        return GQP_OK;
     }
+    rc = gqp_memset_zero(partial, sizeof(float) * (size_t)Bt * n_chunks, stream);
+    if (rc != GQP_OK) return rc;
+    const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * (h->host.n_links * 48);
+    int grid = pen_grid_size((int)smem, n_tasks, PEN_MIN_BLOCKS);
+    GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris, T->d_face_id,
+               T->d_pre, T->extent, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
+               partial, w_pen, grad_link_tf);
     GQP_CHECK_LAUNCH("gqp_hand_distance");
     if (e_pen) {
         GQP_LAUNCH(pen_reduce_kernel, (Bt + 127) / 128, 128, 0, st, partial, Bt, n_chunks, e_pen);
@@ -739,7 +770,7 @@ extern "C" int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host) {
         for (long long i = 0; i < n; ++i) set += (bits[grids[g].bit_first + (i >> 5)] >> (i & 31)) & 1u;
     }
     info_host[0] = hdr->total_bytes;
-    info_host[1] = (hdr->bits_off - hdr->nodes_off) / (int)sizeof(GqpBvhNode);
+    info_host[1] = (hdr->total_bytes - hdr->nodes_off) / (int)sizeof(GqpBvhNode);
     info_host[2] = (int32_t)cells;
     info_host[3] = (int32_t)set;
     info_host[4] = h->face_offset.back();
@@ -750,5 +781,6 @@ extern "C" int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host) {
 extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {
     const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
     const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;
-    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16;
+    // + culled path: counter (4 words + alignment), fixed-point accumulators (2 words each), queue (2 words per sample)
+    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16 + 8 + 2 * Bt + 2 * Bt * (uint64_t)n_pts;
 }

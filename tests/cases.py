@@ -86,7 +86,8 @@ def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5):
                                      be.ptr(g2), be.stream), lib)
     e1h, e2h, g1h, g2h, dh = [be.to_host(a) for a in (e1, e2, g1, g2, dist)]
     assert (e1h > 0).sum() >= B // 4, "poses do not penetrate"
-    np.testing.assert_array_equal(e2h, e1h)  # same winners, same fixed-order sums
+    # same winners; the culled path sums in 2^-40 m fixed point, the full path in fp32 in a fixed order
+    np.testing.assert_allclose(e2h, e1h, rtol=1e-6, atol=1e-9)
     np.testing.assert_allclose(g2h, g1h, rtol=1e-4, atol=1e-4)  # atomics: order differs
     nb = min(B, 6)
     o = HandOracle(pack, torch.float32)
@@ -161,6 +162,9 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3):
             E_in, _, _ = oqp.graspqp_energy(torch.tensor(H(eng.cpts), dtype=torch.float64),
                                             torch.tensor(H(eng.obj_nrm), dtype=torch.float64), orc.obj.cog)
             e_fc = H(eng.losses_new)[engine.TERMS.index("E_fc")]
+            # ... and the engine's object normals are the reference kernel's, bit for bit, at the engine's own contacts
+            _, sg_w, nr_w, _ = osdf.compute_sdf_port(H(eng.cpts)[b], fv)
+            np.testing.assert_array_equal(H(eng.obj_nrm)[b], nr_w * sg_w[:, None].astype(np.float32), err_msg=f"step {t}")
             outliers.append((t, int(b), float(rel[b]), terms, abs(float(e_fc[b]) - E_in[b].item()) / abs(E_in[b].item())))
         worst = max(worst, float(np.max(np.where(rel > 2e-4, 0.0, rel))))
         p_acc = np.exp(np.minimum((orc_energy_before(out) - want) / out["temperature"].numpy(), 0.0))
@@ -175,12 +179,14 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3):
     # contact is unit(p - c) * sign (object_model.py:246) and is not Lipschitz in p near nearest-face ties and on the
     # surface itself; the contact points of the two runs differ by one fp32 ulp (fp32 FK here, fp64 FK in the oracle),
     # which occasionally rotates ONE contact normal by 1e-4..1e-2 rad, and E_fc sees that.  Such steps are re-checked
-    # with the oracle's QP evaluated on the engine's own fp32 contacts/normals (must agree to 1e-5), and are allowed for
-    # at most 1 % of candidate-steps (0.1-0.3 % observed), each below 5e-3 relative.  Everything else is within 2e-4.
+    # with the reference SDF arithmetic on the engine's own fp32 contact points (normals must be bit-identical) and the
+    # oracle's QP on the engine's own contacts/normals (must agree to 1e-5); a nearest-face tie can even flip a normal's
+    # sign (one 9 % event seen in 3000 candidate-steps).  Allowed for at most 1 % of candidate-steps (0.1-0.3 % observed);
+    # everything else is within 2e-4.
     for o in outliers:
         print("trajectory outlier (step, candidate, rel err, per-term diff, E_fc rel err on the engine's inputs):", o)
     assert len(outliers) <= max(1, T * B // 100), outliers
-    assert all(o[2] < 5e-3 and o[4] < 1e-5 and abs(o[3]["E_pen"]) < 1e-5 for o in outliers), outliers
+    assert all(o[4] < 1e-5 and abs(o[3]["E_pen"]) < 1e-5 for o in outliers), outliers
     return n_acc, n_tie, worst
 
 
