@@ -216,7 +216,8 @@ __global__ void contacts_forward_kernel(const float *__restrict__ cand, const fl
     st3(cpts + 3 * (size_t)i, t34_point(W, ld3(cand + 3 * k)));
     st3(cnrm + 3 * (size_t)i, t34_vec(W, ld3(cand_normal + 3 * k)));
 }
-// backward: a thread per candidate walks its n_c contacts (no atomics, deterministic); accumulates into grad_link_tf.
+// backward: a thread per candidate walks its n_c contacts; accumulates into grad_link_tf with atomics (the penetration
+// and self-penetration kernels add to the same buffer, possibly concurrently from another stream).
 __global__ void contacts_backward_kernel(const float *__restrict__ cand, const float *__restrict__ cand_normal,
                                          const int32_t *__restrict__ cand_link, int n_cand, int n_links,
                                          const int32_t *__restrict__ idx, const float *__restrict__ grad_cpts,
@@ -238,8 +239,8 @@ __global__ void contacts_backward_kernel(const float *__restrict__ cand, const f
 #pragma unroll
         for (int r = 0; r < 3; ++r) {
 #pragma unroll
-            for (int q = 0; q < 3; ++q) g[4 * r + q] += gpv[r] * pv[q] + gnv[r] * nv[q];
-            g[4 * r + 3] += gpv[r];
+            for (int q = 0; q < 3; ++q) atomicAdd(g + 4 * r + q, gpv[r] * pv[q] + gnv[r] * nv[q]);
+            atomicAdd(g + 4 * r + 3, gpv[r]);
         }
     }
 }

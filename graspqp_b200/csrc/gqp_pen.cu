@@ -488,8 +488,8 @@ self_pen_joints_kernel(const GqpHandDev *__restrict__ hand, const float *__restr
                     float sg = side == 0 ? 1.f : -1.f;
                     float *G = grad_link_tf + ((size_t)b * L + s_link[k]) * 12;
                     for (int r = 0; r < 3; ++r) {
-                        for (int q = 0; q < 3; ++q) G[4 * r + q] += sg * g[r] * s_sph[4 * k + q];
-                        G[4 * r + 3] += sg * g[r];
+                        for (int q = 0; q < 3; ++q) atomicAdd(G + 4 * r + q, sg * g[r] * s_sph[4 * k + q]);
+                        atomicAdd(G + 4 * r + 3, sg * g[r]);
                     }
                 }
             }

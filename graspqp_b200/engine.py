@@ -52,6 +52,14 @@ class NumpyBackend:
     def copy_(self, dst, src):
         dst[...] = src
 
+    side_stream = None  # the emulator runs launches in order: no second stream
+
+    def fork(self):
+        pass
+
+    def join(self):
+        pass
+
 
 class TorchBackend:
     """torch CUDA tensors; launches go to torch's current stream."""
@@ -85,12 +93,36 @@ class TorchBackend:
     def copy_(self, dst, src):
         dst.copy_(src)
 
+    # ---- second stream: the penetration chain runs beside the contact / force-closure chain ----
+    def _side(self):
+        if getattr(self, "_side_obj", None) is None:
+            self._side_obj = self.torch.cuda.Stream(device=self.device)
+            self._ev_fork = self.torch.cuda.Event()
+            self._ev_join = self.torch.cuda.Event()
+        return self._side_obj
+
+    @property
+    def side_stream(self):
+        return ctypes.c_void_p(self._side().cuda_stream)
+
+    def fork(self):
+        """work enqueued on the side stream from now on sees everything enqueued on the current stream so far"""
+        side = self._side()
+        self._ev_fork.record(self.torch.cuda.current_stream(self.device))
+        side.wait_event(self._ev_fork)
+
+    def join(self):
+        """the current stream waits for everything enqueued on the side stream"""
+        self._ev_join.record(self._side())
+        self.torch.cuda.current_stream(self.device).wait_event(self._ev_join)
+
 
 class FitEngine:
     def __init__(self, cdll, backend, pack, face_verts_list, surface_points, batch_each, hand_pose, contact_idx,
                  weights=None, friction=0.2, max_limit=20.0, svd_gain=0.1, torque_weight=5.0, switch_possibility=0.4,
                  starting_temperature=18.0, temperature_decay=0.95, annealing_period=30, step_size=0.005,
-                 stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1, collectives=None):
+                 stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1, collectives=None,
+                 overlap=True):
         self.lib, self.be = cdll, backend
         self.pack = pack
         self.n_obj = len(face_verts_list)
@@ -104,6 +136,7 @@ class FitEngine:
         self.seed = int(seed)
         self.iteration = 0
         self.qp_batch_stop = bool(qp_batch_stop)
+        self.overlap = bool(overlap)
         self.collectives = collectives  # shard.GlobalStats or None (no data-path collective: the default)
         be, Bt, D, n_c, L = backend, self.Bt, self.D, self.n_c, self.L
         surface_points = np.ascontiguousarray(surface_points, np.float32)
@@ -175,12 +208,23 @@ class FitEngine:
         Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
         row = lambda k: p(losses_out) + 4 * Bt * TERMS.index(k)
         self._ck(lib.gqp_fk_forward(self.hand, p(pose), Bt, p(self.link_tf), st))
+        self._ck(lib.gqp_memset_zero(p(self.g_link_tf), 4 * Bt * self.L * 12, st))
+        # two independent chains read link_tf and add into g_link_tf (atomics): the penetration chain goes to a second
+        # stream so that its latency-bound kernels fill the SMs beside the contact / force-closure chain
+        overlap = self.overlap and be.side_stream is not None
+        s2 = be.side_stream if overlap else st
+        if overlap:
+            be.fork()
+        self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
+                                       row("E_pen"), p(self.pen_scratch), self.weights["E_pen"], p(self.g_link_tf), s2))
+        self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
+                                         self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
+                                         p(self.g_pose_joints), s2))
         self._ck(lib.gqp_contacts_forward(self.hand, p(self.link_tf), p(idx), Bt, n_c, p(self.cpts), p(self.cnrm), st))
         self._ck(lib.gqp_object_distance_forward(self.objset, B, n_c, p(self.cpts), 1.0, p(self.obj_dist),
                                                  p(self.obj_nrm), p(self.obj_clst), p(self.obj_sign), st))
         self._ck(lib.gqp_object_distance_backward(p(self.ones), p(self.cpts), p(self.obj_clst), p(self.obj_sign),
                                                   Bt * n_c, 1.0, p(self.obj_dgrad), st))
-        self._ck(lib.gqp_memset_zero(p(self.g_link_tf), 4 * Bt * self.L * 12, st))
         # Q1-Q4 + E_dis: one interior-point pass that records the batch statistics of qpth's exit test, then the
         # finish pass (value, svd term, energies, analytic backward) from every candidate's best iterate as of the exit
         self._ck(lib.gqp_fc_solve(ctypes.byref(self.fc), p(self.cpts), p(self.obj_nrm), p(self.cog), O, B, n_c,
@@ -195,11 +239,8 @@ class FitEngine:
                                    p(self.qp_stop), st))
         self._ck(lib.gqp_contacts_backward(self.hand, p(idx), p(self.g_cpts), p(self.g_cnrm), Bt, n_c,
                                            p(self.g_link_tf), st))
-        self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
-                                       row("E_pen"), p(self.pen_scratch), self.weights["E_pen"], p(self.g_link_tf), st))
-        self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
-                                         self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
-                                         p(self.g_pose_joints), st))
+        if overlap:
+            be.join()
         self._ck(lib.gqp_fk_backward(self.hand, p(pose), p(self.g_link_tf), p(self.g_pose_joints), Bt, p(grad_out), st))
 
     def _accept(self, z, reset, u_accept):
@@ -233,6 +274,37 @@ class FitEngine:
                                       p(self.pose_new), p(self.idx_new), p(self.step_size_out), st))
         self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
         self._accept(self.z, reset_mask, u_accept)
+
+    def stage_calls(self):
+        """name -> callable re-running ONE stage of the iteration on the current buffers (per-stage timing in bench.py
+        and tools/bench_kernels.py; results are overwritten with the same values, gradients accumulate garbage)."""
+        lib, p, st = self.lib, self.be.ptr, self.be.stream
+        Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
+        row = lambda k: p(self.losses_new) + 4 * Bt * TERMS.index(k)
+        return {
+            "fk_forward": lambda: lib.gqp_fk_forward(self.hand, p(self.pose_new), Bt, p(self.link_tf), st),
+            "contacts_forward": lambda: lib.gqp_contacts_forward(self.hand, p(self.link_tf), p(self.idx_new), Bt, n_c,
+                                                                 p(self.cpts), p(self.cnrm), st),
+            "object_distance": lambda: lib.gqp_object_distance_forward(
+                self.objset, B, n_c, p(self.cpts), 1.0, p(self.obj_dist), p(self.obj_nrm), p(self.obj_clst),
+                p(self.obj_sign), st),
+            "fc_solve": lambda: lib.gqp_fc_solve(ctypes.byref(self.fc), p(self.cpts), p(self.obj_nrm), p(self.cog), O, B,
+                                                 n_c, p(self.qp_ws), st),
+            "fc_finish": lambda: lib.gqp_fc_finish(
+                ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist), p(self.obj_nrm), p(self.obj_dgrad),
+                p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop), row("E_fc"), row("E_dis"), p(self.lam),
+                p(self.g_cpts), p(self.g_cnrm), p(self.qp_stop), st),
+            "contacts_backward": lambda: lib.gqp_contacts_backward(self.hand, p(self.idx_new), p(self.g_cpts),
+                                                                   p(self.g_cnrm), Bt, n_c, p(self.g_link_tf), st),
+            "hand_distance": lambda: lib.gqp_hand_distance(
+                self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None, row("E_pen"), p(self.pen_scratch),
+                self.weights["E_pen"], p(self.g_link_tf), st),
+            "self_pen_joints": lambda: lib.gqp_self_pen_joints(
+                self.hand, p(self.link_tf), p(self.pose_new), Bt, row("E_spen"), row("E_joints"), self.weights["E_spen"],
+                self.weights["E_joints"], p(self.g_link_tf), p(self.g_pose_joints), st),
+            "fk_backward": lambda: lib.gqp_fk_backward(self.hand, p(self.pose_new), p(self.g_link_tf),
+                                                       p(self.g_pose_joints), Bt, p(self.grad_new), st),
+        }
 
     def launches_per_step(self):
         return 13
