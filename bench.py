@@ -37,6 +37,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=None, help="override candidates per object")
     ap.add_argument("--objects", type=int, default=None, help="override objects per GPU")
     ap.add_argument("--no-qp-batch-stop", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="do not replay the energy evaluation from a CUDA graph")
     ap.add_argument("--no-overlap", action="store_true", help="run the penetration chain on the main stream too")
     ap.add_argument("--global-rms", action="store_true",
                     help="N>1: all-reduce the batch-wide MALA*/qpth statistics every iteration (shard.GlobalStats); the "
@@ -153,6 +154,7 @@ def run_b200(args):
                            qp_batch_stop=not args.no_qp_batch_stop, seed=1 + rank,
                            collectives=shard.GlobalStats() if (world > 1 and args.global_rms) else None,
                            overlap=not args.no_overlap)
+    graphed = (not args.no_graph) and eng.capture()
     torch.cuda.synchronize()
     t_setup = time.perf_counter() - t_setup
     K, W = max(1, args.steps), max(3, args.warmup)
@@ -179,7 +181,8 @@ def run_b200(args):
         e1.record()
         evs.append((e0, e1))
     barrier()
-    launches = int(lib.gqp_launch_count() - n0)
+    # kernels of this library executed in the timed region: counted launch calls + the kernels inside each graph replay
+    launches = int(lib.gqp_launch_count() - n0) + (K * eng.graph_launches if graphed else 0)
     clocks = sampler.stop()
     ms_total = sum(a.elapsed_time(b) for a, b in evs)
     # ---- end-to-end: host noise in pinned memory -> device, step, energy + accept back to the host, every step ----
@@ -258,7 +261,7 @@ def run_b200(args):
             "config": {"workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
                                    f"{w['faces_per_mesh']} tris), batch {B}/object, n_contact {n_c}, 2500 surface samples",
                        "candidates_per_gpu": Bt, "l2": "flushed between timed steps (256 MiB write)",
-                       "qp_batch_stop": eng.qp_batch_stop, "streams": 2 if eng.overlap else 1,
+                       "qp_batch_stop": eng.qp_batch_stop, "streams": 2 if eng.overlap else 1, "cuda_graph": bool(graphed),
                        "collectives": ("global rms + qp exit words all-reduced per step" if eng.collectives else
                                        "none on the data path; final all-gather of grasps") if world > 1 else "n/a",
                        "noise": "philox on device (value) / injected from host (e2e)",

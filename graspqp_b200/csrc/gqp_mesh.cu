@@ -30,7 +30,7 @@ static int mesh_steps() {
     if (!v) {
         const char *e = getenv("GQP_MESH_STEPS");
         v = e ? atoi(e) : 4;
-        if (v < 1) v = 1;
+        if (v < 32) v = 32;
     }
     return v;
 }

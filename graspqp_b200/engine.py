@@ -137,6 +137,8 @@ class FitEngine:
         self.iteration = 0
         self.qp_batch_stop = bool(qp_batch_stop)
         self.overlap = bool(overlap)
+        self._graph = None
+        self.graph_launches = 0
         self.collectives = collectives  # shard.GlobalStats or None (no data-path collective: the default)
         be, Bt, D, n_c, L = backend, self.Bt, self.D, self.n_c, self.L
         surface_points = np.ascontiguousarray(surface_points, np.float32)
@@ -243,6 +245,28 @@ class FitEngine:
             be.join()
         self._ck(lib.gqp_fk_backward(self.hand, p(pose), p(self.g_link_tf), p(self.g_pose_joints), Bt, p(grad_out), st))
 
+    def capture(self):
+        """Record the energy evaluation of an iteration (both streams, ~20 launches) into a CUDA graph; step() then
+        replays it.  The MALA* kernels stay ordinary launches (their iteration counter is a by-value argument).
+        Not available with the emulator backend or with per-iteration collectives."""
+        if self.collectives is not None or not hasattr(self.be, "torch"):
+            return False
+        torch = self.be.torch
+        torch.cuda.synchronize(self.be.device)
+        g = torch.cuda.CUDAGraph()
+        cap = torch.cuda.Stream(device=self.be.device)
+        cap.wait_stream(torch.cuda.current_stream(self.be.device))
+        with torch.cuda.stream(cap):
+            n0 = int(self.lib.gqp_launch_count())
+            self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)  # warm-up outside the capture
+            self.graph_launches = int(self.lib.gqp_launch_count()) - n0  # kernels one replay executes
+            cap.synchronize()
+            with torch.cuda.graph(g, stream=cap):
+                self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
+        torch.cuda.current_stream(self.be.device).wait_stream(cap)
+        self._graph = g
+        return True
+
     def _accept(self, z, reset, u_accept):
         lib, p, st = self.lib, self.be.ptr, self.be.stream
         self._ck(lib.gqp_mala_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(TERMS), p(self.w_dev),
@@ -272,7 +296,10 @@ class FitEngine:
                                       p(self.ema), p(self.step_count), p(self.idx), self.Bt, self.D, self.n_c,
                                       self.n_cand, p(u_switch), p(idx_rand), self.seed, self.iteration,
                                       p(self.pose_new), p(self.idx_new), p(self.step_size_out), st))
-        self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
+        if self._graph is not None:
+            self._graph.replay()
+        else:
+            self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
         self._accept(self.z, reset_mask, u_accept)
 
     def stage_calls(self):
