@@ -95,6 +95,9 @@ def cpu_reference_run(args, steps, warmup, sample_batch):
     from graspqp_b200 import workload
     from oracle.pipeline import FitLoopOracle
     subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
+    from oracle import sdf as osdf
+    torch.set_num_threads(os.cpu_count() or 1)   # all host threads, whatever OMP_NUM_THREADS the launcher exported
+    osdf.set_threads(os.cpu_count() or 1)
     w = workload.build(args.workload, batch_each=sample_batch, n_objects=1)
     B, n_c = sample_batch, w["n_contact"]
     orc = FitLoopOracle(w["pack"], w["face_verts"], [w["surface"][0]], B, w["pose"], w["idx"].astype(np.int64),
@@ -122,6 +125,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; this arm is the reference's CPU path on ALL host threads
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+    import torch
+    torch.set_num_threads(os.cpu_count() or 1)
     steps, warmup = max(1, args.steps), max(0, args.warmup)
     # bounded: the oracle does ~1 s per iteration of 16 candidates on 8 cores
     steps, warmup = min(steps, 10), min(warmup, 2)

@@ -42,6 +42,15 @@ def compute_sdf_port(points, face_verts, with_face=False):
     return (d2, sg, nr, cl, fi) if with_face else (d2, sg, nr, cl)
 
 
+def set_threads(n):
+    """OpenMP team size of the C restatement (torchrun exports OMP_NUM_THREADS=1 to its workers)."""
+    global _port
+    if _port is None:
+        _port = _load("_build/libsdf_oracle.so")
+    _port.sdf_oracle_set_threads(int(n))
+    return int(_port.sdf_oracle_get_threads())
+
+
 def have_ref():
     return os.path.exists(os.path.join(_HERE, "_ref", "libtorchsdf_ref.so"))
 

@@ -104,3 +104,13 @@ void sdf_oracle_backward(const float *grad_dist, const float *points, const floa
         for (int k = 0; k < 3; ++k) grad_points[3 * i + k] = (points[3 * i + k] - clst[3 * i + k]) * g;
     }
 }
+
+/* bench.py's reference arm runs under torchrun, which exports OMP_NUM_THREADS=1: set the team size explicitly */
+#ifdef _OPENMP
+#include <omp.h>
+void sdf_oracle_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int sdf_oracle_get_threads(void) { return omp_get_max_threads(); }
+#else
+void sdf_oracle_set_threads(int n) { (void)n; }
+int sdf_oracle_get_threads(void) { return 1; }
+#endif
