@@ -217,11 +217,6 @@ class FitEngine:
         s2 = be.side_stream if overlap else st
         if overlap:
             be.fork()
-        self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
-                                       row("E_pen"), p(self.pen_scratch), self.weights["E_pen"], p(self.g_link_tf), s2))
-        self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
-                                         self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
-                                         p(self.g_pose_joints), s2))
         self._ck(lib.gqp_contacts_forward(self.hand, p(self.link_tf), p(idx), Bt, n_c, p(self.cpts), p(self.cnrm), st))
         self._ck(lib.gqp_object_distance_forward(self.objset, B, n_c, p(self.cpts), 1.0, p(self.obj_dist),
                                                  p(self.obj_nrm), p(self.obj_clst), p(self.obj_sign), st))
@@ -241,6 +236,13 @@ class FitEngine:
                                    p(self.qp_stop), st))
         self._ck(lib.gqp_contacts_backward(self.hand, p(idx), p(self.g_cpts), p(self.g_cnrm), Bt, n_c,
                                            p(self.g_link_tf), st))
+        # the side chain is enqueued AFTER the critical chain: its persistent CTAs then fill what the one-wave
+        # object-distance / QP kernels leave free instead of holding the SMs while the critical chain waits
+        self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
+                                       row("E_pen"), p(self.pen_scratch), self.weights["E_pen"], p(self.g_link_tf), s2))
+        self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
+                                         self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
+                                         p(self.g_pose_joints), s2))
         if overlap:
             be.join()
         self._ck(lib.gqp_fk_backward(self.hand, p(pose), p(self.g_link_tf), p(self.g_pose_joints), Bt, p(grad_out), st))
