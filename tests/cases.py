@@ -98,8 +98,8 @@ def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5):
     lib.gqp_hand_destroy(hand)
 
 
-def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=False):
-    pack = hand_pack.load_pack("allegro")
+def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=False, hand="allegro"):
+    pack = hand_pack.load_pack(hand)
     v, f = synth.make_mesh("hull" if hull else "sphere", 400, seed)
     fv = synth.face_vertices(v, f)
     sp = synth.sample_surface(v, f, n_pts, seed=seed)

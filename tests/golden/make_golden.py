@@ -60,30 +60,35 @@ def gen_sdf():
 
 
 def gen_fk():
-    pack = hand_pack.load_pack("allegro")
-    chain, frames = rh.pk_chain_from_pack(pack)
-    rng = np.random.default_rng(3)
-    B = 6
-    lo, hi = pack["joints_lower"], pack["joints_upper"]
-    theta = (lo + (hi - lo) * rng.random((B, len(lo)))).astype(np.float32)
-    theta[0] = 0.0          # the perturbation's discontinuity: theta == 0 -> -0.01
-    theta[1, ::2] = -0.05   # negative angles
-    th = torch.tensor(theta)
-    th_dict = {f"j{f}": th[:, int(d)] for f, d in enumerate(pack["frame_dof"]) if d >= 0}
-    res = chain.forward_kinematics(th_dict)
-    link_m = np.stack([res[f"l{int(f)}"].get_matrix().expand(B, 4, 4).numpy() for f in pack["mesh_frame"]], 1)
-    # contact candidates through Transform3d.transform_points / transform_normals (hand_model.py:1233-1248)
-    cp, cn = [], []
-    for li, f in enumerate(pack["mesh_frame"]):
-        m = pack["cand_link"] == li
-        if m.sum() == 0:
-            continue
-        T = res[f"l{int(f)}"]
-        cp.append(T.transform_points(torch.tensor(pack["cand"][m])).expand(B, -1, -1))
-        cn.append(T.transform_normals(torch.tensor(pack["cand_normal"][m])).expand(B, -1, -1))
-    np.savez_compressed(os.path.join(HERE, "fk_ref.npz"), theta=theta, link_matrices=link_m.astype(np.float32),
-                        cand_points=torch.cat(cp, 1).numpy(), cand_normals=torch.cat(cn, 1).numpy())
-    print("fk_ref.npz", link_m.shape)
+    out = {}
+    for hand in ("allegro", "shadow_hand", "panda"):
+        pack = hand_pack.load_pack(hand)
+        chain, frames = rh.pk_chain_from_pack(pack)
+        rng = np.random.default_rng(3)
+        B = 6
+        lo, hi = pack["joints_lower"], pack["joints_upper"]
+        theta = (lo + (hi - lo) * rng.random((B, len(lo)))).astype(np.float32)
+        theta[0] = 0.0          # the perturbation's discontinuity: theta == 0 -> -0.01
+        theta[1, ::2] = -0.05   # negative angles
+        th = torch.tensor(theta)
+        # hands/panda.py:6-14 feeds the single parameter to both finger joints: frame_dof repeats the column
+        th_dict = {f"j{f}": th[:, int(d)] for f, d in enumerate(pack["frame_dof"]) if d >= 0}
+        res = chain.forward_kinematics(th_dict)
+        link_m = np.stack([res[f"l{int(f)}"].get_matrix().expand(B, 4, 4).numpy() for f in pack["mesh_frame"]], 1)
+        # contact candidates through Transform3d.transform_points / transform_normals (hand_model.py:1233-1248)
+        cp, cn = [], []
+        for li, f in enumerate(pack["mesh_frame"]):
+            m = pack["cand_link"] == li
+            if m.sum() == 0:
+                continue
+            T = res[f"l{int(f)}"]
+            cp.append(T.transform_points(torch.tensor(pack["cand"][m])).expand(B, -1, -1))
+            cn.append(T.transform_normals(torch.tensor(pack["cand_normal"][m])).expand(B, -1, -1))
+        k = "" if hand == "allegro" else hand + "_"
+        out.update({k + "theta": theta, k + "link_matrices": link_m.astype(np.float32),
+                    k + "cand_points": torch.cat(cp, 1).numpy(), k + "cand_normals": torch.cat(cn, 1).numpy()})
+        print("fk_ref", hand, link_m.shape)
+    np.savez_compressed(os.path.join(HERE, "fk_ref.npz"), **out)
 
 
 def gen_metric():

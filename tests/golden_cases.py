@@ -48,26 +48,31 @@ def check_sdf(lib, be):
         lib.gqp_mesh_destroy(m)
 
 
-def check_fk(lib, be):
+def check_fk(lib, be, hands=("allegro", "shadow_hand", "panda")):
     """H2/H3 against pytorch_kinematics' Chain.forward_kinematics and Transform3d.transform_points/normals."""
     g = load("fk_ref")
-    pack = hand_pack.load_pack("allegro")
-    hand = hand_pack.create_hand(lib, pack)
-    theta = g["theta"]
-    B, L, C = len(theta), len(pack["mesh_frame"]), len(pack["cand"])
-    pose = np.zeros((B, 9 + theta.shape[1]), np.float32)
-    pose[:, 3], pose[:, 7] = 1.0, 1.0  # identity global rotation (ortho6d), zero translation
-    pose[:, 9:] = theta
-    dpose, tf = be.from_host(pose, np.float32), be.empty((B, L, 12), np.float32)
-    _lib.check(lib.gqp_fk_forward(hand, be.ptr(dpose), B, be.ptr(tf), be.stream), lib)
-    np.testing.assert_allclose(be.to_host(tf).reshape(B, L, 3, 4), g["link_matrices"][:, :, :3, :], atol=2e-6)
-    idx = np.tile(np.arange(C, dtype=np.int32), (B, 1))
-    cp, cn = be.empty((B, C, 3), np.float32), be.empty((B, C, 3), np.float32)
-    _lib.check(lib.gqp_contacts_forward(hand, be.ptr(tf), be.ptr(be.from_host(idx, np.int32)), B, C, be.ptr(cp),
-                                        be.ptr(cn), be.stream), lib)
-    np.testing.assert_allclose(be.to_host(cp), g["cand_points"], atol=2e-6)
-    np.testing.assert_allclose(be.to_host(cn), g["cand_normals"], atol=5e-6)
-    lib.gqp_hand_destroy(hand)
+    for name in hands:
+        k = "" if name == "allegro" else name + "_"
+        pack = hand_pack.load_pack(name)
+        hand = hand_pack.create_hand(lib, pack)
+        theta = g[k + "theta"]
+        B, L, C = len(theta), len(pack["mesh_frame"]), len(pack["cand"])
+        pose = np.zeros((B, 9 + theta.shape[1]), np.float32)
+        pose[:, 3], pose[:, 7] = 1.0, 1.0  # identity global rotation (ortho6d), zero translation
+        pose[:, 9:] = theta
+        dpose, tf = be.from_host(pose, np.float32), be.empty((B, L, 12), np.float32)
+        _lib.check(lib.gqp_fk_forward(hand, be.ptr(dpose), B, be.ptr(tf), be.stream), lib)
+        np.testing.assert_allclose(be.to_host(tf).reshape(B, L, 3, 4), g[k + "link_matrices"][:, :, :3, :], atol=2e-6,
+                                   err_msg=name)
+        # candidates in the reference's concatenation order = ascending link, then table order
+        order = np.argsort(pack["cand_link"], kind="stable").astype(np.int32)
+        idx = np.tile(order, (B, 1))
+        cp, cn = be.empty((B, C, 3), np.float32), be.empty((B, C, 3), np.float32)
+        _lib.check(lib.gqp_contacts_forward(hand, be.ptr(tf), be.ptr(be.from_host(idx, np.int32)), B, C, be.ptr(cp),
+                                            be.ptr(cn), be.stream), lib)
+        np.testing.assert_allclose(be.to_host(cp), g[k + "cand_points"], atol=2e-6, err_msg=name)
+        np.testing.assert_allclose(be.to_host(cn), g[k + "cand_normals"], atol=5e-6, err_msg=name)
+        lib.gqp_hand_destroy(hand)
 
 
 def check_metric(lib, be):

@@ -25,13 +25,15 @@ def test_oracle_sdf_port_matches_reference_kernel(oracle_built):
         np.testing.assert_allclose(nr * 2 * np.sqrt(d2)[:, None], 2 * (g[key + "_points"] - cl), atol=5e-7)
 
 
-def test_oracle_fk_matches_pytorch_kinematics():
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda"])
+def test_oracle_fk_matches_pytorch_kinematics(hand):
     g = gc.load("fk_ref")
-    pack = hand_pack.load_pack("allegro")
+    k = "" if hand == "allegro" else hand + "_"
+    pack = hand_pack.load_pack(hand)
     o = HandOracle(pack, torch.float32)
-    st = o.fk(torch.tensor(g["theta"]))
+    st = o.fk(torch.tensor(g[k + "theta"]))
     got = np.stack([st[int(f)].numpy() for f in pack["mesh_frame"]], 1)
-    np.testing.assert_allclose(got, g["link_matrices"], atol=1e-6)
+    np.testing.assert_allclose(got, g[k + "link_matrices"], atol=1e-6)
 
 
 def test_oracle_solver_known_answer():

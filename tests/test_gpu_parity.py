@@ -98,3 +98,8 @@ def test_trajectory_500_steps_teacher_forced(gpu):
     n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=500)
     print(f"500-step trajectory: {n_acc} accepted, {n_tie} borderline accept mismatches, worst energy error {worst:.2e}")
     assert n_acc > 500
+
+
+@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4)])
+def test_engine_vs_oracle_other_hands(gpu, hand, n_c):
+    cases.check_engine_vs_oracle(*gpu, B=6, n_pts=200, n_c=n_c, T=3, seed=5, hand=hand)

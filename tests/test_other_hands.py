@@ -1,0 +1,14 @@
+"""Hands beyond Allegro (Shadow 24 dof / 18 mesh links, Panda 1 dof driving two prismatic fingers):
+the whole iteration through the emulated kernels vs the fp64 oracle.  FK / contact transforms of these hands are pinned
+against pytorch_kinematics itself in tests/test_golden.py (fk_ref.npz)."""
+import numpy as np
+import pytest
+
+import cases
+from graspqp_b200 import engine
+
+
+@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4)])
+def test_iteration_vs_oracle_other_hands(emu, hand, n_c):
+    n_acc = cases.check_engine_vs_oracle(emu, engine.NumpyBackend(), B=3, n_pts=48, n_c=n_c, T=2, seed=5, hand=hand)
+    assert n_acc >= 0

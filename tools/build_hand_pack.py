@@ -38,6 +38,20 @@ HANDS = {
         default_state=[0.0, 0.2, 0.5, 0.5, 0, 0.2, 0.5, 0.5, 0.0, 0.2, 0.5, 0.5, 1.0, 0.5, 0.5, 0.2],
         forward_axis="z", up_axis="x", grasp_axis="y",
     ),
+    # graspqp/src/graspqp/hands/shadow.py
+    "shadow_hand": dict(
+        urdf="shadow_hand/shadow_hand.urdf", mesh_dir="shadow_hand/meshes",
+        pen="shadow_hand/penetration_points.json", use_collision=True, only_collision=False, joint_filter=None,
+        default_state=[0, 0, 0.1, 0, 0.6, 0, 0, -0.2, 0, 0.6, 0, 0, 0.0, 0.6, 0, -0.1, 0, 0.6, 0, 0, 1.2, 0.0, -0.2, 0.0],
+        forward_axis="z", up_axis="x", grasp_axis="y",
+    ),
+    # graspqp/src/graspqp/hands/panda.py: one parameter drives both finger joints (calculate_joints, :6-14)
+    "panda": dict(
+        urdf="panda/franka_panda.urdf", mesh_dir="panda/meshes",
+        pen="panda/penetration_points.json", use_collision=True, only_collision=False,
+        joint_filter=["panda_finger_joint1"], coupled={"panda_finger_joint2": "panda_finger_joint1"},
+        default_state=[0.04], forward_axis="z", up_axis="x", grasp_axis="y",
+    ),
 }
 
 
@@ -157,7 +171,9 @@ def build(hand):
     # joint parameter order = DFS order of non-fixed joints (chain.py:128-138), then joint_filter
     jnames = [f["jname"] for f in frames if f["jtype"] != 0]
     act = [n for n in jnames if cfg["joint_filter"] is None or n in cfg["joint_filter"]]
-    frame_dof = [act.index(f["jname"]) if (f["jtype"] != 0 and f["jname"] in act) else -1 for f in frames]
+    coupled = cfg.get("coupled", {})  # joint -> the actuated joint whose parameter it copies
+    drv = lambda n: coupled.get(n, n)
+    frame_dof = [act.index(drv(f["jname"])) if (f["jtype"] != 0 and drv(f["jname"]) in act) else -1 for f in frames]
     lower = [f["lo"] for f in frames if f["jname"] in act and f["jtype"] != 0]
     upper = [f["hi"] for f in frames if f["jname"] in act and f["jtype"] != 0]
 
