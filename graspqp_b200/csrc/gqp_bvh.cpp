@@ -163,6 +163,91 @@ void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &ou
     }
 }
 
+// ---- 8-wide form of the tree (gqp_bvh.cuh: bvh_query_gang) ---------------------------------------------------------
+// Collapses the binary tree: a wide node starts from a binary node's two children and keeps replacing the inner child
+// with the largest box surface by that child's two children until it has 8 children or only leaves.  Boxes are the
+// binary nodes' (already inflated) boxes, leaves are the binary leaves, so the set of faces and the bounds are unchanged.
+namespace {
+double box_area(const GqpBvhNode &n) {
+    double x = (double)n.hi[0] - n.lo[0], y = (double)n.hi[1] - n.lo[1], z = (double)n.hi[2] - n.lo[2];
+    return x * y + y * z + z * x;
+}
+// Patch record of a leaf (same layout as a face's pre-test record): unit mean normal, radius of the circle around the
+// centre that holds every vertex, centre, half-thickness of the slab |n.(x - c)| <= tau that holds every vertex.  The
+// faces are convex hulls of their vertices, so every point of the patch satisfies both constraints.  Normal and centre
+// are rounded to fp32 FIRST; radius and thickness are measured from the rounded values in double and rounded up.
+void patch_record(const GqpBvhHost &in, int first, int count, float *q) {
+    D3 nsum = {0, 0, 0}, csum = {0, 0, 0};
+    for (int i = first; i < first + count; ++i) {
+        const float *t = &in.tris[9 * (size_t)i];
+        D3 a = ldv(t), b = ldv(t + 3), c = ldv(t + 6);
+        nsum = nsum + cross(b - a, c - a);
+        csum = csum + a + b + c;
+    }
+    D3 cen = csum * (1.0 / (3.0 * count));
+    double l = std::sqrt(dot(nsum, nsum));
+    float nf[3] = {0.f, 0.f, 0.f};
+    if (l > 1e-30) { nf[0] = (float)(nsum.x / l); nf[1] = (float)(nsum.y / l); nf[2] = (float)(nsum.z / l); }
+    float cf[3] = {(float)cen.x, (float)cen.y, (float)cen.z};
+    D3 nr = {nf[0], nf[1], nf[2]}, cr = {cf[0], cf[1], cf[2]};
+    double r = 0, tau = 0;
+    for (int i = first; i < first + count; ++i)
+        for (int v = 0; v < 3; ++v) {
+            D3 x = ldv(&in.tris[9 * (size_t)i + 3 * v]);
+            r = std::max(r, std::sqrt(dot(x - cr, x - cr)));
+            tau = std::max(tau, std::fabs(dot(nr, x - cr)));
+        }
+    const double pad = 1e-7 * (std::fabs(cen.x) + std::fabs(cen.y) + std::fabs(cen.z)) + 1e-30;
+    q[0] = nf[0]; q[1] = nf[1]; q[2] = nf[2];
+    q[3] = (float)(r * 1.0001 + pad);
+    q[4] = cf[0]; q[5] = cf[1]; q[6] = cf[2];
+    q[7] = (float)(tau * 1.0001 + pad);
+}
+int widen(const GqpBvhHost &in, int bin, int depth, GqpBvhHost &out) {
+    const int id = (int)out.wide.size() / 8;
+    out.wide.resize(out.wide.size() + 8, GqpBvhNode());
+    out.wide_pre.resize(out.wide_pre.size() + 64, 0.f);
+    out.wide_depth = std::max(out.wide_depth, depth);
+    std::vector<int> kids;
+    if (in.nodes[bin].b < 0) kids.push_back(bin);  // a mesh of <= leaf_size faces: the root is a leaf
+    else kids = {in.nodes[bin].a, in.nodes[bin].b};
+    while (kids.size() < 8) {
+        int pick = -1;
+        for (size_t i = 0; i < kids.size(); ++i)
+            if (in.nodes[kids[i]].b >= 0 && (pick < 0 || box_area(in.nodes[kids[i]]) > box_area(in.nodes[kids[pick]])))
+                pick = (int)i;
+        if (pick < 0) break;
+        const GqpBvhNode n = in.nodes[kids[pick]];
+        kids[pick] = n.a;
+        kids.push_back(n.b);
+    }
+    for (size_t i = 0; i < kids.size(); ++i) {
+        GqpBvhNode r = in.nodes[kids[i]];
+        if (r.b >= 0) {
+            r.a = widen(in, kids[i], depth + 1, out);
+            r.b = 1;
+        } else {
+            patch_record(in, r.a, -r.b, &out.wide_pre[8 * (8 * (size_t)id + i)]);
+        }
+        out.wide[8 * (size_t)id + i] = r;
+    }
+    return id;
+}
+}  // namespace
+
+void gqp_bvh_widen(GqpBvhHost &bvh) {
+    bvh.wide.clear();
+    bvh.wide_pre.clear();
+    bvh.wide_depth = 0;
+    if (bvh.nodes.empty()) return;
+    GqpBvhHost tmp;
+    tmp.wide_depth = 0;
+    widen(bvh, 0, 1, tmp);
+    bvh.wide.swap(tmp.wide);
+    bvh.wide_pre.swap(tmp.wide_pre);
+    bvh.wide_depth = tmp.wide_depth;
+}
+
 // ---- exact culling of "outside" queries ------------------------------------------------------------------------------
 // The reference's sign is sign(dot(p - c, n_f)) for the WINNING face f (.cu:236); c lies in f's plane, so it is the side
 // of f's plane p is on.  For a closed, consistently outward-oriented manifold mesh and a point p OUTSIDE it, p - c lies

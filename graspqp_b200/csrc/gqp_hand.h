@@ -27,9 +27,14 @@ struct GqpBvhHost {
     std::vector<float> pre;          // (F,8) per slot: unit normal xyz, bounding-circle radius, centroid xyz, 0
     float extent = 0.f;              // max |coordinate| of the mesh
     int max_depth = 0;
+    std::vector<GqpBvhNode> wide;    // 8-wide form (gqp_bvh_widen): 8 child records per wide node, wide node 0 = root
+    std::vector<float> wide_pre;     // (8 per wide node, 8) patch record of each leaf child (gqp_bvh.cpp: patch_record)
+    int wide_depth = 0;
 };
 // leaf_size: max faces per leaf
 void gqp_bvh_build(const float *face_verts, int F, int leaf_size, GqpBvhHost &out);
+// fills bvh.wide / bvh.wide_depth from bvh.nodes (leaf_size must be <= 8)
+void gqp_bvh_widen(GqpBvhHost &bvh);
 
 // Exact culling support (gqp_bvh.cpp): a "nice" mesh is a closed, outward-oriented manifold without creases sharper
 // than 90 degrees; the reference's sign heuristic returns +1 for every point outside such a mesh.
@@ -41,10 +46,11 @@ struct GqpMesh {
     int F = 0;
     int n_nodes = 0;
     int max_depth = 0;
-    GqpBvhNode *d_nodes = nullptr;  // device
+    GqpBvhNode *d_nodes = nullptr;  // device: wide records, 8 per wide node
     float *d_tris = nullptr;        // device (F,9) leaf order
     int32_t *d_face_id = nullptr;   // device (F)
     float *d_pre = nullptr;         // device (F,8) pre-test records in leaf order
+    float *d_wpre = nullptr;        // device (8 per wide node, 8) patch records of leaf children
     float extent = 0.f;
 };
 

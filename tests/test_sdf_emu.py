@@ -58,3 +58,19 @@ def test_sdf_backward_emu(emu):
     out = np.empty((50, 3), np.float32)
     assert emu.gqp_sdf_backward(ptr(g), ptr(p), ptr(c), 50, ptr(out), None) == 0
     np.testing.assert_array_equal(out, (p - c) * (2 * g)[:, None])
+
+
+@pytest.mark.parametrize("kind,nf,P", [("sphere", 3, 5), ("sphere", 8, 1), ("sphere", 9, 37), ("box", 70, 33),
+                                        ("torus", 1100, 41), ("hull", 3000, 24)])
+def test_mesh_sdf_gang_emu_bit_exact(emu, oracle_built, kind, nf, P):
+    """gqp_mesh_sdf_forward (8-lane gangs over the 8-wide BVH) == brute force, winner face included; covers a root that
+    is a leaf, a single partial wide node, ragged last blocks."""
+    import cases
+    from graspqp_b200 import engine
+    v, f = synth.make_mesh(kind if nf > 9 else "sphere", max(nf, 40), 3)
+    fv = synth.face_vertices(v, f)[:nf] if nf <= 9 else synth.face_vertices(v, f)
+    pts = cases.query_points(fv, P, seed=nf)
+    want = osdf.compute_sdf_port(pts, fv, with_face=True)
+    got = cases.mesh_sdf_forward(emu, engine.NumpyBackend(), pts, fv)
+    for g, w in zip(got, want):
+        np.testing.assert_array_equal(g, w)

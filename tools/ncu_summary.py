@@ -74,15 +74,17 @@ def source(path, kernel, top=25):
         elif H and len(r) > 8 and r[2] == '-':
             try:
                 smp, ins = float(r[H.index('# Samples')]), float(r[H.index('Instructions Executed')])
+                thr = float(r[H.index('Thread Instructions Executed')])
             except ValueError:
                 continue
-            a = acc.setdefault((cur, r[0], r[1].strip()[:80]), [0.0, 0.0])
+            a = acc.setdefault((cur, r[0], r[1].strip()[:80]), [0.0, 0.0, 0.0])
             a[0] += smp
             a[1] += ins
+            a[2] += thr
     ts, ti = sum(a[0] for a in acc.values()) or 1, sum(a[1] for a in acc.values()) or 1
     print(f"{kernel}: {ts:.0f} samples, {ti:.3g} warp instructions (summed over captured launches)")
     for k, a in sorted(acc.items(), key=lambda kv: -kv[1][0])[:top]:
-        print(f"{a[0] / ts * 100:5.1f}% smp {a[1] / ti * 100:5.1f}% inst  {k[0]}:{k[1]}  {k[2]}")
+        print(f"{a[0] / ts * 100:5.1f}% smp {a[1] / ti * 100:5.1f}% inst {a[2] / max(a[1], 1):5.1f} thr/inst  {k[0]}:{k[1]}  {k[2]}")
 
 
 if __name__ == '__main__':
