@@ -264,11 +264,74 @@ struct PenGroup {
 };
 #define PEN_FIX_SCALE 1099511627776.0  // 2^40
 
+// Broad phase, a warp per candidate: which links can matter for the candidate's point row at all (row sphere vs link
+// box, lane = link), then, lanes = 32-sample chunks of the row, which of those links each chunk's bounding sphere
+// reaches.  Chunks that reach a link become work items (candidate, chunk, link mask) for the narrow phase.  Exact for
+// "nice" links (see gqp_bvh.cpp); links without an outside-grid are always kept.
+struct PenItem {
+    uint32_t b, chunk, links;
+};
+#define PEN_BROAD_WARPS 4
+__global__ void __launch_bounds__(PEN_BROAD_WARPS * 32)
+pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict__ link_tf,
+                 const float *__restrict__ bounds, int Bt, int batch_each, int n_chunks, int per_candidate_points,
+                 uint32_t *__restrict__ counter, PenItem *__restrict__ items) {
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x * PEN_BROAD_WARPS + (threadIdx.x >> 5);
+    if (b >= Bt) return;
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(blob);
+    const PenLink *links = reinterpret_cast<const PenLink *>(blob + hdr->links_off);
+    const int L = hdr->n_links;
+    const int row = per_candidate_points ? b : b / batch_each;
+    const float *br = bounds + (size_t)row * (n_chunks + 1) * 4;
+    const float *Wb = link_tf + (size_t)b * L * 12;
+    bool keep = false;
+    if (lane < L && links[lane].n_faces > 0) {  // hand_model.py:919-921: links without a mesh are skipped
+        const PenLink &K = links[lane];
+        keep = true;
+        if (K.grid >= 0) {
+            const float rad = br[4 * n_chunks + 3];
+            const V3 q = t34_inv_point(t34_load(Wb + lane * 12), V3{br[4 * n_chunks], br[4 * n_chunks + 1], br[4 * n_chunks + 2]});
+            keep = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
+                     q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
+        }
+    }
+    const uint32_t rowmask = __ballot_sync(GQP_FULL, keep);
+    if (rowmask == 0) return;
+    for (int c0 = 0; c0 < n_chunks; c0 += 32) {
+        const int c = c0 + lane;
+        uint32_t cm = 0;
+        if (c < n_chunks) {
+            const V3 cen = V3{br[4 * c], br[4 * c + 1], br[4 * c + 2]};  // scratch is only 4-byte aligned
+            const float rad = br[4 * c + 3];
+            for (uint32_t m = rowmask; m; m &= m - 1) {
+                const int l = __ffs((int)m) - 1;
+                const PenLink &K = links[l];
+                bool hit = true;
+                if (K.grid >= 0) {
+                    const V3 q = t34_inv_point(t34_load(Wb + l * 12), cen);
+                    hit = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
+                            q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
+                }
+                if (hit) cm |= 1u << l;
+            }
+        }
+        const unsigned em = __ballot_sync(GQP_FULL, cm != 0);
+        if (em) {
+            int base = 0;
+            if (lane == 0) base = (int)atomicAdd(counter + 1, (unsigned)__popc(em));
+            base = __shfl_sync(GQP_FULL, base, 0);
+            if (cm) items[base + __popc(em & ((1u << lane) - 1u))] = PenItem{(uint32_t)b, (uint32_t)c, cm};
+        }
+    }
+}
+
+// Narrow phase, a warp per work item, lane = sample: the sample is dropped for a link when it is provably outside it
+// (outside the box, or in an outside cell of the link's grid); the others are queued for the exact search.
 __global__ void __launch_bounds__(PEN_THREADS)
 pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, const float *__restrict__ link_tf,
-                   const float *__restrict__ x, const float *__restrict__ bounds, const uint32_t *__restrict__ masks,
-                   int n_rows, int cands_per_row, int n_pts, uint32_t *__restrict__ counter,
-                   PenGroup *__restrict__ queue) {
+                   const float *__restrict__ x, int batch_each, int per_candidate_points, int n_pts,
+                   uint32_t *__restrict__ counter, const PenItem *__restrict__ items, PenGroup *__restrict__ queue) {
     GQP_DYN_SMEM(unsigned char, sm);
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) mbar_init(&bar);
@@ -281,60 +344,26 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
     const uint32_t *bits = reinterpret_cast<const uint32_t *>(sm + hdr->bits_off);
     const int L = hdr->n_links;
     const int lane = threadIdx.x & 31, warps_per_block = blockDim.x / 32;
-    float *sW = reinterpret_cast<float *>(sm + prefix_bytes) + (size_t)(threadIdx.x >> 5) * L * 12;
-    const int n_chunks = (n_pts + 31) / 32;
-    const int n_cblk = (cands_per_row + PEN_CB - 1) / PEN_CB;
-    const int n_tasks = n_rows * n_chunks * n_cblk;
-    for (int task = blockIdx.x * warps_per_block + (threadIdx.x >> 5); task < n_tasks;
-         task += gridDim.x * warps_per_block) {
-        const int cb = task % n_cblk, rc = task / n_cblk;
-        const int chunk = rc % n_chunks, row = rc / n_chunks;
-        const int pi = chunk * 32 + lane;
+    const unsigned n_items = counter[1];
+    for (unsigned it = blockIdx.x * warps_per_block + (threadIdx.x >> 5); it < n_items; it += gridDim.x * warps_per_block) {
+        const PenItem I = items[it];
+        const int b = (int)I.b, pi = (int)I.chunk * 32 + lane;
+        const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
         const bool valid = pi < n_pts;
-        const V3 p = ld3(x + ((size_t)row * n_pts + (valid ? pi : n_pts - 1)) * 3);
-        const float *sph = bounds + ((size_t)row * (n_chunks + 1) + chunk) * 4;
-        const V3 cen = V3{sph[0], sph[1], sph[2]};
-        const float rad = sph[3];
-        const int b_end = row * cands_per_row + min(cands_per_row, (cb + 1) * PEN_CB);
-        for (int b = row * cands_per_row + cb * PEN_CB; b < b_end; ++b) {
-            const uint32_t mask = masks[b];
-            if (mask == 0) continue;  // the whole row is outside every link of this candidate
-            const float *Wb = link_tf + (size_t)b * L * 12;
-            bool keep = false;
-            if ((mask >> lane) & 1u) {  // lane l: stage link l's transform, chunk sphere vs link box
-                T34 W = t34_load(Wb + lane * 12);
-#pragma unroll
-                for (int i = 0; i < 12; ++i) sW[lane * 12 + i] = W.m[i];
-                const PenLink &K = links[lane];
-                keep = true;
-                if (K.grid >= 0) {
-                    V3 q = t34_inv_point(W, cen);
-                    if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
-                        q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
-                        keep = false;
-                }
-            }
-            unsigned todo = __ballot_sync(GQP_FULL, keep);
-            if (todo == 0) continue;
-            __syncwarp();
-            uint32_t need = 0;
-            while (todo) {
-                const int l = __ffs((int)todo) - 1;
-                todo &= todo - 1;
-                T34 W;
-#pragma unroll
-                for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
-                if (!pen_outside(links[l], grids, bits, t34_inv_point(W, p))) need |= 1u << l;
-            }
-            if (!valid) need = 0;  // padding lanes of the last chunk
-            const unsigned em = __ballot_sync(GQP_FULL, need != 0);
-            if (em) {
-                int base = 0;
-                if (lane == 0) base = (int)atomicAdd(counter, (unsigned)__popc(em));
-                base = __shfl_sync(GQP_FULL, base, 0);
-                if (need) queue[base + __popc(em & ((1u << lane) - 1u))] = PenGroup{(uint32_t)(b * n_pts + pi), need};
-            }
-            __syncwarp();  // sW is rewritten for the next candidate
+        const V3 p = ld3(x + (row * n_pts + (valid ? pi : n_pts - 1)) * 3);
+        const float *Wb = link_tf + (size_t)b * L * 12;
+        uint32_t need = 0;
+        for (uint32_t m = I.links; m; m &= m - 1) {
+            const int l = __ffs((int)m) - 1;
+            if (!pen_outside(links[l], grids, bits, t34_inv_point(t34_load(Wb + l * 12), p))) need |= 1u << l;
+        }
+        if (!valid) need = 0;  // padding lanes of the last chunk
+        const unsigned em = __ballot_sync(GQP_FULL, need != 0);
+        if (em) {
+            int base = 0;
+            if (lane == 0) base = (int)atomicAdd(counter, (unsigned)__popc(em));
+            base = __shfl_sync(GQP_FULL, base, 0);
+            if (need) queue[base + __popc(em & ((1u << lane) - 1u))] = PenGroup{(uint32_t)(b * n_pts + pi), need};
         }
     }
 }
@@ -643,24 +672,24 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
     int rc = GQP_OK;
     GQP_LAUNCH(pen_bounds_kernel, n_rows, 256, 0, st, x, n_pts, n_chunks, bounds);
     GQP_CHECK_LAUNCH("gqp_hand_distance/bounds");
-    GQP_LAUNCH(pen_mask_kernel, (Bt + 127) / 128, 128, 0, st, T->d_blob, link_tf, bounds, Bt, batch_each, n_chunks,
-               per_candidate_points, cull, masks);
-    GQP_CHECK_LAUNCH("gqp_hand_distance/mask");
     if (cull) {
-        // [counter 4 words][fixed-point energy accumulators Bt x u64][queue Bt*n_pts groups], 8-byte aligned
+        // [counters 4 words][fixed-point energy accumulators Bt x u64][queue Bt*n_pts groups][items Bt*n_chunks]
         uint32_t *tail = masks + Bt;
         tail += ((uintptr_t)tail & 7) ? 1 : 0;
-        uint32_t *counter = tail;
+        uint32_t *counter = tail;  // [0] groups queued for the search, [1] work items of the narrow phase
         unsigned long long *acc = reinterpret_cast<unsigned long long *>(tail + 4);
         PenGroup *queue = reinterpret_cast<PenGroup *>(acc + Bt);
+        PenItem *items = reinterpret_cast<PenItem *>(queue + (size_t)Bt * n_pts);
         rc = gqp_memset_zero(tail, 16 + sizeof(unsigned long long) * (size_t)Bt, stream);
         if (rc != GQP_OK) return rc;
+        GQP_LAUNCH(pen_broad_kernel, (Bt + PEN_BROAD_WARPS - 1) / PEN_BROAD_WARPS, PEN_BROAD_WARPS * 32, 0, st, T->d_blob,
+                   link_tf, bounds, Bt, batch_each, n_chunks, per_candidate_points, counter, items);
+        GQP_CHECK_LAUNCH("gqp_hand_distance/broad");
         const PenHdr *hdr = reinterpret_cast<const PenHdr *>(T->blob_host.data());
         const int prefix = hdr->nodes_off;  // header, links, grids, outside-grid bits
-        const size_t smem1 = (size_t)prefix + (size_t)(PEN_THREADS / 32) * h->host.n_links * 48;
-        int grid1 = pen_grid_size((int)smem1, n_tasks, 3);  // 39 registers x 512 threads: 3 CTAs per SM
-        GQP_LAUNCH(pen_collect_kernel, grid1, PEN_THREADS, smem1, st, T->d_blob, prefix, link_tf, x, bounds, masks,
-                   n_rows, cands_per_row, n_pts, counter, queue);
+        int grid1 = pen_grid_size(prefix, (long long)Bt * n_chunks, 3);
+        GQP_LAUNCH(pen_collect_kernel, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x, batch_each,
+                   per_candidate_points, n_pts, counter, items, queue);
         GQP_CHECK_LAUNCH("gqp_hand_distance/collect");
         int grid2 = pen_grid_size(T->total_bytes, 1LL << 40, 3);
         GQP_LAUNCH(pen_search_kernel, grid2, PEN_Q_THREADS, (size_t)T->total_bytes, st, T->d_blob, T->total_bytes,
@@ -673,6 +702,9 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
         }
         return GQP_OK;
     }
+    GQP_LAUNCH(pen_mask_kernel, (Bt + 127) / 128, 128, 0, st, T->d_blob, link_tf, bounds, Bt, batch_each, n_chunks,
+               per_candidate_points, cull, masks);
+    GQP_CHECK_LAUNCH("gqp_hand_distance/mask");
     rc = gqp_memset_zero(partial, sizeof(float) * (size_t)Bt * n_chunks, stream);
     if (rc != GQP_OK) return rc;
     const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * (h->host.n_links * 48);
@@ -781,6 +813,8 @@ extern "C" int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host) {
 extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {
     const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
     const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;
-    // + culled path: counter (4 words + alignment), fixed-point accumulators (2 words each), queue (2 words per sample)
-    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16 + 8 + 2 * Bt + 2 * Bt * (uint64_t)n_pts;
+    // + culled path: counters (4 words + alignment), fixed-point accumulators (2 words each), queue (2 words per
+    // sample), work items of the narrow phase (3 words per candidate and chunk)
+    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16 + 8 + 2 * Bt + 2 * Bt * (uint64_t)n_pts +
+           3 * Bt * n_chunks;
 }
