@@ -124,10 +124,12 @@ struct BvhTree {
 };
 // A warp owns the queries [q_begin, q_end); a gang that finishes a query takes the warp's next one, so the 4 gangs of a
 // warp stay busy although their searches differ in length.  fetch(i, p, tree) loads query i (executed by the 8 lanes
-// of the gang), emit(i, p, best) stores the result (executed by the lane that holds the winner).
+// of the gang).  done(i, p, tree, winner) is called on all 8 lanes when a search completes, with the winner broadcast;
+// it stores the result and returns false, or replaces p / tree and returns true to run a follow-up search under the
+// same query index (the hand-penetration search walks several link meshes per sample).
 // stk: this gang's GQP_GANG_STACK entries (code, lower bound bits) in shared memory.
-template <bool EXACT, class Fetch, class Emit>
-__device__ __forceinline__ void bvh_query_gang(int q_begin, int q_end, int2 *stk, Fetch fetch, Emit emit) {
+template <bool EXACT, class Fetch, class Done>
+__device__ __forceinline__ void bvh_query_gang(int q_begin, int q_end, int2 *stk, Fetch fetch, Done done) {
     const int lane = threadIdx.x & 31, gl = lane & (GQP_GANG - 1), g0 = lane & ~(GQP_GANG - 1);
     const float INF = __int_as_float(0x7f800000);
     BvhTree tr = {nullptr, nullptr, nullptr, nullptr, nullptr, 0.f};
@@ -254,9 +256,28 @@ __device__ __forceinline__ void bvh_query_gang(int q_begin, int q_end, int2 *stk
             }
         }
         bound = fminf(bound, wd);
-        if (qi >= 0 && sp == 0) {  // nothing pending: the search of this query is complete
-            if (best.face == wf && wf != 0x7fffffff) emit(qi, p, best);
-            qi = -1;
+        const bool fin = qi >= 0 && sp == 0;  // nothing pending: this search is complete
+        if (__any_sync(GQP_FULL, fin)) {
+            const unsigned wm = (__ballot_sync(GQP_FULL, best.face == wf) >> g0) & 0xffu;
+            const int src = g0 + (wm ? __ffs((int)wm) - 1 : 0);
+            SdfBest win;
+            win.d2 = wd;
+            win.face = wf;
+            win.c = V3{__shfl_sync(GQP_FULL, best.c.x, src), __shfl_sync(GQP_FULL, best.c.y, src),
+                       __shfl_sync(GQP_FULL, best.c.z, src)};
+            win.normal = V3{__shfl_sync(GQP_FULL, best.normal.x, src), __shfl_sync(GQP_FULL, best.normal.y, src),
+                            __shfl_sync(GQP_FULL, best.normal.z, src)};
+            if (fin) {
+                if (done(qi, p, tr, win)) {
+                    scale = fmaxf(tr.extent, fmaxf(fabsf(p.x), fmaxf(fabsf(p.y), fabsf(p.z))));
+                    sdf_best_init(best);
+                    bound = INF;
+                    if (gl == 0) stk[0] = make_int2(0, 0);
+                    sp = 1;
+                } else {
+                    qi = -1;
+                }
+            }
         }
     }
 }

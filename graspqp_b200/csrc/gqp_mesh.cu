@@ -49,15 +49,18 @@ mesh_sdf_kernel(const GqpBvhNode *__restrict__ nodes, const float *__restrict__ 
             p = ld3(points + 3 * (size_t)i);
             tr = BvhTree{nodes, wpre, tris, face_id, pre, extent};
         },
-        [&](int i, V3 p, const SdfBest &best) {
-            int sg;
-            V3 un;
-            sdf_finish<true>(p, best, sg, un);
-            dist2[i] = best.d2;
-            sign[i] = sg;
-            st3(normals + 3 * (size_t)i, un);
-            st3(clst + 3 * (size_t)i, best.c);
-            if (face_out) face_out[i] = best.face;
+        [&](int i, V3 &p, BvhTree &, const SdfBest &best) {
+            if ((threadIdx.x & (GQP_GANG - 1)) == 0) {
+                int sg;
+                V3 un;
+                sdf_finish<true>(p, best, sg, un);
+                dist2[i] = best.d2;
+                sign[i] = sg;
+                st3(normals + 3 * (size_t)i, un);
+                st3(clst + 3 * (size_t)i, best.c);
+                if (face_out) face_out[i] = best.face;
+            }
+            return false;
         });
 }
 
@@ -79,15 +82,18 @@ object_distance_kernel(const GqpBvhNode *const *__restrict__ nodes, const float 
             p = V3{p.x / scale, p.y / scale, p.z / scale};  // object_model.py:215-216
             tr = BvhTree{nodes[o], wpre[o], tris[o], face_id[o], pre[o], extent[o]};
         },
-        [&](int i, V3 p, const SdfBest &best) {
-            int sg;
-            V3 un;
-            sdf_finish<true>(p, best, sg, un);
-            float d = sqrtf(best.d2 + 1e-8f) * (float)(-sg);  // :243
-            distance[i] = d * scale;                          // :249
-            st3(normals + 3 * (size_t)i, un * (float)sg);     // :246
-            st3(clst + 3 * (size_t)i, best.c);
-            sign[i] = sg;
+        [&](int i, V3 &p, BvhTree &, const SdfBest &best) {
+            if ((threadIdx.x & (GQP_GANG - 1)) == 0) {
+                int sg;
+                V3 un;
+                sdf_finish<true>(p, best, sg, un);
+                float d = sqrtf(best.d2 + 1e-8f) * (float)(-sg);  // :243
+                distance[i] = d * scale;                          // :249
+                st3(normals + 3 * (size_t)i, un * (float)sg);     // :246
+                st3(clst + 3 * (size_t)i, best.c);
+                sign[i] = sg;
+            }
+            return false;
         });
 }
 

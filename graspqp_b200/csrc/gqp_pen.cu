@@ -24,7 +24,7 @@ struct PenHdr {
 struct PenLink {
     int32_t node_first, n_nodes, tri_first, n_faces;
     int32_t grid;  // index of the link's outside-grid, or -1 when the mesh is not "nice" (no culling)
-    int32_t pad;
+    int32_t wide_first;  // first wide node of the link's 8-wide tree in GqpPenTables::d_wide
     float lo[3], hi[3];  // bounding box, slightly inflated
     int32_t pad2[4];
 };
@@ -40,6 +40,8 @@ struct GqpPenTables {
     float *d_tris = nullptr;       // (F_total, 9) leaf order, links concatenated
     int32_t *d_face_id = nullptr;  // (F_total) index inside the link's original face list
     float *d_pre = nullptr;        // (F_total, 8) pre-test records, leaf order
+    GqpBvhNode *d_wide = nullptr;  // 8-wide trees of all links (gqp_bvh_widen), link l starts at wide node links[l].wide_first
+    float *d_wpre = nullptr;       // patch records of the wide trees' leaf children
     float extent = 0.f;            // max |coordinate| over all link meshes
     int total_bytes = 0;
 };
@@ -368,70 +370,86 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
     }
 }
 
-#define PEN_Q_THREADS 256
-__global__ void __launch_bounds__(PEN_Q_THREADS)
-pen_search_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
+// Exact search of the queued samples: 8 lanes per sample over the links' 8-wide trees (gqp_bvh.cuh: bvh_query_gang),
+// links in ascending order (first maximum, hand_model.py:986).  Tree nodes, patch records and faces are read through
+// L1/L2 (all link meshes of a hand are ~0.3 MB), so the kernel's occupancy does not depend on the size of the tables.
+#define PEN_Q_WARPS 4
+#define PEN_Q_QPW 16  // groups per warp and round
+__global__ void __launch_bounds__(PEN_Q_WARPS * 32, 8)
+pen_search_kernel(const unsigned char *__restrict__ blob, const GqpBvhNode *__restrict__ wide,
+                  const float *__restrict__ wpre, const float *__restrict__ tris,
                   const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
                   const float *__restrict__ link_tf, const float *__restrict__ x, int batch_each, int n_pts,
                   int per_candidate_points, const uint32_t *__restrict__ counter, const PenGroup *__restrict__ queue,
                   unsigned long long *__restrict__ acc, float w_pen, float *__restrict__ grad_link_tf) {
-    GQP_DYN_SMEM(unsigned char, sm);
-    __shared__ __align__(8) uint64_t bar;
-    if (threadIdx.x == 0) mbar_init(&bar);
-    __syncthreads();
-    if (threadIdx.x == 0) bulk_load(sm, blob, (uint32_t)blob_bytes, &bar);
-    mbar_wait(&bar, 0);
-    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(sm);
-    const PenLink *links = reinterpret_cast<const PenLink *>(sm + hdr->links_off);
-    const GqpBvhNode *nodes = reinterpret_cast<const GqpBvhNode *>(sm + hdr->nodes_off);
+    __shared__ int2 stk[PEN_Q_WARPS * 32 / GQP_GANG][GQP_GANG_STACK];
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(blob);
+    const PenLink *links = reinterpret_cast<const PenLink *>(blob + hdr->links_off);
     const int L = hdr->n_links;
-    const unsigned n_groups = *counter;
-    for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += gridDim.x * blockDim.x) {
-        const PenGroup G = queue[g];
-        const int b = (int)(G.sample / (unsigned)n_pts), pi = (int)(G.sample % (unsigned)n_pts);
-        const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
-        const V3 p = ld3(x + (row * n_pts + pi) * 3);
-        float best_d = -__int_as_float(0x7f800000);
-        int best_l = -1;
-        V3 best_g = V3{0, 0, 0};
-        uint32_t m = G.need;
-        while (m) {  // ascending link order: first maximum, hand_model.py:986
-            const int l = __ffs((int)m) - 1;
-            m &= m - 1;
-            const PenLink &K = links[l];
-            const T34 W = t34_load(link_tf + ((size_t)b * L + l) * 12);
-            const V3 q = t34_inv_point(W, p);
-            SdfBest best;
-            sdf_best_init(best);
-            bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first,
-                             pre + (size_t)K.tri_first * 8, extent, q, best);
-            const V3 dv = q - best.c;
-            const float sgn = dot3(dv, best.normal) >= 0.f ? 1.f : -1.f;
-            const float r = sqrtf(best.d2 + 1e-8f);
-            const float d = r * (-sgn);  // hand_model.py:975-976
-            if (d > best_d) {
-                best_d = d;
-                best_l = l;
-                best_g = dv * (1.0f / r);
-            }
-        }
-        if (best_d > 0.f) {  // energy.py:60-61
-            if (acc) atomicAdd(acc + b, (unsigned long long)__double2ll_rn((double)best_d * PEN_FIX_SCALE));
-            if (grad_link_tf) {
-                // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
-                const size_t wl = ((size_t)b * L + best_l) * 12;
-                const float *W = link_tf + wl;
-                float *Gm = grad_link_tf + wl;
-                const V3 gg = best_g * w_pen;
-                const float pt[3] = {p.x - W[3], p.y - W[7], p.z - W[11]}, gv[3] = {gg.x, gg.y, gg.z};
-#pragma unroll
-                for (int r2 = 0; r2 < 3; ++r2) {
-#pragma unroll
-                    for (int i = 0; i < 3; ++i) atomicAdd(Gm + 4 * r2 + i, pt[r2] * gv[i]);
-                    atomicAdd(Gm + 4 * r2 + 3, -(W[4 * r2] * gv[0] + W[4 * r2 + 1] * gv[1] + W[4 * r2 + 2] * gv[2]));
+    const int n_groups = (int)*counter;
+    const int gl = threadIdx.x & (GQP_GANG - 1);
+    // per-gang state of the sample being searched (identical on the 8 lanes)
+    V3 P = V3{0, 0, 0}, best_g = V3{0, 0, 0};
+    uint32_t m = 0;
+    int b = 0, cur_l = 0, best_l = -1;
+    float best_d = 0.f;
+    auto enter_link = [&](V3 &q, BvhTree &tr) {
+        cur_l = __ffs((int)m) - 1;
+        m &= m - 1;
+        const PenLink &K = links[cur_l];
+        q = t34_inv_point(t34_load(link_tf + ((size_t)b * L + cur_l) * 12), P);
+        tr = BvhTree{wide + GQP_GANG * (size_t)K.wide_first, wpre + 8 * GQP_GANG * (size_t)K.wide_first,
+                     tris + (size_t)K.tri_first * 9, face_id + K.tri_first, pre + (size_t)K.tri_first * 8, extent};
+    };
+    const int warp = blockIdx.x * PEN_Q_WARPS + (threadIdx.x >> 5), n_warps = gridDim.x * PEN_Q_WARPS;
+    for (int base = warp * PEN_Q_QPW; base < n_groups; base += n_warps * PEN_Q_QPW) {
+        bvh_query_gang<false>(
+            base, min(base + PEN_Q_QPW, n_groups), stk[threadIdx.x / GQP_GANG],
+            [&](int g, V3 &q, BvhTree &tr) {
+                const PenGroup G = queue[g];
+                b = (int)(G.sample / (unsigned)n_pts);
+                const int pi = (int)(G.sample % (unsigned)n_pts);
+                const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
+                P = ld3(x + (row * n_pts + pi) * 3);
+                m = G.need;
+                best_d = -__int_as_float(0x7f800000);
+                best_l = -1;
+                enter_link(q, tr);
+            },
+            [&](int, V3 &q, BvhTree &tr, const SdfBest &win) {
+                const V3 dv = q - win.c;
+                const float sgn = dot3(dv, win.normal) >= 0.f ? 1.f : -1.f;
+                const float r = sqrtf(win.d2 + 1e-8f);
+                const float d = r * (-sgn);  // hand_model.py:975-976
+                if (d > best_d) {
+                    best_d = d;
+                    best_l = cur_l;
+                    best_g = dv * (1.0f / r);
                 }
-            }
-        }
+                if (m) {
+                    enter_link(q, tr);
+                    return true;
+                }
+                if (best_d > 0.f && gl == 0) {  // energy.py:60-61
+                    if (acc) atomicAdd(acc + b, (unsigned long long)__double2ll_rn((double)best_d * PEN_FIX_SCALE));
+                    if (grad_link_tf) {
+                        // d = sqrt(d2+1e-8) with sign = -1; d(d)/dq = (q-c)/r; q = R^T (p - t)
+                        const size_t wl = ((size_t)b * L + best_l) * 12;
+                        const float *W = link_tf + wl;
+                        float *Gm = grad_link_tf + wl;
+                        const V3 gg = best_g * w_pen;
+                        const float pt[3] = {P.x - W[3], P.y - W[7], P.z - W[11]}, gv[3] = {gg.x, gg.y, gg.z};
+#pragma unroll
+                        for (int r2 = 0; r2 < 3; ++r2) {
+#pragma unroll
+                            for (int i = 0; i < 3; ++i) atomicAdd(Gm + 4 * r2 + i, pt[r2] * gv[i]);
+                            atomicAdd(Gm + 4 * r2 + 3,
+                                      -(W[4 * r2] * gv[0] + W[4 * r2 + 1] * gv[1] + W[4 * r2 + 2] * gv[2]));
+                        }
+                    }
+                }
+                return false;
+            });
     }
 }
 
@@ -542,10 +560,13 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     std::vector<float> tris;
     std::vector<int32_t> fid;
     std::vector<float> pre;
+    std::vector<GqpBvhNode> wide;
+    std::vector<float> wpre;
     for (int l = 0; l < L; ++l) {
         int f0 = h->face_offset[l], F = h->face_offset[l + 1] - f0;
         PenLink K{};
         K.node_first = (int)nodes.size();
+        K.wide_first = (int)(wide.size() / 8);
         K.tri_first = (int)(tris.size() / 9);
         K.n_faces = F;
         K.grid = -1;
@@ -554,6 +575,11 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
             gqp_bvh_build(face_verts_host + 9 * (size_t)f0, F, 8, bvh);
             if (bvh.max_depth > GQP_BVH_STACK - 2)
                 return gqp_set_error(GQP_ERR_LIMIT, "hand link %d: BVH too deep (%d)", l, bvh.max_depth);
+            gqp_bvh_widen(bvh);
+            if (7 * bvh.wide_depth + 1 > GQP_GANG_STACK)
+                return gqp_set_error(GQP_ERR_LIMIT, "hand link %d: wide BVH too deep (%d)", l, bvh.wide_depth);
+            wide.insert(wide.end(), bvh.wide.begin(), bvh.wide.end());
+            wpre.insert(wpre.end(), bvh.wide_pre.begin(), bvh.wide_pre.end());
             K.n_nodes = (int)bvh.nodes.size();
             nodes.insert(nodes.end(), bvh.nodes.begin(), bvh.nodes.end());
             tris.insert(tris.end(), bvh.tris.begin(), bvh.tris.end());
@@ -619,10 +645,12 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     T->d_tris = (float *)gqp_dev_alloc_upload(tris.data(), tris.size() * sizeof(float));
     T->d_face_id = (int32_t *)gqp_dev_alloc_upload(fid.data(), fid.size() * sizeof(int32_t));
     T->d_pre = (float *)gqp_dev_alloc_upload(pre.data(), pre.size() * sizeof(float));
-    if (!T->d_blob || !T->d_tris || !T->d_face_id || !T->d_pre) return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
+    T->d_wide = (GqpBvhNode *)gqp_dev_alloc_upload(wide.data(), wide.size() * sizeof(GqpBvhNode));
+    T->d_wpre = (float *)gqp_dev_alloc_upload(wpre.data(), wpre.size() * sizeof(float));
+    if (!T->d_blob || !T->d_tris || !T->d_face_id || !T->d_pre || !T->d_wide || !T->d_wpre)
+        return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
 #ifndef GQP_EMU
     cudaFuncSetAttribute(pen_collect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
-    cudaFuncSetAttribute(pen_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
     cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
 #endif
     return GQP_OK;
@@ -631,7 +659,7 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
 void gqp_pen_tables_destroy(GqpHand *h) {
     if (!h || !h->pen) return;
     gqp_dev_free(h->pen->d_blob); gqp_dev_free(h->pen->d_tris); gqp_dev_free(h->pen->d_face_id);
-    gqp_dev_free(h->pen->d_pre);
+    gqp_dev_free(h->pen->d_pre); gqp_dev_free(h->pen->d_wide); gqp_dev_free(h->pen->d_wpre);
     delete h->pen;
     h->pen = nullptr;
 }
@@ -648,6 +676,18 @@ static int pen_grid_size(int blob_bytes, long long n_tasks, int max_per_sm) {
     (void)blob_bytes;
     (void)max_per_sm;
     return (int)std::max(1LL, std::min<long long>(2, n_tasks));
+#endif
+}
+
+// the search kernel is persistent over a queue whose length only the device knows: fill the GPU
+static int pen_search_grid() {
+#ifndef GQP_EMU
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms * 8;
+#else
+    return 2;
 #endif
 }
 
@@ -691,10 +731,9 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
         GQP_LAUNCH(pen_collect_kernel, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x, batch_each,
                    per_candidate_points, n_pts, counter, items, queue);
         GQP_CHECK_LAUNCH("gqp_hand_distance/collect");
-        int grid2 = pen_grid_size(T->total_bytes, 1LL << 40, 3);
-        GQP_LAUNCH(pen_search_kernel, grid2, PEN_Q_THREADS, (size_t)T->total_bytes, st, T->d_blob, T->total_bytes,
-                   T->d_tris, T->d_face_id, T->d_pre, T->extent, link_tf, x, batch_each, n_pts, per_candidate_points,
-                   counter, queue, e_pen ? acc : nullptr, w_pen, grad_link_tf);
+        GQP_LAUNCH(pen_search_kernel, pen_search_grid(), PEN_Q_WARPS * 32, 0, st, T->d_blob, T->d_wide, T->d_wpre, T->d_tris,
+                   T->d_face_id, T->d_pre, T->extent, link_tf, x, batch_each, n_pts, per_candidate_points, counter, queue,
+                   e_pen ? acc : nullptr, w_pen, grad_link_tf);
         GQP_CHECK_LAUNCH("gqp_hand_distance/search");
         if (e_pen) {
             GQP_LAUNCH(pen_reduce_fixed_kernel, (Bt + 127) / 128, 128, 0, st, acc, Bt, e_pen);
