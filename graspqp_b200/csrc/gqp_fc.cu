@@ -67,17 +67,46 @@ __device__ __forceinline__ void warp_allreduce(double *sm, double (&v)[K], int l
     __syncwarp();
 }
 
+// Reciprocal and reciprocal square root of a positive normal double: the hardware seed (about 20 bits) and two Newton
+// steps, without the library routines' special-case branches (a dozen of them sit on the critical path of every
+// interior-point iteration).  Within an ulp or two of the correctly rounded result; NaN for negative input.
+__device__ __forceinline__ double fc_rcp(double x) {
+#ifdef GQP_EMU
+    return 1.0 / x;
+#else
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    return fma(r, e, r);
+#endif
+}
+__device__ __forceinline__ double fc_rsqrt(double x) {
+#ifdef GQP_EMU
+    return rsqrt(x);
+#else
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-(x * y), y, 1.0);
+    y = fma(0.5 * y, e, y);
+    e = fma(-(x * y), y, 1.0);
+    return fma(0.5 * y, e, y);
+#endif
+}
+
 // packed lower-triangular index
 __device__ __forceinline__ int tri_ix(int i, int j) { return i * (i + 1) / 2 + j; }
 
 // in-place Cholesky of a packed 6x6 SPD matrix (lower), A = L L'; diagonal entries are stored INVERTED
+template <bool FAST>
 __device__ __forceinline__ void chol6(double *A) {
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
         double s = A[tri_ix(j, j)];
 #pragma unroll
         for (int k = 0; k < j; ++k) s -= A[tri_ix(j, k)] * A[tri_ix(j, k)];
-        double inv = rsqrt(s);  // the diagonal holds 1/L_jj: the solves multiply instead of dividing
+        double inv = FAST ? fc_rsqrt(s) : rsqrt(s);  // the diagonal holds 1/L_jj: the solves multiply instead of dividing
         A[tri_ix(j, j)] = inv;
 #pragma unroll
         for (int i = j + 1; i < 6; ++i) {
@@ -129,7 +158,7 @@ __device__ __forceinline__ double step_lane(const double *zu, const double *zl, 
             step_min(f, zu[v], d.dzu[v]); step_min(f, zl[v], d.dzl[v]);
             step_min(f, su[v], d.dsu[v]); step_min(f, sl[v], d.dsl[v]);
         }
-    return f.num / f.den;
+    return f.num * fc_rcp(f.den);
 }
 
 // Workspace of the split form (gqp_fc_solve -> gqp_fc_finish).  The interior-point pass keeps, per candidate, every
@@ -233,7 +262,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             for (int i = 0; i < 21; ++i) a[i] = 0.0;
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
-                Minv[v] = valid[v] ? 1.0 / (P.ridge + du[v] + dl[v]) : 0.0;
+                Minv[v] = valid[v] ? fc_rcp(P.ridge + du[v] + dl[v]) : 0.0;
 #pragma unroll
                 for (int i = 0; i < 6; ++i)
 #pragma unroll
@@ -242,13 +271,14 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             warp_allreduce<21, false>(sm, a, lane);
 #pragma unroll
             for (int i = 0; i < 6; ++i) a[tri_ix(i, i)] += 1.0;
-            chol6(a);
+            chol6<true>(a);  // I + F M^-1 F': pivots >= 1
 #pragma unroll
             for (int i = 0; i < 21; ++i) L6[i] = a[i];
         };
+        // also returns y = (I + F M^-1 F')^-1 F M^-1 r, which equals F dx
         auto solve = [&](const double *du, const double *dl, const double *rx, const double *rsu, const double *rsl,
-                         const double *rzu, const double *rzl, Dir &d) {
-            double r[2], t[6];
+                         const double *rzu, const double *rzl, Dir &d, double (&t)[6]) {
+            double r[2];
 #pragma unroll
             for (int i = 0; i < 6; ++i) t[i] = 0.0;
 #pragma unroll
@@ -273,6 +303,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             }
         };
         double x[2], su[2], sl[2], zu[2], zl[2];
+        double fxv[6];  // F x, carried along: F dx comes out of every Newton solve, no reduction needed
         double bx[2] = {0, 0}, bsu[2] = {1, 1}, bsl[2] = {1, 1}, bzu[2] = {1, 1}, bzl[2] = {1, 1};
         const double zero2[2] = {0.0, 0.0};
         if (MODE != FC_FINISH) {
@@ -281,7 +312,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             double rzu[2] = {-P.hi, -P.hi}, rzl[2] = {P.lo, P.lo};
             factor(one2, one2);
             Dir d;
-            solve(one2, one2, zero2, zero2, zero2, rzu, rzl, d);
+            solve(one2, one2, zero2, zero2, zero2, rzu, rzl, d, fxv);  // x = dx, so F x = y
             double mn[2] = {INF, INF};
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
@@ -300,17 +331,9 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         }
         double best_res = INF;
         int best_it = 0;
+        const double inv_m = 1.0 / m;
         for (int it = 0; it < P.max_iter; ++it) {
-            double fxv[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) fxv[i] = 0.0;
-#pragma unroll
-            for (int v = 0; v < 2; ++v)
-                if (valid[v])
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) fxv[i] += F[v][i] * x[v];
-            warp_allreduce<6, false>(sm, fxv, lane);
-            double rx[2], rzu[2], rzl[2], du[2], dl[2], acc[3] = {0.0, 0.0, 0.0};
+            double rx[2], rzu[2], rzl[2], du[2], dl[2], isu[2], isl[2], acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
                 double ftfx = 0.0;
@@ -319,8 +342,10 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 rx[v] = zu[v] - zl[v] + ftfx + P.ridge * x[v];
                 rzu[v] = x[v] + su[v] - P.hi;
                 rzl[v] = -x[v] + sl[v] + P.lo;
-                du[v] = zu[v] / su[v];
-                dl[v] = zl[v] / sl[v];
+                isu[v] = fc_rcp(su[v]);
+                isl[v] = fc_rcp(sl[v]);
+                du[v] = zu[v] * isu[v];
+                dl[v] = zl[v] * isl[v];
                 if (valid[v]) {
                     acc[0] += su[v] * zu[v] + sl[v] * zl[v];
                     acc[1] += rzu[v] * rzu[v] + rzl[v] * rzl[v];
@@ -331,8 +356,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 }
             }
             warp_allreduce<3, false>(sm, acc, lane);
-            const double mu = fabs(acc[0] / m);
-            const double res = sqrt(acc[1]) + sqrt(acc[2]) + m * mu;
+            const double mu = fabs(acc[0]) * inv_m;
+            const double res = acc[1] * fc_rsqrt(fmax(acc[1], 1e-300)) + acc[2] * fc_rsqrt(fmax(acc[2], 1e-300)) + m * mu;
             if (trace && lane == 0) trace[(size_t)b * P.max_iter + it] = (float)res;
             const bool improved = it == 0 || res < best_res;
             if (improved) {
@@ -345,8 +370,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                         if (valid[v]) {
                             const int j = lane + 32 * v;
                             sn[j] = x[v];
-                            sn[n + j] = fmax(zu[v], 1e-8) / fmax(su[v], 1e-8);
-                            sn[2 * n + j] = fmax(zl[v], 1e-8) / fmax(sl[v], 1e-8);
+                            sn[n + j] = fmax(zu[v], 1e-8) * (su[v] >= 1e-8 ? isu[v] : 1e8);
+                            sn[2 * n + j] = fmax(zl[v], 1e-8) * (sl[v] >= 1e-8 ? isl[v] : 1e8);
                         }
                 } else {
 #pragma unroll
@@ -363,7 +388,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             if (it >= stop || it == P.max_iter - 1) break;  // the step after the last examined iterate is never used
             factor(du, dl);
             Dir aff;
-            solve(du, dl, rx, zu, zl, rzu, rzl, aff);  // rs = z
+            double ya[6], yc[6];
+            solve(du, dl, rx, zu, zl, rzu, rzl, aff, ya);  // rs = z
             double al[1] = {step_lane(zu, zl, su, sl, aff, valid)};
             warp_allreduce<1, true>(sm, al, lane);
             const double a1 = fmin(al[0], 1.0);
@@ -374,16 +400,16 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                     t3[0] += (su[v] + a1 * aff.dsu[v]) * (zu[v] + a1 * aff.dzu[v]) +
                              (sl[v] + a1 * aff.dsl[v]) * (zl[v] + a1 * aff.dzl[v]);
             warp_allreduce<1, false>(sm, t3, lane);
-            const double ratio = t3[0] / acc[0];
+            const double ratio = t3[0] * fc_rcp(acc[0]);
             const double sig = ratio * ratio * ratio;
             double rs2u[2], rs2l[2];
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
-                rs2u[v] = valid[v] ? (-mu * sig + aff.dsu[v] * aff.dzu[v]) / su[v] : 0.0;
-                rs2l[v] = valid[v] ? (-mu * sig + aff.dsl[v] * aff.dzl[v]) / sl[v] : 0.0;
+                rs2u[v] = valid[v] ? (-mu * sig + aff.dsu[v] * aff.dzu[v]) * isu[v] : 0.0;
+                rs2l[v] = valid[v] ? (-mu * sig + aff.dsl[v] * aff.dzl[v]) * isl[v] : 0.0;
             }
             Dir cor;
-            solve(du, dl, zero2, rs2u, rs2l, zero2, zero2, cor);
+            solve(du, dl, zero2, rs2u, rs2l, zero2, zero2, cor, yc);
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
                 aff.dx[v] += cor.dx[v]; aff.dsu[v] += cor.dsu[v]; aff.dsl[v] += cor.dsl[v];
@@ -397,6 +423,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 x[v] += a2 * aff.dx[v]; su[v] += a2 * aff.dsu[v]; sl[v] += a2 * aff.dsl[v];
                 zu[v] += a2 * aff.dzu[v]; zl[v] += a2 * aff.dzl[v];
             }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) fxv[i] += a2 * (ya[i] + yc[i]);
         }
         }  // MODE != FC_FINISH
         if (MODE == FC_SOLVE) continue;
@@ -440,7 +468,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         for (int i = 0; i < 6; ++i) { Fx[i] = red[i]; value += 0.5 * red[i] * red[i]; }
 #pragma unroll
         for (int i = 0; i < 21; ++i) Lg[i] = red[6 + i];
-        chol6(Lg);  // F F' = Lg Lg'  ->  prod(svdvals(F)) = prod(diag Lg)
+        chol6<false>(Lg);  // F F' = Lg Lg'  ->  prod(svdvals(F)) = prod(diag Lg)
         double logdet = 0.0;
 #pragma unroll
         for (int i = 0; i < 6; ++i) logdet -= log(Lg[tri_ix(i, i)]);  // diagonal is stored inverted
@@ -493,16 +521,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             }
             factor(du, dl);
             Dir bd;
-            solve(du, dl, rxb, zero2, zero2, zero2, zero2, bd);
-            double fdx[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) fdx[i] = 0.0;
-#pragma unroll
-            for (int v = 0; v < 2; ++v)
-                if (valid[v])
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) fdx[i] += F[v][i] * bd.dx[v];
-            warp_allreduce<6, false>(sm, fdx, lane);
+            double fdx[6];  // F dx
+            solve(du, dl, rxb, zero2, zero2, zero2, zero2, bd, fdx);
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
                 if (!valid[v]) continue;
