@@ -27,6 +27,24 @@ METRIC = "grasp-steps/sec"
 UNIT = "grasp-steps/s"
 
 
+def ncu_traffic_bytes(kernels):
+    """dram__bytes_read + dram__bytes_write per launch of the named kernels, from the committed `ncu --set full`
+    summary of this workload (profiles/r1c_ncu_full_top.txt, config 2); None when the summary is absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1c_ncu_full_top.txt")
+    if not os.path.exists(path):
+        return None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, cur, seen = 0.0, None, set()
+    for ln in open(path):
+        t = ln.split()
+        if ln.startswith("=="):
+            cur = ln[2:].strip()
+        elif cur in kernels and len(t) == 3 and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            total += float(t[1]) * unit.get(t[2], 1.0)
+            seen.add(cur)
+    return total if len(seen) == len(kernels) else None
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -281,7 +299,8 @@ def run_b200(args):
                                                     "(98.5 % of a grasp-step's brute-force-equivalent work)",
                          "achieved": achieved,
                          "peak": fp32_peak_tflops, "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops,
-                         "traffic": None, "ms_per_launch": ms_pen,
+                         "traffic": ncu_traffic_bytes(("pen_broad_kernel", "pen_collect_kernel", "pen_search_kernel")),
+                         "ms_per_launch": ms_pen,
                          "note": "achieved = brute-force-equivalent flops (80 x n_pts x F_hand x candidates) / launch "
                                  "time; exact culling skips most pairs, so frac may exceed 1 (SURVEY 8d). peak = FP32 "
                                  "FMA probe measured live in this run",

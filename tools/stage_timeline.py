@@ -1,3 +1,4 @@
+"""Kernel timeline (torch profiler / CUPTI) of one stage call, cold and warm L2.  python tools/stage_timeline.py [stage]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -7,7 +8,7 @@ lib, be = _lib.lib(), engine.TorchBackend("cuda:0")
 w = workload.build("config2")
 e = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], w["batch_each"], w["pose"], w["idx"])
 for _ in range(30): e.step()
-fn = e.stage_calls()["hand_distance"]
+fn = e.stage_calls()[sys.argv[1] if len(sys.argv) > 1 else "hand_distance"]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for _ in range(3): fn()
 torch.cuda.synchronize()
