@@ -304,6 +304,18 @@ class FitEngine:
             self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
         self._accept(self.z, reset_mask, u_accept)
 
+    _STATE = ("pose", "idx", "grad", "ema", "step_count", "energy", "losses")
+
+    def snapshot(self):
+        """copy of the optimiser state scripts/fit.py carries between iterations (pose, contact indices, gradient, RMS
+        accumulator, step counters, energies) + the iteration number; see restore()"""
+        return {k: self.be.to_host(getattr(self, k)) for k in self._STATE} | {"iteration": self.iteration}
+
+    def restore(self, snap):
+        for k in self._STATE:
+            self.be.copy_(getattr(self, k), self.be.from_host(snap[k], snap[k].dtype))
+        self.iteration = int(snap["iteration"])
+
     def stage_calls(self):
         """name -> callable re-running ONE stage of the iteration on the current buffers (per-stage timing in bench.py
         and tools/bench_kernels.py; results are overwritten with the same values, gradients accumulate garbage)."""

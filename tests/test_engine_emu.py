@@ -57,3 +57,23 @@ def test_short_trajectory_teacher_forced(emu):
     import cases
     n_acc, n_tie, worst = cases.check_trajectory(emu, engine.NumpyBackend(), T=3, B=3, n_pts=48)
     assert n_tie == 0 and worst < 2e-4
+
+
+def test_snapshot_restore_replays_the_same_iterations(emu):
+    """restore(snapshot()) brings back the optimiser state: the Philox noise is keyed by the iteration number, so the
+    replayed iterations are identical (bench.py times the same iterations twice this way)."""
+    B, n_c = 3, 4
+    pack, fv, sp, pose, idx = make_case(B=B, n_c=n_c, n_pts=64)
+    eng = engine.FitEngine(emu, engine.NumpyBackend(), pack, [fv], sp[None], B, pose, idx.astype(np.int32))
+    eng.step()
+    snap = eng.snapshot()
+    for _ in range(2):
+        eng.step()
+    want = (eng.energy.copy(), eng.pose.copy(), eng.idx.copy(), eng.iteration)
+    eng.restore(snap)
+    for _ in range(2):
+        eng.step()
+    np.testing.assert_array_equal(eng.energy, want[0])
+    np.testing.assert_array_equal(eng.pose, want[1])
+    np.testing.assert_array_equal(eng.idx, want[2])
+    assert eng.iteration == want[3]
