@@ -16,7 +16,15 @@
 #include "gqp_common.cuh"
 #include "graspqp_b200.h"
 
-#define FC_WARPS 4
+// One warp per block, 16 blocks per SM (128 registers, 136 B of spills).  Measured on B200, fc_solve at Bt = 8192 /
+// 32768: 4 warps x 3 blocks (168 registers) 313 / 1174 us; 1 x 10-12 (168) 250 / 931; 1 x 14-16 (128) 234 / 848;
+// 1 x 20 (96) 253 / 928; 1 x 24 (80) 311 / 1116.
+#ifndef FC_WARPS
+#define FC_WARPS 1
+#endif
+#ifndef FC_MIN_BLOCKS
+#define FC_MIN_BLOCKS 16
+#endif
 #define FC_RED_K 29  // widest reduction (odd: conflict-free column sums)
 #define FC_SM_PER_WARP (32 * FC_RED_K + 32 + 64 * 3)
 
@@ -98,23 +106,29 @@ __device__ __forceinline__ double fc_rsqrt(double x) {
 // packed lower-triangular index
 __device__ __forceinline__ int tri_ix(int i, int j) { return i * (i + 1) / 2 + j; }
 
-// in-place Cholesky of a packed 6x6 SPD matrix (lower), A = L L'; diagonal entries are stored INVERTED
+// in-place Cholesky of a packed 6x6 SPD matrix (lower), A = L L'; diagonal entries are stored INVERTED.
+// Every loop has the constant trip count 6 with the triangular condition as a predicate: the compiler then unrolls all
+// of them and the matrix stays in registers (with data-dependent bounds it kept one loop rolled and the 21 entries went
+// to local memory, indexed dynamically).
 template <bool FAST>
 __device__ __forceinline__ void chol6(double *A) {
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
         double s = A[tri_ix(j, j)];
 #pragma unroll
-        for (int k = 0; k < j; ++k) s -= A[tri_ix(j, k)] * A[tri_ix(j, k)];
+        for (int k = 0; k < 6; ++k)
+            if (k < j) s -= A[tri_ix(j, k)] * A[tri_ix(j, k)];
         double inv = FAST ? fc_rsqrt(s) : rsqrt(s);  // the diagonal holds 1/L_jj: the solves multiply instead of dividing
         A[tri_ix(j, j)] = inv;
 #pragma unroll
-        for (int i = j + 1; i < 6; ++i) {
-            double t = A[tri_ix(i, j)];
+        for (int i = 0; i < 6; ++i)
+            if (i > j) {
+                double t = A[tri_ix(i, j)];
 #pragma unroll
-            for (int k = 0; k < j; ++k) t -= A[tri_ix(i, k)] * A[tri_ix(j, k)];
-            A[tri_ix(i, j)] = t * inv;
-        }
+                for (int k = 0; k < 6; ++k)
+                    if (k < j) t -= A[tri_ix(i, k)] * A[tri_ix(j, k)];
+                A[tri_ix(i, j)] = t * inv;
+            }
     }
 }
 __device__ __forceinline__ void chol6_solve(const double *L, double *y) {
@@ -122,14 +136,16 @@ __device__ __forceinline__ void chol6_solve(const double *L, double *y) {
     for (int i = 0; i < 6; ++i) {
         double t = y[i];
 #pragma unroll
-        for (int k = 0; k < i; ++k) t -= L[tri_ix(i, k)] * y[k];
+        for (int k = 0; k < 6; ++k)
+            if (k < i) t -= L[tri_ix(i, k)] * y[k];
         y[i] = t * L[tri_ix(i, i)];
     }
 #pragma unroll
     for (int i = 5; i >= 0; --i) {
         double t = y[i];
 #pragma unroll
-        for (int k = i + 1; k < 6; ++k) t -= L[tri_ix(k, i)] * y[k];
+        for (int k = 0; k < 6; ++k)
+            if (k > i) t -= L[tri_ix(k, i)] * y[k];
         y[i] = t * L[tri_ix(i, i)];
     }
 }
@@ -200,7 +216,7 @@ __device__ __forceinline__ int fc_batch_stop(const unsigned *gmax, const unsigne
 enum { FC_FUSED = 0, FC_SOLVE = 1, FC_FINISH = 2 };
 
 template <int MODE>
-__global__ void __launch_bounds__(FC_WARPS * 32, 3)
+__global__ void __launch_bounds__(FC_WARPS * 32, FC_MIN_BLOCKS)
 fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
               const float *__restrict__ obj_dist, const float *__restrict__ obj_nrm,
               const float *__restrict__ obj_dgrad, const float *__restrict__ cog, int Bt, int batch_each, int n_c,
