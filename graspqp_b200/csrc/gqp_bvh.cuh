@@ -14,15 +14,6 @@ __device__ __forceinline__ float bvh_box_lb(const float4 &lo, const float4 &hi, 
     return (dx * dx + dy * dy + dz * dz) * (1.0f - 1e-5f);
 }
 
-// upper bound of the fp32 squared distance from p to ANY face inside the box (farthest corner), with room for the face
-// test's rounding (closest point off by a few ulp of `scale`, as in bvh_face_skip)
-__device__ __forceinline__ float bvh_box_ub(const float4 &lo, const float4 &hi, V3 p, float scale) {
-    float dx = fmaxf(fabsf(p.x - lo.x), fabsf(p.x - hi.x));
-    float dy = fmaxf(fabsf(p.y - lo.y), fabsf(p.y - hi.y));
-    float dz = fmaxf(fabsf(p.z - lo.z), fabsf(p.z - hi.z));
-    return (dx * dx + dy * dy + dz * dz) * (1.0f + 1e-4f) + 1e-5f * scale * (dx + dy + dz) + 1e-30f;
-}
-
 // Cheap lower bound of the squared distance point -> face from the face's pre-test record (gqp_bvh.cpp): with h the
 // distance to the face's plane and t the in-plane distance to the circle that holds the face, d^2 >= h^2 + t^2.  An
 // axis-aligned box around a tilted surface patch is as thick as the patch is wide, so box bounds alone let tens of
@@ -182,7 +173,7 @@ __device__ __forceinline__ void bvh_query_gang(int q_begin, int q_end, int2 *stk
                 }
             }
             __syncwarp();  // all lanes have read the popped entry before its slot is reused
-            float d = INF, ub = INF;
+            float d = INF;
             int ccode = 0;
             bool alive = false;
             if (expand) {
@@ -191,7 +182,6 @@ __device__ __forceinline__ void bvh_query_gang(int q_begin, int q_end, int2 *stk
                 const int a = __float_as_int(lo.w), b = __float_as_int(hi.w);
                 if (b != 0) {
                     d = bvh_box_lb(lo, hi, p);
-                    ub = bvh_box_ub(lo, hi, p, scale);
                     alive = d <= bound;
                     ccode = b < 0 ? -(a * 8 + (-b - 1)) - 1 : a;
                     if (alive && b < 0) {
@@ -209,12 +199,6 @@ __device__ __forceinline__ void bvh_query_gang(int q_begin, int q_end, int2 *stk
             }
             // survivors go on the stack with the nearest one on top (examined next); the others keep lane order — they are
             // re-checked against the bound when popped.  Ordering key: the bound's bits (d >= 0) with the lane in the low 3
-            // every child box holds at least one face, none of it farther than the box's farthest corner: the bound can
-            // tighten before any face has been tested (the first descent would otherwise push every sibling)
-#pragma unroll
-            for (int o = 1; o < GQP_GANG; o <<= 1) ub = fminf(ub, __shfl_xor_sync(GQP_FULL, ub, o));
-            bound = fminf(bound, ub);
-            alive = alive && d <= bound;
             const unsigned am = (__ballot_sync(GQP_FULL, alive) >> g0) & 0xffu;
             int kmin = alive ? ((__float_as_int(d) & ~7) | gl) : 0x7fffffff;
 #pragma unroll

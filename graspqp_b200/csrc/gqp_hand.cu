@@ -11,7 +11,9 @@
 #include "gqp_hand.h"
 #include "graspqp_b200.h"
 
+#ifndef FK_THREADS
 #define FK_THREADS 128
+#endif
 
 __device__ __forceinline__ void load_hand_tables(GqpHandDev *dst, const GqpHandDev *src) {
     const int n = sizeof(GqpHandDev) / 4;
