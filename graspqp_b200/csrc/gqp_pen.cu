@@ -373,8 +373,10 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
 // Exact search of the queued samples: 8 lanes per sample over the links' 8-wide trees (gqp_bvh.cuh: bvh_query_gang),
 // links in ascending order (first maximum, hand_model.py:986).  Tree nodes, patch records and faces are read through
 // L1/L2 (all link meshes of a hand are ~0.3 MB), so the kernel's occupancy does not depend on the size of the tables.
-#define PEN_Q_WARPS 4
-#define PEN_Q_QPW 16  // groups per warp and round
+#define PEN_Q_WARPS 4  // PEN_Q_QPW measured on B200 (config 2 hand_distance): 8 -> 484 us, 16 -> 518, 32 -> 598
+#ifndef PEN_Q_QPW
+#define PEN_Q_QPW 8
+#endif  // groups per warp and round
 __global__ void __launch_bounds__(PEN_Q_WARPS * 32, 8)
 pen_search_kernel(const unsigned char *__restrict__ blob, const GqpBvhNode *__restrict__ wide,
                   const float *__restrict__ wpre, const float *__restrict__ tris,
