@@ -32,6 +32,16 @@ __device__ __forceinline__ T34 t34_load(const float *p) {
     for (int i = 0; i < 12; ++i) r.m[i] = p[i];
     return r;
 }
+// the same from a 16-byte aligned address: three 128-bit loads
+__device__ __forceinline__ T34 t34_load4(const float *p) {
+    const float4 *q = reinterpret_cast<const float4 *>(p);
+    const float4 a = q[0], b = q[1], c = q[2];
+    T34 r;
+    r.m[0] = a.x; r.m[1] = a.y; r.m[2] = a.z; r.m[3] = a.w;
+    r.m[4] = b.x; r.m[5] = b.y; r.m[6] = b.z; r.m[7] = b.w;
+    r.m[8] = c.x; r.m[9] = c.y; r.m[10] = c.z; r.m[11] = c.w;
+    return r;
+}
 __device__ __forceinline__ T34 t34_identity() {
     T34 r;
 #pragma unroll

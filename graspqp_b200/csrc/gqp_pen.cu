@@ -270,8 +270,8 @@ struct PenGroup {
 // box, lane = link), then, lanes = 32-sample chunks of the row, which of those links each chunk's bounding sphere
 // reaches.  Chunks that reach a link become work items (candidate, chunk, link mask) for the narrow phase.  Exact for
 // "nice" links (see gqp_bvh.cpp); links without an outside-grid are always kept.
-struct PenItem {
-    uint32_t b, chunk, links;
+struct alignas(16) PenItem {
+    uint32_t b, chunk, links, row;  // row = index of the candidate's point row (saves a division per item and lane)
 };
 #define PEN_BROAD_WARPS 4
 __global__ void __launch_bounds__(PEN_BROAD_WARPS * 32)
@@ -287,6 +287,7 @@ pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict
     const int row = per_candidate_points ? b : b / batch_each;
     const float *br = bounds + (size_t)row * (n_chunks + 1) * 4;
     const float *Wb = link_tf + (size_t)b * L * 12;
+    const bool tf16 = ((uintptr_t)link_tf & 15) == 0;
     bool keep = false;
     if (lane < L && links[lane].n_faces > 0) {  // hand_model.py:919-921: links without a mesh are skipped
         const PenLink &K = links[lane];
@@ -311,7 +312,7 @@ pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict
                 const PenLink &K = links[l];
                 bool hit = true;
                 if (K.grid >= 0) {
-                    const V3 q = t34_inv_point(t34_load(Wb + l * 12), cen);
+                    const V3 q = t34_inv_point(tf16 ? t34_load4(Wb + l * 12) : t34_load(Wb + l * 12), cen);
                     hit = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
                             q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
                 }
@@ -323,17 +324,19 @@ pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict
             int base = 0;
             if (lane == 0) base = (int)atomicAdd(counter + 1, (unsigned)__popc(em));
             base = __shfl_sync(GQP_FULL, base, 0);
-            if (cm) items[base + __popc(em & ((1u << lane) - 1u))] = PenItem{(uint32_t)b, (uint32_t)c, cm};
+            if (cm) items[base + __popc(em & ((1u << lane) - 1u))] = PenItem{(uint32_t)b, (uint32_t)c, cm, (uint32_t)row};
         }
     }
 }
 
 // Narrow phase, a warp per work item, lane = sample: the sample is dropped for a link when it is provably outside it
 // (outside the box, or in an outside cell of the link's grid); the others are queued for the exact search.
+// TF16: link_tf is 16-byte aligned (128-bit loads of the transforms).
+template <bool TF16>
 __global__ void __launch_bounds__(PEN_THREADS)
 pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, const float *__restrict__ link_tf,
-                   const float *__restrict__ x, int batch_each, int per_candidate_points, int n_pts,
-                   uint32_t *__restrict__ counter, const PenItem *__restrict__ items, PenGroup *__restrict__ queue) {
+                   const float *__restrict__ x, int n_pts, uint32_t *__restrict__ counter,
+                   const PenItem *__restrict__ items, PenGroup *__restrict__ queue) {
     GQP_DYN_SMEM(unsigned char, sm);
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) mbar_init(&bar);
@@ -350,14 +353,15 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
     for (unsigned it = blockIdx.x * warps_per_block + (threadIdx.x >> 5); it < n_items; it += gridDim.x * warps_per_block) {
         const PenItem I = items[it];
         const int b = (int)I.b, pi = (int)I.chunk * 32 + lane;
-        const size_t row = per_candidate_points ? (size_t)b : (size_t)(b / batch_each);
+        const size_t row = I.row;
         const bool valid = pi < n_pts;
         const V3 p = ld3(x + (row * n_pts + (valid ? pi : n_pts - 1)) * 3);
         const float *Wb = link_tf + (size_t)b * L * 12;
         uint32_t need = 0;
         for (uint32_t m = I.links; m; m &= m - 1) {
             const int l = __ffs((int)m) - 1;
-            if (!pen_outside(links[l], grids, bits, t34_inv_point(t34_load(Wb + l * 12), p))) need |= 1u << l;
+            const T34 W = TF16 ? t34_load4(Wb + l * 12) : t34_load(Wb + l * 12);
+            if (!pen_outside(links[l], grids, bits, t34_inv_point(W, p))) need |= 1u << l;
         }
         if (!valid) need = 0;  // padding lanes of the last chunk
         const unsigned em = __ballot_sync(GQP_FULL, need != 0);
@@ -390,6 +394,7 @@ pen_search_kernel(const unsigned char *__restrict__ blob, const GqpBvhNode *__re
     const int L = hdr->n_links;
     const int n_groups = (int)*counter;
     const int gl = threadIdx.x & (GQP_GANG - 1);
+    const bool tf16 = ((uintptr_t)link_tf & 15) == 0;  // 128-bit loads of the link transforms when aligned
     // per-gang state of the sample being searched (identical on the 8 lanes)
     V3 P = V3{0, 0, 0}, best_g = V3{0, 0, 0};
     uint32_t m = 0;
@@ -399,7 +404,8 @@ pen_search_kernel(const unsigned char *__restrict__ blob, const GqpBvhNode *__re
         cur_l = __ffs((int)m) - 1;
         m &= m - 1;
         const PenLink &K = links[cur_l];
-        q = t34_inv_point(t34_load(link_tf + ((size_t)b * L + cur_l) * 12), P);
+        const float *Wp = link_tf + ((size_t)b * L + cur_l) * 12;
+        q = t34_inv_point(tf16 ? t34_load4(Wp) : t34_load(Wp), P);
         tr = BvhTree{wide + GQP_GANG * (size_t)K.wide_first, wpre + 8 * GQP_GANG * (size_t)K.wide_first,
                      tris + (size_t)K.tri_first * 9, face_id + K.tri_first, pre + (size_t)K.tri_first * 8, extent};
     };
@@ -652,7 +658,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     if (!T->d_blob || !T->d_tris || !T->d_face_id || !T->d_pre || !T->d_wide || !T->d_wpre)
         return gqp_set_error(GQP_ERR_CUDA, "pen tables: allocation failed");
 #ifndef GQP_EMU
-    cudaFuncSetAttribute(pen_collect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
+    cudaFuncSetAttribute(pen_collect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
+    cudaFuncSetAttribute(pen_collect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
     cudaFuncSetAttribute(hand_pen_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PEN_MAX_SMEM + 24 * 1024);
 #endif
     return GQP_OK;
@@ -722,6 +729,7 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
         unsigned long long *acc = reinterpret_cast<unsigned long long *>(tail + 4);
         PenGroup *queue = reinterpret_cast<PenGroup *>(acc + Bt);
         PenItem *items = reinterpret_cast<PenItem *>(queue + (size_t)Bt * n_pts);
+        items = reinterpret_cast<PenItem *>(((uintptr_t)items + 15) & ~(uintptr_t)15);
         rc = gqp_memset_zero(tail, 16 + sizeof(unsigned long long) * (size_t)Bt, stream);
         if (rc != GQP_OK) return rc;
         GQP_LAUNCH(pen_broad_kernel, (Bt + PEN_BROAD_WARPS - 1) / PEN_BROAD_WARPS, PEN_BROAD_WARPS * 32, 0, st, T->d_blob,
@@ -730,8 +738,13 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
         const PenHdr *hdr = reinterpret_cast<const PenHdr *>(T->blob_host.data());
         const int prefix = hdr->nodes_off;  // header, links, grids, outside-grid bits
         int grid1 = pen_grid_size(prefix, (long long)Bt * n_chunks, 3);
-        GQP_LAUNCH(pen_collect_kernel, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x, batch_each,
-                   per_candidate_points, n_pts, counter, items, queue);
+        if (((uintptr_t)link_tf & 15) == 0) {
+            GQP_LAUNCH(pen_collect_kernel<true>, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x,
+                       n_pts, counter, items, queue);
+        } else {
+            GQP_LAUNCH(pen_collect_kernel<false>, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x,
+                       n_pts, counter, items, queue);
+        }
         GQP_CHECK_LAUNCH("gqp_hand_distance/collect");
         GQP_LAUNCH(pen_search_kernel, pen_search_grid(), PEN_Q_WARPS * 32, 0, st, T->d_blob, T->d_wide, T->d_wpre, T->d_tris,
                    T->d_face_id, T->d_pre, T->extent, link_tf, x, batch_each, n_pts, per_candidate_points, counter, queue,
@@ -855,7 +868,7 @@ extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, 
     const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
     const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;
     // + culled path: counters (4 words + alignment), fixed-point accumulators (2 words each), queue (2 words per
-    // sample), work items of the narrow phase (3 words per candidate and chunk)
+    // sample), work items of the narrow phase (4 words per candidate and chunk, 16-byte aligned)
     return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16 + 8 + 2 * Bt + 2 * Bt * (uint64_t)n_pts +
-           3 * Bt * n_chunks;
+           4 * Bt * n_chunks + 4;
 }
