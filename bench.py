@@ -29,8 +29,8 @@ UNIT = "grasp-steps/s"
 
 def ncu_traffic_bytes(kernels):
     """dram__bytes_read + dram__bytes_write per launch of the named kernels, from the committed `ncu --set full`
-    summary of this workload (profiles/r1c_ncu_full_top.txt, config 2); None when the summary is absent."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1c_ncu_full_top.txt")
+    summary of this workload (profiles/r1d_ncu_full_top.txt, config 2); None when the summary is absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1d_ncu_full_top.txt")
     if not os.path.exists(path):
         return None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
