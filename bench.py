@@ -38,7 +38,7 @@ def ncu_traffic_bytes(kernels):
     for ln in open(path):
         t = ln.split()
         if ln.startswith("=="):
-            cur = ln[2:].strip()
+            cur = next((k for k in kernels if k in ln), None)   # "== void pen_collect_kernel<1>" -> pen_collect_kernel
         elif cur in kernels and len(t) == 3 and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
             total += float(t[1]) * unit.get(t[2], 1.0)
             seen.add(cur)
@@ -148,8 +148,8 @@ def run_reference(args):
     import torch
     torch.set_num_threads(os.cpu_count() or 1)
     steps, warmup = max(1, args.steps), max(0, args.warmup)
-    # bounded: the oracle does ~1 s per iteration of 16 candidates on 8 cores
-    steps, warmup = min(steps, 10), min(warmup, 2)
+    # bounded: the oracle does ~0.15 s per iteration of 16 candidates on 16 cores
+    steps, warmup = min(steps, 100), min(warmup, 3)
     cb, sec_per_step = cpu_reference_run(args, steps, warmup, args.cpu_sample_batch)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * sec_per_step, "higher_is_better": True,
@@ -342,7 +342,7 @@ def run_b200(args):
                                  "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}},
         }
         if world == 1 and not args.skip_cpu_baseline:
-            cb, _ = cpu_reference_run(args, 10, 1, args.cpu_sample_batch)
+            cb, _ = cpu_reference_run(args, 100, 1, args.cpu_sample_batch)   # ~15 s of host work
             line["cpu_baseline"] = cb
         print(json.dumps(line))
     eng.close()

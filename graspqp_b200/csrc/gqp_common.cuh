@@ -117,7 +117,10 @@ void gqp_count_launch(int n = 1);
 #include <cstdlib>
 #include <cstring>
 static inline void *gqp_dev_alloc_upload(const void *src, size_t bytes) {
-    if (bytes == 0) bytes = 16;
+    if (bytes == 0) {  // empty table (e.g. a hand without penetration spheres): a valid pointer, nothing to read
+        bytes = 16;
+        src = nullptr;
+    }
     void *d = nullptr;
 #ifndef GQP_EMU
     if (cudaMalloc(&d, bytes) != cudaSuccess) return nullptr;

@@ -70,11 +70,34 @@ __device__ __forceinline__ T34 joint_tf(const GqpHandDev &H, int f, const float 
     return J;
 }
 
+// The joint vector the chain is evaluated on: the pose row's joint columns, or, for a hand with a coupling network
+// (Robotiq 2F-140: utils/fk.py:23-51, hands/robotiq2.py:9-13), q = [c, W2 tanh(w1 c + b1) + b2] with
+// c = clamp(theta_0).  dq (when wanted) = dq/dtheta_0 for the backward; torch.clamp passes the gradient on [lo, hi].
+__device__ __forceinline__ const float *joint_vector(const GqpHandDev &H, const float *theta, float *q, float *dq) {
+    if (H.mlp_hidden == 0) return theta;
+    float c = fminf(fmaxf(theta[0], H.mlp_lo), H.mlp_hi);
+    float pass = (theta[0] >= H.mlp_lo && theta[0] <= H.mlp_hi) ? 1.0f : 0.0f;
+    q[0] = c;
+    if (dq) dq[0] = pass;
+    for (int o = 0; o < H.mlp_out; ++o) {
+        q[1 + o] = H.mlp_b2[o];
+        if (dq) dq[1 + o] = 0.f;
+    }
+    for (int k = 0; k < H.mlp_hidden; ++k) {
+        float t = tanhf(H.mlp_w1[k] * c + H.mlp_b1[k]);
+        float dt = (1.0f - t * t) * H.mlp_w1[k] * pass;
+        for (int o = 0; o < H.mlp_out; ++o) {
+            q[1 + o] += H.mlp_w2[o][k] * t;
+            if (dq) dq[1 + o] += H.mlp_w2[o][k] * dt;
+        }
+    }
+    return q;
+}
+
 // world transform of every frame BEFORE its link offset (children hang on it): A[f] = A[parent] * (joff * jt);
 // B[f] = A[parent] * joff is the joint frame (axis / origin for the backward), returned only when wanted.
 template <bool WANT_JOINT_FRAME>
-__device__ __forceinline__ void fk_frames(const GqpHandDev &H, const float *pose, const T34 &G, T34 *A, T34 *Bj) {
-    const float *theta = pose + 9;
+__device__ __forceinline__ void fk_frames(const GqpHandDev &H, const float *theta, const T34 &G, T34 *A, T34 *Bj) {
     for (int f = 0; f < H.n_frames; ++f) {
         int par = H.frame_parent[f];
         T34 joff = t34_load(H.frame_joff[f]);
@@ -99,7 +122,8 @@ fk_forward_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict__
     GramSchmidt gs;
     T34 G = global_tf(prow, gs);
     T34 A[GQP_MAX_FRAMES];
-    fk_frames<false>(H, prow, G, A, nullptr);
+    float q[1 + GQP_MAX_MLP_OUT];
+    fk_frames<false>(H, joint_vector(H, prow + 9, q, nullptr), G, A, nullptr);
     for (int l = 0; l < H.n_links; ++l) {
         int f = H.link_frame[l];
         T34 W = t34_mul(A[f], t34_load(H.frame_loff[f]));
@@ -120,14 +144,13 @@ fk_backward_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict_
     if (b >= Bt) return;
     const int D = 9 + H.n_dofs;
     float prow[9 + GQP_MAX_DOFS], gp[9 + GQP_MAX_DOFS];
-    for (int i = 0; i < D; ++i) {
-        prow[i] = pose[(size_t)b * D + i];
-        gp[i] = 0.f;
-    }
+    for (int i = 0; i < D; ++i) prow[i] = pose[(size_t)b * D + i];
+    for (int i = 0; i < 9 + GQP_MAX_DOFS; ++i) gp[i] = 0.f;  // joint slots: one per entry of the joint vector
     GramSchmidt gs;
     T34 G = global_tf(prow, gs);
     T34 A[GQP_MAX_FRAMES], Bj[GQP_MAX_FRAMES];
-    fk_frames<true>(H, prow, G, A, Bj);
+    float q[1 + GQP_MAX_MLP_OUT], dq[1 + GQP_MAX_MLP_OUT];
+    fk_frames<true>(H, joint_vector(H, prow + 9, q, dq), G, A, Bj);
     // wrench (torque about the world origin, force) that the loss exerts on every frame
     float accM[GQP_MAX_FRAMES][3], accF[GQP_MAX_FRAMES][3];
     for (int f = 0; f < H.n_frames; ++f)
@@ -177,6 +200,11 @@ fk_backward_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict_
         } else {
             Ftot = Ftot + F;
         }
+    }
+    if (H.mlp_hidden > 0) {  // chain rule through the coupling network: d/dtheta_0 = sum_j d/dq_j dq_j/dtheta_0
+        float g = 0.f;
+        for (int j = 0; j <= H.mlp_out; ++j) g += gp[9 + j] * dq[j];
+        gp[9] = g;
     }
     gp[0] = Ftot.x; gp[1] = Ftot.y; gp[2] = Ftot.z;
     // dL/dR_g = S R_g, columns -> (x^, y^, z); then back through the Gram-Schmidt
@@ -254,9 +282,25 @@ extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
         d->n_dofs < 0 || d->n_dofs > GQP_MAX_DOFS || d->n_cand <= 0 || d->n_spheres < 0)
         return gqp_set_error(GQP_ERR_LIMIT, "gqp_hand_create: sizes out of range (frames %d/%d links %d/%d dofs %d/%d)",
                              d->n_frames, GQP_MAX_FRAMES, d->n_links, GQP_MAX_LINKS, d->n_dofs, GQP_MAX_DOFS);
+    if (d->mlp_hidden < 0 || d->mlp_hidden > GQP_MAX_MLP_HIDDEN || d->mlp_out < 0 || d->mlp_out > GQP_MAX_MLP_OUT)
+        return gqp_set_error(GQP_ERR_LIMIT, "gqp_hand_create: coupling network %d x %d exceeds %d x %d", d->mlp_hidden,
+                             d->mlp_out, GQP_MAX_MLP_HIDDEN, GQP_MAX_MLP_OUT);
+    if (d->mlp_hidden > 0 && (d->n_dofs != 1 || !d->mlp_w1_host || !d->mlp_b1_host || !d->mlp_w2_host ||
+                              !d->mlp_b2_host))
+        return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: a coupling network needs n_dofs == 1 and all four tables");
+    const int n_q = d->mlp_hidden > 0 ? 1 + d->mlp_out : d->n_dofs;  // entries of the joint vector frame_dof indexes
     GqpHand *h = new GqpHand();
     GqpHandDev &H = h->host;
     std::memset(&H, 0, sizeof(H));
+    if (d->mlp_hidden > 0) {
+        H.mlp_hidden = d->mlp_hidden; H.mlp_out = d->mlp_out; H.mlp_lo = d->mlp_lo; H.mlp_hi = d->mlp_hi;
+        for (int k = 0; k < d->mlp_hidden; ++k) {
+            H.mlp_w1[k] = d->mlp_w1_host[k];
+            H.mlp_b1[k] = d->mlp_b1_host[k];
+            for (int o = 0; o < d->mlp_out; ++o) H.mlp_w2[o][k] = d->mlp_w2_host[o * d->mlp_hidden + k];
+        }
+        for (int o = 0; o < d->mlp_out; ++o) H.mlp_b2[o] = d->mlp_b2_host[o];
+    }
     H.n_frames = d->n_frames; H.n_dofs = d->n_dofs; H.n_links = d->n_links; H.n_cand = d->n_cand;
     H.n_spheres = d->n_spheres;
     for (int f = 0; f < d->n_frames; ++f) {
@@ -264,9 +308,9 @@ extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
         H.frame_jtype[f] = d->frame_jtype_host[f];
         H.frame_dof[f] = d->frame_dof_host[f];
         H.frame_link[f] = -1;
-        if (H.frame_parent[f] >= f || H.frame_dof[f] >= d->n_dofs) {
+        if (H.frame_parent[f] >= f || H.frame_dof[f] >= n_q) {
             delete h;
-            return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: frame %d: parent must precede it, dof < n_dofs", f);
+            return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: frame %d: parent must precede it, dof < %d", f, n_q);
         }
         for (int k = 0; k < 3; ++k) H.frame_axis[f][k] = d->frame_axis_host[3 * f + k];
         for (int k = 0; k < 12; ++k) {

@@ -7,6 +7,8 @@
 #define GQP_MAX_FRAMES 48
 #define GQP_MAX_LINKS 32
 #define GQP_MAX_DOFS 32
+#define GQP_MAX_MLP_HIDDEN 16
+#define GQP_MAX_MLP_OUT 7
 
 // ---- BVH over a triangle mesh (built on the host, gqp_bvh.cpp) ----------------------------------------------------
 // Node = 32 bytes: box min (3 floats), `a`, box max (3 floats), `b`.
@@ -64,6 +66,11 @@ struct GqpHandDev {
     float frame_loff[GQP_MAX_FRAMES][12];
     int32_t link_frame[GQP_MAX_LINKS];
     float joints_lower[GQP_MAX_DOFS], joints_upper[GQP_MAX_DOFS];
+    // joint-coupling network (GqpHandDesc::mlp_*); mlp_hidden == 0: frame_dof indexes the pose row directly
+    int32_t mlp_hidden, mlp_out;
+    float mlp_lo, mlp_hi;
+    float mlp_w1[GQP_MAX_MLP_HIDDEN], mlp_b1[GQP_MAX_MLP_HIDDEN];
+    float mlp_w2[GQP_MAX_MLP_OUT][GQP_MAX_MLP_HIDDEN], mlp_b2[GQP_MAX_MLP_OUT];
 };
 
 struct GqpPenTables;  // gqp_pen.cu

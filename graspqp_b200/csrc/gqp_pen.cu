@@ -139,7 +139,7 @@ __global__ void pen_mask_kernel(const unsigned char *__restrict__ blob, const fl
 
 template <bool CULL>
 __global__ void __launch_bounds__(PEN_THREADS, PEN_MIN_BLOCKS)
-hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const float *__restrict__ tris,
+hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, int nodes_staged, const float *__restrict__ tris,
                 const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
                 const float *__restrict__ link_tf, const float *__restrict__ x, const float *__restrict__ bounds, const uint32_t *__restrict__ masks, int n_rows, int cands_per_row,
                 int n_pts, float *__restrict__ dist_out, int32_t *__restrict__ arg_link_out,
@@ -154,7 +154,9 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, const fl
     const PenHdr *hdr = reinterpret_cast<const PenHdr *>(sm);
     const PenLink *links = reinterpret_cast<const PenLink *>(sm + hdr->links_off);
     const PenGrid *grids = reinterpret_cast<const PenGrid *>(sm + hdr->grids_off);
-    const GqpBvhNode *nodes = reinterpret_cast<const GqpBvhNode *>(sm + hdr->nodes_off);
+    // the link trees ride along in shared memory when the whole blob fits (blob_bytes == total), else they are read
+    // through L1/L2 (Robotiq 2F-140: 22.7k faces, 180 KB of nodes)
+    const GqpBvhNode *nodes = reinterpret_cast<const GqpBvhNode *>((nodes_staged ? sm : blob) + hdr->nodes_off);
     const uint32_t *bits = reinterpret_cast<const uint32_t *>(sm + hdr->bits_off);
     const int L = hdr->n_links;
 
@@ -645,9 +647,9 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     pad16(B);
     hdr.total_bytes = (int)B.size();
     std::memcpy(B.data(), &hdr, sizeof(hdr));
-    if (hdr.total_bytes > PEN_MAX_SMEM)
+    if (hdr.nodes_off > PEN_MAX_SMEM)  // links, grids and outside-grid bits must fit; the trees may stay in global memory
         return gqp_set_error(GQP_ERR_LIMIT, "hand penetration tables need %d B of shared memory (limit %d)",
-                             hdr.total_bytes, PEN_MAX_SMEM);
+                             hdr.nodes_off, PEN_MAX_SMEM);
     T->total_bytes = hdr.total_bytes;
     T->d_blob = (unsigned char *)gqp_dev_alloc_upload(B.data(), B.size());
     T->d_tris = (float *)gqp_dev_alloc_upload(tris.data(), tris.size() * sizeof(float));
@@ -761,9 +763,11 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
     GQP_CHECK_LAUNCH("gqp_hand_distance/mask");
     rc = gqp_memset_zero(partial, sizeof(float) * (size_t)Bt * n_chunks, stream);
     if (rc != GQP_OK) return rc;
-    const size_t smem = (size_t)T->total_bytes + (size_t)(PEN_THREADS / 32) * (h->host.n_links * 48);
+    const int nodes_staged = T->total_bytes <= PEN_MAX_SMEM;
+    const int staged = nodes_staged ? T->total_bytes : reinterpret_cast<const PenHdr *>(T->blob_host.data())->nodes_off;
+    const size_t smem = (size_t)staged + (size_t)(PEN_THREADS / 32) * (h->host.n_links * 48);
     int grid = pen_grid_size((int)smem, n_tasks, PEN_MIN_BLOCKS);
-    GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, T->total_bytes, T->d_tris, T->d_face_id,
+    GQP_LAUNCH(hand_pen_kernel<false>, grid, PEN_THREADS, smem, st, T->d_blob, staged, nodes_staged, T->d_tris, T->d_face_id,
                T->d_pre, T->extent, link_tf, x, bounds, masks, n_rows, cands_per_row, n_pts, dist, arg_link, dgrad,
                partial, w_pen, grad_link_tf);
     GQP_CHECK_LAUNCH("gqp_hand_distance");

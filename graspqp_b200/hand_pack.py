@@ -49,6 +49,11 @@ def make_desc(pack):
     d.sphere_link = arr("sphere_link", np.int32)
     d.joints_lower = arr("joints_lower", np.float32)
     d.joints_upper = arr("joints_upper", np.float32)
+    if "mlp_w1" in pack:  # joint-coupling network (Robotiq 2F-140)
+        d.mlp_hidden, d.mlp_out = len(pack["mlp_w1"]), len(pack["mlp_b2"])
+        d.mlp_lo, d.mlp_hi = float(pack["mlp_clamp"][0]), float(pack["mlp_clamp"][1])
+        d.mlp_w1, d.mlp_b1 = arr("mlp_w1", np.float32), arr("mlp_b1", np.float32)
+        d.mlp_w2, d.mlp_b2 = arr("mlp_w2", np.float32), arr("mlp_b2", np.float32)
     return d, keep
 
 

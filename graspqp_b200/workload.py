@@ -11,6 +11,7 @@ CONFIGS = {
     # per-GPU shares of the 8-GPU configs (objects are dealt round-robin over the ranks, shard.py)
     "config3": ("shadow_hand", ["box", "cylinder", "torus", "hull", "hull", "hull", "hull", "hull"], 10000, 4096, 12),
     "config4": ("panda", ["box", "cylinder", "torus", "hull"] * 8, 10000, 16384, 4),
+    "config4_robotiq2": ("robotiq2", ["box", "cylinder", "torus", "hull"] * 8, 10000, 16384, 4),
     "config5": ("allegro", ["hull"] * 4, 50000, 4096, 16),
 }
 

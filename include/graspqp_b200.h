@@ -92,6 +92,14 @@ typedef struct GqpHandDesc {
     const float *spheres_host;                 /* (n_spheres,4) */
     const int32_t *sphere_link_host;           /* (n_spheres) */
     const float *joints_lower_host, *joints_upper_host; /* (n_dofs) */
+    /* Joint-coupling network of the Robotiq 2F-140 (hands/robotiq2.py:9-13, utils/fk.py:23-51); mlp_hidden == 0: none.
+     * With it n_dofs must be 1 and frame_dof indexes the expanded joint vector
+     *   q = [c, W2 tanh(w1 c + b1) + b2],  c = clamp(pose[9], mlp_lo, mlp_hi)        (1 + mlp_out entries)
+     * instead of the pose row.  w1, b1: (mlp_hidden); w2: (mlp_out, mlp_hidden) row-major; b2: (mlp_out).
+     * Limits: mlp_hidden <= 16, mlp_out <= 7. */
+    int32_t mlp_hidden, mlp_out;
+    float mlp_lo, mlp_hi;
+    const float *mlp_w1_host, *mlp_b1_host, *mlp_w2_host, *mlp_b2_host;
 } GqpHandDesc;
 
 int gqp_hand_create(const GqpHandDesc *desc, GqpHand **out);

@@ -93,10 +93,24 @@ class HandOracle:
         self.n_contact_candidates = len(self.cand)
         self.L = len(self.mesh_frame)
         self.hand_pose = None
+        # hands/robotiq2.py:9-13 + utils/fk.py:23-51: Linear(1,10)-Tanh-Linear(10,5) joint-coupling network
+        self.mlp = None
+        if "mlp_w1" in pack:
+            self.mlp = (g("mlp_w1").to(dtype).reshape(-1, 1), g("mlp_b1").to(dtype), g("mlp_w2").to(dtype),
+                        g("mlp_b2").to(dtype), float(pack["mlp_clamp"][0]), float(pack["mlp_clamp"][1]))
+
+    def joint_vector(self, theta):
+        """utils/fk.py:32-39: cat([clamp(theta), net(clamp(theta))]); frame_dof indexes these columns."""
+        if self.mlp is None:
+            return theta
+        w1, b1, w2, b2, lo, hi = self.mlp
+        c = torch.clamp(theta, min=lo, max=hi)
+        return torch.cat([c, torch.tanh(c @ w1.T + b1) @ w2.T + b2], -1)
 
     # pk/chain.py:146-168 + frame.py:98-114
     def fk(self, theta):
         B = theta.shape[0]
+        theta = self.joint_vector(theta)
         trans, out = [None] * len(self.parent), [None] * len(self.parent)
         for f, par in enumerate(self.parent):
             world = torch.eye(4, dtype=self.dtype).expand(B, 4, 4) if par < 0 else trans[par]

@@ -61,7 +61,7 @@ def gen_sdf():
 
 def gen_fk():
     out = {}
-    for hand in ("allegro", "shadow_hand", "panda"):
+    for hand in ("allegro", "shadow_hand", "panda", "robotiq2"):
         pack = hand_pack.load_pack(hand)
         chain, frames = rh.pk_chain_from_pack(pack)
         rng = np.random.default_rng(3)
@@ -72,7 +72,23 @@ def gen_fk():
         theta[1, ::2] = -0.05   # negative angles
         th = torch.tensor(theta)
         # hands/panda.py:6-14 feeds the single parameter to both finger joints: frame_dof repeats the column
-        th_dict = {f"j{f}": th[:, int(d)] for f, d in enumerate(pack["frame_dof"]) if d >= 0}
+        if hand != "robotiq2":
+            th_dict = {f"j{f}": th[:, int(d)] for f, d in enumerate(pack["frame_dof"]) if d >= 0}
+        else:
+            # hands/robotiq2.py:9-13: the reference's own robotiq2f140_fk (clamp + its pickled network) expands the
+            # parameter to the chain's joints, ordered like HandModel.joints_names (DFS over non-fixed joints)
+            import importlib.util
+            spec = importlib.util.spec_from_file_location(
+                "ref_utils_fk", os.path.join(rh.REF, "graspqp", "src", "graspqp", "utils", "fk.py"))
+            ref_fk = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(ref_fk)
+            theta[2] = 0.9      # beyond the clamp (utils/fk.py:33)
+            theta[3] = -0.2
+            th = torch.tensor(theta)
+            movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
+            with torch.no_grad():
+                q = ref_fk.robotiq2f140_fk(th, joint_order=[str(pack["frame_joint"][f]) for f in movable])
+            th_dict = {f"j{f}": q[:, k] for k, f in enumerate(movable)}
         res = chain.forward_kinematics(th_dict)
         link_m = np.stack([res[f"l{int(f)}"].get_matrix().expand(B, 4, 4).numpy() for f in pack["mesh_frame"]], 1)
         # contact candidates through Transform3d.transform_points / transform_normals (hand_model.py:1233-1248)

@@ -48,7 +48,7 @@ def check_sdf(lib, be):
         lib.gqp_mesh_destroy(m)
 
 
-def check_fk(lib, be, hands=("allegro", "shadow_hand", "panda")):
+def check_fk(lib, be, hands=("allegro", "shadow_hand", "panda", "robotiq2")):
     """H2/H3 against pytorch_kinematics' Chain.forward_kinematics and Transform3d.transform_points/normals."""
     g = load("fk_ref")
     for name in hands:

@@ -25,7 +25,7 @@ def test_oracle_sdf_port_matches_reference_kernel(oracle_built):
         np.testing.assert_allclose(nr * 2 * np.sqrt(d2)[:, None], 2 * (g[key + "_points"] - cl), atol=5e-7)
 
 
-@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda"])
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2"])
 def test_oracle_fk_matches_pytorch_kinematics(hand):
     g = gc.load("fk_ref")
     k = "" if hand == "allegro" else hand + "_"

@@ -100,6 +100,6 @@ def test_trajectory_500_steps_teacher_forced(gpu):
     assert n_acc > 500
 
 
-@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4)])
+@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4), ("robotiq2", 4)])
 def test_engine_vs_oracle_other_hands(gpu, hand, n_c):
     cases.check_engine_vs_oracle(*gpu, B=6, n_pts=200, n_c=n_c, T=3, seed=5, hand=hand)

@@ -8,7 +8,7 @@ import cases
 from graspqp_b200 import engine
 
 
-@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4)])
+@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4), ("robotiq2", 4)])
 def test_iteration_vs_oracle_other_hands(emu, hand, n_c):
     n_acc = cases.check_engine_vs_oracle(emu, engine.NumpyBackend(), B=3, n_pts=48, n_c=n_c, T=2, seed=5, hand=hand)
     assert n_acc >= 0

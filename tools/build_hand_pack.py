@@ -52,6 +52,18 @@ HANDS = {
         joint_filter=["panda_finger_joint1"], coupled={"panda_finger_joint2": "panda_finger_joint1"},
         default_state=[0.04], forward_axis="z", up_axis="x", grasp_axis="y",
     ),
+    # graspqp/src/graspqp/hands/robotiq2.py: the single parameter "finger_joint" is clamped to [-0.05, 0.8] and a small
+    # network (utils/fk.py:23-51, Linear(1,10)-Tanh-Linear(10,5)) gives the other five joints of the closed linkage.
+    # penetration_points.json is keyed by Robotiq-3F link names -> no spheres (hand_model.py:312-313).
+    "robotiq2": dict(
+        urdf="robotiq2/robotiq_2f140.urdf", mesh_dir="robotiq2/meshes",
+        pen="robotiq2/penetration_points.json", use_collision=True, only_collision=False,
+        joint_filter=["finger_joint"], default_state=[0.0], forward_axis="z", up_axis="x", grasp_axis="y",
+        mlp=dict(weights="robotiq2/robotiq2f_fk.pth", clamp=[-0.05, 0.8],
+                 # utils/fk.py:13-20: column order of cat([clamped parameter, network output])
+                 order=["finger_joint", "left_inner_knuckle_joint", "right_inner_knuckle_joint",
+                        "right_outer_knuckle_joint", "left_inner_finger_joint", "right_inner_finger_joint"]),
+    ),
 }
 
 
@@ -174,6 +186,18 @@ def build(hand):
     coupled = cfg.get("coupled", {})  # joint -> the actuated joint whose parameter it copies
     drv = lambda n: coupled.get(n, n)
     frame_dof = [act.index(drv(f["jname"])) if (f["jtype"] != 0 and drv(f["jname"]) in act) else -1 for f in frames]
+    extra = {}
+    if cfg.get("mlp"):
+        # frame_dof indexes the expanded joint vector q = [clamp(theta_0), net(clamp(theta_0))] instead of the pose row;
+        # every non-fixed joint of the chain must be in the network's table (utils/fk.py:41-47 raises otherwise)
+        import torch
+        m = cfg["mlp"]
+        assert len(act) == 1 and act[0] == m["order"][0]
+        frame_dof = [m["order"].index(f["jname"]) if f["jtype"] != 0 else -1 for f in frames]
+        sd = torch.load(os.path.join(ASSETS, m["weights"]), weights_only=False).state_dict()
+        extra = dict(mlp_w1=sd["0.weight"].numpy().reshape(-1).astype(np.float32), mlp_b1=sd["0.bias"].numpy(),
+                     mlp_w2=sd["2.weight"].numpy().astype(np.float32), mlp_b2=sd["2.bias"].numpy(),
+                     mlp_clamp=np.array(m["clamp"], np.float32))
     lower = [f["lo"] for f in frames if f["jname"] in act and f["jtype"] != 0]
     upper = [f["hi"] for f in frames if f["jname"] in act and f["jtype"] != 0]
 
@@ -226,6 +250,7 @@ def build(hand):
         frame_jtype=np.array([f["jtype"] for f in frames], np.int32),
         frame_axis=np.array([f["axis"] for f in frames], np.float32), frame_dof=np.array(frame_dof, np.int32),
         frame_joff=T34("joff"), frame_loff=T34("loff"), frame_link=np.array([f["link"] for f in frames]),
+        frame_joint=np.array([f["jname"] for f in frames]),
         joint_names=np.array(act), joints_lower=np.array(lower, np.float32), joints_upper=np.array(upper, np.float32),
         default_state=np.array(cfg["default_state"], np.float32),
         mesh_frame=np.array(mesh_frame, np.int32), mesh_names=np.array(mesh_names),
@@ -233,7 +258,7 @@ def build(hand):
         cand=np.array(cand, np.float32).reshape(-1, 3), cand_normal=np.array(cand_n, np.float32).reshape(-1, 3),
         cand_link=np.array(cand_link, np.int32), spheres=np.array(sph, np.float32).reshape(-1, 4),
         sphere_link=np.array(sph_link, np.int32),
-        axes=np.array([cfg["forward_axis"], cfg["up_axis"], cfg["grasp_axis"]]),
+        axes=np.array([cfg["forward_axis"], cfg["up_axis"], cfg["grasp_axis"]]), **extra,
     )
     os.makedirs(OUT, exist_ok=True)
     np.savez_compressed(os.path.join(OUT, hand + ".npz"), **pack)
