@@ -252,7 +252,8 @@ void gqp_bvh_widen(GqpBvhHost &bvh) {
 // The reference's sign is sign(dot(p - c, n_f)) for the WINNING face f (.cu:236); c lies in f's plane, so it is the side
 // of f's plane p is on.  For a closed, consistently outward-oriented manifold mesh and a point p OUTSIDE it, p - c lies
 // in the cone spanned by the normals of the faces incident to the nearest feature; if all faces sharing a vertex have
-// pairwise non-negative normal products ("nice" mesh: no crease sharper than 90 degrees), that cone has a non-negative
+// pairwise non-negative normal products ("nice" mesh: no crease sharper than 90 degrees, except creases that no outside
+// point can be nearest to — see gqp_mesh_is_nice), that cone has a non-negative
 // product with every incident normal, so the reference returns +1 for EVERY outside point, whichever tying face wins.
 // Hence for a nice mesh a query can be skipped as soon as the point is known to be outside: outside the bounding box,
 // or inside a grid cell that lies entirely outside the mesh.
@@ -291,12 +292,13 @@ bool gqp_mesh_is_nice(const float *fv, int F) {
         idx[i] = it->second;
     }
     // closed + consistently oriented: every directed edge appears once and its reverse appears once
-    std::map<std::pair<int, int>, int> edges;
+    std::map<std::pair<int, int>, int> edges, edge_face;
     for (int f = 0; f < F; ++f)
         for (int k = 0; k < 3; ++k) {
             int u = idx[3 * f + k], v = idx[3 * f + (k + 1) % 3];
             if (u == v) return false;
             if (++edges[{u, v}] > 1) return false;
+            edge_face[{u, v}] = f;
         }
     for (auto &e : edges)
         if (!edges.count({e.first.second, e.first.first})) return false;
@@ -311,12 +313,72 @@ bool gqp_mesh_is_nice(const float *fv, int F) {
         nh[f] = n * (1.0 / l);
     }
     std::vector<std::vector<int>> inc(vid.size());
+    std::vector<D3> vpos(vid.size());
     for (int f = 0; f < F; ++f)
-        for (int k = 0; k < 3; ++k) inc[idx[3 * f + k]].push_back(f);
-    for (auto &fs : inc)
-        for (size_t i = 0; i < fs.size(); ++i)
+        for (int k = 0; k < 3; ++k) {
+            inc[idx[3 * f + k]].push_back(f);
+            vpos[idx[3 * f + k]] = ldv(fv + 9 * f + 3 * k);
+        }
+    // creases sharper than 90 degrees are tolerated where no OUTSIDE point can have them as its nearest feature:
+    // (a) an edge whose two faces have opposed normals must be concave (the far corner of each face lies above the
+    //     other's plane): the points nearest to a concave edge are behind both faces, and for a point in the valley the
+    //     nearer face beats the edge by a factor <= sin(45 deg), far beyond fp32 ties;
+    // (b) a vertex with an opposed pair among its faces must have an empty normal cone with a margin: for EVERY direction
+    //     d some incident edge direction u has d.u >= rho, so the edge (v,u) is nearer than v by a relative
+    //     rho*|u-v|/|p-v| in squared distance, which must stay above fp32 rounding (4e-6 at 2 m) so that no incident
+    //     face that files p under its corner v (distance |p-v|, any face order) can win.
+    for (int f = 0; f < F; ++f)
+        for (int k = 0; k < 3; ++k) {
+            int u = idx[3 * f + k], v = idx[3 * f + (k + 1) % 3];
+            int g = edge_face[{v, u}];
+            if (dot(nh[f], nh[g]) >= -1e-6) continue;
+            int og = -1;  // corner of g opposite the shared edge
+            for (int q = 0; q < 3; ++q)
+                if (idx[3 * g + q] != u && idx[3 * g + q] != v) og = idx[3 * g + q];
+            if (og < 0 || !(dot(nh[f], vpos[og] - vpos[u]) > 1e-6)) return false;  // convex (or flat-folded) sharp crease
+        }
+    for (size_t v = 0; v < inc.size(); ++v) {
+        const std::vector<int> &fs = inc[v];
+        bool sharp = false;
+        for (size_t i = 0; i < fs.size() && !sharp; ++i)
             for (size_t j = i + 1; j < fs.size(); ++j)
-                if (dot(nh[fs[i]], nh[fs[j]]) < -1e-6) return false;
+                if (dot(nh[fs[i]], nh[fs[j]]) < -1e-6) { sharp = true; break; }
+        if (!sharp) continue;
+        std::vector<D3> dir;  // unit directions of the incident edges
+        double emin = 1e30;
+        for (int f : fs)
+            for (int k = 0; k < 3; ++k) {
+                int w = idx[3 * f + k];
+                if (w == (int)v) continue;
+                D3 e = vpos[w] - vpos[v];
+                double l = std::sqrt(dot(e, e));
+                emin = std::min(emin, l);
+                dir.push_back(e * (1.0 / l));
+            }
+        // rho = radius of the largest ball about the origin inside conv{dir}: min over the hull's facets
+        double rho = 1e30;
+        bool any = false;
+        const int n = (int)dir.size();
+        for (int i = 0; i < n; ++i)
+            for (int j = i + 1; j < n; ++j)
+                for (int k = j + 1; k < n; ++k) {
+                    D3 m = cross(dir[j] - dir[i], dir[k] - dir[i]);
+                    double l = std::sqrt(dot(m, m));
+                    if (l < 1e-9) continue;
+                    m = m * (1.0 / l);
+                    double h = dot(m, dir[i]);
+                    bool below = true, above = true;
+                    for (int t = 0; t < n; ++t) {
+                        double sd = dot(m, dir[t]) - h;
+                        if (sd > 1e-9) below = false;
+                        if (sd < -1e-9) above = false;
+                    }
+                    if (below == above) continue;  // not a supporting plane (or everything coplanar)
+                    any = true;
+                    rho = std::min(rho, below ? h : -h);
+                }
+        if (!any || !(rho > 0.05) || !(rho * emin > 8e-6)) return false;
+    }
     // outward orientation: signed volume > 0
     double vol = 0;
     for (int f = 0; f < F; ++f) vol += dot(ldv(fv + 9 * f), cross(ldv(fv + 9 * f + 3), ldv(fv + 9 * f + 6)));

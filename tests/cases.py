@@ -65,14 +65,16 @@ def fk_state(lib, be, hand, pack, pose):
     return dpose, tf
 
 
-def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5):
+def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5, hand="allegro"):
     """culled E_pen / gradient == un-culled at the reference's sample count; distances vs the oracle on a subset."""
-    pack = hand_pack.load_pack("allegro")
+    pack = hand_pack.load_pack(hand)
+    allegro = hand == "allegro"
     hand = hand_pack.create_hand(lib, pack)
     v, f = synth.make_mesh("hull", 2000, seed)
     sp = synth.sample_surface(v, f, n_pts, seed=seed, oversample=2)
     pose, idx = synth.random_grasp_init(pack, [v], B, 12, seed)
-    pose[:, :3] *= np.linspace(0.4, 1.0, B, dtype=np.float32)[:, None]
+    # push the hand into the object: grippers have a wide open palm, they need to go deeper to touch anything
+    pose[:, :3] *= np.linspace(0.4 if allegro else 0.0, 1.0, B, dtype=np.float32)[:, None]
     dpose, tf = fk_state(lib, be, hand, pack, pose)
     L = len(pack["mesh_frame"])
     x = be.from_host(sp[None], np.float32)
@@ -85,7 +87,7 @@ def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5):
     _lib.check(lib.gqp_hand_distance(hand, be.ptr(tf), be.ptr(x), 1, B, n_pts, 0, None, be.ptr(e2), be.ptr(sc), 100.0,
                                      be.ptr(g2), be.stream), lib)
     e1h, e2h, g1h, g2h, dh = [be.to_host(a) for a in (e1, e2, g1, g2, dist)]
-    assert (e1h > 0).sum() >= B // 4, "poses do not penetrate"
+    assert (e1h > 0).sum() >= (B // 4 if allegro else B // 8), "poses do not penetrate"
     # same winners; the culled path sums in 2^-40 m fixed point, the full path in fp32 in a fixed order
     np.testing.assert_allclose(e2h, e1h, rtol=1e-6, atol=1e-9)
     np.testing.assert_allclose(g2h, g1h, rtol=1e-4, atol=1e-4)  # atomics: order differs

@@ -44,6 +44,13 @@ def test_hand_distance(gpu):
     cases.check_hand_distance(*gpu)
 
 
+@pytest.mark.parametrize("hand", ["shadow_hand", "panda", "robotiq2"])
+def test_hand_distance_other_hands(gpu, hand):
+    """Culled E_pen == un-culled (every sample searched) with samples all around the links: the Panda fingers carry a
+    concave crease sharper than 90 degrees that the far-field culling proof (gqp_mesh_is_nice) has to get right."""
+    cases.check_hand_distance(*gpu, B=192, hand=hand)
+
+
 def test_engine_vs_oracle(gpu):
     n_acc = cases.check_engine_vs_oracle(*gpu, B=8, n_pts=256, T=4)
     assert n_acc > 0
