@@ -387,12 +387,19 @@ bool gqp_mesh_is_nice(const float *fv, int F) {
 
 // bit = 1 when the whole cell is outside the (nice) mesh with a 10 micron margin.  Cell (x,y,z) -> bit
 // ((z*dim[1]+y)*dim[0]+x).
+// A cell is FREE when the surface stays farther from its centre than its circumradius (+ margin).  A free cell is convex
+// and untouched by the surface, so it lies in ONE region of space, and two free cells sharing a face lie in the same
+// one.  Free cells of the outermost layer reach beyond the mesh's bounding box (the grid overhangs it by at least half
+// a cell on every side), hence are outside; outside-ness is flood-filled from them through face-adjacent free cells.
+// (Judging a cell by the side of its centre's nearest face alone is wrong for meshes with nested shells, e.g. the
+// Shadow Hand's thumb base: between two outward-oriented shells the nearest face may be the inner one.)
 void gqp_outside_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
                             std::vector<uint32_t> &bits) {
     size_t ncell = (size_t)dim[0] * dim[1] * dim[2];
     bits.assign((ncell + 31) / 32, 0u);
     if (bvh.nodes.empty()) return;
     const double r = 0.5 * std::sqrt(3.0) * cell * 1.001 + 1e-5;  // circumradius + slack for the fp32 cell index + margin
+    std::vector<unsigned char> state(ncell, 0);                   // 0 = touched by the surface, 1 = free, 2 = outside
     for (int z = 0; z < dim[2]; ++z)
         for (int y = 0; y < dim[1]; ++y)
             for (int x = 0; x < dim[0]; ++x) {
@@ -405,7 +412,26 @@ void gqp_outside_grid_build(const GqpBvhHost &bvh, const float origin[3], float 
                 const float *t = &bvh.tris[9 * (size_t)slot];
                 D3 a = ldv(t), b = ldv(t + 3), cc = ldv(t + 6);
                 if (dot(c - a, cross(b - a, cc - a)) <= 0) continue;  // centre is inside
-                size_t i = ((size_t)z * dim[1] + y) * dim[0] + x;
-                bits[i >> 5] |= 1u << (i & 31);
+                state[((size_t)z * dim[1] + y) * dim[0] + x] = 1;
             }
+    std::vector<size_t> todo;
+    auto visit = [&](int x, int y, int z) {
+        if (x < 0 || y < 0 || z < 0 || x >= dim[0] || y >= dim[1] || z >= dim[2]) return;
+        size_t i = ((size_t)z * dim[1] + y) * dim[0] + x;
+        if (state[i] != 1) return;
+        state[i] = 2;
+        todo.push_back(i);
+    };
+    for (int z = 0; z < dim[2]; ++z)
+        for (int y = 0; y < dim[1]; ++y)
+            for (int x = 0; x < dim[0]; ++x)
+                if (x == 0 || y == 0 || z == 0 || x == dim[0] - 1 || y == dim[1] - 1 || z == dim[2] - 1) visit(x, y, z);
+    while (!todo.empty()) {
+        size_t i = todo.back();
+        todo.pop_back();
+        int x = (int)(i % dim[0]), y = (int)((i / dim[0]) % dim[1]), z = (int)(i / ((size_t)dim[0] * dim[1]));
+        visit(x - 1, y, z); visit(x + 1, y, z); visit(x, y - 1, z); visit(x, y + 1, z); visit(x, y, z - 1); visit(x, y, z + 1);
+    }
+    for (size_t i = 0; i < ncell; ++i)
+        if (state[i] == 2) bits[i >> 5] |= 1u << (i & 31);
 }

@@ -90,7 +90,8 @@ def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5, hand="allegro"):
     assert (e1h > 0).sum() >= (B // 4 if allegro else B // 8), "poses do not penetrate"
     # same winners; the culled path sums in 2^-40 m fixed point, the full path in fp32 in a fixed order
     np.testing.assert_allclose(e2h, e1h, rtol=1e-6, atol=1e-9)
-    np.testing.assert_allclose(g2h, g1h, rtol=1e-4, atol=1e-4)  # atomics: order differs
+    # atomics: order differs; deep poses reach |g| ~ 1e3, the absolute slack follows the largest entry
+    np.testing.assert_allclose(g2h, g1h, rtol=1e-4, atol=1e-4 * max(1.0, float(np.abs(g1h).max()) / 10))
     nb = min(B, 6)
     o = HandOracle(pack, torch.float32)
     o.set_parameters(torch.tensor(pose[:nb]), torch.tensor(idx[:nb]).long())
