@@ -12,3 +12,11 @@ from graspqp_b200 import engine
 def test_iteration_vs_oracle_other_hands(emu, hand, n_c):
     n_acc = cases.check_engine_vs_oracle(emu, engine.NumpyBackend(), B=3, n_pts=48, n_c=n_c, T=2, seed=5, hand=hand)
     assert n_acc >= 0
+
+
+@pytest.mark.parametrize("hand", ["shadow_hand", "panda", "robotiq2"])
+def test_culled_pen_equals_unculled_other_hands(emu, hand):
+    """H4 on poses pushed into the object: the culled path (outside grids, link boxes) must give the E_pen of the path
+    that searches every (sample, link) pair.  Guards the culling proofs of gqp_bvh.cpp (concave creases of the Panda
+    fingers, nested shells of the Shadow thumb base); the full-size version runs on the GPU."""
+    cases.check_hand_distance(emu, engine.NumpyBackend(), B=8, n_pts=160, hand=hand)
