@@ -19,4 +19,4 @@ def test_culled_pen_equals_unculled_other_hands(emu, hand):
     """H4 on poses pushed into the object: the culled path (outside grids, link boxes) must give the E_pen of the path
     that searches every (sample, link) pair.  Guards the culling proofs of gqp_bvh.cpp (concave creases of the Panda
     fingers, nested shells of the Shadow thumb base); the full-size version runs on the GPU."""
-    cases.check_hand_distance(emu, engine.NumpyBackend(), B=8, n_pts=160, hand=hand)
+    cases.check_hand_distance(emu, engine.NumpyBackend(), B=4, n_pts=64, hand=hand)
