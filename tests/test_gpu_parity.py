@@ -107,6 +107,19 @@ def test_trajectory_500_steps_teacher_forced(gpu):
     assert n_acc > 500
 
 
+@pytest.mark.parametrize("hand,n_c,fc_tol", [("shadow_hand", 12, 1e-5), ("robotiq2", 4, 5e-3)])
+def test_trajectory_other_hands(gpu, hand, n_c, fc_tol):
+    """150 teacher-forced steps with the Shadow Hand (24 dof, 18 links) and the Robotiq 2F-140 (coupling network in the
+    FK backward, small QP): same per-step tolerances as the Allegro trajectory, with ONE stated exception.  OPEN ITEM
+    (profiles/r1_notes.md, r1g): with 4 contacts on two parallel pads the grasp matrix is nearly rank deficient, and on
+    the < 1 % of candidate-steps that are already flagged as conditioning events the kernel's E_fc (6x6 Woodbury form of
+    the KKT solves, fp64) and the oracle's (full KKT LU, fp64) differ by up to 8e-4 relative ON IDENTICAL INPUTS; for
+    n_c = 12 that difference stays below 1e-5.  Tolerance for those flagged steps at n_c = 4: 5e-3."""
+    n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=150, n_c=n_c, hand=hand, fc_tol=fc_tol)
+    print(f"{hand}: {n_acc} accepted, {n_tie} borderline, worst energy error {worst:.2e}")
+    assert n_acc > 50
+
+
 @pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("panda", 4), ("robotiq2", 4)])
 def test_engine_vs_oracle_other_hands(gpu, hand, n_c):
     cases.check_engine_vs_oracle(*gpu, B=6, n_pts=200, n_c=n_c, T=3, seed=5, hand=hand)
