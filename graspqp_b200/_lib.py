@@ -68,6 +68,7 @@ SIGNATURES = {
                                  c_uint64, P, P, P, P]),
     "gqp_mala_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, P, P, c_uint64, c_uint64,
                                 P, P, P, P, P, P, P, P, P, P, P, P, P]),
+    "gqp_mala_reset": (c_int, [c_int, c_int, c_int, P, c_float, P, P, P, P, P, P, P, P, P, P, P]),
     "gqp_memset_zero": (c_int, [P, c_uint64, P]),
     "gqp_fma_peak_probe": (c_int, [c_int, P, POINTER(c_uint64), P]),
 }

@@ -484,11 +484,65 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         for (int i = 0; i < 6; ++i) { Fx[i] = red[i]; value += 0.5 * red[i] * red[i]; }
 #pragma unroll
         for (int i = 0; i < 21; ++i) Lg[i] = red[6 + i];
-        chol6<false>(Lg);  // F F' = Lg Lg'  ->  prod(svdvals(F)) = prod(diag Lg)
+        double piv = 1.0;  // smallest pivot of the factorisation relative to its diagonal entry of F F'
+        {
+            double gd[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) gd[i] = Lg[tri_ix(i, i)];
+            chol6<false>(Lg);  // F F' = Lg Lg'  ->  prod(svdvals(F)) = prod(diag Lg)
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const double li = Lg[tri_ix(i, i)];  // 1 / L_ii
+                const double r = 1.0 / (li * li * gd[i]);
+                piv = (r == r) ? fmin(piv, r) : 0.0;
+            }
+        }
+        if (piv < 1e-6) {
+            // Nearly rank-deficient grasp matrix (contacts on one line, duplicated contact indices: n_c = 4 on parallel
+            // pads).  Cholesky of F F' squares the condition number and resolves sigma_min/sigma_max only down to 1e-8,
+            // where svdvals (span.py:402) resolves 1e-16, and prod(sigma)^(1/6) magnifies exactly that.  Re-factorise
+            // F' = Q R by classical Gram-Schmidt with re-orthogonalisation (CGS2) over the warp: R'R = F F' and the
+            // entries of R carry an absolute error of eps * |F|, as svdvals' do.  Warp-uniform, rare branch.
+            double a[2][6], R[6][6];
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int i = 0; i < 6; ++i) a[v][i] = valid[v] ? F[v][i] : 0.0;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) R[k][j] = 0.0;
+#pragma unroll
+                for (int pass = 0; pass < 2; ++pass) {
+                    double c[6];
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) c[k] = (k < j) ? a[0][k] * a[0][j] + a[1][k] * a[1][j] : 0.0;
+                    warp_allreduce<6, false>(sm, c, lane);
+#pragma unroll
+                    for (int k = 0; k < 6; ++k)
+                        if (k < j) {
+                            a[0][j] -= c[k] * a[0][k];
+                            a[1][j] -= c[k] * a[1][k];
+                            R[k][j] += c[k];
+                        }
+                }
+                double nn[1] = {a[0][j] * a[0][j] + a[1][j] * a[1][j]};
+                warp_allreduce<1, false>(sm, nn, lane);
+                const double rjj = sqrt(nn[0]);
+                R[j][j] = rjj;
+                const double inv = rjj > 0.0 ? 1.0 / rjj : 0.0;
+                a[0][j] *= inv;
+                a[1][j] *= inv;
+            }
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+#pragma unroll
+                for (int k = 0; k <= i; ++k) Lg[tri_ix(i, k)] = (k == i) ? 1.0 / R[i][i] : R[k][i];
+        }
         double logdet = 0.0;
 #pragma unroll
         for (int i = 0; i < 6; ++i) logdet -= log(Lg[tri_ix(i, i)]);  // diagonal is stored inverted
-        const bool rank_ok = logdet == logdet;  // NaN when F F' is numerically singular
+        const bool rank_ok = logdet == logdet && logdet > -1e300;  // NaN / -inf when F F' is numerically singular
         const double svd = rank_ok ? exp(logdet / 6.0) : 0.0;
         const double ex = exp(-P.svd_gain * svd);
         const double Efc = P.values_gain * (value + P.values_offset) * ex;

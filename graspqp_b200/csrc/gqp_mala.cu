@@ -39,10 +39,7 @@ mala_stats_kernel(const float *__restrict__ grad, const float *__restrict__ ener
             float s = 0.f;
             for (int r = r0; r < r1; ++r) {
                 float g = grad[(size_t)r * D + d];
-                if (clip_grad) {
-                    g = fminf(fmaxf(g, -100.f), 100.f);
-                    if (g != g) g = 0.f;
-                }
+                if (clip_grad) g = (g != g) ? 0.f : fminf(fmaxf(g, -100.f), 100.f);  // :211-213 (clip keeps NaN, then NaN -> 0)
                 s += g * g;
             }
             partial[(size_t)blockIdx.x * D + d] = s;
@@ -99,18 +96,20 @@ mala_propose_kernel(GqpMalaParams P, const float *__restrict__ pose, const float
     if (b >= Bt) return;
     const int st = step[b];
     const float s = P.step_size * powf(P.temperature_decay, (float)(st / P.stepsize_period));  // :209
+    bool row_nan = false;
     for (int d = 0; d < D; ++d) {
         const size_t i = (size_t)b * D + d;
         float g = grad[i];
-        if (P.clip_grad) {
-            g = fminf(fmaxf(g, -100.f), 100.f);
-            if (g != g) g = 0.f;
-        }
+        if (P.clip_grad) g = (g != g) ? 0.f : fminf(fmaxf(g, -100.f), 100.f);  // :211-213
         float e = P.mu * grad2_mean[d] + (1.0f - P.mu) * ema[i];  // :233
         if (e != e) e = 0.f;                                       // :235-236
         ema[i] = e;
-        pose_new[i] = pose[i] - s * g / (sqrtf(e) + 1e-6f);  // :240
+        const float pn = pose[i] - s * g / (sqrtf(e) + 1e-6f);  // :240
+        row_nan |= pn != pn;
+        pose_new[i] = pn;
     }
+    if (row_nan)  // :242-244: a row with any NaN entry is zeroed as a whole
+        for (int d = 0; d < D; ++d) pose_new[(size_t)b * D + d] = 0.f;
     for (int c = 0; c < n_c; ++c) {  // :252-257
         const size_t i = (size_t)b * n_c + c;
         float u;
@@ -167,6 +166,63 @@ mala_accept_kernel(GqpMalaParams P, int Bt, int D, int n_c, int n_terms, const f
     if (new_energy_out) new_energy_out[b] = en;
     if (accept_out) accept_out[b] = acc ? 1 : 0;
     if (temperature_out) temperature_out[b] = T;
+}
+
+// M3: MalaStar.reset_envs (optimizer.py:275-287) + HandModel.set_parameters(..., env_mask) (hand_model.py:845-850,
+// 816-831) as scripts/fit.py:408-422 applies them between try_step and the energy evaluation.
+__global__ void __launch_bounds__(128)
+mala_reset_kernel(int Bt, int D, int n_c, const float *__restrict__ z, float z_threshold,
+                  const uint8_t *__restrict__ mask_in, const float *__restrict__ pose_init,
+                  const int32_t *__restrict__ idx_init, float *__restrict__ pose_new, int32_t *__restrict__ idx_new,
+                  int32_t *__restrict__ idx_eval, int32_t *__restrict__ step, float *__restrict__ ema,
+                  uint8_t *__restrict__ mask_out, int32_t *__restrict__ count_out) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    bool m = false;
+    if (b < Bt) {
+        m = mask_in ? mask_in[b] != 0 : z[b] > z_threshold;  // fit.py:409 (NaN z: false, as torch's comparison)
+        if (m) {
+            for (int d = 0; d < D; ++d) {
+                pose_new[(size_t)b * D + d] = pose_init[(size_t)b * D + d];
+                ema[(size_t)b * D + d] = 0.f;  // :277
+            }
+            step[b] = 0;  // :276
+        }
+        for (int c = 0; c < n_c; ++c) {
+            const int32_t r = idx_init[(size_t)b * n_c + c];
+            if (m) idx_new[(size_t)b * n_c + c] = r;
+            // hand_model.py:830-831 gathers the contact points of EVERY row with the freshly drawn indices, masked or
+            // not, while contact_point_indices keeps the proposal's for unmasked rows: the energies of a reset
+            // iteration are evaluated at idx_eval, the state that is committed is idx_new
+            if (idx_eval) idx_eval[(size_t)b * n_c + c] = r;
+        }
+        mask_out[b] = m ? 1 : 0;
+    }
+    if (count_out) {
+        const unsigned bal = __ballot_sync(GQP_FULL, m);
+        if ((threadIdx.x & 31) == 0 && bal) atomicAdd(count_out, __popc(bal));
+    }
+}
+
+extern "C" int gqp_mala_reset(int Bt, int D, int n_c, const float *z, float z_threshold, const uint8_t *mask_in,
+                              const float *pose_init, const int32_t *idx_init, float *pose_new, int32_t *idx_new,
+                              int32_t *idx_eval, int32_t *step, float *ema, uint8_t *mask_out, int32_t *count_out,
+                              void *stream) {
+    if (Bt < 0 || D <= 0 || n_c <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_mala_reset: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if ((!z && !mask_in) || !pose_init || !idx_init || !pose_new || !idx_new || !step || !ema || !mask_out)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_mala_reset: null pointer");
+    if (count_out) {
+#ifndef GQP_EMU
+        if (cudaMemsetAsync(count_out, 0, sizeof(int32_t), (cudaStream_t)stream) != cudaSuccess)
+            return gqp_set_error(GQP_ERR_CUDA, "gqp_mala_reset: memset failed");
+#else
+        *count_out = 0;
+#endif
+    }
+    GQP_LAUNCH(mala_reset_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, Bt, D, n_c, z, z_threshold, mask_in,
+               pose_init, idx_init, pose_new, idx_new, idx_eval, step, ema, mask_out, count_out);
+    GQP_CHECK_LAUNCH("gqp_mala_reset");
+    return GQP_OK;
 }
 
 extern "C" int gqp_mala_stats(const float *grad, const float *energy, int n_obj, int batch_each, int D, int clip_grad,

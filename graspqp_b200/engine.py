@@ -198,6 +198,8 @@ class FitEngine:
         self.qp_ws = be.empty(((int(cdll.gqp_fc_workspace_bytes(Bt, n_c, self.fc.max_iter)) + 7) // 8,), np.float64)
         self.qp_stop = be.empty((1,), i32)
         self.reset_all = be.from_host(np.ones(Bt, u8))
+        self.reset_mask, self.reset_count = be.empty((Bt,), u8), be.empty((1,), i32)
+        self.idx_eval = be.empty((Bt, n_c), i32)
         self._init_energy()
 
     # ------------------------------------------------------------------------------------------------------------
@@ -286,8 +288,15 @@ class FitEngine:
         self.first_grad = self.be.to_host(self.grad)
         self._ck(self.lib.gqp_memset_zero(self.be.ptr(self.grad), 4 * self.Bt * self.D, self.be.stream))
 
-    def step(self, u_switch=None, idx_rand=None, u_accept=None, reset_mask=None):
-        """One iteration of fit.py:399-458.  Noise arrays (device buffers) are injected, or drawn by Philox if None."""
+    def step(self, u_switch=None, idx_rand=None, u_accept=None, reset_init=None, reset_mask=None,
+             z_score_threshold=1.0):
+        """One iteration of fit.py:399-458.  Noise arrays (device buffers) are injected, or drawn by Philox if None.
+
+        reset_init = (pose_init (Bt,D), idx_init (Bt,n_c)) makes this a RESET iteration (fit.py:408-422): rows with
+        z-score > z_score_threshold (or the injected uint8 `reset_mask`) are re-initialised from it between the proposal
+        and the energy evaluation, their step counter and RMS accumulator restart (MalaStar.reset_envs) and their
+        proposal is accepted unconditionally.  As in the reference (hand_model.py:830-831), the energies of a reset
+        iteration are evaluated at the freshly drawn contact indices for EVERY row."""
         lib, p, st = self.lib, self.be.ptr, self.be.stream
         self.iteration += 1
         self._ck(lib.gqp_mala_stats(p(self.grad), p(self.energy), self.n_obj, self.batch_each, self.D,
@@ -298,11 +307,19 @@ class FitEngine:
                                       p(self.ema), p(self.step_count), p(self.idx), self.Bt, self.D, self.n_c,
                                       self.n_cand, p(u_switch), p(idx_rand), self.seed, self.iteration,
                                       p(self.pose_new), p(self.idx_new), p(self.step_size_out), st))
+        if reset_init is not None:
+            pose_init, idx_init = reset_init
+            self._ck(lib.gqp_mala_reset(self.Bt, self.D, self.n_c, p(self.z), float(z_score_threshold), p(reset_mask),
+                                        p(pose_init), p(idx_init), p(self.pose_new), p(self.idx_new), p(self.idx_eval),
+                                        p(self.step_count), p(self.ema), p(self.reset_mask), p(self.reset_count), st))
+            self.evaluate(self.pose_new, self.idx_eval, self.losses_new, self.grad_new)
+            self._accept(self.z, self.reset_mask, u_accept)
+            return
         if self._graph is not None:
             self._graph.replay()
         else:
             self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
-        self._accept(self.z, reset_mask, u_accept)
+        self._accept(self.z, None, u_accept)
 
     _STATE = ("pose", "idx", "grad", "ema", "step_count", "energy", "losses")
 
@@ -346,9 +363,6 @@ class FitEngine:
             "fk_backward": lambda: lib.gqp_fk_backward(self.hand, p(self.pose_new), p(self.g_link_tf),
                                                        p(self.g_pose_joints), Bt, p(self.grad_new), st),
         }
-
-    def launches_per_step(self):
-        return 13
 
     def close(self):
         lib = self.lib

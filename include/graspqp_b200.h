@@ -201,6 +201,8 @@ int gqp_fc_finish(const GqpFcParams *p_host, const float *cpts, const float *cnr
  * gqp_mala_stats: grad2_mean (D) = mean over ALL rows of grad^2 (optimizer.py:231) and the per-object z-score of
  *   `energy` (fit.py:403-406, unbiased std) -> z (Bt).   Deterministic two-pass reduction.
  * gqp_mala_propose: ema = mu*grad2_mean + (1-mu)*ema (NaN->0); pose_new = pose - s_i*grad/(sqrt(ema)+1e-6);
+ *   with clip_grad NaN gradients count as 0 and the rest is clamped to +-100 (:211-213); a row of pose_new with a NaN
+ *   entry is zeroed as a whole (:242-244);
  *   idx_new = switch ? idx_rand : idx;  step += 1; step_size_out (Bt) = s_i (may be NULL).
  * gqp_mala_accept: new_energy = sum_k w_k*losses_new[k]; T = T0*decay^(step/period)*(1+Phi(z));
  *   accept = u < exp((E-E')/T) or reset; accepted rows copy pose_new/idx_new/grad_new/energy/losses into the state. */
@@ -221,6 +223,20 @@ int gqp_mala_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n_t
                     const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose, int32_t *idx,
                     float *grad, float *energy, float *losses /* (n_terms,Bt) */, float *new_energy_out,
                     uint8_t *accept_out, float *temperature_out, void *stream);
+
+/* ---- M3: outlier reset (fit.py:408-422: reset_mask = z > threshold; initialize_convex_hull(env_mask); reset_envs) ----
+ * Called between gqp_mala_propose and the energy evaluation of a reset iteration.  pose_init (Bt,D) / idx_init (Bt,n_c)
+ * hold a fresh initialisation of EVERY row (initialize_convex_hull recomputes all rows, core/initializations.py:15-193:
+ * gqp_init_convex_hull below, or injected).  mask = mask_in (uint8, injected) or, if NULL, z > z_threshold.  Masked rows:
+ * pose_new <- pose_init, idx_new <- idx_init (HandModel.set_parameters(env_mask), hand_model.py:845-850, 816-822),
+ * step <- 0, ema <- 0 (MalaStar.reset_envs, optimizer.py:275-287).  mask_out (Bt) uint8 is what gqp_mala_accept takes as
+ * reset_mask (forced accept, optimizer.py:315-316); *count_out (device int, may be NULL) = number of masked rows.
+ * idx_eval (Bt,n_c), may be NULL: receives idx_init for EVERY row — the reference gathers the contact points of a reset
+ * iteration with the freshly drawn indices for all rows (hand_model.py:830-831 uses the argument, not the merged
+ * member), so that iteration's energies are evaluated at idx_eval while idx_new is what gets committed. */
+int gqp_mala_reset(int Bt, int D, int n_c, const float *z, float z_threshold, const uint8_t *mask_in,
+                   const float *pose_init, const int32_t *idx_init, float *pose_new, int32_t *idx_new,
+                   int32_t *idx_eval, int32_t *step, float *ema, uint8_t *mask_out, int32_t *count_out, void *stream);
 
 /* cudaMemsetAsync(ptr, 0, bytes) on the stream: the per-step reset of grad_link_tf. */
 int gqp_memset_zero(void *ptr, uint64_t bytes, void *stream);

@@ -136,14 +136,24 @@ class HandOracle:
     def link_matrix(self, li):
         return self.current_status[self.mesh_frame[li]]
 
-    def set_parameters(self, hand_pose, contact_point_indices):
-        self.hand_pose = hand_pose.clone()
+    def set_parameters(self, hand_pose, contact_point_indices, env_mask=None):
+        if env_mask is not None:  # hand_model.py:845-850
+            with torch.no_grad():
+                self.hand_pose = torch.where(env_mask.unsqueeze(-1), hand_pose, self.hand_pose)
+            self.hand_pose.requires_grad = True
+            self.hand_pose.retain_grad()
+        else:
+            self.hand_pose = hand_pose.clone()
         if self.hand_pose.requires_grad:
             self.hand_pose.retain_grad()
         self.global_translation = self.hand_pose[:, 0:3]
         self.global_rotation = special_gramschmidt(torch.stack([self.hand_pose[:, 3:6], self.hand_pose[:, 6:9]], -1))
         self.current_status = self.fk(self.hand_pose[:, 9:])
-        self.contact_point_indices = contact_point_indices.clone()
+        if env_mask is None:  # hand_model.py:816-822
+            self.contact_point_indices = contact_point_indices.clone()
+        else:
+            self.contact_point_indices = torch.where(env_mask.unsqueeze(-1), contact_point_indices,
+                                                     self.contact_point_indices)
         pts, nrm = [], []
         for li in range(self.L):
             m = self.cand_link == li
@@ -155,6 +165,8 @@ class HandOracle:
             nrm.append(self.cand_normal[m] @ torch.linalg.inv(R))  # transform_normals: n @ R^-1
         pts = torch.cat(pts, -2) @ self.global_rotation.transpose(1, 2) + self.global_translation.unsqueeze(1)
         nrm = torch.cat(nrm, -2) @ self.global_rotation.transpose(1, 2)
+        # hand_model.py:830-831: the gather uses the ARGUMENT (with env_mask: the fresh indices of every row), not the
+        # merged member
         idx = contact_point_indices.unsqueeze(-1).expand(-1, -1, 3)
         self.contact_points = pts.gather(1, idx)
         self.contact_normals = nrm.gather(1, idx)

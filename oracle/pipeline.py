@@ -65,8 +65,9 @@ def total_energy(losses, weights=WEIGHTS):
 
 class MalaStarOracle:
     def __init__(self, hand, switch_possibility=0.4, starting_temperature=18.0, temperature_decay=0.95,
-                 annealing_period=30, step_size=0.005, stepsize_period=50, mu=0.98):
+                 annealing_period=30, step_size=0.005, stepsize_period=50, mu=0.98, clip_grad=False):
         self.hand = hand
+        self.clip_grad = clip_grad
         self.switch_possibility = switch_possibility
         dt = hand.dtype
         self.starting_temperature = torch.tensor(starting_temperature, dtype=dt)
@@ -82,12 +83,18 @@ class MalaStarOracle:
         h = self.hand
         s = self.step_size * self.temperature_decay ** torch.div(self.step, self.step_size_period, rounding_mode="floor")
         step_size = torch.zeros_like(h.hand_pose) + s[..., None]
-        gradient = h.hand_pose.grad
+        if self.clip_grad:  # optimizer.py:211-213
+            gradient = h.hand_pose.grad.clip(min=-100, max=100)
+            gradient[torch.isnan(gradient)] = 0
+        else:
+            gradient = h.hand_pose.grad
         grad = (gradient ** 2).mean(0)
         self.ema = self.mu * grad + (1 - self.mu) * self.ema
         self.ema[torch.isnan(self.ema)] = 0
         hand_pose = h.hand_pose - step_size * gradient / (torch.sqrt(self.ema) + 1e-6)
         hand_pose = hand_pose.detach()
+        if hand_pose.isnan().any():  # optimizer.py:242-244
+            hand_pose[hand_pose.isnan().any(dim=-1)] = 0
         switch_mask = u_switch < self.switch_possibility
         idx = h.contact_point_indices.clone()
         idx[switch_mask] = idx_new[switch_mask]
@@ -96,13 +103,24 @@ class MalaStarOracle:
         self.step += 1
         return s
 
-    def accept_step(self, energy, new_energy, u_accept, z_score):
+    def reset_envs(self, mask):  # optimizer.py:275-287
+        h = self.hand
+        self.step[mask] = 0
+        self.ema[mask] = 0
+        with torch.no_grad():
+            self.old["pose"][mask] = h.hand_pose[mask]
+        self.old["idx"][mask] = h.contact_point_indices[mask]
+        self.old["grad"][mask] = 0 * self.old["grad"][mask]
+
+    def accept_step(self, energy, new_energy, u_accept, z_score, reset_mask=None):
         h = self.hand
         temperature = self.starting_temperature * self.temperature_decay ** torch.div(
             self.step, self.annealing_period, rounding_mode="floor")
         proba = torch.distributions.normal.Normal(0.0, 1.0).cdf(z_score.detach())
         temperature = temperature * (1 + proba)
         accept = u_accept < torch.exp((energy - new_energy) / temperature)
+        if reset_mask is not None:
+            accept[reset_mask] = True  # optimizer.py:315-316
         with torch.no_grad():
             reject = ~accept
             h.hand_pose[reject] = self.old["pose"][reject]
@@ -139,10 +157,19 @@ class FitLoopOracle:
         self.opt.ema = torch.as_tensor(ema, dtype=dt).clone()
         self.opt.step = torch.as_tensor(step).long().clone()
 
-    def iterate(self, u_switch, idx_new, u_accept):
+    def iterate(self, u_switch, idx_new, u_accept, reset=None, z_score_threshold=1.0):
+        """reset = (pose_init (Bt,D), idx_init (Bt,n_c), mask or None): a reset iteration, scripts/fit.py:408-422 with
+        initialize_convex_hull's result injected (initializations.py:190-193 -> set_parameters(env_mask))."""
         s = self.opt.try_step(u_switch, idx_new)
         Eb = self.energy.view(-1, self.B)
         z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        reset_mask = None
+        if reset is not None:
+            pose_init, idx_init, mask = reset
+            reset_mask = (z > z_score_threshold) if mask is None else torch.as_tensor(mask).bool()
+            hp = torch.as_tensor(pose_init, dtype=self.hand.dtype).clone().requires_grad_(True)
+            self.hand.set_parameters(hp, torch.as_tensor(idx_init).long(), env_mask=reset_mask)
+            self.opt.reset_envs(reset_mask)
         new_losses, info = calculate_energy(self.hand, self.obj)
         new_energy = total_energy(new_losses)
         new_energy.sum().backward()
@@ -150,9 +177,9 @@ class FitLoopOracle:
                    new_losses={k: v.detach().clone() for k, v in new_losses.items()}, z=z, s=s,
                    proposal=self.hand.hand_pose.detach().clone(), idx_prop=self.hand.contact_point_indices.clone())
         with torch.no_grad():
-            accept, t = self.opt.accept_step(self.energy, new_energy.detach(), u_accept, z)
+            accept, t = self.opt.accept_step(self.energy, new_energy.detach(), u_accept, z, reset_mask)
             self.energy[accept] = new_energy.detach()[accept]
             for k, v in new_losses.items():
                 self.losses[k][accept] = v.detach()[accept]
-        out.update(accept=accept, temperature=t)
+        out.update(accept=accept, temperature=t, reset_mask=reset_mask)
         return out

@@ -9,6 +9,7 @@ from oracle import qp as oqp
 from oracle import sdf as osdf
 from oracle.hand import HandOracle
 from oracle.pipeline import FitLoopOracle
+import tol
 
 
 def sdf_forward(lib, be, pts, fv):
@@ -111,9 +112,9 @@ def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=Fa
     eng = engine.FitEngine(lib, be, pack, [fv], sp[None], B, pose, idx.astype(np.int32))
     orc = FitLoopOracle(pack, [fv], [sp], B, pose, idx, dtype=torch.float64)
     H = be.to_host
-    np.testing.assert_allclose(H(eng.energy), orc.energy.numpy(), rtol=1e-4)
-    g0 = orc.first_grad.numpy()
-    np.testing.assert_allclose(eng.first_grad, g0, rtol=2e-3, atol=2e-3 * np.abs(g0).max())
+    ex = lambda b: tol.normal_unstable(H(eng.cpts)[b], fv)
+    tol.assert_energy(H(eng.energy), orc.energy.numpy(), f"{hand} n_c={n_c} initial energy")
+    tol.assert_grad(eng.first_grad, orc.first_grad.numpy(), f"{hand} n_c={n_c} first gradient")
     rng = np.random.default_rng(0)
     n_acc = 0
     for t in range(T):
@@ -121,11 +122,10 @@ def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=Fa
         eng.step(be.from_host(us), be.from_host(ir), be.from_host(ua))
         out = orc.iterate(torch.tensor(us, dtype=torch.float64), torch.tensor(ir).long(), torch.tensor(ua, dtype=torch.float64))
         np.testing.assert_array_equal(H(eng.idx_new), out["idx_prop"].numpy())
-        np.testing.assert_allclose(H(eng.new_energy), out["new_energy"].numpy(), rtol=2e-4)
-        g = out["new_grad"].numpy()
-        np.testing.assert_allclose(H(eng.grad_new), g, rtol=2e-3, atol=2e-3 * np.abs(g).max())
+        tol.assert_energy(H(eng.new_energy), out["new_energy"].numpy(), f"{hand} n_c={n_c} step {t} new energy", excuse=ex)
+        tol.assert_grad(H(eng.grad_new), out["new_grad"].numpy(), f"{hand} n_c={n_c} step {t} gradient", excuse=ex)
         np.testing.assert_array_equal(H(eng.accept).astype(bool), out["accept"].numpy())
-        np.testing.assert_allclose(H(eng.energy), orc.energy.numpy(), rtol=2e-4)
+        np.testing.assert_allclose(H(eng.energy), orc.energy.numpy(), rtol=tol.ENERGY_RTOL)
         np.testing.assert_allclose(H(eng.pose), orc.hand.hand_pose.detach().numpy(), rtol=1e-4, atol=1e-5)
         n_acc += int(out["accept"].sum())
     eng.close()
@@ -135,9 +135,9 @@ def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=Fa
 def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, hand="allegro", fc_tol=1e-5):
     """A T-step fixed-noise trajectory of the engine, every step checked against the fp64 oracle started from the
     engine's own state (teacher forcing: two chaotic trajectories cannot be compared open-loop for 500 steps).
-    Stated tolerances: proposal 1e-5 abs, new energy 2e-4 relative, contact indices bit-exact, accept decisions
-    bit-exact except where the uniform draw lies within `tie` of the acceptance probability (must stay below 1 %).
-    -> (accepted, borderline)"""
+    Stated tolerances (tests/tol.py): proposal 1e-5 abs, new energy and gradient 1e-4 relative, contact indices
+    bit-exact, accept decisions bit-exact except where the uniform draw lies within `tie` of the acceptance probability
+    (must stay below 1 %).  -> (accepted, borderline, worst energy error)"""
     pack = hand_pack.load_pack(hand)
     v, f = synth.make_mesh("hull", 400, seed)
     fv = synth.face_vertices(v, f)
@@ -149,8 +149,9 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
     H = be.to_host
     rng = np.random.default_rng(seed)
     n_acc = n_tie = 0
-    worst = 0.0
-    outliers = []
+    worst = worst_g = 0.0
+    outliers, grad_events, grad_errs = [], 0, []
+    E_TOL = tol.ENERGY_RTOL
     for t in range(T):
         orc.load_state(H(eng.pose), H(eng.idx), H(eng.grad), H(eng.energy), H(eng.ema), H(eng.step_count))
         us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, len(pack["cand"]), (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
@@ -160,19 +161,32 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
         np.testing.assert_allclose(H(eng.pose_new), out["proposal"].numpy(), rtol=1e-5, atol=1e-5, err_msg=f"step {t}")
         e_new, want = H(eng.new_energy), out["new_energy"].numpy()
         rel = np.abs(e_new - want) / np.abs(want)
-        for b in np.nonzero(rel > 2e-4)[0]:  # discontinuity events, see the assertion below
-            terms = {k: float(H(eng.losses_new)[i][b] - out["new_losses"][k][b]) for i, k in enumerate(engine.TERMS)}
-            E_in, _, _ = oqp.graspqp_energy(torch.tensor(H(eng.cpts), dtype=torch.float64),
-                                            torch.tensor(H(eng.obj_nrm), dtype=torch.float64), orc.obj.cog)
+        flagged = rel > E_TOL
+        if flagged.any():  # discontinuity events, see the assertion below
+            cp64, nn64 = torch.tensor(H(eng.cpts), dtype=torch.float64), torch.tensor(H(eng.obj_nrm), dtype=torch.float64)
+            E_in, _, info = oqp.graspqp_energy(cp64, nn64, orc.obj.cog)
+            sv = torch.linalg.svdvals(info["F"])
             e_fc = H(eng.losses_new)[engine.TERMS.index("E_fc")]
+        for b in np.nonzero(flagged)[0]:
+            terms = {k: float(H(eng.losses_new)[i][b] - out["new_losses"][k][b]) for i, k in enumerate(engine.TERMS)}
             # ... and the engine's object normals are the reference kernel's, bit for bit, at the engine's own contacts
             _, sg_w, nr_w, _ = osdf.compute_sdf_port(H(eng.cpts)[b], fv)
             np.testing.assert_array_equal(H(eng.obj_nrm)[b], nr_w * sg_w[:, None].astype(np.float32), err_msg=f"step {t}")
-            outliers.append((t, int(b), float(rel[b]), terms, abs(float(e_fc[b]) - E_in[b].item()) / abs(E_in[b].item())))
-        worst = max(worst, float(np.max(np.where(rel > 2e-4, 0.0, rel))))
+            # E_fc of the oracle's QP + svd term on the ENGINE's own contacts / normals.  When the grasp matrix is rank
+            # deficient to fp64 rounding (sigma_6 < 1e-12 sigma_1: all contacts on one line, e.g. duplicated contact
+            # indices at n_c = 4) the reference's term prod(sigma)^(1/6) (span.py:402) is rounding noise to the power
+            # 1/6 in ANY arithmetic; E_fc can then only agree up to svd_gain x that term.
+            fc_err = abs(float(e_fc[b]) - E_in[b].item()) / abs(E_in[b].item())
+            fc_allow = fc_tol if sv[b, -1] > 1e-12 * sv[b, 0] else fc_tol + 2 * 0.1 * float(info["svd"][b])
+            outliers.append((t, int(b), float(rel[b]), terms, fc_err, fc_allow))
+        worst = max(worst, float(np.max(np.where(flagged, 0.0, rel))))
+        # gradient of the proposal: 1e-4 relative per pose column on every candidate that is not a conditioning event
+        ge = tol.grad_error(H(eng.grad_new), out["new_grad"].numpy()).max(1)
+        grad_events += int(((ge > tol.GRAD_TOL) & ~flagged).sum())
+        grad_errs.append(ge[~flagged & (ge <= tol.GRAD_TOL)])
         p_acc = np.exp(np.minimum((orc_energy_before(out) - want) / out["temperature"].numpy(), 0.0))
         got, exp = H(eng.accept).astype(bool), out["accept"].numpy()
-        border = (np.abs(ua - p_acc) < tie) | (rel > 2e-4)
+        border = (np.abs(ua - p_acc) < tie) | flagged
         assert np.array_equal(got[~border], exp[~border]), f"step {t}: accept mismatch away from a tie"
         n_tie += int((got != exp).sum())
         n_acc += int(got.sum())
@@ -183,13 +197,19 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
     # surface itself; the contact points of the two runs differ by one fp32 ulp (fp32 FK here, fp64 FK in the oracle),
     # which occasionally rotates ONE contact normal by 1e-4..1e-2 rad, and E_fc sees that.  Such steps are re-checked
     # with the reference SDF arithmetic on the engine's own fp32 contact points (normals must be bit-identical) and the
-    # oracle's QP on the engine's own contacts/normals (must agree to 1e-5); a nearest-face tie can even flip a normal's
-    # sign (one 9 % event seen in 3000 candidate-steps).  Allowed for at most 1 % of candidate-steps (0.1-0.3 % observed);
-    # everything else is within 2e-4.
+    # oracle's QP on the engine's own contacts/normals (must agree to fc_tol = 1e-5); a nearest-face tie can even flip a
+    # normal's sign (one 9 % event seen in 3000 candidate-steps).  Allowed for at most 1 % of candidate-steps (0.1-0.3 %
+    # observed); everything else is within 1e-4.
     for o in outliers:
-        print("trajectory outlier (step, candidate, rel err, per-term diff, E_fc rel err on the engine's inputs):", o)
+        print("trajectory outlier (step, candidate, rel err, per-term diff, E_fc rel err on the engine's inputs, allowed):", o)
+    ge = np.concatenate(grad_errs) if grad_errs else np.zeros(1)
+    tol.MEASURED.append((f"{hand} n_c={n_c} {T}-step trajectory", "grad", float(ge.max()), float(np.median(ge))))
+    print(f"[traj] {hand} n_c={n_c}: {T * B} candidate-steps, {len(outliers)} energy conditioning events, "
+          f"{grad_events} gradient-only events; elsewhere energy error max {worst:.2e}, gradient error max {ge.max():.2e} "
+          f"median {np.median(ge):.2e}")
     assert len(outliers) <= max(1, T * B // 100), outliers
-    assert all(o[4] < fc_tol and abs(o[3]["E_pen"]) < 1e-5 for o in outliers), outliers
+    assert grad_events <= max(1, T * B // 100), f"{grad_events} candidate-steps with a gradient error above {tol.GRAD_TOL}"
+    assert all(o[4] < o[5] and abs(o[3]["E_pen"]) < 1e-5 for o in outliers), outliers
     return n_acc, n_tie, worst
 
 

@@ -189,8 +189,57 @@ def gen_fit(dtype=torch.float32, name="fit_ref_f32.npz"):
     print(name, "accepts", [out[f"t{t}_accept"].sum() for t in range(T)])
 
 
+def gen_fit_reset(name="fit_reset_ref_f64.npz"):
+    """M3: iterations around two RESET iterations (fit.py:408-422) with the reference's own MalaStar (clip_grad=True:
+    optimizer.py:211-213), a NaN gradient entry injected before iteration 1, the reset mask once derived from the z-score
+    (threshold 0.3 so that some rows are masked and some are not) and once injected; initialize_convex_hull's output
+    is injected (a second random grasp initialisation)."""
+    dtype = torch.float64
+    pack = hand_pack.load_pack("allegro")
+    B, n_c, n_pts, seed = 6, 12, 192, 3
+    v, f = synth.make_mesh("sphere", 400, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.7
+    torch.set_default_dtype(torch.float64)
+    st = rh.make_fit_state(pack, [fv], [sp], B, pose.astype(np.float32), idx, dtype=dtype, clip_grad=True)
+    out = dict(face_verts=fv, surface=sp.astype(np.float32), pose0=pose.astype(np.float32), idx0=idx.astype(np.int32))
+    rng = np.random.default_rng(7)
+    n_cand = len(pack["cand"])
+    plan = ["plain", "nan", "reset_z", "plain", "reset_mask", "plain"]
+    out["plan"] = np.array(plan)
+    for t, kind in enumerate(plan):
+        us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, n_cand, (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+        reset = None
+        if kind == "nan":
+            st.hand.hand_pose.grad[1, 4] = float("nan")
+            st.hand.hand_pose.grad[2, 11] = 1e4  # beyond the clip
+        if kind.startswith("reset"):
+            pi, ii = synth.random_grasp_init(pack, [v], B, n_c, 50 + t)
+            pi[:, :3] *= 0.8
+            mask = None if kind == "reset_z" else torch.tensor([True, False, False, True, False, False])
+            reset = (torch.tensor(pi.astype(np.float32)), torch.tensor(ii), mask)
+            out.update({f"t{t}_pose_init": pi.astype(np.float32), f"t{t}_idx_init": ii.astype(np.int32)})
+            if mask is not None:
+                out[f"t{t}_mask_in"] = mask.numpy()
+        o = rh.fit_iterate(st, torch.tensor(us), torch.tensor(ir).long(), torch.tensor(ua), reset=reset,
+                           z_score_threshold=0.3)
+        out.update({f"t{t}_u_switch": us, f"t{t}_idx_rand": ir, f"t{t}_u_accept": ua})
+        for k in ("s", "z", "proposal", "idx_prop", "new_energy", "new_grad", "accept", "temperature", "energy", "pose",
+                  "idx", "step", "ema") + (("reset_mask",) if reset is not None else ()):
+            out[f"t{t}_{k}"] = o[k].numpy()
+        for k, v_ in o["new_losses"].items():
+            out[f"t{t}_loss_{k}"] = v_.numpy()
+        if reset is not None:
+            print("  reset iteration", t, "mask", o["reset_mask"].numpy().astype(int))
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, "accepts", [int(out[f"t{t}_accept"].sum()) for t in range(len(plan))])
+
+
 if __name__ == "__main__":
     assert rh.available(), "reference not present"
     import subprocess
     subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
-    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz")
+    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset()

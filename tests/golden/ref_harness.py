@@ -159,8 +159,11 @@ def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_
     return st
 
 
-def fit_iterate(st, u_switch, idx_new, u_accept):
-    """One pass of scripts/fit.py:399-458 with the reference optimizer and energy code and injected noise."""
+def fit_iterate(st, u_switch, idx_new, u_accept, reset=None, z_score_threshold=1.0):
+    """One pass of scripts/fit.py:399-458 with the reference optimizer and energy code and injected noise.
+    reset = (pose_init, idx_init, mask or None): a reset iteration (fit.py:408-422) — the reference's own
+    MalaStar.reset_envs, with the result of initialize_convex_hull (trimesh / pytorch3d: absent here) injected through
+    HandOracle.set_parameters(env_mask=...), the restatement of hand_model.py:845-850, 816-831."""
     ref, opt, hand = st.ref, st.opt, st.hand
     noise = _Noise()
     noise.u_switch, noise.idx_new, noise.u_accept = u_switch, idx_new, u_accept
@@ -172,6 +175,12 @@ def fit_iterate(st, u_switch, idx_new, u_accept):
         s = opt.try_step()
         Eb = st.energy.view(-1, st.B)
         z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        reset_mask = None
+        if reset is not None:
+            pose_init, idx_init, mask = reset
+            reset_mask = (z > z_score_threshold) if mask is None else mask.bool()
+            hand.set_parameters(pose_init.to(hand.dtype).clone().requires_grad_(True), idx_init.long(), env_mask=reset_mask)
+            opt.reset_envs(reset_mask)
         opt.zero_grad()
         new_losses, new_energy = st.energies()
         new_energy.sum().backward()
@@ -180,12 +189,15 @@ def fit_iterate(st, u_switch, idx_new, u_accept):
                    new_grad=hand.hand_pose.grad.clone(),
                    new_losses={k: v.detach().clone() for k, v in new_losses.items()})
         with torch.no_grad():
-            accept, t = opt.accept_step(st.energy, new_energy, None, z, 1.0)
+            accept, t = opt.accept_step(st.energy, new_energy, reset_mask, z, z_score_threshold)
             st.energy[accept] = new_energy[accept]
             for k, v in new_losses.items():
                 st.losses[k][accept] = v[accept]
         out.update(accept=accept.clone(), temperature=t.clone(), energy=st.energy.detach().clone(),
-                   pose=hand.hand_pose.detach().clone(), idx=hand.contact_point_indices.clone())
+                   pose=hand.hand_pose.detach().clone(), idx=hand.contact_point_indices.clone(),
+                   step=opt.step.clone(), ema=opt.ema_grad_hand_pose.clone())
+        if reset_mask is not None:
+            out["reset_mask"] = reset_mask.clone()
     finally:
         mod.torch = real
     return out

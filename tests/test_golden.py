@@ -83,6 +83,40 @@ def test_oracle_loop_matches_reference_loop():
         np.testing.assert_allclose(orc.energy.numpy(), g[f"t{t}_energy"], rtol=1e-5)
 
 
+def test_oracle_reset_iterations_match_reference():
+    """oracle.pipeline's reset path (MalaStarOracle.reset_envs, HandOracle.set_parameters(env_mask)) and clip_grad / NaN
+    handling vs the reference's own MalaStar.reset_envs / try_step (fit_reset_ref_f64.npz), fp64 on both sides."""
+    g = gc.load("fit_reset_ref_f64")
+    pack = hand_pack.load_pack("allegro")
+    B = len(g["pose0"])
+    orc = FitLoopOracle(pack, [g["face_verts"]], [g["surface"]], B, g["pose0"], g["idx0"].astype(np.int64),
+                        dtype=torch.float64, clip_grad=True)
+    t64 = lambda a: torch.tensor(a, dtype=torch.float64)
+    for t, kind in enumerate(g["plan"]):
+        if kind == "nan":
+            orc.hand.hand_pose.grad[1, 4] = float("nan")
+            orc.hand.hand_pose.grad[2, 11] = 1e4
+        reset = None
+        if str(kind).startswith("reset"):
+            mask = g[f"t{t}_mask_in"] if f"t{t}_mask_in" in g else None
+            reset = (g[f"t{t}_pose_init"], g[f"t{t}_idx_init"], mask)
+        out = orc.iterate(t64(g[f"t{t}_u_switch"]), torch.tensor(g[f"t{t}_idx_rand"]).long(), t64(g[f"t{t}_u_accept"]),
+                          reset=reset, z_score_threshold=0.3)
+        if reset is not None:
+            np.testing.assert_array_equal(out["reset_mask"].numpy(), g[f"t{t}_reset_mask"])
+        np.testing.assert_array_equal(out["idx_prop"].numpy(), g[f"t{t}_idx_prop"])
+        # the reference keeps mu / step_size / temperature_decay as float32 tensors (optimizer.py:176-181) even in an
+        # fp64 run, the oracle as doubles: 5e-8 relative in the proposal, amplified by the energy's curvature
+        np.testing.assert_allclose(out["proposal"].numpy(), g[f"t{t}_proposal"], rtol=1e-6, atol=1e-9)
+        np.testing.assert_allclose(out["new_energy"].numpy(), g[f"t{t}_new_energy"], rtol=1e-5)
+        gw = g[f"t{t}_new_grad"]
+        np.testing.assert_allclose(out["new_grad"].numpy(), gw, rtol=1e-4, atol=1e-5 * np.abs(gw).max())
+        np.testing.assert_array_equal(out["accept"].numpy(), g[f"t{t}_accept"])
+        np.testing.assert_allclose(orc.energy.numpy(), g[f"t{t}_energy"], rtol=1e-5)
+        np.testing.assert_array_equal(orc.opt.step.numpy(), g[f"t{t}_step"])
+        np.testing.assert_allclose(orc.opt.ema.numpy(), g[f"t{t}_ema"], rtol=1e-5, atol=1e-12)
+
+
 def test_emulated_kernels_sdf(emu):
     gc.check_sdf(emu, engine.NumpyBackend())
 
@@ -99,6 +133,11 @@ def test_emulated_kernels_fit_iteration(emu):
     assert gc.check_fit(emu, engine.NumpyBackend(), T=2) > 0
 
 
+def test_emulated_kernels_reset_iterations(emu):
+    """M3 + clip_grad / NaN through the emulated kernels against the reference's own MalaStar"""
+    assert gc.check_fit_reset(emu, engine.NumpyBackend()) == 4
+
+
 @pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference is only present in the build container")
 def test_golden_vectors_are_reproducible(tmp_path, oracle_built):
     """Re-run the reference through the harness and compare with the committed fixtures (build container only)."""
@@ -113,3 +152,15 @@ def test_golden_vectors_are_reproducible(tmp_path, oracle_built):
     o = rh.fit_iterate(st, torch.tensor(g["t0_u_switch"]), torch.tensor(g["t0_idx_rand"]).long(), torch.tensor(g["t0_u_accept"]))
     np.testing.assert_allclose(o["new_energy"].numpy(), g["t0_new_energy"], rtol=1e-6)
     np.testing.assert_array_equal(o["accept"].numpy(), g["t0_accept"])
+    # the reset fixture: regenerate it whole (reference MalaStar.reset_envs, clip_grad, injected NaN) and compare
+    import make_golden as mg
+    torch.manual_seed(0)
+    mg.HERE = str(tmp_path)
+    mg.gen_fit_reset()
+    new, old = np.load(tmp_path / "fit_reset_ref_f64.npz"), gc.load("fit_reset_ref_f64")
+    assert sorted(new.files) == sorted(old)
+    for k in new.files:
+        if new[k].dtype.kind == "f":
+            np.testing.assert_allclose(new[k], old[k], rtol=1e-9, atol=1e-12, equal_nan=True, err_msg=k)
+        else:
+            np.testing.assert_array_equal(new[k], old[k], err_msg=k)

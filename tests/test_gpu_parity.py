@@ -101,21 +101,26 @@ def test_golden_fit_iterations(gpu):
     assert gc.check_fit(*gpu, T=4) > 0
 
 
+def test_golden_reset_iterations(gpu):
+    """M3 (reset_envs, reset mask, forced accept), clip_grad and NaN gradients against the reference's own MalaStar"""
+    import golden_cases as gc
+    assert gc.check_fit_reset(*gpu) == 4
+
+
 def test_trajectory_500_steps_teacher_forced(gpu):
     n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=500)
     print(f"500-step trajectory: {n_acc} accepted, {n_tie} borderline accept mismatches, worst energy error {worst:.2e}")
     assert n_acc > 500
 
 
-@pytest.mark.parametrize("hand,n_c,fc_tol", [("shadow_hand", 12, 1e-5), ("robotiq2", 4, 5e-3)])
-def test_trajectory_other_hands(gpu, hand, n_c, fc_tol):
-    """150 teacher-forced steps with the Shadow Hand (24 dof, 18 links) and the Robotiq 2F-140 (coupling network in the
-    FK backward, small QP): same per-step tolerances as the Allegro trajectory, with ONE stated exception.  OPEN ITEM
-    (profiles/r1_notes.md, r1g): with 4 contacts on two parallel pads the grasp matrix is nearly rank deficient, and on
-    the < 1 % of candidate-steps that are already flagged as conditioning events the kernel's E_fc (6x6 Woodbury form of
-    the KKT solves, fp64) and the oracle's (full KKT LU, fp64) differ by up to 8e-4 relative ON IDENTICAL INPUTS; for
-    n_c = 12 that difference stays below 1e-5.  Tolerance for those flagged steps at n_c = 4: 5e-3."""
-    n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=150, n_c=n_c, hand=hand, fc_tol=fc_tol)
+@pytest.mark.parametrize("hand,n_c", [("shadow_hand", 12), ("robotiq2", 4), ("panda", 4)])
+def test_trajectory_other_hands(gpu, hand, n_c):
+    """150 teacher-forced steps with the Shadow Hand (24 dof, 18 links), the Robotiq 2F-140 (coupling network in the FK
+    backward) and the Panda gripper (both small-QP regime, n_c = 4): same per-step tolerances as the Allegro trajectory,
+    E_fc on flagged conditioning events within 1e-5 of the oracle on the engine's own inputs.  (Round 1 needed 5e-3 at
+    n_c = 4: the svd term was taken from a Cholesky factor of F F', which loses sigma_min below 1e-8 sigma_max on
+    rank-deficient grasp matrices — tests/test_fc_emu.py::test_rank_deficient_grasp_matrix_small_qp.)"""
+    n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=150, n_c=n_c, hand=hand, fc_tol=1e-5)
     print(f"{hand}: {n_acc} accepted, {n_tie} borderline, worst energy error {worst:.2e}")
     assert n_acc > 50
 

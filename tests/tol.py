@@ -1,0 +1,73 @@
+"""Tolerances of the parity tests (BASELINE.json north_star) and helpers that PRINT the achieved error next to every
+assertion, so that the logs of `pytest -s` / the GPU runs under profiles/ show how much of the tolerance is used.
+
+* per-step energies and gradients: 1e-4 relative (fp32 kernels vs the fp64 run of the oracle / of the reference code);
+* gradients are compared per pose column, relative to the column's largest reference entry over the batch: the columns of
+  `hand_pose` (translation, ortho6d, joint angles) have different physical scales, an entry-wise relative error has no
+  meaning for entries that cancel to ~0.
+"""
+import numpy as np
+
+ENERGY_RTOL = 1e-4
+GRAD_TOL = 1e-4
+MEASURED = []  # (label, kind, max, median) of every check of this process; tests/conftest.py prints it at the end
+
+
+def grad_error(got, want):
+    """(Bt, D) matrix of |got - want| / max_b |want[:, d]|"""
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    scale = np.maximum(np.abs(want).max(0, keepdims=True), 1e-30)
+    return np.abs(got - want) / scale
+
+
+def normal_unstable(cpts_row, face_verts, jump=1e-5):
+    """True if some contact of this candidate sits at a nearest-face tie of the reference's SDF arithmetic: moving the
+    fp32 contact point by ONE ulp changes the winning face's unit(p - c) by more than `jump`.  There the object normal
+    (object_model.py:246) is not a function of the pose that fp32 and fp64 evaluations can agree on — a conditioning
+    event of the reference's formulation, not an error of either implementation (seen: 4.6e-4 rad at a 26 mm distance)."""
+    from oracle import sdf as osdf
+    p = np.asarray(cpts_row, np.float32).reshape(-1, 3)
+    base = None
+    for k in range(7):
+        q = p.copy()
+        if k:
+            ax, sgn = (k - 1) % 3, (1.0 if k <= 3 else -1.0)
+            q[:, ax] = np.nextafter(q[:, ax], np.float32(sgn * np.inf))
+        _, sg, nr, _ = osdf.compute_sdf_port(q, face_verts)
+        n = nr * sg[:, None]
+        if base is None:
+            base = n
+        elif np.abs(n - base).max() > jump:
+            return True
+    return False
+
+
+def assert_grad(got, want, label, tol=GRAD_TOL, excuse=None, max_excused=1):
+    """excuse(row) -> bool: evidence that the row is a conditioning event (normal_unstable); at most `max_excused` rows
+    may exceed the tolerance, each with that evidence."""
+    e = grad_error(got, want)
+    col = e.max(0)
+    rows = e.max(1)
+    MEASURED.append((label, "grad", float(col.max()), float(np.median(col))))
+    print(f"[grad] {label}: per-column relative error max {col.max():.2e} median {np.median(col):.2e} "
+          f"(worst column {int(col.argmax())}); tolerance {tol:.0e}")
+    bad = [int(b) for b in np.nonzero(rows > tol)[0]]
+    excused = [b for b in bad if excuse is not None and excuse(b)]
+    for b in excused:
+        print(f"[grad] {label}: candidate {b} error {rows[b]:.2e} — nearest-face tie at one of its contacts (excused)")
+    assert len(bad) == len(excused) <= max_excused, \
+        f"{label}: gradient error {rows[bad]} on candidates {bad} exceeds {tol} (excused: {excused})"
+    return rows
+
+
+def assert_energy(got, want, label, rtol=ENERGY_RTOL, excuse=None, max_excused=1):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    rel = np.abs(got - want) / np.maximum(np.abs(want), 1e-30)
+    MEASURED.append((label, "energy", float(rel.max()), float(np.median(rel))))
+    print(f"[energy] {label}: relative error max {rel.max():.2e} median {np.median(rel):.2e}; tolerance {rtol:.0e}")
+    bad = [int(b) for b in np.nonzero(rel > rtol)[0]]
+    excused = [b for b in bad if excuse is not None and excuse(b)]
+    for b in excused:
+        print(f"[energy] {label}: candidate {b} error {rel[b]:.2e} — nearest-face tie at one of its contacts (excused)")
+    assert len(bad) == len(excused) <= max_excused, f"{label}: energy error {rel[bad]} on candidates {bad} exceeds {rtol}"
+    return rel
