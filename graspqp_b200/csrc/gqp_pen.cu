@@ -868,6 +868,36 @@ extern "C" int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host) {
     return GQP_OK;
 }
 
+// diagnostics for the culling-proof tests: the outside grid of one link, as the kernels use it
+extern "C" int gqp_hand_link_grid(const GqpHand *h, int link, float *geom_host, int32_t *dim_host, uint32_t *bits_host,
+                                  int max_words) {
+    if (!h || !h->pen || !geom_host || !dim_host) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_grid: bad argument");
+    const std::vector<unsigned char> &B = h->pen->blob_host;
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(B.data());
+    if (link < 0 || link >= hdr->n_links) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_grid: no such link");
+    const PenLink &K = reinterpret_cast<const PenLink *>(B.data() + hdr->links_off)[link];
+    for (int k = 0; k < 3; ++k) {
+        geom_host[4 + k] = K.lo[k];
+        geom_host[7 + k] = K.hi[k];
+    }
+    dim_host[0] = dim_host[1] = dim_host[2] = 0;
+    geom_host[0] = geom_host[1] = geom_host[2] = geom_host[3] = 0.f;
+    if (K.grid < 0) return GQP_OK;
+    const PenGrid &G = reinterpret_cast<const PenGrid *>(B.data() + hdr->grids_off)[K.grid];
+    const uint32_t *bits = reinterpret_cast<const uint32_t *>(B.data() + hdr->bits_off) + G.bit_first;
+    for (int k = 0; k < 3; ++k) {
+        geom_host[k] = G.org[k];
+        dim_host[k] = G.dim[k];
+    }
+    geom_host[3] = G.inv_cell;
+    const long long words = ((long long)G.dim[0] * G.dim[1] * G.dim[2] + 31) / 32;
+    if (bits_host) {
+        if (max_words < words) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_grid: bits_host too small");
+        std::memcpy(bits_host, bits, (size_t)words * 4);
+    }
+    return GQP_OK;
+}
+
 extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {
     const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
     const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;

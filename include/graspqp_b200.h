@@ -151,6 +151,14 @@ uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, 
 /* diagnostics: info_host[6] = {shared-memory blob bytes, BVH nodes, sign-grid cells, cells proven positive, faces, grids} */
 int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host);
 
+/* diagnostics for the culling-proof tests: the outside grid of mesh link `link` exactly as the kernels use it.
+ * geom_host[10] = grid origin xyz, 1/cell, link box lo xyz, hi xyz (link frame); dim_host[3] = cells per axis, all 0 when
+ * the link has no grid (mesh not proven "nice": never culled); bits_host (may be NULL) receives ceil(cells/32) words,
+ * cell (x,y,z) -> bit (z*dim[1]+y)*dim[0]+x.  The kernels look a point q up as cell = (int)((q - origin) * (1/cell)).
+ * A SET bit, or q outside [lo,hi], is the claim "the reference's sign is +1 for every point there". */
+int gqp_hand_link_grid(const GqpHand *h, int link, float *geom_host, int32_t *dim_host, uint32_t *bits_host,
+                       int max_words);
+
 /* ---- H5 + E_joints: self_penetration (hand_model.py:989-1040) and joint limits (energy.py:47-54) ------------------
  * e_spen (Bt), e_joints (Bt); ACCUMULATES w_spen*d(e_spen) into grad_link_tf and OVERWRITES grad_pose_joints
  * (Bt, 9+n_dofs) with w_joints*d(e_joints)/d(pose) (both may be NULL). */

@@ -79,7 +79,7 @@ class MalaStarOracle:
         self.step = torch.zeros(B, dtype=torch.long)
         self.ema = torch.zeros(B, hand.n_dofs + 9, dtype=dt)
 
-    def try_step(self, u_switch, idx_new):
+    def try_step(self, u_switch, idx_new, grad2_mean=None):
         h = self.hand
         s = self.step_size * self.temperature_decay ** torch.div(self.step, self.step_size_period, rounding_mode="floor")
         step_size = torch.zeros_like(h.hand_pose) + s[..., None]
@@ -89,6 +89,8 @@ class MalaStarOracle:
         else:
             gradient = h.hand_pose.grad
         grad = (gradient ** 2).mean(0)
+        if grad2_mean is not None:  # sub-batch checks: the statistic of the FULL batch this subset was taken from
+            grad = torch.as_tensor(grad2_mean, dtype=h.dtype)
         self.ema = self.mu * grad + (1 - self.mu) * self.ema
         self.ema[torch.isnan(self.ema)] = 0
         hand_pose = h.hand_pose - step_size * gradient / (torch.sqrt(self.ema) + 1e-6)
@@ -157,12 +159,18 @@ class FitLoopOracle:
         self.opt.ema = torch.as_tensor(ema, dtype=dt).clone()
         self.opt.step = torch.as_tensor(step).long().clone()
 
-    def iterate(self, u_switch, idx_new, u_accept, reset=None, z_score_threshold=1.0):
+    def iterate(self, u_switch, idx_new, u_accept, reset=None, z_score_threshold=1.0, grad2_mean=None, z=None,
+                qp_stop=None):
         """reset = (pose_init (Bt,D), idx_init (Bt,n_c), mask or None): a reset iteration, scripts/fit.py:408-422 with
-        initialize_convex_hull's result injected (initializations.py:190-193 -> set_parameters(env_mask))."""
-        s = self.opt.try_step(u_switch, idx_new)
-        Eb = self.energy.view(-1, self.B)
-        z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        initialize_convex_hull's result injected (initializations.py:190-193 -> set_parameters(env_mask)).
+        grad2_mean / z / qp_stop: batch-wide statistics of the full batch when this oracle holds a SUBSET of it."""
+        from . import qp as _qp
+        s = self.opt.try_step(u_switch, idx_new, grad2_mean)
+        if z is None:
+            Eb = self.energy.view(-1, self.B)
+            z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        else:
+            z = torch.as_tensor(z, dtype=self.hand.dtype)
         reset_mask = None
         if reset is not None:
             pose_init, idx_init, mask = reset
@@ -170,7 +178,11 @@ class FitLoopOracle:
             hp = torch.as_tensor(pose_init, dtype=self.hand.dtype).clone().requires_grad_(True)
             self.hand.set_parameters(hp, torch.as_tensor(idx_init).long(), env_mask=reset_mask)
             self.opt.reset_envs(reset_mask)
-        new_losses, info = calculate_energy(self.hand, self.obj)
+        _qp.FORCE_STOP = qp_stop
+        try:
+            new_losses, info = calculate_energy(self.hand, self.obj)
+        finally:
+            _qp.FORCE_STOP = None
         new_energy = total_energy(new_losses)
         new_energy.sum().backward()
         out = dict(energy_before=self.energy.detach().clone(), new_energy=new_energy.detach().clone(), new_grad=self.hand.hand_pose.grad.clone(),

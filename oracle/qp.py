@@ -56,6 +56,12 @@ class _KKT:
         return dx, g2 / d, w
 
 
+# Sub-batch checks (tests/cases.py:check_benched_state): qpth's exit test is batch-wide, so a SUBSET of a large batch
+# can only be reproduced if the loop leaves at the iteration the FULL batch left at.  FORCE_STOP = that iteration
+# (max_iter = never left early); None = qpth's own test on the batch at hand.
+FORCE_STOP = None
+
+
 def pdipm_forward(Q, p, G, h, eps=5e-2, maxIter=12, notImprovedLim=3, trace=None):
     """Returns x, lam (z), slack (s), kkt.  `trace`, if a list, receives per-iteration residual vectors."""
     nB, nineq, nz = G.shape[0], G.shape[1], G.shape[2]
@@ -89,7 +95,10 @@ def pdipm_forward(Q, p, G, h, eps=5e-2, maxIter=12, notImprovedLim=3, trace=None
             best["x"][I] = x[I]
             best["z"][I] = z[I]
             best["s"][I] = s[I]
-        if nNotImproved == notImprovedLim or best["resids"].max() < eps or mu.min() > 1e32:
+        if FORCE_STOP is not None:
+            if i == FORCE_STOP:
+                return best["x"], best["z"], best["s"], kkt
+        elif nNotImproved == notImprovedLim or best["resids"].max() < eps or mu.min() > 1e32:
             return best["x"], best["z"], best["s"], kkt
         dx_aff, ds_aff, dz_aff = kkt.solve(d, rx, rs, rz)
         alpha = torch.min(torch.min(_get_step(z, dz_aff), _get_step(s, ds_aff)), torch.ones(nB, dtype=Q.dtype))

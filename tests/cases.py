@@ -215,3 +215,136 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
 
 def orc_energy_before(out):
     return out["energy_before"].numpy()
+
+
+def link_grid(lib, hand, link):
+    geom, dim = np.zeros(10, np.float32), np.zeros(3, np.int32)
+    _lib.check(lib.gqp_hand_link_grid(hand, link, geom.ctypes.data, dim.ctypes.data, None, 0), lib)
+    bits = None
+    if dim.prod() > 0:
+        words = (int(dim.prod()) + 31) // 32
+        bits = np.zeros(words, np.uint32)
+        _lib.check(lib.gqp_hand_link_grid(hand, link, geom.ctypes.data, dim.ctypes.data, bits.ctypes.data, words), lib)
+    return geom, dim, bits
+
+
+def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0, max_cells=None):
+    """Direct test of the culling proof that carries > 98 % of H4's work (csrc/gqp_bvh.cpp: gqp_mesh_is_nice +
+    gqp_outside_grid_build): for every link with an outside grid, for every SET cell, points drawn inside the cell
+    (uniform + the eight corners pulled in by 1e-6 of the cell) must get sign +1 from the reference's brute-force
+    arithmetic (`sign_fn(points, face_verts) -> int32 signs`: the TorchSDF port on the CPU, gqp_sdf_forward on the GPU);
+    likewise points outside the link's box out to 1.5 m.  The cell of a point is computed exactly as pen_outside() does
+    (fp32 (q - origin) * inv_cell, truncation).  -> (links with a grid, cells checked, points checked)"""
+    pack = hand_pack.load_pack(hand_name)
+    hand = hand_pack.create_hand(lib, pack)
+    rng = np.random.default_rng(seed)
+    L = len(pack["mesh_frame"])
+    n_links = n_cells = n_points = 0
+    for l in range(L):
+        f0, f1 = int(pack["face_offset"][l]), int(pack["face_offset"][l + 1])
+        geom, dim, bits = link_grid(lib, hand, l)
+        if bits is None or f1 == f0:
+            continue
+        fv = np.ascontiguousarray(pack["face_verts"][f0:f1], np.float32).reshape(-1, 3, 3)
+        org, inv_cell, lo, hi = geom[:3], geom[3], geom[4:7], geom[7:10]
+        cell = np.float32(1.0) / inv_cell
+        idx = np.nonzero(np.unpackbits(bits.view(np.uint8), bitorder="little")[:int(dim.prod())])[0]
+        if max_cells is not None and len(idx) > max_cells:
+            idx = rng.choice(idx, max_cells, replace=False)
+        cx, cy, cz = idx % dim[0], (idx // dim[0]) % dim[1], idx // (dim[0] * dim[1])
+        c0 = np.stack([cx, cy, cz], 1).astype(np.float64)
+        corners = np.array([[i, j, k] for i in (1e-6, 1 - 1e-6) for j in (1e-6, 1 - 1e-6) for k in (1e-6, 1 - 1e-6)])
+        frac = np.concatenate([rng.random((len(idx), per_cell, 3)), np.broadcast_to(corners, (len(idx), 8, 3))], 1)
+        pts = (org.astype(np.float64) + (c0[:, None, :] + frac) * float(cell)).reshape(-1, 3).astype(np.float32)
+        # keep the points the KERNEL would file under a set cell (fp32 arithmetic of pen_outside)
+        fcell = (pts - org) * inv_cell
+        ic = fcell.astype(np.int32)
+        ok = (fcell >= 0).all(1) & (ic < dim).all(1)
+        lin = (ic[:, 2].astype(np.int64) * dim[1] + ic[:, 1]) * dim[0] + ic[:, 0]
+        lin = np.where(ok, lin, 0)
+        setbit = ((bits[lin >> 5] >> (lin & 31).astype(np.uint32)) & 1).astype(bool) & ok
+        inside_box = ((pts >= lo) & (pts <= hi)).all(1)
+        pts = pts[setbit & inside_box]
+        # far field: outside the link's box (pen_outside returns true before looking at the grid)
+        d = rng.normal(size=(n_far, 3))
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        ctr, half = 0.5 * (lo + hi), 0.5 * (hi - lo)
+        far = (ctr + d * (np.linalg.norm(half) * (1.0 + rng.random((n_far, 1)) ** 3 * 15.0) + 1e-4)).astype(np.float32)
+        far = far[~((far >= lo) & (far <= hi)).all(1)]
+        near = (ctr + (rng.random((n_far, 3)) * 2 - 1) * half * 1.3).astype(np.float32)  # just outside the box faces
+        near = near[~((near >= lo) & (near <= hi)).all(1)]
+        q = np.concatenate([pts, far, near])
+        sg = sign_fn(q, fv)
+        bad = np.nonzero(sg != 1)[0]
+        assert len(bad) == 0, (f"{hand_name} link {l}: {len(bad)} of {len(q)} points in culled regions get sign -1 from "
+                               f"the reference arithmetic, e.g. {q[bad[:3]]} (first {len(pts)} are grid points)")
+        n_links += 1
+        n_cells += len(idx)
+        n_points += len(q)
+    lib.gqp_hand_destroy(hand)
+    print(f"[culling proof] {hand_name}: {n_links} links with a grid, {n_cells} set cells, {n_points} points, all +1")
+    return n_links, n_cells, n_points
+
+
+def check_benched_state(lib, be, name="config2", iters=(0, 50, 500), per_object=2, seed=0, n_objects=None,
+                        batch_each=None):
+    """Parity AT THE BENCHED SHAPES: builds the workload bench.py times (full candidate count, 2500 surface samples,
+    10k / 50k-face meshes), runs the engine to iteration n (Philox noise), then takes `per_object` random candidates of
+    every object OF THAT STATE and checks one more iteration (injected noise, shared by both sides) against the fp64
+    oracle holding only those candidates, seeded with the batch-wide statistics of the full batch: (g^2).mean(0)
+    (optimizer.py:231), the per-object z-scores (fit.py:403-406) and qpth's batch-wide exit iteration.
+    Tolerances: tests/tol.py (1e-4 energies / gradients, nearest-face-tie evidence for excused rows), indices bit-exact,
+    accept decisions bit-exact away from ties.  -> dict of measured errors per checkpoint"""
+    from graspqp_b200 import workload
+    w = workload.build(name, n_objects=n_objects, batch_each=batch_each)
+    pack, B, n_c, O = w["pack"], w["batch_each"], w["n_contact"], len(w["face_verts"])
+    Bt = O * B
+    eng = engine.FitEngine(lib, be, pack, w["face_verts"], w["surface"], B, w["pose"], w["idx"])
+    H = be.to_host
+    rng = np.random.default_rng(seed)
+    sub = np.concatenate([o * B + np.sort(rng.choice(B, per_object, replace=False)) for o in range(O)])
+    n_cand = len(pack["cand"])
+    report = {}
+    done = 0
+    orc = None
+    for n in iters:
+        while done < n:
+            eng.step()
+            done += 1
+        st = {k: H(getattr(eng, k)) for k in ("pose", "idx", "grad", "energy", "ema", "step_count")}
+        us, ir, ua = rng.random((Bt, n_c), dtype=np.float32), rng.integers(0, n_cand, (Bt, n_c)).astype(np.int32), rng.random(Bt, dtype=np.float32)
+        eng.step(be.from_host(us), be.from_host(ir), be.from_host(ua))
+        done += 1
+        if orc is None:
+            orc = FitLoopOracle(pack, w["face_verts"], list(w["surface"]), per_object, st["pose"][sub], st["idx"][sub],
+                                dtype=torch.float64)
+        orc.load_state(st["pose"][sub], st["idx"][sub], st["grad"][sub], st["energy"][sub], st["ema"][sub],
+                       st["step_count"][sub])
+        t64 = lambda a: torch.tensor(a, dtype=torch.float64)
+        out = orc.iterate(t64(us[sub]), torch.tensor(ir[sub]).long(), t64(ua[sub]), grad2_mean=H(eng.grad2_mean),
+                          z=H(eng.z)[sub], qp_stop=int(H(eng.qp_stop)[0]))
+        cp = H(eng.cpts)
+        ex = lambda r: tol.normal_unstable(cp[sub[r]], w["face_verts"][sub[r] // B])
+        lab = f"{name} Bt={Bt} iteration {n}"
+        np.testing.assert_array_equal(H(eng.idx_new)[sub], out["idx_prop"].numpy(), err_msg=lab)
+        np.testing.assert_allclose(H(eng.pose_new)[sub], out["proposal"].numpy(), rtol=1e-5, atol=1e-5, err_msg=lab)
+        e_rel = tol.assert_energy(H(eng.new_energy)[sub], out["new_energy"].numpy(), lab + " new energy", excuse=ex,
+                                  max_excused=max(1, len(sub) // 8))
+        excused = set(int(r) for r in np.nonzero(e_rel > tol.ENERGY_RTOL)[0])
+        for k, term in enumerate(engine.TERMS):
+            got, want = H(eng.losses_new)[k][sub], out["new_losses"][term].numpy()
+            keep = np.array([r not in excused or term in ("E_pen", "E_spen", "E_joints") for r in range(len(sub))])
+            np.testing.assert_allclose(got[keep], want[keep], rtol=1e-4, atol=1e-6, err_msg=f"{lab} {term}")
+        g_rows = tol.assert_grad(H(eng.grad_new)[sub], out["new_grad"].numpy(), lab + " gradient", excuse=ex,
+                                 max_excused=max(1, len(sub) // 8))
+        p_acc = np.exp(np.minimum((out["energy_before"].numpy() - out["new_energy"].numpy()) / out["temperature"].numpy(), 0.0))
+        got, exp = H(eng.accept)[sub].astype(bool), out["accept"].numpy()
+        border = (np.abs(ua[sub] - p_acc) < 2e-3) | (e_rel > tol.ENERGY_RTOL)
+        assert np.array_equal(got[~border], exp[~border]), f"{lab}: accept mismatch away from a tie"
+        report[n] = dict(energy_max=float(np.where(e_rel > tol.ENERGY_RTOL, 0, e_rel).max()),
+                         grad_max=float(np.where(g_rows > tol.GRAD_TOL, 0, g_rows).max()), excused=len(excused),
+                         qp_stop=int(H(eng.qp_stop)[0]), accepted=int(got.sum()),
+                         e_pen_mean=float(H(eng.losses)[engine.TERMS.index("E_pen")].mean()))
+        print(f"[benched] {lab}: {report[n]}")
+    eng.close()
+    return report

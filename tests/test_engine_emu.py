@@ -76,3 +76,20 @@ def test_snapshot_restore_replays_the_same_iterations(emu):
     np.testing.assert_array_equal(eng.pose, want[1])
     np.testing.assert_array_equal(eng.idx, want[2])
     assert eng.iteration == want[3]
+
+
+def test_sub_batch_check_with_batch_wide_statistics(emu):
+    """logic of tests/cases.py:check_benched_state (the GPU test of BASELINE.json's configs at their benched shapes) at
+    emulator size: a subset of the candidates vs the oracle seeded with the full batch's (g^2).mean(0), z-scores and
+    QP exit iteration"""
+    import cases
+    import graspqp_b200.workload as wl
+    wl.CONFIGS["tiny"] = ("allegro", ["sphere", "box"], 300, 4, 12)
+    real = wl.build
+    try:
+        wl.build = lambda name, **kw: real(name, n_surface=64, **{k: v for k, v in kw.items() if v is not None})
+        rep = cases.check_benched_state(emu, engine.NumpyBackend(), "tiny", iters=(0, 2), per_object=2)
+    finally:
+        wl.build = real
+        del wl.CONFIGS["tiny"]
+    assert all(r["energy_max"] <= 1e-4 and r["grad_max"] <= 1e-4 for r in rep.values())

@@ -41,14 +41,40 @@ def test_sdf_self_consistency_full_size(gpu):
 
 
 def test_hand_distance(gpu):
-    cases.check_hand_distance(*gpu)
+    cases.check_hand_distance(*gpu, B=448)
 
 
 @pytest.mark.parametrize("hand", ["shadow_hand", "panda", "robotiq2"])
 def test_hand_distance_other_hands(gpu, hand):
-    """Culled E_pen == un-culled (every sample searched) with samples all around the links: the Panda fingers carry a
-    concave crease sharper than 90 degrees that the far-field culling proof (gqp_mesh_is_nice) has to get right."""
-    cases.check_hand_distance(*gpu, B=192, hand=hand)
+    """Culled E_pen == un-culled (every sample searched) for 448 poses x 2500 samples = 1.1 M (pose, sample) pairs per
+    hand, samples all around the links: the Panda fingers carry a concave crease sharper than 90 degrees that the
+    far-field culling proof (gqp_mesh_is_nice) has to get right."""
+    cases.check_hand_distance(*gpu, B=448, hand=hand)
+
+
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2"])
+def test_culling_proof_outside_cells_have_positive_sign(gpu, hand):
+    """Direct test of the proof behind the culling: 16 random points + 8 corners in EVERY set cell of every link's outside
+    grid and 400k points outside the link boxes -> the brute-force kernel (bit-exact TorchSDF arithmetic) says +1."""
+    lib, be = gpu
+    sign = lambda pts, fv: cases.sdf_forward(lib, be, pts, fv)[1]
+    n_links, n_cells, n_points = cases.check_culling_proof(lib, sign, hand, per_cell=16, n_far=200000)
+    assert n_links >= 1 and n_points > 100000
+
+
+@pytest.mark.parametrize("name,iters,kw", [
+    ("config2", (0, 50, 500), {}),
+    ("config3", (0, 50, 300), {}),
+    ("config4", (0, 50, 200), {"n_objects": 8}),
+    ("config4_robotiq2", (0, 50, 200), {"n_objects": 8}),
+    ("config5", (0, 50, 300), {}),
+])
+def test_parity_at_benched_shapes(gpu, name, iters, kw):
+    """BASELINE.json's configs at the shapes bench.py runs (full candidate count per object, 2500 surface samples,
+    10k / 50k-face meshes, batch-wide QP exit over the whole batch): a random subset of the candidates of the state
+    after 0 / 50 / 300-500 iterations against the fp64 oracle seeded with the full batch's statistics."""
+    rep = cases.check_benched_state(*gpu, name=name, iters=iters, **kw)
+    assert all(r["energy_max"] <= 1e-4 and r["grad_max"] <= 1e-4 for r in rep.values())
 
 
 def test_engine_vs_oracle(gpu):

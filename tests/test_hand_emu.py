@@ -152,3 +152,15 @@ def test_self_pen_joints(emu, pack, hand):
     gp = np.zeros_like(pose)
     assert emu.gqp_fk_backward(hand, ptr(pose), ptr(gtf), ptr(gj), B, ptr(gp), None) == 0
     np.testing.assert_allclose(gp, p64.grad.numpy(), rtol=1e-3, atol=1e-4)
+
+
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2"])
+def test_culling_proof_outside_cells_have_positive_sign(emu, hand, oracle_built):
+    """every SET cell of every link's outside grid, and the region outside the link's box: the reference's brute-force
+    sign (TorchSDF arithmetic, oracle port) is +1 for the points drawn there (all set cells; the GPU test draws more
+    points per cell)"""
+    import cases
+    from oracle import sdf as osdf
+    sign = lambda pts, fv: osdf.compute_sdf_port(pts, fv)[1]
+    n_links, n_cells, n_points = cases.check_culling_proof(emu, sign, hand, per_cell=2, n_far=5000)
+    assert n_links >= 1 and n_points > 1000
