@@ -62,8 +62,8 @@ def quaternion_to_matrix(q):
     return o.reshape(q.shape[:-1] + (3, 3))
 
 
-def _mat44(R=None, t=None, B=1, dtype=torch.float32):
-    m = torch.eye(4, dtype=dtype).repeat(B, 1, 1)
+def _mat44(R=None, t=None, B=1, dtype=torch.float32, device="cpu"):
+    m = torch.eye(4, dtype=dtype, device=device).repeat(B, 1, 1)
     if R is not None:
         m = m.clone()
         m[:, :3, :3] = R
@@ -73,18 +73,24 @@ def _mat44(R=None, t=None, B=1, dtype=torch.float32):
 
 
 class HandOracle:
-    def __init__(self, pack, dtype=torch.float32):
-        self.dtype = dtype
-        g = lambda k: torch.from_numpy(np.asarray(pack[k]))
+    def __init__(self, pack, dtype=torch.float32, device="cpu", sdf=None):
+        """device / sdf: the GPU baseline leg (baseline/gpu_reference.py) runs this same restatement on CUDA tensors with
+        sdf = the reference's own torchsdf.compute_sdf; the default is the CPU port of that kernel."""
+        self.dtype, self.device = dtype, torch.device(device)
+        self.sdf = sdf if sdf is not None else compute_sdf
+        g = lambda k: torch.from_numpy(np.asarray(pack[k])).to(self.device)
         self.parent = [int(v) for v in pack["frame_parent"]]
         self.jtype = [int(v) for v in pack["frame_jtype"]]
         self.frame_dof = [int(v) for v in pack["frame_dof"]]
         self.axis = g("frame_axis").to(dtype)
-        to44 = lambda a: torch.cat([a, torch.tensor([0, 0, 0, 1.0]).expand(a.shape[0], 1, 4)], 1).to(dtype)
+        to44 = lambda a: torch.cat([a, torch.tensor([0, 0, 0, 1.0], device=self.device).expand(a.shape[0], 1, 4)], 1).to(dtype)
         self.joff, self.loff = to44(g("frame_joff")), to44(g("frame_loff"))
         self.mesh_frame = [int(v) for v in pack["mesh_frame"]]
         self.face_verts = np.asarray(pack["face_verts"], np.float32)
         self.face_offset = [int(v) for v in pack["face_offset"]]
+        if sdf is not None:  # link meshes as device tensors for torchsdf
+            self.face_verts_dev = [torch.from_numpy(self.face_verts[a:b].reshape(-1, 3, 3)).to(self.device).contiguous()
+                                   for a, b in zip(self.face_offset[:-1], self.face_offset[1:])]
         self.cand, self.cand_normal = g("cand").to(dtype), g("cand_normal").to(dtype)
         self.cand_link = g("cand_link").long()
         self.spheres, self.sphere_link = g("spheres").to(dtype), g("sphere_link").long()
@@ -113,22 +119,22 @@ class HandOracle:
         theta = self.joint_vector(theta)
         trans, out = [None] * len(self.parent), [None] * len(self.parent)
         for f, par in enumerate(self.parent):
-            world = torch.eye(4, dtype=self.dtype).expand(B, 4, 4) if par < 0 else trans[par]
+            world = torch.eye(4, dtype=self.dtype, device=self.device).expand(B, 4, 4) if par < 0 else trans[par]
             d = self.frame_dof[f]
             if self.jtype[f] == 1 and d >= 0:
                 th = theta[:, d:d + 1]
                 th = th + 2 * ((th > 0).to(self.dtype) - 0.5) * 1e-2
                 quat = torch.cat([torch.cos(th / 2), torch.sin(th / 2) * self.axis[f]], -1)
-                jt = _mat44(quaternion_to_matrix(quat), None, B, self.dtype)
+                jt = _mat44(quaternion_to_matrix(quat), None, B, self.dtype, self.device)
             elif self.jtype[f] == 2 and d >= 0:
-                jt = _mat44(None, theta[:, d:d + 1] * self.axis[f], B, self.dtype)
+                jt = _mat44(None, theta[:, d:d + 1] * self.axis[f], B, self.dtype, self.device)
             elif self.jtype[f] == 1:  # movable joint that is not in the parameter vector: th_dict.get(name, 0.0)
-                th = torch.zeros(B, 1, dtype=self.dtype)
+                th = torch.zeros(B, 1, dtype=self.dtype, device=self.device)
                 th = th + 2 * ((th > 0).to(self.dtype) - 0.5) * 1e-2
                 quat = torch.cat([torch.cos(th / 2), torch.sin(th / 2) * self.axis[f]], -1)
-                jt = _mat44(quaternion_to_matrix(quat), None, B, self.dtype)
+                jt = _mat44(quaternion_to_matrix(quat), None, B, self.dtype, self.device)
             else:
-                jt = torch.eye(4, dtype=self.dtype).expand(B, 4, 4)
+                jt = torch.eye(4, dtype=self.dtype, device=self.device).expand(B, 4, 4)
             trans[f] = world @ (self.joff[f] @ jt)
             out[f] = trans[f] @ self.loff[f]
         return out
@@ -178,9 +184,11 @@ class HandOracle:
             fv = self.face_verts[self.face_offset[li]:self.face_offset[li + 1]]
             if len(fv) == 0:
                 continue
+            if self.sdf is not compute_sdf:
+                fv = self.face_verts_dev[li]
             T = self.link_matrix(li)
             xl = ((x - T[:, :3, 3].unsqueeze(1)) @ T[:, :3, :3]).reshape(-1, 3)
-            d2, sg, _, _ = compute_sdf(xl, fv)
+            d2, sg, _, _ = self.sdf(xl, fv)
             d = torch.sqrt(d2 + 1e-8) * (-sg)
             dis.append(d.reshape(x.shape[0], x.shape[1]))
         dis = torch.stack(dis, 0)
@@ -189,7 +197,7 @@ class HandOracle:
     def self_penetration(self):
         B = self.global_translation.shape[0]
         if len(self.spheres) == 0:
-            return torch.zeros(B, dtype=self.dtype)
+            return torch.zeros(B, dtype=self.dtype, device=self.device)
         points, radii = [], []
         for li in range(self.L):
             m = self.sphere_link == li
@@ -201,7 +209,7 @@ class HandOracle:
             radii.append(self.spheres[m, 3])
         all_pts, all_r = torch.cat(points, -2), torch.cat(radii)
         counter = 0
-        distances = torch.zeros(B, len(points) - 1, dtype=self.dtype)
+        distances = torch.zeros(B, len(points) - 1, dtype=self.dtype, device=self.device)
         for idx, ls in enumerate(points[:-1]):
             r = all_r[counter:counter + ls.shape[1]]
             counter += ls.shape[1]

@@ -9,6 +9,7 @@ Restatement of the per-iteration loop body of scripts/fit.py:399-458 with INJECT
 The reference draws `torch.rand(B,n_c)`, `torch.randint(C, [switch.sum()])` and `torch.rand(B)`; here they are the
 arguments u_switch (B,n_c), idx_new (B,n_c) (only entries under the switch mask are used) and u_accept (B).
 """
+import numpy as np
 import torch
 
 from .hand import HandOracle, compute_sdf
@@ -18,11 +19,16 @@ WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_pen=100.0, E_spen=10.0, E_joints=1.0)  #
 
 
 class ObjectOracle:
-    def __init__(self, face_verts_list, surface_points_list, batch_size_each, dtype=torch.float32):
+    def __init__(self, face_verts_list, surface_points_list, batch_size_each, dtype=torch.float32, device="cpu",
+                 sdf=None):
         self.face_verts_list = face_verts_list  # list of (F,3,3) float32 numpy
+        self.sdf = sdf if sdf is not None else compute_sdf
+        if sdf is not None:  # GPU baseline leg: meshes as device tensors for the reference's torchsdf.compute_sdf
+            self.face_verts_list = [torch.as_tensor(np.asarray(f, np.float32).reshape(-1, 3, 3)).to(device).contiguous()
+                                    for f in face_verts_list]
         self.batch_size_each = batch_size_each
         self.dtype = dtype
-        sp = torch.stack([torch.as_tensor(s, dtype=dtype) for s in surface_points_list], 0)
+        sp = torch.stack([torch.as_tensor(s, dtype=dtype) for s in surface_points_list], 0).to(device)
         self.surface_points_tensor = sp.repeat_interleave(batch_size_each, dim=0)
         self.object_scale = 1.0  # object_model.py:60 — always 1.0
         self.cog = self.surface_points_tensor.mean(1)
@@ -32,7 +38,7 @@ class ObjectOracle:
         xo = x.reshape(-1, self.batch_size_each * n_points, 3) / self.object_scale
         distance, normals = [], []
         for i, fv in enumerate(self.face_verts_list):
-            dis, sg, normal, _ = compute_sdf(xo[i], fv)
+            dis, sg, normal, _ = self.sdf(xo[i], fv)
             dis = torch.sqrt(dis + 1e-8) * (-sg)
             distance.append(dis)
             normals.append(normal * sg.unsqueeze(1))

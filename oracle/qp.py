@@ -42,7 +42,7 @@ class _KKT:
 
     def factor(self, d):
         T = self.R.clone()
-        idx = torch.arange(T.shape[1])
+        idx = torch.arange(T.shape[1], device=T.device)
         T[:, idx, idx] += 1.0 / d
         self.S_LU = torch.linalg.lu_factor(T)
 
@@ -66,9 +66,9 @@ def pdipm_forward(Q, p, G, h, eps=5e-2, maxIter=12, notImprovedLim=3, trace=None
     """Returns x, lam (z), slack (s), kkt.  `trace`, if a list, receives per-iteration residual vectors."""
     nB, nineq, nz = G.shape[0], G.shape[1], G.shape[2]
     kkt = _KKT(Q, G)
-    d = torch.ones(nB, nineq, dtype=Q.dtype)
+    d = torch.ones(nB, nineq, dtype=Q.dtype, device=Q.device)
     kkt.factor(d)
-    x, s, z = kkt.solve(d, p, torch.zeros(nB, nineq, dtype=Q.dtype), -h)
+    x, s, z = kkt.solve(d, p, torch.zeros(nB, nineq, dtype=Q.dtype, device=Q.device), -h)
     for v in (s, z):
         M = torch.min(v, 1)[0].view(-1, 1).repeat(1, nineq)
         I = M < 0
@@ -101,16 +101,16 @@ def pdipm_forward(Q, p, G, h, eps=5e-2, maxIter=12, notImprovedLim=3, trace=None
         elif nNotImproved == notImprovedLim or best["resids"].max() < eps or mu.min() > 1e32:
             return best["x"], best["z"], best["s"], kkt
         dx_aff, ds_aff, dz_aff = kkt.solve(d, rx, rs, rz)
-        alpha = torch.min(torch.min(_get_step(z, dz_aff), _get_step(s, ds_aff)), torch.ones(nB, dtype=Q.dtype))
+        alpha = torch.min(torch.min(_get_step(z, dz_aff), _get_step(s, ds_aff)), torch.ones(nB, dtype=Q.dtype, device=Q.device))
         a = alpha.view(-1, 1)
         t3 = torch.sum((s + a * ds_aff) * (z + a * dz_aff), 1)
         t4 = torch.sum(s * z, 1)
         sig = (t3 / t4) ** 3
         rs2 = ((-mu * sig).view(-1, 1) + ds_aff * dz_aff) / s
-        zx, zi = torch.zeros(nB, nz, dtype=Q.dtype), torch.zeros(nB, nineq, dtype=Q.dtype)
+        zx, zi = torch.zeros(nB, nz, dtype=Q.dtype, device=Q.device), torch.zeros(nB, nineq, dtype=Q.dtype, device=Q.device)
         dx_cor, ds_cor, dz_cor = kkt.solve(d, zx, rs2, zi)
         dx, ds, dz = dx_aff + dx_cor, ds_aff + ds_cor, dz_aff + dz_cor
-        alpha = torch.min(0.999 * torch.min(_get_step(z, dz), _get_step(s, ds)), torch.ones(nB, dtype=Q.dtype))
+        alpha = torch.min(0.999 * torch.min(_get_step(z, dz), _get_step(s, ds)), torch.ones(nB, dtype=Q.dtype, device=Q.device))
         a = alpha.view(-1, 1)
         x = x + a * dx
         s = s + a * ds
@@ -144,12 +144,13 @@ class QPFunction(torch.autograd.Function):
 def lsq_solve(A, b, min_bound, max_bound):
     """qp_solver.py:60-134 (SQPLsqSolver.solve) for A (B,6,n), b (B,6). Returns value (B), x (B,n)."""
     n = A.shape[-1]
-    u = torch.ones(A.shape[0], n, dtype=A.dtype) * max_bound
-    l = torch.ones(A.shape[0], n, dtype=A.dtype) * min_bound
+    kw = dict(dtype=A.dtype, device=A.device)
+    u = torch.ones(A.shape[0], n, **kw) * max_bound
+    l = torch.ones(A.shape[0], n, **kw) * min_bound
     Q = A.mT @ A
-    Q = Q + torch.eye(n, dtype=A.dtype).unsqueeze(0) * 1e-4
+    Q = Q + torch.eye(n, **kw).unsqueeze(0) * 1e-4
     p = (-A.mT @ b[..., None]).squeeze(-1)
-    G = torch.cat([torch.eye(n, dtype=A.dtype), -torch.eye(n, dtype=A.dtype)], dim=-2)
+    G = torch.cat([torch.eye(n, **kw), -torch.eye(n, **kw)], dim=-2)
     h = torch.cat([u, -l], dim=-1)
     x = QPFunction.apply(Q, p, G, h)
     value = 0.5 * torch.sum((b - (A @ x.unsqueeze(-1)).squeeze(-1)).pow(2), -1)
@@ -181,7 +182,7 @@ def graspqp_energy(contact_pts, contact_normals, cog, friction=0.2, max_limit=20
                    values_gain=2.0):
     """registry.py:31-89 with span.py:313-415: returns E_fc (B), per-contact force sums (B,n_c), and pieces."""
     F = grasp_matrix(contact_pts, contact_normals, cog, friction, torque_weight)
-    b = torch.zeros(F.shape[0], 6, dtype=F.dtype)
+    b = torch.zeros(F.shape[0], 6, dtype=F.dtype, device=F.device)
     value, x = lsq_solve(F, b, 1.0, max_limit + 1.0)
     svd = torch.linalg.svdvals(F).prod(-1) ** (1.0 / 6.0)
     E = values_gain * (value + 1e-2) * torch.exp(-svd_gain * svd)

@@ -22,7 +22,6 @@ code are therefore driven with oracle.hand.HandOracle / oracle.pipeline.ObjectOr
 golden vectors produced through this harness pin is the reference's own glue: MALA* update and accept rules, energy
 assembly, friction cone, grasp matrix, QP construction, E_fc wrapper, pk forward kinematics and transforms.
 """
-import importlib
 import os
 import sys
 import types
@@ -39,63 +38,14 @@ def available():
     return os.path.isdir(os.path.join(REF, "graspqp", "src", "graspqp"))
 
 
-def _pkg(name, path):
-    m = types.ModuleType(name)
-    m.__path__ = [path]
-    m.__package__ = name
-    sys.modules[name] = m
-    return m
-
-
-_loaded = {}
-
-
 def load():
     """-> dict of reference modules (optimizer, energy, span, registry, qp_solver, transforms, pk_chain, pk_frame, pk_tf)"""
-    if _loaded:
-        return _loaded
     if not available():
         raise RuntimeError("reference not present at " + REF)
-    from oracle import hand as ohand
-    from oracle import qp as oqp
-
-    # ---- stubs of the un-vendored third-party modules ----
-    class QPFunction:  # qpth.qp.QPFunction(verbose, maxIter, eps)(Q, p, G, h, A, b)
-        def __init__(self, eps=1e-12, verbose=0, notImprovedLim=3, maxIter=20, **kw):
-            self.eps, self.maxIter, self.notImprovedLim = eps, maxIter, notImprovedLim
-
-        def __call__(self, Q, p, G, h, A, b):
-            assert A.numel() == 0 and b.numel() == 0, "the hot path has no equality constraints"
-            assert (self.eps, self.maxIter) == (5e-2, 12), "oracle.qp is specialised to the reference's settings"
-            if G.ndim == 3:
-                G = G[0]
-            return oqp.QPFunction.apply(Q, p, G.to(Q.dtype), h)
-
-    qpth = types.ModuleType("qpth")
-    qpth.qp = types.ModuleType("qpth.qp")
-    qpth.qp.QPFunction = QPFunction
-    sys.modules.setdefault("qpth", qpth)
-    sys.modules.setdefault("qpth.qp", qpth.qp)
-    roma = types.ModuleType("roma")
-    roma.special_gramschmidt = ohand.special_gramschmidt
-    sys.modules.setdefault("roma", roma)
-
-    # ---- the reference's own packages, without their __init__ ----
-    g = os.path.join(REF, "graspqp", "src", "graspqp")
-    for name, path in [("graspqp", g), ("graspqp.core", g + "/core"), ("graspqp.metrics", g + "/metrics"),
-                       ("graspqp.metrics.ops", g + "/metrics/ops"), ("graspqp.metrics.solver", g + "/metrics/solver"),
-                       ("graspqp.utils", g + "/utils")]:
-        _pkg(name, path)
-    pk = os.path.join(REF, "thirdparty", "pytorch_kinematics", "pytorch_kinematics")
-    _pkg("pytorch_kinematics", pk)
-    imp = importlib.import_module
-    _loaded.update(
-        optimizer=imp("graspqp.core.optimizer"), energy=imp("graspqp.core.energy"),
-        span=imp("graspqp.metrics.ops.span"), registry=imp("graspqp.metrics.ops.registry"),
-        qp_solver=imp("graspqp.metrics.solver.qp_solver"), transforms=imp("graspqp.utils.transforms"),
-        pk_tf=imp("pytorch_kinematics.transforms"), pk_frame=imp("pytorch_kinematics.frame"),
-        pk_chain=imp("pytorch_kinematics.chain"))
-    return _loaded
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import ref_loader
+    return ref_loader.load(os.path.join(REF, "graspqp", "src", "graspqp"),
+                           os.path.join(REF, "thirdparty", "pytorch_kinematics", "pytorch_kinematics"))
 
 
 class _Noise:
