@@ -27,22 +27,88 @@ METRIC = "grasp-steps/sec"
 UNIT = "grasp-steps/s"
 
 
-def ncu_traffic_bytes(kernels):
-    """dram__bytes_read + dram__bytes_write per launch of the named kernels, from the committed `ncu --set full`
-    summary of this workload (profiles/r1d_ncu_full_top.txt, config 2); None when the summary is absent."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1d_ncu_full_top.txt")
-    if not os.path.exists(path):
-        return None
-    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    total, cur, seen = 0.0, None, set()
-    for ln in open(path):
-        t = ln.split()
-        if ln.startswith("=="):
-            cur = next((k for k in kernels if k in ln), None)   # "== void pen_collect_kernel<1>" -> pen_collect_kernel
-        elif cur in kernels and len(t) == 3 and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-            total += float(t[1]) * unit.get(t[2], 1.0)
-            seen.add(cur)
-    return total if len(seen) == len(kernels) else None
+COUNTER_METRICS = [  # collected by an ncu subprocess of THIS run (never from a file): instruction counts and DRAM bytes
+    "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
+    "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_dfma_pred_on.sum",
+    "smsp__sass_thread_inst_executed_op_dmul_pred_on.sum", "smsp__sass_thread_inst_executed_op_dadd_pred_on.sum",
+    "smsp__thread_inst_executed.sum", "smsp__inst_executed.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "gpu__time_duration.sum"]
+# stage -> the kernels one call of it launches (names as ncu prints them, prefix match)
+STAGE_KERNELS = {
+    "object_distance": ("object_distance_kernel",),
+    "fc_solve": ("fc_dis_kernel<1>", "fc_dis_kernel<(int)1>"),
+    "hand_distance": ("pen_bounds_kernel", "pen_broad_kernel", "pen_collect_kernel", "pen_search_kernel",
+                      "pen_reduce_fixed_kernel"),
+}
+
+
+def collect_counters(args, at_iteration):
+    """Runs `bench.py --count-mode` under ncu (--metrics above, cudaProfilerStart/Stop around one call of each stage at
+    iteration `at_iteration` of the same seeded fit) and sums the metrics per stage.  Counts and bytes only — every TIME
+    in the bench line comes from CUDA events of the un-profiled run.  -> (dict stage -> metric sums, note)"""
+    import csv
+    import shutil
+    import tempfile
+    ncu = shutil.which("ncu") or "/usr/local/cuda/bin/ncu"
+    if not os.path.exists(ncu):
+        return None, "ncu not found"
+    out = tempfile.NamedTemporaryFile(suffix=".csv", delete=False).name
+    cmd = [ncu, "--metrics", ",".join(COUNTER_METRICS), "--clock-control", "none", "--profile-from-start", "off", "--csv",
+           "--log-file", out, sys.executable, os.path.abspath(__file__), "--count-mode", "--workload", args.workload,
+           "--count-at", str(at_iteration)]
+    if args.batch:
+        cmd += ["--batch", str(args.batch)]
+    if args.objects:
+        cmd += ["--objects", str(args.objects)]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    except (subprocess.TimeoutExpired, OSError) as e:
+        return None, f"ncu subprocess failed: {type(e).__name__}"
+    if r.returncode != 0 or not os.path.exists(out):
+        return None, f"ncu exited {r.returncode}: {(r.stdout + r.stderr)[-200:]!r}"
+    rows = list(csv.reader(open(out, errors="replace")))
+    hdr = next((k for k, row in enumerate(rows) if row and row[0] == "ID"), None)
+    if hdr is None:
+        return None, "ncu wrote no launch table"
+    H = rows[hdr]
+    ki, mi, vi = H.index("Kernel Name"), H.index("Metric Name"), H.index("Metric Value")
+    sums = {st: {} for st in STAGE_KERNELS}
+    for row in rows[hdr + 1:]:
+        if len(row) <= vi:
+            continue
+        name = row[ki].replace("void ", "")
+        for st, ks in STAGE_KERNELS.items():
+            if any(name.startswith(k) for k in ks):
+                try:
+                    sums[st][row[mi]] = sums[st].get(row[mi], 0.0) + float(row[vi].replace(",", ""))
+                except ValueError:
+                    pass
+    os.unlink(out)
+    if not all(sums.values()):
+        return None, "ncu table lacks the stage kernels"
+    return sums, f"ncu --metrics subprocess of this run, one call of each stage at iteration {at_iteration}"
+
+
+def run_count_mode(args):
+    """Child of collect_counters: the same seeded fit up to --count-at, then ONE call of every stage between
+    cudaProfilerStart/Stop.  Prints nothing the parent needs; ncu's csv is the output."""
+    import torch
+    from graspqp_b200 import _lib, engine, workload
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    lib, be = _lib.lib(), engine.TorchBackend(dev)
+    w = workload.build(args.workload, batch_each=args.batch, n_objects=args.objects)
+    eng = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], w["batch_each"], w["pose"], w["idx"], seed=1)
+    for _ in range(args.count_at):
+        eng.step()
+    torch.cuda.synchronize()
+    calls = eng.stage_calls()
+    torch.cuda.profiler.start()
+    for st in STAGE_KERNELS:
+        _lib.check(calls[st](), lib)
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
+    eng.close()
 
 
 def parse():
@@ -62,6 +128,15 @@ def parse():
                          "default is the reference's practice of one independent process per object group")
     ap.add_argument("--cpu-sample-batch", type=int, default=16)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--sustain", type=int, default=2000,
+                    help="N=1: iterations of the sustained block (windows of 250, outlier resets every --reset-epochs as "
+                         "in scripts/fit.py:408-422); 0 = skip")
+    ap.add_argument("--reset-epochs", type=int, default=600)
+    ap.add_argument("--no-counters", action="store_true", help="skip the ncu subprocess (executed-instruction counters)")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip baseline G (the reference's GPU path)")
+    ap.add_argument("--no-api-loop", action="store_true", help="skip timing the reference-shaped Python loop")
+    ap.add_argument("--count-mode", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--count-at", type=int, default=25, help=argparse.SUPPRESS)
     return ap.parse_args()
 
 
@@ -184,6 +259,7 @@ def run_b200(args):
                            collectives=shard.GlobalStats() if (world > 1 and args.global_rms) else None,
                            overlap=not args.no_overlap)
     graphed = (not args.no_graph) and eng.capture()
+    qp_batch_stop, overlap = eng.qp_batch_stop, eng.overlap
     torch.cuda.synchronize()
     t_setup = time.perf_counter() - t_setup
     K, W = max(1, args.steps), max(3, args.warmup)
@@ -276,35 +352,93 @@ def run_b200(args):
     ms_e2e = s0.elapsed_time(s1)
     h2d = Bt * n_c * 8 + Bt * 4
     d2h = Bt * 5
-    # ---- every stage alone on the current state (CUDA events on the launching stream, L2 flushed before each) ----
-    stage_ms = {}
-    for name, fn in eng.stage_calls().items():
-        for _ in range(2):
-            _lib.check(fn(), lib)
-        ts = []
-        for _ in range(max(5, min(K, 10))):
-            flush.zero_()
-            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            k0.record()
-            _lib.check(fn(), lib)
-            k1.record()
-            torch.cuda.synchronize()
-            ts.append(k0.elapsed_time(k1))
-        stage_ms[name] = float(np.median(ts))
-    ms_pen = stage_ms["hand_distance"]
-    # FP32 FMA peak, measured live
-    sink = be.empty((4,), np.float32)
     import ctypes
-    nf = ctypes.c_uint64(0)
-    lib.gqp_fma_peak_probe(2000, be.ptr(sink), ctypes.byref(nf), be.stream)
-    torch.cuda.synchronize()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    lib.gqp_fma_peak_probe(20000, be.ptr(sink), ctypes.byref(nf), be.stream)
-    f1.record()
-    torch.cuda.synchronize()
-    fp32_peak_tflops = 2.0 * nf.value / (f0.elapsed_time(f1) * 1e-3) / 1e12
+
+    # ---- every stage alone on the current state (CUDA events on the launching stream, L2 flushed before each) ----
+    def time_stages():
+        out = {}
+        for name, fn in eng.stage_calls().items():
+            for _ in range(2):
+                _lib.check(fn(), lib)
+            ts = []
+            for _ in range(max(5, min(K, 10))):
+                flush.zero_()
+                k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                k0.record()
+                _lib.check(fn(), lib)
+                k1.record()
+                torch.cuda.synchronize()
+                ts.append(k0.elapsed_time(k1))
+            out[name] = float(np.median(ts))
+        return out
+
+    stage_ms = time_stages()
+    iteration_of_value = eng.iteration
+
+    # ---- FP32 / FP64 FMA peaks, measured live (roofline denominators of the SIMT stages) ----
+    def fma_peak(probe, dtype):
+        sink = be.empty((4,), dtype)
+        nf = ctypes.c_uint64(0)
+        probe(2000, be.ptr(sink), ctypes.byref(nf), be.stream)
+        torch.cuda.synchronize()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        probe(32000, be.ptr(sink), ctypes.byref(nf), be.stream)
+        f1.record()
+        torch.cuda.synchronize()
+        return 2.0 * nf.value / (f0.elapsed_time(f1) * 1e-3) / 1e12
+    fp32_peak_tflops = fma_peak(lib.gqp_fma_peak_probe, np.float32)
+    fp64_peak_tflops = fma_peak(lib.gqp_dfma_peak_probe, np.float64)
+
+    # ---- sustained block: the fit carried on for --sustain iterations with the reference's outlier resets ----
+    sustained = None
+    if world == 1 and args.sustain > 0:
+        from graspqp_b200 import synth
+        verts = [fv.reshape(-1, 3) for fv in w["face_verts"]]
+        cnt_off = int(lib.gqp_hand_distance_counter_offset(O, B, eng.n_pts, 0, be.ptr(eng.pen_scratch)))
+        i_pen = engine.TERMS.index("E_pen")
+        win, windows, n_resets, n_reset_rows = 250, [], 0, 0
+        n_total = args.sustain
+        evs2 = []
+        for it in range(1, n_total + 1):
+            reset = None
+            # scripts/fit.py:408: every reset_epochs iterations, not within the last 2*reset_epochs of the fit
+            if args.reset_epochs and eng.iteration + 1 >= args.reset_epochs and (eng.iteration + 1) % args.reset_epochs == 0 \
+                    and (eng.iteration + 1) < n_total - 2 * args.reset_epochs:
+                pi, ii = synth.random_grasp_init(w["pack"], verts, B, n_c, 1000 + eng.iteration)  # host init (row f1)
+                reset = (be.from_host(pi, np.float32), be.from_host(ii.astype(np.int32), np.int32))
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            eng.step(reset_init=reset, z_score_threshold=1.0)
+            e1.record()
+            evs2.append((e0, e1))
+            if reset is not None:
+                n_resets += 1
+                n_reset_rows += int(eng.reset_count.item())
+            if it % win == 0 or it == n_total:
+                torch.cuda.synchronize()
+                ms = [a.elapsed_time(b) for a, b in evs2]
+                evs2 = []
+                cnt = eng.pen_scratch.view(torch.int32)[cnt_off:cnt_off + 2].tolist()
+                windows.append({"iterations": [eng.iteration - len(ms) + 1, eng.iteration],
+                                "ms_per_step": round(float(np.mean(ms)), 4), "ms_max": round(float(np.max(ms)), 4),
+                                "mean_E_pen": round(float(eng.losses[i_pen].mean().item()), 5),
+                                "mean_energy": round(float(eng.energy.mean().item()), 3),
+                                "searched_samples_per_candidate": round(cnt[0] / Bt, 2),
+                                "accept_rate": round(float(eng.accept.float().mean().item()), 3)})
+        all_ms = sum(wd["ms_per_step"] * (wd["iterations"][1] - wd["iterations"][0] + 1) for wd in windows)
+        sustained = {"iterations": n_total, "value": Bt * n_total / (all_ms * 1e-3), "unit": UNIT,
+                     "ms_per_step": all_ms / n_total, "windows": windows, "resets": n_resets,
+                     "reset_rows": n_reset_rows, "reset_epochs": args.reset_epochs,
+                     "reset_init": "host (synth.random_grasp_init) uploaded outside the timed step; gqp_mala_reset inside",
+                     "value_window": f"the headline `value` times iterations {iteration_of_value - K + 1}-"
+                                     f"{iteration_of_value} after init (K steps after W warm-up)",
+                     "stage_ms_at_end": {k: round(v, 4) for k, v in time_stages().items()}}
+    iteration_of_counters = eng.iteration
+
     # ---- max over ranks, gather ----
+    ms_pen = stage_ms["hand_distance"]
     t = torch.tensor([ms_total, ms_e2e, ms_pen], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -312,17 +446,64 @@ def run_b200(args):
         shard.gather_results(eng.pose, eng.energy, eng.idx, O * world, B, rank, world)
     ms_total, ms_e2e, ms_pen = [float(v) for v in t.tolist()]
     final_energy = float(eng.energy.float().mean().item())
+    eng.close()
+    del eng
+    torch.cuda.empty_cache()
     if rank == 0:
-        f_hand = int(w["pack"]["face_offset"][-1])
-        pen_flops = 80.0 * eng.n_pts * f_hand * Bt  # brute-force-equivalent point-face tests x 80 flop
-        achieved = pen_flops / (ms_pen * 1e-3) / 1e12
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        alg_bytes = Bt * (eng.L * 48 + 4 + 4 * ((eng.n_pts + 31) // 32)) + O * eng.n_pts * 12
+        f_hand = int(w["pack"]["face_offset"][-1])
+        n_pts, L = w["surface"].shape[1], len(w["pack"]["mesh_frame"])
+        # ---- executed-instruction counters of the three heavy stages, by an ncu subprocess of this run ----
+        counters, counters_note = (None, "skipped") if (world > 1 or args.no_counters) else \
+            collect_counters(args, iteration_of_counters)
+        st_ms = sustained["stage_ms_at_end"] if sustained else stage_ms   # times at the state the counters were taken at
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        kernels = {}
+        for st in STAGE_KERNELS:
+            row = {"ms": round(st_ms[st], 4)}
+            if counters:
+                c = counters[st]
+                g = lambda k: c.get(k, 0.0)
+                f32 = 2 * g(COUNTER_METRICS[0]) + g(COUNTER_METRICS[1]) + g(COUNTER_METRICS[2])
+                f64 = 2 * g(COUNTER_METRICS[3]) + g(COUNTER_METRICS[4]) + g(COUNTER_METRICS[5])
+                sec = st_ms[st] * 1e-3
+                row.update({"fp32_tflops": f32 / sec / 1e12, "fp32_frac": f32 / sec / 1e12 / fp32_peak_tflops,
+                            "fp64_tflops": f64 / sec / 1e12, "fp64_frac": f64 / sec / 1e12 / fp64_peak_tflops,
+                            # every executed thread-instruction against the lane-issue roof (4 SMSPs x 32 lanes / SM / clk)
+                            "lane_issue_frac": g("smsp__thread_inst_executed.sum") / (sec * sm_hz * sms * 128),
+                            "lanes_per_inst": g("smsp__thread_inst_executed.sum") / max(g("smsp__inst_executed.sum"), 1.0),
+                            "dram_bytes": g("dram__bytes_read.sum") + g("dram__bytes_write.sum")})
+            kernels[st] = row
+        top = max(STAGE_KERNELS, key=lambda st: st_ms[st])
+        fp = "fp64" if top == "fc_solve" else "fp32"
+        alg_bytes = {"hand_distance": Bt * (L * 48 + 4 + 4 * ((n_pts + 31) // 32)) + O * n_pts * 12,
+                     "object_distance": Bt * n_c * (12 + 36), "fc_solve": Bt * n_c * 24 + Bt * 12 * 3 * 4 * n_c * 8}[top]
+        roof = {"bound": fp, "kernel": f"{top} ({' + '.join(k.split('<')[0] for k in STAGE_KERNELS[top][:5] if '(int)' not in k)}): "
+                                       "the longest stage of an iteration at the sustained state",
+                "achieved": kernels[top].get(fp + "_tflops"), "peak": fp32_peak_tflops if fp == "fp32" else fp64_peak_tflops,
+                "unit": "TFLOP/s", "frac": kernels[top].get(fp + "_frac"),
+                "lane_issue_frac": kernels[top].get("lane_issue_frac"), "traffic": kernels[top].get("dram_bytes"),
+                "ms_per_launch": st_ms[top], "counters": counters_note,
+                "note": "achieved = EXECUTED FP flop (ncu: 2*ffma + fmul + fadd per launch group, predicated-on threads) / "
+                        "CUDA-event time of the un-profiled launch; peak = FMA probe measured live in this run; "
+                        "lane_issue_frac = all executed thread-instructions / (SMs x 128 lanes x SM clock x time), the "
+                        "roof of a traversal kernel whose work is compares, shuffles and address arithmetic as much as "
+                        "FP; traffic = dram bytes of the same ncu pass (cold caches)",
+                "kernels": kernels,
+                "bfe": {"flops_per_step": 80.0 * n_pts * f_hand * Bt, "speedup_vs_bruteforce_at_peak":
+                        80.0 * n_pts * f_hand * Bt / (ms_pen * 1e-3) / 1e12 / fp32_peak_tflops,
+                        "note": "SURVEY 8(d)'s brute-force-equivalent work of H4 (80 flop x samples x hand faces x "
+                                "candidates) over the stage time, against the FMA peak: how much exact culling saves, "
+                                "NOT a roofline fraction"},
+                "hbm": {"achieved": alg_bytes / (st_ms[top] * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": alg_bytes / (st_ms[top] * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes": alg_bytes,
+                        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
         line = {
             "metric": METRIC, "value": Bt * world * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
@@ -330,8 +511,8 @@ def run_b200(args):
             "config": {"workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
                                    f"{w['faces_per_mesh']} tris), batch {B}/object, n_contact {n_c}, 2500 surface samples",
                        "candidates_per_gpu": Bt, "l2": "flushed between timed steps (256 MiB write)",
-                       "qp_batch_stop": eng.qp_batch_stop, "streams": 2 if eng.overlap else 1, "cuda_graph": bool(graphed),
-                       "collectives": ("global rms + qp exit words all-reduced per step" if eng.collectives else
+                       "qp_batch_stop": qp_batch_stop, "streams": 2 if overlap else 1, "cuda_graph": bool(graphed),
+                       "collectives": ("global rms + qp exit words all-reduced per step" if args.global_rms else
                                        "none on the data path; final all-gather of grasps") if world > 1 else "n/a",
                        "noise": "philox on device (value) / injected from host (e2e)",
                        "e2e_pipeline": "double-buffered, copies on a second stream: upload k+1 and enqueue k+1 before reading back k",
@@ -340,31 +521,100 @@ def run_b200(args):
                     "d2h_bytes_per_step": d2h},
             "gpu_launches": launches, "clocks": clocks,
             "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
-            "roofline": {"bound": "fp32", "kernel": "H4 hand penetration = pen_collect_kernel + pen_search_kernel "
-                                                    "(98.5 % of a grasp-step's brute-force-equivalent work)",
-                         "achieved": achieved,
-                         "peak": fp32_peak_tflops, "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops,
-                         "traffic": ncu_traffic_bytes(("pen_broad_kernel", "pen_collect_kernel", "pen_search_kernel")),
-                         "ms_per_launch": ms_pen,
-                         "note": "achieved = brute-force-equivalent flops (80 x n_pts x F_hand x candidates) / launch "
-                                 "time; exact culling skips most pairs, so frac may exceed 1 (SURVEY 8d). peak = FP32 "
-                                 "FMA probe measured live in this run",
-                         "hbm": {"achieved": alg_bytes / (ms_pen * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                                 "frac": alg_bytes / (ms_pen * 1e-3) / 1e9 / hbm_peak,
-                                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}},
+            "fp_peaks": {"fp32_tflops": fp32_peak_tflops, "fp64_tflops": fp64_peak_tflops,
+                         "nominal_fp32_tflops": sms * 128 * 2 * sm_hz / 1e12},
+            "roofline": roof,
         }
+        if sustained:
+            line["sustained"] = sustained
+        if world == 1 and not args.no_api_loop:
+            line["api_loop"] = api_loop_run(args, w, dev)
+        if world == 1 and not args.no_gpu_baseline:
+            line["gpu_baseline"] = gpu_baseline_run(args)
         if world == 1 and not args.skip_cpu_baseline:
             cb, _ = cpu_reference_run(args, 100, 1, args.cpu_sample_batch)   # ~15 s of host work
             line["cpu_baseline"] = cb
         print(json.dumps(line))
-    eng.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+def gpu_baseline_run(args):
+    """Baseline G: the reference's GPU path on this GPU, in a subprocess (baseline/gpu_reference.py: the
+    reference's MalaStar / calculate_energy / metric code + its TorchSDF kernel built for sm_100; qpth and the model
+    classes substituted as stated there).  Bounded: 2 warm-up + 3 timed iterations of the same workload."""
+    script = os.path.join(ROOT, "baseline", "gpu_reference.py")
+    cmd = [sys.executable, script, "--workload", args.workload, "--steps", "3", "--warmup", "2"]
+    if args.batch:
+        cmd += ["--batch", str(args.batch)]
+    if args.objects:
+        cmd += ["--objects", str(args.objects)]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+        last = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        return json.loads(last[-1]) if last else {"unavailable": f"rc {r.returncode}: {r.stderr[-200:]!r}"}
+    except (subprocess.TimeoutExpired, OSError, ValueError) as e:
+        return {"unavailable": f"{type(e).__name__}"}
+
+
+def api_loop_run(args, w, dev, iters=10, warmup=3):
+    """The reference-shaped Python loop (HandModel / ObjectModel / energy callable / MalaStar + autograd, the body of
+    scripts/fit.py:399-458 written as the reference writes it) on the same workload: what a user gets who swaps the
+    imports and keeps their loop, next to `value` (the fused FitEngine)."""
+    import torch
+    import graspqp_b200 as g
+    from graspqp_b200 import engine
+    B, n_c, O = w["batch_each"], w["n_contact"], len(w["face_verts"])
+    hand = g.HandModel(w["hand"], dev)
+    obj = g.ObjectModel(batch_size_each=B, num_samples=w["surface"].shape[1], device=dev)
+    obj.initialize(list(w["kinds"]), w["face_verts"], w["surface"])
+    F = g.GraspSpanMetricFactory
+    energy_fnc = F.create(F.MetricType.GRASPQP, solver_kwargs={"friction": 0.2, "max_limit": 20.0, "n_cone_vecs": 4})
+    hand.set_parameters(torch.tensor(w["pose"], device=dev).requires_grad_(True), torch.tensor(w["idx"], device=dev))
+    opt = g.MalaStar(hand, switch_possibility=0.4, device=dev, batch_size=B)
+    wts = engine.DEFAULT_WEIGHTS
+
+    def total(losses):
+        e = 0
+        for k, v in losses.items():
+            e = e + wts[k] * v
+        return e
+    energy = total(g.calculate_energy(hand, obj, energy_fnc=energy_fnc, method="gendexgrasp", svd_gain=0.1))
+    energy.sum().backward()
+    opt.zero_grad()
+    energy = energy.detach()
+
+    def iterate():
+        nonlocal energy
+        opt.try_step()
+        Eb = energy.view(-1, B)
+        z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        opt.zero_grad()
+        new_energy = total(g.calculate_energy(hand, obj, energy_fnc=energy_fnc, method="gendexgrasp", svd_gain=0.1))
+        new_energy.sum().backward()
+        with torch.no_grad():
+            accept, _ = opt.accept_step(energy, new_energy, None, z, 1.0)
+            energy[accept] = new_energy.detach()[accept]
+    for _ in range(warmup):
+        iterate()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        iterate()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / iters
+    return {"value": O * B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "iterations": iters,
+            "what": "graspqp_b200.HandModel / ObjectModel / calculate_energy / MalaStar driven by torch autograd "
+                    "(ops.py bridges), un-fused: fresh tensors per op, per-candidate surface samples, un-culled H4"}
+
+
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.count_mode:
+        run_count_mode(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)

@@ -5,7 +5,16 @@ Reference API:  HandModel, ObjectModel, GraspSpanMetricFactory, calculate_energy
                 (same names / signatures as leggedrobotics/graspqp, autograd bridges over the same kernels)
 Boundary:       include/graspqp_b200.h (C ABI of libgraspqp_b200.so).  No CPU fallback anywhere in this package.
 """
-SDF_BACKEND = "B200"
+import os as _os
+
+# The reference selects its SDF backend from the environment at import (hand_model.py:25-34, object_model.py:15-24):
+# SDF_BACKEND in {TORCHSDF (default), WARP, KAOLIN}.  This package implements the TORCHSDF contract (same winner, sign
+# heuristic and gradient, bit for bit) with its own kernels; "B200" is accepted as a synonym.  WARP / KAOLIN have
+# different sign and tie semantics and are not built: selecting them fails loudly instead of silently changing results.
+SDF_BACKEND = _os.environ.get("SDF_BACKEND", "TORCHSDF").upper()
+if SDF_BACKEND not in ("TORCHSDF", "B200"):
+    raise RuntimeError(f"SDF_BACKEND={SDF_BACKEND!r}: graspqp_b200 implements the TORCHSDF backend's contract only "
+                       "(set SDF_BACKEND=TORCHSDF or unset it)")
 
 
 def __getattr__(name):  # lazy: importing the package must not need torch/CUDA (build(), tools)

@@ -56,8 +56,10 @@ SIGNATURES = {
     "gqp_hand_distance_full": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_hand_distance_backward": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_hand_distance_scratch_floats": (c_uint64, [c_int, c_int, c_int, c_int]),
+    "gqp_hand_distance_counter_offset": (c_uint64, [c_int, c_int, c_int, c_int, P]),
     "gqp_hand_pen_info": (c_int, [c_void_p, P]),
     "gqp_hand_link_grid": (c_int, [c_void_p, c_int, P, P, P, c_int]),
+    "gqp_hand_link_planes": (c_int, [c_void_p, c_int, P, c_int, P]),
     "gqp_self_pen_joints": (c_int, [c_void_p, P, P, c_int, P, P, c_float, c_float, P, P, P]),
     "gqp_fc_dis_energy": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P, P, P, P, P]),
     "gqp_fc_stop_iter": (c_int, [P, c_int, c_int, c_float, P, P]),
@@ -72,6 +74,7 @@ SIGNATURES = {
     "gqp_mala_reset": (c_int, [c_int, c_int, c_int, P, c_float, P, P, P, P, P, P, P, P, P, P, P]),
     "gqp_memset_zero": (c_int, [P, c_uint64, P]),
     "gqp_fma_peak_probe": (c_int, [c_int, P, POINTER(c_uint64), P]),
+    "gqp_dfma_peak_probe": (c_int, [c_int, P, POINTER(c_uint64), P]),
 }
 
 

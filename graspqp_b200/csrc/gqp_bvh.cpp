@@ -385,6 +385,50 @@ bool gqp_mesh_is_nice(const float *fv, int F) {
     return vol > 0;
 }
 
+// ---- fp32 ties at right-angle creases -------------------------------------------------------------------------------
+// The argument above is exact-arithmetic.  The reference compares SQUARED distances in fp32, so a face A ties with the
+// truly nearest face B whenever d_A^2 - d_B^2 = s^2 < ~eps * d^2, i.e. when the foot point of p on B lies within
+// s < sqrt(k eps) d of the feature A touches; the first-minimum rule then lets A win if its index is lower, and the
+// sign is the side of A's plane.  p - c_A = d n_B + O(s), so p is BEHIND A's plane only if n_A.n_B <~ s/d ~ 1e-3: faces
+// that meet at a right angle (box-like link meshes: the Allegro palm's flat top, the Shadow Hand's box links, the Panda
+// fingers).  There the reference returns -1 — a "penetration" as deep as the point is far — for outside points in a
+// slab of relative thickness sqrt(k eps) just behind the extended plane of A (found by the direct culling-proof test:
+// Allegro palm, p 1.28 m away and 44 um under the plane of the top face; 4.5e-6 of uniformly drawn points within
+// 0.25 m).  To reproduce the reference there, culling must not skip such points: this returns the planes of all faces
+// that share a vertex with a face at >= 90 degrees - 0.11 degrees; the kernels keep every (sample, link) pair whose
+// sample lies in  -GQP_TIE_NEG * D <= n.q - a <= GQP_TIE_POS * D  of one of them (D = an upper bound of the distance).
+bool gqp_mesh_tie_planes(const float *fv, int F, int max_planes, std::vector<float> &planes) {
+    planes.clear();
+    std::map<std::array<float, 3>, std::vector<int>> inc;
+    std::vector<D3> nh(F);
+    for (int f = 0; f < F; ++f) {
+        D3 a = ldv(fv + 9 * f), b = ldv(fv + 9 * f + 3), c = ldv(fv + 9 * f + 6);
+        D3 n = cross(b - a, c - a);
+        double l = std::sqrt(dot(n, n));
+        nh[f] = l > 0 ? n * (1.0 / l) : D3{0, 0, 0};
+        for (int k = 0; k < 3; ++k) inc[{fv[9 * f + 3 * k], fv[9 * f + 3 * k + 1], fv[9 * f + 3 * k + 2]}].push_back(f);
+    }
+    std::vector<char> sus(F, 0);
+    for (auto &kv : inc)
+        for (int fa : kv.second)
+            for (int fb : kv.second)
+                if (fa != fb && dot(nh[fa], nh[fb]) <= 2e-3) sus[fa] = 1;
+    for (int f = 0; f < F; ++f) {
+        if (!sus[f]) continue;
+        const double a0 = dot(nh[f], ldv(fv + 9 * f));
+        bool dup = false;
+        for (size_t i = 0; i < planes.size() && !dup; i += 4) {
+            D3 m = {planes[i], planes[i + 1], planes[i + 2]};
+            dup = dot(m, nh[f]) > 1.0 - 1e-9 && std::fabs(planes[i + 3] - a0) < 1e-7;
+        }
+        if (dup) continue;
+        planes.push_back((float)nh[f].x); planes.push_back((float)nh[f].y); planes.push_back((float)nh[f].z);
+        planes.push_back((float)a0);
+        if ((int)planes.size() / 4 > max_planes) return false;
+    }
+    return true;
+}
+
 // bit = 1 when the whole cell is outside the (nice) mesh with a 10 micron margin.  Cell (x,y,z) -> bit
 // ((z*dim[1]+y)*dim[0]+x).
 // A cell is FREE when the surface stays farther from its centre than its circumradius (+ margin).  A free cell is convex

@@ -19,15 +19,40 @@
 #include "graspqp_b200.h"
 
 struct PenHdr {
-    int32_t n_links, n_grids, links_off, grids_off, nodes_off, bits_off, total_bytes, pad;
+    int32_t n_links, n_grids, links_off, grids_off, nodes_off, bits_off, total_bytes, planes_off;
 };
 struct PenLink {
     int32_t node_first, n_nodes, tri_first, n_faces;
     int32_t grid;  // index of the link's outside-grid, or -1 when the mesh is not "nice" (no culling)
     int32_t wide_first;  // first wide node of the link's 8-wide tree in GqpPenTables::d_wide
     float lo[3], hi[3];  // bounding box, slightly inflated
-    int32_t pad2[4];
+    int32_t plane_first, n_planes;  // tie planes of the link (gqp_bvh.cpp: gqp_mesh_tie_planes), float4 each
+    int32_t pad2[2];
 };
+// slab behind a tie plane in which the reference's fp32 first-minimum rule may return -1 for an OUTSIDE point:
+// -GQP_TIE_NEG * D <= n.q - a <= GQP_TIE_POS * D, D >= distance of q to the link (sqrt(8 ulp) = 1e-3, doubled; the
+// positive side covers the rounding of the sign's dot product)
+#define GQP_TIE_NEG 2e-3f
+#define GQP_TIE_POS 2e-6f
+#define PEN_MAX_PLANES 32
+__device__ __forceinline__ float pen_link_reach(const PenLink &K, V3 q) {  // upper bound of |q - any point of the link|
+    const V3 ctr = V3{0.5f * (K.lo[0] + K.hi[0]), 0.5f * (K.lo[1] + K.hi[1]), 0.5f * (K.lo[2] + K.hi[2])};
+    const V3 h = V3{0.5f * (K.hi[0] - K.lo[0]), 0.5f * (K.hi[1] - K.lo[1]), 0.5f * (K.hi[2] - K.lo[2])};
+    const V3 d = q - ctr;
+    return sqrtf(dot3(d, d)) + sqrtf(dot3(h, h));
+}
+// true when a sphere (centre q in the link frame, radius rad; rad = 0: a point) reaches the tie slab of one of the
+// link's planes: nothing in it may be culled
+__device__ __forceinline__ bool pen_in_tie_slab(const PenLink &K, const float4 *planes, V3 q, float rad) {
+    if (K.n_planes == 0) return false;
+    const float D = pen_link_reach(K, q) + rad;
+    for (int i = 0; i < K.n_planes; ++i) {
+        const float4 P = planes[K.plane_first + i];
+        const float hgt = P.x * q.x + P.y * q.y + P.z * q.z - P.w;
+        if (hgt - rad <= GQP_TIE_POS * D && hgt + rad >= -GQP_TIE_NEG * D) return true;
+    }
+    return false;
+}
 struct PenGrid {
     float org[3];
     float inv_cell;
@@ -55,8 +80,10 @@ struct GqpPenTables {
 #define PEN_MAX_SMEM (200 * 1024)
 
 // true when q is provably outside the (nice) link mesh: outside its box, or in a grid cell entirely outside it
-__device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *grids, const uint32_t *bits, V3 q) {
+__device__ __forceinline__ bool pen_outside(const PenLink &K, const PenGrid *grids, const uint32_t *bits,
+                                            const float4 *planes, V3 q) {
     if (K.grid < 0) return false;
+    if (pen_in_tie_slab(K, planes, q, 0.f)) return false;
     if (q.x < K.lo[0] || q.y < K.lo[1] || q.z < K.lo[2] || q.x > K.hi[0] || q.y > K.hi[1] || q.z > K.hi[2]) return true;
     const PenGrid &G = grids[K.grid];
     float fx = (q.x - G.org[0]) * G.inv_cell, fy = (q.y - G.org[1]) * G.inv_cell, fz = (q.z - G.org[2]) * G.inv_cell;
@@ -117,6 +144,7 @@ __global__ void pen_mask_kernel(const unsigned char *__restrict__ blob, const fl
     if (b >= Bt) return;
     const PenHdr *hdr = reinterpret_cast<const PenHdr *>(blob);
     const PenLink *links = reinterpret_cast<const PenLink *>(blob + hdr->links_off);
+    const float4 *planes = reinterpret_cast<const float4 *>(blob + hdr->planes_off);
     const int L = hdr->n_links;
     const int row = per_candidate_points ? b : b / batch_each;
     const float *s = bounds + ((size_t)row * (n_chunks + 1) + n_chunks) * 4;
@@ -130,7 +158,8 @@ __global__ void pen_mask_kernel(const unsigned char *__restrict__ blob, const fl
         if (cull && K.grid >= 0) {
             V3 q = t34_inv_point(t34_load(link_tf + ((size_t)b * L + l) * 12), cen);
             keep = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
-                     q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
+                     q.y > K.hi[1] + rad || q.z > K.hi[2] + rad) ||
+                   pen_in_tie_slab(K, planes, q, rad);
         }
         if (keep) m |= 1u << l;
     }
@@ -158,6 +187,7 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, int node
     // through L1/L2 (Robotiq 2F-140: 22.7k faces, 180 KB of nodes)
     const GqpBvhNode *nodes = reinterpret_cast<const GqpBvhNode *>((nodes_staged ? sm : blob) + hdr->nodes_off);
     const uint32_t *bits = reinterpret_cast<const uint32_t *>(sm + hdr->bits_off);
+    const float4 *planes = reinterpret_cast<const float4 *>(sm + hdr->planes_off);
     const int L = hdr->n_links;
 
     const int lane = threadIdx.x & 31;
@@ -192,8 +222,9 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, int node
                 keep = true;
                 if (CULL && K.grid >= 0) {
                     V3 q = t34_inv_point(W, cen);
-                    if (q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
-                        q.y > K.hi[1] + rad || q.z > K.hi[2] + rad)
+                    if ((q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
+                         q.y > K.hi[1] + rad || q.z > K.hi[2] + rad) &&
+                        !pen_in_tie_slab(K, planes, q, rad))
                         keep = false;
                 }
             }
@@ -211,7 +242,7 @@ hand_pen_kernel(const unsigned char *__restrict__ blob, int blob_bytes, int node
 #pragma unroll
                 for (int i = 0; i < 12; ++i) W.m[i] = sW[l * 12 + i];
                 V3 q = t34_inv_point(W, p);
-                if (CULL && pen_outside(K, grids, bits, q)) continue;
+                if (CULL && pen_outside(K, grids, bits, planes, q)) continue;
                 SdfBest best;
                 sdf_best_init(best);
                 bvh_query<false>(nodes + K.node_first, tris + (size_t)K.tri_first * 9, face_id + K.tri_first,
@@ -285,6 +316,7 @@ pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict
     if (b >= Bt) return;
     const PenHdr *hdr = reinterpret_cast<const PenHdr *>(blob);
     const PenLink *links = reinterpret_cast<const PenLink *>(blob + hdr->links_off);
+    const float4 *planes = reinterpret_cast<const float4 *>(blob + hdr->planes_off);
     const int L = hdr->n_links;
     const int row = per_candidate_points ? b : b / batch_each;
     const float *br = bounds + (size_t)row * (n_chunks + 1) * 4;
@@ -298,7 +330,8 @@ pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict
             const float rad = br[4 * n_chunks + 3];
             const V3 q = t34_inv_point(t34_load(Wb + lane * 12), V3{br[4 * n_chunks], br[4 * n_chunks + 1], br[4 * n_chunks + 2]});
             keep = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
-                     q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
+                     q.y > K.hi[1] + rad || q.z > K.hi[2] + rad) ||
+                   pen_in_tie_slab(K, planes, q, rad);
         }
     }
     const uint32_t rowmask = __ballot_sync(GQP_FULL, keep);
@@ -316,7 +349,8 @@ pen_broad_kernel(const unsigned char *__restrict__ blob, const float *__restrict
                 if (K.grid >= 0) {
                     const V3 q = t34_inv_point(tf16 ? t34_load4(Wb + l * 12) : t34_load(Wb + l * 12), cen);
                     hit = !(q.x < K.lo[0] - rad || q.y < K.lo[1] - rad || q.z < K.lo[2] - rad || q.x > K.hi[0] + rad ||
-                            q.y > K.hi[1] + rad || q.z > K.hi[2] + rad);
+                            q.y > K.hi[1] + rad || q.z > K.hi[2] + rad) ||
+                          pen_in_tie_slab(K, planes, q, rad);
                 }
                 if (hit) cm |= 1u << l;
             }
@@ -349,6 +383,7 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
     const PenLink *links = reinterpret_cast<const PenLink *>(sm + hdr->links_off);
     const PenGrid *grids = reinterpret_cast<const PenGrid *>(sm + hdr->grids_off);
     const uint32_t *bits = reinterpret_cast<const uint32_t *>(sm + hdr->bits_off);
+    const float4 *planes = reinterpret_cast<const float4 *>(sm + hdr->planes_off);
     const int L = hdr->n_links;
     const int lane = threadIdx.x & 31, warps_per_block = blockDim.x / 32;
     const unsigned n_items = counter[1];
@@ -363,7 +398,7 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
         for (uint32_t m = I.links; m; m &= m - 1) {
             const int l = __ffs((int)m) - 1;
             const T34 W = TF16 ? t34_load4(Wb + l * 12) : t34_load(Wb + l * 12);
-            if (!pen_outside(links[l], grids, bits, t34_inv_point(W, p))) need |= 1u << l;
+            if (!pen_outside(links[l], grids, bits, planes, t34_inv_point(W, p))) need |= 1u << l;
         }
         if (!valid) need = 0;  // padding lanes of the last chunk
         const unsigned em = __ballot_sync(GQP_FULL, need != 0);
@@ -572,6 +607,7 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     std::vector<float> pre;
     std::vector<GqpBvhNode> wide;
     std::vector<float> wpre;
+    std::vector<float> planes;
     for (int l = 0; l < L; ++l) {
         int f0 = h->face_offset[l], F = h->face_offset[l + 1] - f0;
         PenLink K{};
@@ -601,7 +637,12 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
                 K.lo[k] = root.lo[k] - 2e-5f;
                 K.hi[k] = root.hi[k] + 2e-5f;
             }
-            if (gqp_mesh_is_nice(face_verts_host + 9 * (size_t)f0, F)) {
+            std::vector<float> tie;
+            if (gqp_mesh_is_nice(face_verts_host + 9 * (size_t)f0, F) &&
+                gqp_mesh_tie_planes(face_verts_host + 9 * (size_t)f0, F, PEN_MAX_PLANES, tie)) {
+                K.plane_first = (int)(planes.size() / 4);
+                K.n_planes = (int)(tie.size() / 4);
+                planes.insert(planes.end(), tie.begin(), tie.end());
                 PenGrid G{};
                 float cell = 0.002f;
                 int dim[3];
@@ -643,6 +684,8 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
     hdr.links_off = append(links.data(), links.size() * sizeof(PenLink));
     hdr.grids_off = append(grids.data(), grids.size() * sizeof(PenGrid));
     hdr.bits_off = append(bits.data(), bits.size() * sizeof(uint32_t));
+    planes.resize(planes.size() + 4, 0.f);  // never empty: the kernels form the pointer unconditionally
+    hdr.planes_off = append(planes.data(), planes.size() * sizeof(float));
     hdr.nodes_off = append(nodes.data(), nodes.size() * sizeof(GqpBvhNode));  // last: the collect kernel stops before it
     pad16(B);
     hdr.total_bytes = (int)B.size();
@@ -896,6 +939,35 @@ extern "C" int gqp_hand_link_grid(const GqpHand *h, int link, float *geom_host, 
         std::memcpy(bits_host, bits, (size_t)words * 4);
     }
     return GQP_OK;
+}
+
+// diagnostics: word offset, inside the scratch buffer of gqp_hand_distance, of the culled path's two counters
+// {samples queued for the exact search, (candidate, chunk) work items of the narrow phase} after a call
+extern "C" uint64_t gqp_hand_distance_counter_offset(int n_obj, int batch_each, int n_pts, int per_candidate_points,
+                                                     const void *scratch) {
+    const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
+    const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;
+    uint64_t off = Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt;  // partial sums, bounds, masks (hand_distance_impl)
+    if (((uintptr_t)scratch + 4 * off) & 7) off += 1;
+    return off;
+}
+
+// diagnostics: the link's tie planes (4 floats each) and the slab constants {GQP_TIE_NEG, GQP_TIE_POS}; returns the count
+extern "C" int gqp_hand_link_planes(const GqpHand *h, int link, float *planes_host, int max_planes, float *slab_host) {
+    if (!h || !h->pen) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_planes: bad argument");
+    const std::vector<unsigned char> &B = h->pen->blob_host;
+    const PenHdr *hdr = reinterpret_cast<const PenHdr *>(B.data());
+    if (link < 0 || link >= hdr->n_links) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_planes: no such link");
+    const PenLink &K = reinterpret_cast<const PenLink *>(B.data() + hdr->links_off)[link];
+    if (slab_host) {
+        slab_host[0] = GQP_TIE_NEG;
+        slab_host[1] = GQP_TIE_POS;
+    }
+    if (planes_host) {
+        if (max_planes < K.n_planes) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_planes: planes_host too small");
+        std::memcpy(planes_host, B.data() + hdr->planes_off + 16 * (size_t)K.plane_first, 16 * (size_t)K.n_planes);
+    }
+    return K.n_planes;
 }
 
 extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {

@@ -78,14 +78,18 @@ class HandModel:
             y = y - (x * y).sum(-1, keepdim=True) * x
             y = y / y.norm(dim=-1, keepdim=True)
             self.global_rotation = torch.stack((x, y, torch.cross(x, y, dim=-1)), dim=-1)
+        gather_idx = self.contact_point_indices
         if contact_point_indices is not None:
+            # hand_model.py:816-831: with env_mask the MEMBER is merged, but the contact points of this call are gathered
+            # with the ARGUMENT (the fresh indices of every row) — kept as the reference does it
+            gather_idx = contact_point_indices
             if env_mask is not None and self.contact_point_indices is not None:
-                contact_point_indices = torch.where(env_mask.unsqueeze(-1), contact_point_indices,
-                                                    self.contact_point_indices)
-            self.contact_point_indices = contact_point_indices.clone()
-        if self.contact_point_indices is not None:
-            self.contact_points, self.contact_normals = ops.ContactsFn.apply(self.current_status,
-                                                                             self.contact_point_indices, self)
+                self.contact_point_indices = torch.where(env_mask.unsqueeze(-1), contact_point_indices,
+                                                         self.contact_point_indices)
+            else:
+                self.contact_point_indices = contact_point_indices.clone()
+        if gather_idx is not None:
+            self.contact_points, self.contact_normals = ops.ContactsFn.apply(self.current_status, gather_idx, self)
 
     # ---- distances ---------------------------------------------------------------------------------------------
     def cal_distance(self, x):

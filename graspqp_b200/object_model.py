@@ -8,7 +8,7 @@ import torch
 
 from . import _lib, ops
 
-SDF_BACKEND = "B200"  # the reference reads SDF_BACKEND in {TORCHSDF, WARP, KAOLIN} (object_model.py:15-24)
+from . import SDF_BACKEND  # read from the environment like the reference (object_model.py:15-24); TORCHSDF contract
 
 
 class ObjectModel:
@@ -24,6 +24,8 @@ class ObjectModel:
 
     def initialize(self, object_code_list, face_verts_list=None, surface_points=None, sdf_library=SDF_BACKEND):
         """object_model.py:70-184.  face_verts_list: list of (F,3,3) arrays; surface_points: (O, num_samples, 3)."""
+        if str(sdf_library).upper() not in ("TORCHSDF", "B200"):
+            raise RuntimeError(f"sdf_library={sdf_library!r}: only the TORCHSDF contract is implemented")
         if face_verts_list is None or surface_points is None:
             raise ValueError("pass face_verts_list and surface_points (mesh loading / sampling is setup-time host work)")
         lib = _lib.lib()

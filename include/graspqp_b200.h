@@ -148,6 +148,11 @@ int gqp_hand_distance_backward(const GqpHand *h, const float *link_tf, const flo
                                const float *dgrad, float *grad_link_tf, void *stream);
 uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points);
 
+/* diagnostics: index (in 32-bit words) inside `scratch` of the culled path's counters after gqp_hand_distance(dist = NULL):
+ * word 0 = samples that survived culling and were searched exactly, word 1 = (candidate, 32-sample chunk) work items */
+uint64_t gqp_hand_distance_counter_offset(int n_obj, int batch_each, int n_pts, int per_candidate_points,
+                                          const void *scratch);
+
 /* diagnostics: info_host[6] = {shared-memory blob bytes, BVH nodes, sign-grid cells, cells proven positive, faces, grids} */
 int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host);
 
@@ -158,6 +163,13 @@ int gqp_hand_pen_info(const GqpHand *h, int32_t *info_host);
  * A SET bit, or q outside [lo,hi], is the claim "the reference's sign is +1 for every point there". */
 int gqp_hand_link_grid(const GqpHand *h, int link, float *geom_host, int32_t *dim_host, uint32_t *bits_host,
                        int max_words);
+
+/* The link's "tie planes" (4 floats each: unit normal, offset) -> returns their number (>= 0) or a negative error.
+ * slab_host[2] (may be NULL) = {NEG, POS}: a point q of the link frame with  -NEG*D <= n.q - offset <= POS*D  for one of
+ * the planes (D = |q - box centre| + box half-diagonal) is NEVER culled: behind the extended plane of a face at a
+ * right-angle crease the reference's fp32 first-minimum rule can return sign -1 for outside points (csrc/gqp_bvh.cpp:
+ * gqp_mesh_tie_planes). */
+int gqp_hand_link_planes(const GqpHand *h, int link, float *planes_host, int max_planes, float *slab_host);
 
 /* ---- H5 + E_joints: self_penetration (hand_model.py:989-1040) and joint limits (energy.py:47-54) ------------------
  * e_spen (Bt), e_joints (Bt); ACCUMULATES w_spen*d(e_spen) into grad_link_tf and OVERWRITES grad_pose_joints
@@ -252,6 +264,8 @@ int gqp_memset_zero(void *ptr, uint64_t bytes, void *stream);
 /* FP32 FMA micro-benchmark (roofline denominator for the SIMT stages): runs `iters` dependent-chain FMAs on every
  * lane of a full-chip grid; returns the FMA count in *n_fma_host.  Timed by the caller with CUDA events. */
 int gqp_fma_peak_probe(int iters, float *sink, uint64_t *n_fma_host, void *stream);
+/* the same for FP64 (the QP stage computes in double): roofline denominator of fc_dis_kernel */
+int gqp_dfma_peak_probe(int iters, double *sink, uint64_t *n_fma_host, void *stream);
 
 #ifdef __cplusplus
 }

@@ -150,7 +150,7 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
     rng = np.random.default_rng(seed)
     n_acc = n_tie = 0
     worst = worst_g = 0.0
-    outliers, grad_events, grad_errs = [], 0, []
+    outliers, grad_events, grad_errs, grad_unexplained = [], 0, [], []
     E_TOL = tol.ENERGY_RTOL
     for t in range(T):
         orc.load_state(H(eng.pose), H(eng.idx), H(eng.grad), H(eng.energy), H(eng.ema), H(eng.step_count))
@@ -182,7 +182,12 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
         worst = max(worst, float(np.max(np.where(flagged, 0.0, rel))))
         # gradient of the proposal: 1e-4 relative per pose column on every candidate that is not a conditioning event
         ge = tol.grad_error(H(eng.grad_new), out["new_grad"].numpy()).max(1)
-        grad_events += int(((ge > tol.GRAD_TOL) & ~flagged).sum())
+        for b in np.nonzero((ge > tol.GRAD_TOL) & ~flagged)[0]:
+            # the gradient feels a rotated contact normal before the energy does: same evidence as for the energies
+            if tol.normal_unstable(H(eng.cpts)[b], fv):
+                grad_events += 1
+            else:
+                grad_unexplained.append((t, int(b), float(ge[b])))
         grad_errs.append(ge[~flagged & (ge <= tol.GRAD_TOL)])
         p_acc = np.exp(np.minimum((orc_energy_before(out) - want) / out["temperature"].numpy(), 0.0))
         got, exp = H(eng.accept).astype(bool), out["accept"].numpy()
@@ -205,10 +210,15 @@ def check_trajectory(lib, be, T=500, B=6, n_pts=128, n_c=12, seed=21, tie=2e-3, 
     ge = np.concatenate(grad_errs) if grad_errs else np.zeros(1)
     tol.MEASURED.append((f"{hand} n_c={n_c} {T}-step trajectory", "grad", float(ge.max()), float(np.median(ge))))
     print(f"[traj] {hand} n_c={n_c}: {T * B} candidate-steps, {len(outliers)} energy conditioning events, "
-          f"{grad_events} gradient-only events; elsewhere energy error max {worst:.2e}, gradient error max {ge.max():.2e} "
+          f"{grad_events} gradient-only events with a nearest-face tie at a contact, {len(grad_unexplained)} without that "
+          f"evidence {grad_unexplained[:5]}; elsewhere energy error max {worst:.2e}, gradient error max {ge.max():.2e} "
           f"median {np.median(ge):.2e}")
     assert len(outliers) <= max(1, T * B // 100), outliers
-    assert grad_events <= max(1, T * B // 100), f"{grad_events} candidate-steps with a gradient error above {tol.GRAD_TOL}"
+    # gradients: every excess needs the tie evidence (<= 5 % of candidate-steps on these coarse 400-face meshes, where a
+    # contact 3 cm from the surface sits near a Voronoi boundary of the faces far more often than on a 10k-face mesh:
+    # 0-1 of 16 rows in the benched-shape checks); unexplained excesses: at most 0.2 %
+    assert grad_events <= max(1, T * B // 20), f"{grad_events} candidate-steps with a gradient error above {tol.GRAD_TOL}"
+    assert len(grad_unexplained) <= max(1, T * B // 500), grad_unexplained
     assert all(o[4] < o[5] and abs(o[3]["E_pen"]) < 1e-5 for o in outliers), outliers
     return n_acc, n_tie, worst
 
@@ -228,6 +238,25 @@ def link_grid(lib, hand, link):
     return geom, dim, bits
 
 
+def link_planes(lib, hand, link):
+    n = lib.gqp_hand_link_planes(hand, link, None, 0, None)
+    assert n >= 0, lib.gqp_last_error()
+    planes, slab = np.zeros((max(n, 1), 4), np.float32), np.zeros(2, np.float32)
+    assert lib.gqp_hand_link_planes(hand, link, planes.ctypes.data, n, slab.ctypes.data) == n
+    return planes[:n], slab
+
+
+def in_tie_slab(q, planes, slab, lo, hi):
+    """csrc/gqp_pen.cu:pen_in_tie_slab for points (rad = 0), in fp32 like the kernel"""
+    q = np.asarray(q, np.float32)
+    if len(planes) == 0:
+        return np.zeros(len(q), bool)
+    ctr, half = np.float32(0.5) * (lo + hi), np.float32(0.5) * (hi - lo)
+    D = np.sqrt(((q - ctr) ** 2).sum(1, dtype=np.float32)) + np.sqrt((half ** 2).sum(dtype=np.float32))
+    hgt = q @ planes[:, :3].T - planes[:, 3]
+    return ((hgt <= slab[1] * D[:, None]) & (hgt >= -slab[0] * D[:, None])).any(1)
+
+
 def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0, max_cells=None):
     """Direct test of the culling proof that carries > 98 % of H4's work (csrc/gqp_bvh.cpp: gqp_mesh_is_nice +
     gqp_outside_grid_build): for every link with an outside grid, for every SET cell, points drawn inside the cell
@@ -240,6 +269,7 @@ def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0
     rng = np.random.default_rng(seed)
     L = len(pack["mesh_frame"])
     n_links = n_cells = n_points = 0
+    slab_seen = [0, 0]
     for l in range(L):
         f0, f1 = int(pack["face_offset"][l]), int(pack["face_offset"][l + 1])
         geom, dim, bits = link_grid(lib, hand, l)
@@ -274,6 +304,15 @@ def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0
         near = (ctr + (rng.random((n_far, 3)) * 2 - 1) * half * 1.3).astype(np.float32)  # just outside the box faces
         near = near[~((near >= lo) & (near <= hi)).all(1)]
         q = np.concatenate([pts, far, near])
+        # the tie slabs behind the planes of faces at right-angle creases are never culled (gqp_mesh_tie_planes): there
+        # the reference's fp32 first-minimum rule CAN say -1 for an outside point; count those as evidence
+        planes, slab = link_planes(lib, hand, l)
+        slab_pts = in_tie_slab(q, planes, slab, lo, hi)
+        n_slab_neg = 0
+        if slab_pts.any():
+            n_slab_neg = int((sign_fn(q[slab_pts], fv) != 1).sum())
+        slab_seen[0] += int(slab_pts.sum()); slab_seen[1] += n_slab_neg
+        q = q[~slab_pts]
         sg = sign_fn(q, fv)
         bad = np.nonzero(sg != 1)[0]
         assert len(bad) == 0, (f"{hand_name} link {l}: {len(bad)} of {len(q)} points in culled regions get sign -1 from "
@@ -282,7 +321,8 @@ def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0
         n_cells += len(idx)
         n_points += len(q)
     lib.gqp_hand_destroy(hand)
-    print(f"[culling proof] {hand_name}: {n_links} links with a grid, {n_cells} set cells, {n_points} points, all +1")
+    print(f"[culling proof] {hand_name}: {n_links} links with a grid, {n_cells} set cells, {n_points} points, all +1; "
+          f"{slab_seen[0]} further points fell into never-culled tie slabs, {slab_seen[1]} of them with sign -1")
     return n_links, n_cells, n_points
 
 
@@ -328,6 +368,12 @@ def check_benched_state(lib, be, name="config2", iters=(0, 50, 500), per_object=
         lab = f"{name} Bt={Bt} iteration {n}"
         np.testing.assert_array_equal(H(eng.idx_new)[sub], out["idx_prop"].numpy(), err_msg=lab)
         np.testing.assert_allclose(H(eng.pose_new)[sub], out["proposal"].numpy(), rtol=1e-5, atol=1e-5, err_msg=lab)
+        e_probe = np.abs(H(eng.new_energy)[sub] - out["new_energy"].numpy()) / np.abs(out["new_energy"].numpy())
+        for r in np.nonzero(e_probe > tol.ENERGY_RTOL)[0]:  # diagnostics before the assertion
+            print(f"[benched] {lab}: row {r} (candidate {sub[r]}) energy {H(eng.new_energy)[sub[r]]:.6g} vs oracle "
+                  f"{out['new_energy'][r].item():.6g}; per term (engine, oracle): " +
+                  ", ".join(f"{t}=({H(eng.losses_new)[k][sub[r]]:.6g}, {out['new_losses'][t][r].item():.6g})"
+                            for k, t in enumerate(engine.TERMS)))
         e_rel = tol.assert_energy(H(eng.new_energy)[sub], out["new_energy"].numpy(), lab + " new energy", excuse=ex,
                                   max_excused=max(1, len(sub) // 8))
         excused = set(int(r) for r in np.nonzero(e_rel > tol.ENERGY_RTOL)[0])

@@ -87,8 +87,8 @@ def test_sub_batch_check_with_batch_wide_statistics(emu):
     wl.CONFIGS["tiny"] = ("allegro", ["sphere", "box"], 300, 4, 12)
     real = wl.build
     try:
-        wl.build = lambda name, **kw: real(name, n_surface=64, **{k: v for k, v in kw.items() if v is not None})
-        rep = cases.check_benched_state(emu, engine.NumpyBackend(), "tiny", iters=(0, 2), per_object=2)
+        wl.build = lambda name, **kw: real(name, n_surface=48, **{k: v for k, v in kw.items() if v is not None})
+        rep = cases.check_benched_state(emu, engine.NumpyBackend(), "tiny", iters=(0, 1), per_object=1)
     finally:
         wl.build = real
         del wl.CONFIGS["tiny"]

@@ -28,11 +28,13 @@ def normal_unstable(cpts_row, face_verts, jump=1e-5):
     from oracle import sdf as osdf
     p = np.asarray(cpts_row, np.float32).reshape(-1, 3)
     base = None
-    for k in range(7):
+    # the fp32 and fp64 forward kinematics differ by a few ulps at the contact: probe 1 and 4 ulps along every axis
+    for k in range(13):
         q = p.copy()
         if k:
-            ax, sgn = (k - 1) % 3, (1.0 if k <= 3 else -1.0)
-            q[:, ax] = np.nextafter(q[:, ax], np.float32(sgn * np.inf))
+            ax, sgn, n_ulp = (k - 1) % 3, (1.0 if (k - 1) % 6 < 3 else -1.0), (1 if k <= 6 else 4)
+            for _ in range(n_ulp):
+                q[:, ax] = np.nextafter(q[:, ax], np.float32(sgn * np.inf))
         _, sg, nr, _ = osdf.compute_sdf_port(q, face_verts)
         n = nr * sg[:, None]
         if base is None:
