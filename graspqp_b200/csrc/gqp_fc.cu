@@ -10,7 +10,7 @@
 // diagonal, i.e. by the Woodbury identity  dx = M^-1 r - M^-1 F'(I6 + F M^-1 F')^-1 F M^-1 r : one 6x6 SPD system per
 // solve.  Every lane owns <= 2 variables (its F columns, x, slacks, duals: registers); the 6x6 matrix is reduced across
 // the warp through shared memory and factorised redundantly by every lane.  All QP arithmetic is fp64 (B200 runs fp64
-// at half the fp32 rate; the stage is < 1 % of a grasp-step), so the iterates are the exact-arithmetic iterates of
+// at half the fp32 rate; the stage is ~25 % of an iteration at config 2), so the iterates are the exact-arithmetic iterates of
 // qpth's algorithm rather than one fp32 realisation of them.
 // Implicit differentiation (qpth QPFunction.backward): one more solve with d = clamp(lam)/clamp(slack).
 #include "gqp_common.cuh"
@@ -543,6 +543,20 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
 #pragma unroll
         for (int i = 0; i < 6; ++i) logdet -= log(Lg[tri_ix(i, i)]);  // diagonal is stored inverted
         const bool rank_ok = logdet == logdet && logdet > -1e300;  // NaN / -inf when F F' is numerically singular
+        // Gradient of the svd term: d prod(sigma)^(1/6) / dF = svd/6 * (F F')^-1 F grows like 1/sigma_min.  When F is rank
+        // deficient (sigma_min / sigma_max below fp32 resolution: all contacts on one line, duplicated contact indices at
+        // n_c = 4) the reference's own fp32 value of it is rounding noise of size ~1e3..1e5 in an arbitrary direction, and
+        // the rounding-free value is ~1e14+: it overflowed fp32 here, and ONE inf/NaN gradient row poisons (g^2).mean(0)
+        // of the whole batch (optimizer.py:231-236 turns the NaN into ema = 0, i.e. a 1e6 x step for every candidate —
+        // seen at config 4, 131072 Panda candidates, within 50 iterations).  The term's gradient is dropped there.
+        double rmin = 1e300, rmax = 0.0;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const double ri = 1.0 / Lg[tri_ix(i, i)];
+            rmin = fmin(rmin, ri);
+            rmax = fmax(rmax, ri);
+        }
+        const bool svd_grad_ok = rank_ok && rmin > 1e-7 * rmax;
         const double svd = rank_ok ? exp(logdet / 6.0) : 0.0;
         const double ex = exp(-P.svd_gain * svd);
         const double Efc = P.values_gain * (value + P.values_offset) * ex;
@@ -599,11 +613,11 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 double pin[6];  // (F F')^-1 F_j
 #pragma unroll
                 for (int i = 0; i < 6; ++i) pin[i] = F[v][i];
-                if (rank_ok) chol6_solve(Lg, pin);
+                if (svd_grad_ok) chol6_solve(Lg, pin);
 #pragma unroll
                 for (int i = 0; i < 6; ++i)
                     gF[v][i] = (gv * Fx[i] + fdx[i]) * bx[v] + Fx[i] * bd.dx[v] +
-                               (rank_ok ? gs * (svd / 6.0) * pin[i] : 0.0);
+                               (svd_grad_ok ? gs * (svd / 6.0) * pin[i] : 0.0);
             }
         }
         // ---- per-contact sums: force solution (span.py:414) and d/d(contact point) through tau = tw (r x f) ----

@@ -20,7 +20,7 @@ def grad_error(got, want):
     return np.abs(got - want) / scale
 
 
-def normal_unstable(cpts_row, face_verts, jump=1e-5):
+def normal_unstable(cpts_row, face_verts, jump=2e-6):
     """True if some contact of this candidate sits at a nearest-face tie of the reference's SDF arithmetic: moving the
     fp32 contact point by ONE ulp changes the winning face's unit(p - c) by more than `jump`.  There the object normal
     (object_model.py:246) is not a function of the pose that fp32 and fp64 evaluations can agree on — a conditioning
