@@ -393,29 +393,30 @@ def run_b200(args):
     # ---- sustained block: the fit carried on for --sustain iterations with the reference's outlier resets ----
     sustained = None
     if world == 1 and args.sustain > 0:
-        from graspqp_b200 import synth
-        verts = [fv.reshape(-1, 3) for fv in w["face_verts"]]
+        from graspqp_b200 import initializations
+        eng.enable_device_init([initializations.convex_hull(fv.reshape(-1, 3)) for fv in w["face_verts"]])
         cnt_off = int(lib.gqp_hand_distance_counter_offset(O, B, eng.n_pts, 0, be.ptr(eng.pen_scratch)))
         i_pen = engine.TERMS.index("E_pen")
-        win, windows, n_resets, n_reset_rows = 250, [], 0, 0
+        win, windows, n_resets, n_reset_rows, reset_ms = 250, [], 0, 0, []
         n_total = args.sustain
         evs2 = []
         for it in range(1, n_total + 1):
-            reset = None
             # scripts/fit.py:408: every reset_epochs iterations, not within the last 2*reset_epochs of the fit
-            if args.reset_epochs and eng.iteration + 1 >= args.reset_epochs and (eng.iteration + 1) % args.reset_epochs == 0 \
-                    and (eng.iteration + 1) < n_total - 2 * args.reset_epochs:
-                pi, ii = synth.random_grasp_init(w["pack"], verts, B, n_c, 1000 + eng.iteration)  # host init (row f1)
-                reset = (be.from_host(pi, np.float32), be.from_host(ii.astype(np.int32), np.int32))
+            reset = bool(args.reset_epochs) and (eng.iteration + 1) % args.reset_epochs == 0 \
+                and (eng.iteration + 1) < n_total - 2 * args.reset_epochs
             flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            eng.step(reset_init=reset, z_score_threshold=1.0)
+            if reset:  # initialize_convex_hull on the device (3 launches) + gqp_mala_reset, INSIDE the timed step
+                eng.reset_step(z_score_threshold=1.0)
+            else:
+                eng.step()
             e1.record()
             evs2.append((e0, e1))
-            if reset is not None:
+            if reset:
                 n_resets += 1
                 n_reset_rows += int(eng.reset_count.item())
+                reset_ms.append(e0.elapsed_time(e1))
             if it % win == 0 or it == n_total:
                 torch.cuda.synchronize()
                 ms = [a.elapsed_time(b) for a, b in evs2]
@@ -431,7 +432,8 @@ def run_b200(args):
         sustained = {"iterations": n_total, "value": Bt * n_total / (all_ms * 1e-3), "unit": UNIT,
                      "ms_per_step": all_ms / n_total, "windows": windows, "resets": n_resets,
                      "reset_rows": n_reset_rows, "reset_epochs": args.reset_epochs,
-                     "reset_init": "host (synth.random_grasp_init) uploaded outside the timed step; gqp_mala_reset inside",
+                     "reset_init": "device (gqp_init_convex_hull: hull pool, FPS, poses) + gqp_mala_reset, inside the timed step",
+                     "reset_step_ms": [round(v, 3) for v in reset_ms],
                      "value_window": f"the headline `value` times iterations {iteration_of_value - K + 1}-"
                                      f"{iteration_of_value} after init (K steps after W warm-up)",
                      "stage_ms_at_end": {k: round(v, 4) for k, v in time_stages().items()}}

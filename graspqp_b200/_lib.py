@@ -29,6 +29,12 @@ class GqpMalaParams(ctypes.Structure):
                                                                         "clip_grad")]
 
 
+class GqpInitParams(ctypes.Structure):
+    _fields_ = [(n, c_float) for n in ("distance_lower", "distance_upper", "rotate_lower", "rotate_upper", "pitch_lower",
+                                       "pitch_upper", "tilt_lower", "tilt_upper", "jitter_strength", "inflate")] + [
+        ("pool_factor", c_int32), ("forward_axis", c_float * 3), ("up_axis", c_float * 3), ("default_state", c_float * 32)]
+
+
 P = c_void_p  # device / host pointers are passed as integers (tensor.data_ptr())
 
 # name -> (restype, argtypes); every symbol include/graspqp_b200.h declares
@@ -72,6 +78,11 @@ SIGNATURES = {
     "gqp_mala_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, P, P, c_uint64, c_uint64,
                                 P, P, P, P, P, P, P, P, P, P, P, P, P]),
     "gqp_mala_reset": (c_int, [c_int, c_int, c_int, P, c_float, P, P, P, P, P, P, P, P, P, P, P]),
+    "gqp_init_create": (c_int, [P, P, c_int, POINTER(c_void_p)]),
+    "gqp_init_destroy": (None, [c_void_p]),
+    "gqp_init_scratch_bytes": (c_uint64, [c_int, c_int, c_int]),
+    "gqp_init_convex_hull": (c_int, [c_void_p, c_void_p, POINTER(GqpInitParams), c_int, c_int, P, P, P, c_uint64,
+                                     c_uint64, P, P, P, P, P]),
     "gqp_memset_zero": (c_int, [P, c_uint64, P]),
     "gqp_fma_peak_probe": (c_int, [c_int, P, POINTER(c_uint64), P]),
     "gqp_dfma_peak_probe": (c_int, [c_int, P, POINTER(c_uint64), P]),

@@ -321,6 +321,30 @@ class FitEngine:
             self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
         self._accept(self.z, None, u_accept)
 
+    # ---- (f1) outlier resets with the re-initialisation on the device --------------------------------------------------
+    def enable_device_init(self, hull_tris_list, **params):
+        """hull_tris_list: outward-oriented convex-hull triangles per object (initializations.convex_hull)."""
+        from . import initializations
+        self.init = initializations.DeviceInit(self.lib, self.be, self.pack, hull_tris_list, self.batch_each, self.n_c,
+                                               **params)
+        self.pose_init = self.be.empty((self.Bt, self.D), np.float32)
+        self.idx_init = self.be.empty((self.Bt, self.n_c), np.int32)
+
+    def reset_step(self, z_score_threshold=1.0, u_pool=None, u_pose=None, idx_rand_init=None, **step_noise):
+        """A reset iteration (fit.py:408-422): initialize_convex_hull for every row on the device, then step() with it."""
+        self.init.run(self.hand, self.pose_init, self.idx_init, u_pool, u_pose, idx_rand_init, seed=self.seed)
+        self.step(reset_init=(self.pose_init, self.idx_init), z_score_threshold=z_score_threshold, **step_noise)
+
+    def fit(self, n_iter, reset_epochs=600, z_score_threshold=1.0):
+        """scripts/fit.py:399-458 for n_iter iterations, counted from this engine's first one: resets every reset_epochs
+        iterations except in the last 2*reset_epochs (fit.py:408)."""
+        for step in range(self.iteration + 1, n_iter + 1):
+            if reset_epochs and getattr(self, "init", None) is not None and step % reset_epochs == 0 \
+                    and step < n_iter - 2 * reset_epochs:
+                self.reset_step(z_score_threshold)
+            else:
+                self.step()
+
     _STATE = ("pose", "idx", "grad", "ema", "step_count", "energy", "losses")
 
     def snapshot(self):
@@ -366,6 +390,9 @@ class FitEngine:
 
     def close(self):
         lib = self.lib
+        if getattr(self, "init", None) is not None:
+            self.init.close()
+            self.init = None
         if getattr(self, "objset", None):
             lib.gqp_objset_destroy(self.objset)
             self.objset = None

@@ -258,6 +258,35 @@ int gqp_mala_reset(int Bt, int D, int n_c, const float *z, float z_threshold, co
                    const float *pose_init, const int32_t *idx_init, float *pose_new, int32_t *idx_new,
                    int32_t *idx_eval, int32_t *step, float *ema, uint8_t *mask_out, int32_t *count_out, void *stream);
 
+/* ---- (f1) initialize_convex_hull on the device (core/initializations.py:15-193; the reference runs it on the host with
+ * trimesh + pytorch3d for ALL objects at every reset, scripts/fit.py:421) --------------------------------------------------
+ * gqp_init_create: hull_tris_host (H_total,3,3) outward-oriented convex-hull triangles of the objects, object o owns faces
+ *   [hull_offset_host[o], hull_offset_host[o+1]) (the hull itself is setup-time host work, as trimesh's .convex_hull).
+ * gqp_init_convex_hull: for every object pool_factor*batch_each area-uniform hull samples pushed `inflate` along their
+ *   face normal, farthest point sampling of batch_each of them (start index 0), then per candidate the pose
+ *   [p - distance*n, first two columns of look_at(p, p+n) @ euler_rxyz(tilt, pitch, rotate), truncated-normal joints]
+ *   and n_c contact indices.  Noise: u_pool (n_obj, pool_factor*batch_each, 3), u_pose (Bt, 4+n_dofs) uniforms in [0,1)
+ *   (distance, rotate, pitch, tilt, joints) and idx_rand (Bt,n_c) injected, or NULL = Philox4x32-10 keyed (seed, counter).
+ *   pose_init (Bt, 9+n_dofs), idx_init (Bt,n_c) are what gqp_mala_reset consumes; picked_out (Bt) int32, may be NULL,
+ *   receives the pool index picked for every candidate.  scratch: gqp_init_scratch_bytes bytes, 16-byte aligned.
+ *   Not restated: trimesh.sample.sample_surface_even's removal of samples closer than a radius before the FPS (the FPS
+ *   does the spreading). */
+typedef struct GqpInit GqpInit;
+typedef struct GqpInitParams {
+    float distance_lower, distance_upper, rotate_lower, rotate_upper, pitch_lower, pitch_upper, tilt_lower, tilt_upper;
+    float jitter_strength, inflate;
+    int32_t pool_factor;
+    float forward_axis[3], up_axis[3]; /* HandModel.forward_axis / up_axis (hand_model.py:459-468) */
+    float default_state[32];           /* HandModel.default_state (n_dofs entries) */
+} GqpInitParams;
+int gqp_init_create(const float *hull_tris_host, const int32_t *hull_offset_host, int n_obj, GqpInit **out);
+void gqp_init_destroy(GqpInit *init);
+uint64_t gqp_init_scratch_bytes(int n_obj, int batch_each, int pool_factor);
+int gqp_init_convex_hull(const GqpInit *init, const GqpHand *h, const GqpInitParams *p_host, int batch_each, int n_c,
+                         const float *u_pool, const float *u_pose, const int32_t *idx_rand, uint64_t seed,
+                         uint64_t counter, void *scratch, float *pose_init, int32_t *idx_init, int32_t *picked_out,
+                         void *stream);
+
 /* cudaMemsetAsync(ptr, 0, bytes) on the stream: the per-step reset of grad_link_tf. */
 int gqp_memset_zero(void *ptr, uint64_t bytes, void *stream);
 

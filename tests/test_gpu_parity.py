@@ -133,6 +133,14 @@ def test_golden_reset_iterations(gpu):
     assert gc.check_fit_reset(*gpu) == 4
 
 
+@pytest.mark.parametrize("hand,B", [("allegro", 256), ("shadow_hand", 128), ("robotiq2", 64)])
+def test_device_init_vs_oracle(gpu, hand, B):
+    """(f1) initialize_convex_hull on the device at the reference's pool factor (100 x B samples per object): FPS picks
+    bit-exact, poses within 2e-6 of the restatement under injected noise"""
+    import test_init
+    test_init.check_device_init(*gpu, hand=hand, B=B, pool_factor=100)
+
+
 def test_trajectory_500_steps_teacher_forced(gpu):
     n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=500)
     print(f"500-step trajectory: {n_acc} accepted, {n_tie} borderline accept mismatches, worst energy error {worst:.2e}")
