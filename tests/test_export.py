@@ -1,0 +1,99 @@
+"""(f2) export path (graspqp_b200/export.py) vs restatements of scripts/fit.py:224-300 and
+HandModel.get_req_joint_velocities (hand_model.py:1155-1218), and the contact Jacobian against pytorch_kinematics' own
+vectorised Jacobian (pk/chain.py:197-252) run in this container."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from graspqp_b200 import engine, export, hand_pack, synth
+from oracle.hand import HandOracle
+
+
+def _engine(emu, hand="allegro", B=3, n_c=4, seed=2, be=None):
+    pack = hand_pack.load_pack(hand)
+    v, f = synth.make_mesh("sphere", 200, seed)
+    fv, sp = synth.face_vertices(v, f), synth.sample_surface(v, f, 32, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.8
+    return pack, engine.FitEngine(emu, be or engine.NumpyBackend(), pack, [fv], sp[None], B, pose, idx.astype(np.int32)), fv
+
+
+def test_quaternion_matches_scipy():
+    from scipy.spatial.transform import Rotation
+    R = Rotation.random(200, random_state=0)
+    q = export.rotmat_to_quat_wxyz(torch.tensor(R.as_matrix(), dtype=torch.float64)).numpy()
+    want = R.as_quat()[:, [3, 0, 1, 2]]
+    want = want * np.sign(want[:, :1])
+    np.testing.assert_allclose(q, want, atol=1e-12)
+
+
+@pytest.mark.parametrize("hand", ["allegro", "panda"])
+def test_contact_jacobian_and_joint_velocities(emu, hand):
+    check_jacobian_and_velocities(emu, None, hand)
+
+
+def check_jacobian_and_velocities(lib, be, hand, B=3, n_c=4):
+    pack, eng, fv = _engine(lib, hand, B=B, n_c=n_c, be=be)
+    H = eng.be.to_host
+    ex = export.Exporter(eng)
+    J = H(ex.contact_jacobian(eng.idx))  # (Bt, n_c, 3, dof), world frame
+    # oracle: autograd through the restated HandModel (pk FK incl. the +-0.01 rad perturbation)
+    o = HandOracle(pack, torch.float64)
+    hp = torch.tensor(H(eng.pose), dtype=torch.float64)
+    idx = torch.tensor(H(eng.idx)).long()
+
+    def cpts(theta):
+        o.set_parameters(torch.cat([hp[:, :9], theta], 1), idx)
+        return o.contact_points
+    Jw = torch.autograd.functional.jacobian(lambda th: cpts(th).sum(0), hp[:, 9:].clone())  # (n_c,3,Bt,dof)
+    Jw = Jw.permute(2, 0, 1, 3).numpy()
+    np.testing.assert_allclose(J, Jw, atol=2e-6)
+    # get_req_joint_velocities restated in the reference's own frame conventions (hand frame + rotated directions)
+    Rg = o.global_rotation.detach()
+    v = torch.tensor(np.random.default_rng(0).normal(size=(eng.Bt, eng.n_c, 3)))
+    Jh = (Rg.mT.unsqueeze(1) @ torch.tensor(Jw))                       # hand-frame Jacobian, as hand_model.py:1190-1196
+    vh = (Rg.mT.unsqueeze(1) @ v.unsqueeze(-1)).squeeze(-1)            # :1164
+    want = (export.pinv(Jh.flatten(1, 2)) @ vh.flatten(1, 2).unsqueeze(-1)).squeeze(-1)
+    theta, res, ee = ex.get_req_joint_velocities(eng.be.from_host(v.float().numpy(), np.float32), eng.idx, return_ee_vel=True)
+    np.testing.assert_allclose(theta.cpu().numpy(), want.numpy(), rtol=2e-3, atol=2e-4 * np.abs(want.numpy()).max())
+    eng.close()
+
+
+def test_jacobian_linear_part_is_pk_jacobian():
+    """pk's Chain.jacobian (vectorised, what HandModel.jacobian calls) == d(link position)/d(theta): the premise of
+    building the contact Jacobian from the FK backward kernels"""
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("reference only in the build container")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import ref_harness as rh
+    pack = hand_pack.load_pack("allegro")
+    chain, frames = rh.pk_chain_from_pack(pack, torch.float32)
+    th = torch.tensor(np.random.default_rng(0).uniform(0.1, 0.6, (2, 16)), dtype=torch.float32)
+    J = chain.jacobian(th)
+
+    def pos(t):
+        res = chain.forward_kinematics(t)
+        return torch.stack([res[f"l{i}"].get_matrix()[:, :3, 3].expand(2, 3) for i in range(len(frames))], 1)
+    Jt = torch.autograd.functional.jacobian(lambda t: pos(t).sum(0), th).permute(2, 0, 1, 3)
+    np.testing.assert_allclose(J[:, :, :3, :].numpy(), Jt.numpy(), atol=1e-6)
+
+
+def test_export_writes_the_reference_dict(emu, tmp_path):
+    pack, eng, fv = _engine(emu, "allegro", B=2, n_c=4)
+    ex = export.Exporter(eng)
+    paths = ex.export_poses(str(tmp_path), ["obj_a"], "allegro", suffix="_0")
+    assert paths[0].endswith(os.path.join("obj_a", "grasp_predictions", "allegro", "4_contacts", "graspqp", "default",
+                                          "obj_a_0.dexgrasp.pt"))
+    d = torch.load(paths[0])
+    assert set(d) == {"values", "parameters", "grasp_velocities", "full_grasp_velocities", "grasp_velocities_off",
+                      "contact_idx", "grasp_type", "contact_links"}  # fit.py:253-297
+    names = [str(s) for s in pack["joint_names"]]
+    assert set(d["parameters"]) == set(names) | {"root_pose"} and d["parameters"]["root_pose"].shape == (2, 7)
+    assert set(d["grasp_velocities"]) == set(names) and d["contact_idx"].shape == (2, 4)
+    np.testing.assert_allclose(d["parameters"]["root_pose"][:, :3].numpy(), eng.pose[:, :3])
+    np.testing.assert_allclose(d["parameters"]["root_pose"][:, 3:].norm(dim=1).numpy(), 1.0, atol=1e-6)
+    assert all(torch.isfinite(v).all() for v in d["full_grasp_velocities"].values())
+    eng.close()

@@ -141,6 +141,14 @@ def test_device_init_vs_oracle(gpu, hand, B):
     test_init.check_device_init(*gpu, hand=hand, B=B, pool_factor=100)
 
 
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2"])
+def test_export_jacobian_and_joint_velocities(gpu, hand):
+    """(f2) contact Jacobian from the FK backward kernels == autograd through the restated HandModel; joint velocities ==
+    the reference's damped pseudo-inverse formula in its own (hand) frame"""
+    import test_export
+    test_export.check_jacobian_and_velocities(*gpu, hand, B=16, n_c=12 if hand in ("allegro", "shadow_hand") else 4)
+
+
 def test_trajectory_500_steps_teacher_forced(gpu):
     n_acc, n_tie, worst = cases.check_trajectory(*gpu, T=500)
     print(f"500-step trajectory: {n_acc} accepted, {n_tie} borderline accept mismatches, worst energy error {worst:.2e}")
