@@ -58,6 +58,8 @@ SIGNATURES = {
     "gqp_fk_backward": (c_int, [c_void_p, P, P, P, c_int, P, P]),
     "gqp_contacts_forward": (c_int, [c_void_p, P, P, c_int, c_int, P, P, P]),
     "gqp_contacts_backward": (c_int, [c_void_p, P, P, P, c_int, c_int, P, P]),
+    "gqp_fk_contacts_forward": (c_int, [c_void_p, P, P, c_int, c_int, P, P, P, P]),
+    "gqp_fk_contacts_backward": (c_int, [c_void_p, P, P, P, P, P, P, c_int, c_int, P, P]),
     "gqp_hand_distance": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, c_float, P, P]),
     "gqp_hand_distance_full": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_hand_distance_backward": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),

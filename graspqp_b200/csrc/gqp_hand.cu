@@ -7,6 +7,8 @@
 // links contiguous (the consumers assign one candidate to a warp or block).  A thread owns a candidate: the chain is
 // short (19 frames for Allegro), the tables sit in shared memory, per-frame transforms in thread-local arrays.
 // FK is < 0.1 % of a grasp-step's work; it is bound by nothing but launch latency.
+#include <algorithm>
+
 #include "gqp_common.cuh"
 #include "gqp_hand.h"
 #include "graspqp_b200.h"
@@ -275,6 +277,239 @@ __global__ void contacts_backward_kernel(const float *__restrict__ cand, const f
     }
 }
 
+// ---- warp per candidate (north_star stage 1): lane = frame of the kinematic tree ------------------------------------------
+// The thread-per-candidate kernels above walk 19-27 frames serially with ~2 KB of thread-local transforms: 0.03 + 0.05 ms
+// of pure latency on the critical chain at 8192 candidates, on 64 of 148 SMs.  Here a warp owns a candidate: every lane
+// builds its frame's local transform, the tree is swept level by level (a lane multiplies its parent's world transform,
+// read from shared memory, by its own local one), and the contact gather / scatter rides in the same launch.  The
+// backward sweeps the levels upwards; a parent sums its children's wrenches in child order and every reduction has a
+// fixed order, so the result is run-to-run reproducible (no atomics).  Requires n_frames <= 32 and n_links <= 32.
+#define FKW_WARPS 4
+struct FkwLane {
+    T34 A;    // world transform of the frame before its link offset
+    T34 Bj;   // world joint frame A[parent] * joff (axis / origin of the joint for the backward)
+    GramSchmidt gs;
+    T34 G;
+};
+// the sweep shared by both kernels; sA: this warp's 32 x 12 floats
+template <bool WANT_JOINT_FRAME>
+__device__ __forceinline__ void fkw_sweep(const GqpHandDev &H, const float *prow, int f, bool active, float *sA,
+                                          FkwLane &o, float *dq) {
+    float p9[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) p9[i] = prow[i];
+    o.G = global_tf(p9, o.gs);
+    float q[1 + GQP_MAX_MLP_OUT];
+    const float *theta = joint_vector(H, prow + 9, q, dq);
+    T34 joff = t34_identity(), Lc = t34_identity();
+    if (active) {
+        joff = t34_load(H.frame_joff[f]);
+        Lc = t34_mul(joff, joint_tf(H, f, theta));
+    }
+    const int depth = active ? H.frame_depth[f] : -1, par = active ? H.frame_parent[f] : -1;
+    for (int d = 0; d <= H.max_depth; ++d) {
+        if (depth == d) {
+            T34 Ap = o.G;
+            if (par >= 0) Ap = t34_load(sA + 12 * par);
+            o.A = t34_mul(Ap, Lc);
+            if (WANT_JOINT_FRAME) o.Bj = t34_mul(Ap, joff);
+#pragma unroll
+            for (int i = 0; i < 12; ++i) sA[12 * f + i] = o.A.m[i];
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(FKW_WARPS * 32)
+fk_contacts_forward_warp_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict__ cand,
+                                const float *__restrict__ cand_normal, const int32_t *__restrict__ cand_link,
+                                const float *__restrict__ pose, const int32_t *__restrict__ idx, int Bt, int n_c,
+                                float *__restrict__ link_tf, float *__restrict__ cpts, float *__restrict__ cnrm) {
+    __shared__ float sA[FKW_WARPS][32 * 12];
+    __shared__ float sW[FKW_WARPS][GQP_MAX_LINKS * 12];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x * FKW_WARPS + warp;
+    if (b >= Bt) return;
+    const GqpHandDev &H = *hand;
+    const int D = 9 + H.n_dofs, L = H.n_links;
+    const bool active = lane < H.n_frames;
+    FkwLane st;
+    fkw_sweep<false>(H, pose + (size_t)b * D, lane, active, sA[warp], st, nullptr);
+    if (active && H.frame_link[lane] >= 0) {
+        const T34 W = t34_mul(st.A, t34_load(H.frame_loff[lane]));
+        float *o = sW[warp] + 12 * H.frame_link[lane];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) o[i] = W.m[i];
+    }
+    __syncwarp();
+    for (int i = lane; i < L * 12; i += 32) link_tf[(size_t)b * L * 12 + i] = sW[warp][i];
+    if (idx)
+        for (int c = lane; c < n_c; c += 32) {
+            const size_t i = (size_t)b * n_c + c;
+            int k = idx[i];
+            k = k < 0 ? 0 : (k >= H.n_cand ? H.n_cand - 1 : k);
+            const T34 W = t34_load(sW[warp] + 12 * cand_link[k]);
+            st3(cpts + 3 * i, t34_point(W, ld3(cand + 3 * k)));
+            st3(cnrm + 3 * i, t34_vec(W, ld3(cand_normal + 3 * k)));
+        }
+}
+
+__global__ void __launch_bounds__(FKW_WARPS * 32)
+fk_contacts_backward_warp_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict__ cand,
+                                 const float *__restrict__ cand_normal, const int32_t *__restrict__ cand_link,
+                                 const float *__restrict__ pose, const int32_t *__restrict__ idx,
+                                 const float *__restrict__ grad_cpts, const float *__restrict__ grad_cnrm,
+                                 const float *__restrict__ grad_link_tf, const float *__restrict__ grad_pose_extra,
+                                 int Bt, int n_c, float *__restrict__ grad_pose) {
+    __shared__ float sA[FKW_WARPS][32 * 12];
+    __shared__ float sG[FKW_WARPS][GQP_MAX_LINKS * 12];  // d loss / d link_tf incl. the contacts
+    __shared__ float sMF[FKW_WARPS][32 * 6];             // wrench of every frame's subtree
+    __shared__ float sJ[FKW_WARPS][32];                  // joint-gradient contribution of every frame
+    __shared__ int sCk[FKW_WARPS][32];                   // contact -> candidate id / link (n_c <= 32 per round)
+    __shared__ int sCl[FKW_WARPS][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x * FKW_WARPS + warp;
+    if (b >= Bt) return;
+    const GqpHandDev &H = *hand;
+    const int D = 9 + H.n_dofs, L = H.n_links, f = lane;
+    const bool active = lane < H.n_frames;
+    const float *prow = pose + (size_t)b * D;
+    FkwLane st;
+    float dq[1 + GQP_MAX_MLP_OUT];
+    fkw_sweep<true>(H, prow, lane, active, sA[warp], st, dq);
+    // ---- d loss / d link_tf of link `lane`: what the other stages left in global memory + this candidate's contacts, in
+    //      contact order (contacts_backward_kernel's formula)
+    float g[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) g[i] = (lane < L && grad_link_tf) ? grad_link_tf[((size_t)b * L + lane) * 12 + i] : 0.f;
+    for (int c0 = 0; idx && c0 < n_c; c0 += 32) {
+        const int c = c0 + lane;
+        if (c < n_c) {
+            int k = idx[(size_t)b * n_c + c];
+            k = k < 0 ? 0 : (k >= H.n_cand ? H.n_cand - 1 : k);
+            sCk[warp][lane] = k;
+            sCl[warp][lane] = cand_link[k];
+        }
+        __syncwarp();
+        const int nc = min(32, n_c - c0);
+        for (int j = 0; j < nc; ++j) {
+            if (sCl[warp][j] != lane) continue;
+            const int k = sCk[warp][j];
+            const size_t i = (size_t)b * n_c + c0 + j;
+            const V3 p = ld3(cand + 3 * k), nn = ld3(cand_normal + 3 * k);
+            const V3 gp = grad_cpts ? ld3(grad_cpts + 3 * i) : V3{0, 0, 0}, gn = grad_cnrm ? ld3(grad_cnrm + 3 * i) : V3{0, 0, 0};
+            const float gpv[3] = {gp.x, gp.y, gp.z}, gnv[3] = {gn.x, gn.y, gn.z}, pv[3] = {p.x, p.y, p.z},
+                        nv[3] = {nn.x, nn.y, nn.z};
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int q2 = 0; q2 < 3; ++q2) g[4 * r + q2] += gpv[r] * pv[q2] + gnv[r] * nv[q2];
+                g[4 * r + 3] += gpv[r];
+            }
+        }
+        __syncwarp();
+    }
+    if (lane < L) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) sG[warp][12 * lane + i] = g[i];
+    }
+    __syncwarp();
+    // ---- wrench (torque about the world origin, force) the loss exerts on this lane's frame through its link ----
+    float M[3] = {0.f, 0.f, 0.f}, F[3] = {0.f, 0.f, 0.f}, S[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) S[i] = 0.f;
+    const V3 tg = V3{prow[0], prow[1], prow[2]};
+    if (active && H.frame_link[f] >= 0) {
+        const T34 W = t34_mul(st.A, t34_load(H.frame_loff[f]));
+        const T34 gl = t34_load(sG[warp] + 12 * H.frame_link[f]);
+        const V3 gt = V3{gl.m[3], gl.m[7], gl.m[11]}, wt = V3{W.m[3], W.m[7], W.m[11]};
+        V3 Mv = cross3(wt, gt);
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            Mv = Mv + cross3(V3{W.m[k], W.m[4 + k], W.m[8 + k]}, V3{gl.m[k], gl.m[4 + k], gl.m[8 + k]});
+        M[0] = Mv.x; M[1] = Mv.y; M[2] = Mv.z;
+        F[0] = gt.x; F[1] = gt.y; F[2] = gt.z;
+        const V3 dt = wt - tg;
+        const float dtv[3] = {dt.x, dt.y, dt.z};
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                S[3 * i + j] = gl.m[4 * i] * W.m[4 * j] + gl.m[4 * i + 1] * W.m[4 * j + 1] + gl.m[4 * i + 2] * W.m[4 * j + 2] +
+                               F[i] * dtv[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) S[i] = warp_sum(S[i]);
+    // ---- upward sweep: a frame's wrench = its own + its children's (child order), then its joint's gradient ----
+    const int depth = active ? H.frame_depth[f] : -1;
+    float jg = 0.f;
+    for (int d = H.max_depth; d >= 0; --d) {
+        if (depth == d) {
+            const int nch = min(H.frame_nchild[f], GQP_MAX_CHILDREN);
+            for (int k = 0; k < nch; ++k) {
+                const float *ch = sMF[warp] + 6 * H.frame_child[f][k];
+                M[0] += ch[0]; M[1] += ch[1]; M[2] += ch[2];
+                F[0] += ch[3]; F[1] += ch[4]; F[2] += ch[5];
+            }
+            float *me = sMF[warp] + 6 * f;
+            me[0] = M[0]; me[1] = M[1]; me[2] = M[2]; me[3] = F[0]; me[4] = F[1]; me[5] = F[2];
+            const int jt = H.frame_jtype[f], dd = H.frame_dof[f];
+            if (jt != 0 && dd >= 0) {
+                const V3 a = t34_vec(st.Bj, V3{H.frame_axis[f][0], H.frame_axis[f][1], H.frame_axis[f][2]});
+                const V3 Mv = V3{M[0], M[1], M[2]}, Fv = V3{F[0], F[1], F[2]};
+                if (jt == 1) jg = dot3(a, Mv - cross3(V3{st.Bj.m[3], st.Bj.m[7], st.Bj.m[11]}, Fv));
+                else jg = dot3(a, Fv);
+            }
+        }
+        __syncwarp();
+    }
+    sJ[warp][lane] = jg;
+    __syncwarp();
+    // ---- joint gradients: entry j of the joint vector sums the frames it drives, in frame order ----
+    float *out = grad_pose + (size_t)b * D;
+    const int n_q = H.mlp_hidden > 0 ? 1 + H.mlp_out : H.n_dofs;
+    float gq = 0.f;
+    if (lane < n_q)
+        for (int ff = 0; ff < H.n_frames; ++ff)
+            if (H.frame_jtype[ff] != 0 && H.frame_dof[ff] == lane) gq += sJ[warp][ff];
+    if (H.mlp_hidden > 0) {  // chain rule through the coupling network: d/dtheta_0 = sum_j d/dq_j dq_j/dtheta_0
+        float t = lane < n_q ? gq * dq[lane] : 0.f;
+        t = warp_sum(t);
+        if (lane == 0) out[9] = t + (grad_pose_extra ? grad_pose_extra[(size_t)b * D + 9] : 0.f);
+    } else if (lane < n_q) {
+        out[9 + lane] = gq + (grad_pose_extra ? grad_pose_extra[(size_t)b * D + 9 + lane] : 0.f);
+    }
+    if (lane == 0) {
+        V3 Ftot = V3{0, 0, 0};
+        for (int ff = 0; ff < H.n_frames; ++ff)
+            if (H.frame_parent[ff] < 0) Ftot = Ftot + V3{sMF[warp][6 * ff + 3], sMF[warp][6 * ff + 4], sMF[warp][6 * ff + 5]};
+        float gp[9];
+        gp[0] = Ftot.x; gp[1] = Ftot.y; gp[2] = Ftot.z;
+        // dL/dR_g = S R_g, columns -> (x^, y^, z); then back through the Gram-Schmidt (as fk_backward_kernel)
+        const T34 &G = st.G;
+        const GramSchmidt &gs = st.gs;
+        const float Rg[9] = {G.m[0], G.m[1], G.m[2], G.m[4], G.m[5], G.m[6], G.m[8], G.m[9], G.m[10]};
+        float gR[9];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) gR[3 * i + j] = S[3 * i] * Rg[j] + S[3 * i + 1] * Rg[3 + j] + S[3 * i + 2] * Rg[6 + j];
+        V3 gxh = V3{gR[0], gR[3], gR[6]}, gyh = V3{gR[1], gR[4], gR[7]}, gz = V3{gR[2], gR[5], gR[8]};
+        gxh = gxh + cross3(gs.yh, gz);
+        gyh = gyh + cross3(gz, gs.xh);
+        const V3 gyp = (gyh - gs.yh * dot3(gs.yh, gyh)) * (1.0f / gs.ny);
+        V3 gy = gyp;
+        const float gd = -dot3(gs.xh, gyp);
+        gxh = gxh - gyp * gs.d;
+        gxh = gxh + gs.y * gd;
+        gy = gy + gs.xh * gd;
+        const V3 gx = (gxh - gs.xh * dot3(gs.xh, gxh)) * (1.0f / gs.nx);
+        gp[3] = gx.x; gp[4] = gx.y; gp[5] = gx.z;
+        gp[6] = gy.x; gp[7] = gy.y; gp[8] = gy.z;
+        for (int i = 0; i < 9; ++i) out[i] = gp[i] + (grad_pose_extra ? grad_pose_extra[(size_t)b * D + i] : 0.f);
+    }
+}
+
 // ---- host side ------------------------------------------------------------------------------------------------------
 extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
     if (!d || !out) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: null argument");
@@ -316,6 +551,16 @@ extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
         for (int k = 0; k < 12; ++k) {
             H.frame_joff[f][k] = d->frame_joff_host[12 * f + k];
             H.frame_loff[f][k] = d->frame_loff_host[12 * f + k];
+        }
+    }
+    for (int f = 0; f < d->n_frames; ++f) {  // tree shape (parents precede their children)
+        const int par = H.frame_parent[f];
+        H.frame_depth[f] = par < 0 ? 0 : H.frame_depth[par] + 1;
+        H.max_depth = std::max(H.max_depth, H.frame_depth[f]);
+        if (par >= 0) {
+            if (H.frame_nchild[par] < GQP_MAX_CHILDREN) H.frame_child[par][H.frame_nchild[par]] = f;
+            H.frame_nchild[par]++;
+            H.max_children = std::max(H.max_children, H.frame_nchild[par]);
         }
     }
     for (int l = 0; l < d->n_links; ++l) {
@@ -400,5 +645,41 @@ extern "C" int gqp_contacts_backward(const GqpHand *h, const int32_t *idx, const
     GQP_LAUNCH(contacts_backward_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, h->d_cand, h->d_cand_normal,
                h->d_cand_link, h->host.n_cand, h->host.n_links, idx, grad_cpts, grad_cnrm, Bt, n_c, grad_link_tf);
     GQP_CHECK_LAUNCH("gqp_contacts_backward");
+    return GQP_OK;
+}
+
+// ---- fused, warp-per-candidate entry points (what the engine launches) ----------------------------------------------
+extern "C" int gqp_fk_contacts_forward(const GqpHand *h, const float *pose, const int32_t *idx, int Bt, int n_c,
+                                       float *link_tf, float *cpts, float *cnrm, void *stream) {
+    if (!h || Bt < 0 || n_c < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_contacts_forward: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!pose || !link_tf || (idx && (!cpts || !cnrm))) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_contacts_forward: null pointer");
+    if (h->host.n_frames > 32 || h->host.max_children > GQP_MAX_CHILDREN) {  // wide trees: the thread-per-candidate kernels
+        int rc = gqp_fk_forward(h, pose, Bt, link_tf, stream);
+        if (rc == GQP_OK && idx) rc = gqp_contacts_forward(h, link_tf, idx, Bt, n_c, cpts, cnrm, stream);
+        return rc;
+    }
+    GQP_LAUNCH(fk_contacts_forward_warp_kernel, (Bt + FKW_WARPS - 1) / FKW_WARPS, FKW_WARPS * 32, 0, (cudaStream_t)stream,
+               h->d_dev, h->d_cand, h->d_cand_normal, h->d_cand_link, pose, idx, Bt, n_c, link_tf, cpts, cnrm);
+    GQP_CHECK_LAUNCH("gqp_fk_contacts_forward");
+    return GQP_OK;
+}
+
+extern "C" int gqp_fk_contacts_backward(const GqpHand *h, const float *pose, const int32_t *idx, const float *grad_cpts,
+                                        const float *grad_cnrm, float *grad_link_tf, const float *grad_pose_extra,
+                                        int Bt, int n_c, float *grad_pose, void *stream) {
+    if (!h || Bt < 0 || n_c < 0) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_contacts_backward: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!pose || !grad_pose) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_contacts_backward: null pointer");
+    if (h->host.n_frames > 32 || h->host.max_children > GQP_MAX_CHILDREN) {
+        if (!grad_link_tf) return gqp_set_error(GQP_ERR_ARG, "gqp_fk_contacts_backward: grad_link_tf needed for this hand");
+        int rc = idx ? gqp_contacts_backward(h, idx, grad_cpts, grad_cnrm, Bt, n_c, grad_link_tf, stream) : GQP_OK;
+        if (rc == GQP_OK) rc = gqp_fk_backward(h, pose, grad_link_tf, grad_pose_extra, Bt, grad_pose, stream);
+        return rc;
+    }
+    GQP_LAUNCH(fk_contacts_backward_warp_kernel, (Bt + FKW_WARPS - 1) / FKW_WARPS, FKW_WARPS * 32, 0, (cudaStream_t)stream,
+               h->d_dev, h->d_cand, h->d_cand_normal, h->d_cand_link, pose, idx, grad_cpts, grad_cnrm, grad_link_tf,
+               grad_pose_extra, Bt, n_c, grad_pose);
+    GQP_CHECK_LAUNCH("gqp_fk_contacts_backward");
     return GQP_OK;
 }

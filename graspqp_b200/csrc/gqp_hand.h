@@ -7,6 +7,7 @@
 #define GQP_MAX_FRAMES 48
 #define GQP_MAX_LINKS 32
 #define GQP_MAX_DOFS 32
+#define GQP_MAX_CHILDREN 8
 #define GQP_MAX_MLP_HIDDEN 16
 #define GQP_MAX_MLP_OUT 7
 
@@ -68,6 +69,10 @@ struct GqpHandDev {
     float frame_joff[GQP_MAX_FRAMES][12];
     float frame_loff[GQP_MAX_FRAMES][12];
     int32_t link_frame[GQP_MAX_LINKS];
+    // tree shape for the warp-per-candidate kernels (gqp_fkw.cu): depth of every frame (roots 0), its children in
+    // frame order, the deepest level
+    int32_t frame_depth[GQP_MAX_FRAMES], frame_nchild[GQP_MAX_FRAMES], frame_child[GQP_MAX_FRAMES][GQP_MAX_CHILDREN];
+    int32_t max_depth, max_children;
     float joints_lower[GQP_MAX_DOFS], joints_upper[GQP_MAX_DOFS];
     // joint-coupling network (GqpHandDesc::mlp_*); mlp_hidden == 0: frame_dof indexes the pose row directly
     int32_t mlp_hidden, mlp_out;

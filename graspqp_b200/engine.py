@@ -211,15 +211,16 @@ class FitEngine:
         lib, be, p, st = self.lib, self.be, self.be.ptr, self.be.stream
         Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
         row = lambda k: p(losses_out) + 4 * Bt * TERMS.index(k)
-        self._ck(lib.gqp_fk_forward(self.hand, p(pose), Bt, p(self.link_tf), st))
+        # H1-H3 in one launch, a warp per candidate: link transforms + the n_c chosen contact points / normals
+        self._ck(lib.gqp_fk_contacts_forward(self.hand, p(pose), p(idx), Bt, n_c, p(self.link_tf), p(self.cpts),
+                                             p(self.cnrm), st))
         self._ck(lib.gqp_memset_zero(p(self.g_link_tf), 4 * Bt * self.L * 12, st))
-        # two independent chains read link_tf and add into g_link_tf (atomics): the penetration chain goes to a second
-        # stream so that its latency-bound kernels fill the SMs beside the contact / force-closure chain
+        # two independent chains read link_tf: the penetration chain (which adds into g_link_tf with atomics) goes to a
+        # second stream so that its latency-bound kernels fill the SMs beside the contact / force-closure chain
         overlap = self.overlap and be.side_stream is not None
         s2 = be.side_stream if overlap else st
         if overlap:
             be.fork()
-        self._ck(lib.gqp_contacts_forward(self.hand, p(self.link_tf), p(idx), Bt, n_c, p(self.cpts), p(self.cnrm), st))
         self._ck(lib.gqp_object_distance_forward(self.objset, B, n_c, p(self.cpts), 1.0, p(self.obj_dist),
                                                  p(self.obj_nrm), p(self.obj_clst), p(self.obj_sign), st))
         self._ck(lib.gqp_object_distance_backward(p(self.ones), p(self.cpts), p(self.obj_clst), p(self.obj_sign),
@@ -236,8 +237,6 @@ class FitEngine:
                                    p(self.obj_dgrad), p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop),
                                    row("E_fc"), row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm),
                                    p(self.qp_stop), st))
-        self._ck(lib.gqp_contacts_backward(self.hand, p(idx), p(self.g_cpts), p(self.g_cnrm), Bt, n_c,
-                                           p(self.g_link_tf), st))
         # the side chain is enqueued AFTER the critical chain: its persistent CTAs then fill what the one-wave
         # object-distance / QP kernels leave free instead of holding the SMs while the critical chain waits
         self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
@@ -247,7 +246,10 @@ class FitEngine:
                                          p(self.g_pose_joints), s2))
         if overlap:
             be.join()
-        self._ck(lib.gqp_fk_backward(self.hand, p(pose), p(self.g_link_tf), p(self.g_pose_joints), Bt, p(grad_out), st))
+        # contact scatter + analytic J' of the chain in one launch (fixed summation order): reads what the penetration
+        # chain accumulated in g_link_tf, adds the contact terms, writes d(sum w E)/d pose
+        self._ck(lib.gqp_fk_contacts_backward(self.hand, p(pose), p(idx), p(self.g_cpts), p(self.g_cnrm),
+                                              p(self.g_link_tf), p(self.g_pose_joints), Bt, n_c, p(grad_out), st))
 
     def capture(self):
         """Record the energy evaluation of an iteration (both streams, ~20 launches) into a CUDA graph; step() then
@@ -364,9 +366,8 @@ class FitEngine:
         Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
         row = lambda k: p(self.losses_new) + 4 * Bt * TERMS.index(k)
         return {
-            "fk_forward": lambda: lib.gqp_fk_forward(self.hand, p(self.pose_new), Bt, p(self.link_tf), st),
-            "contacts_forward": lambda: lib.gqp_contacts_forward(self.hand, p(self.link_tf), p(self.idx_new), Bt, n_c,
-                                                                 p(self.cpts), p(self.cnrm), st),
+            "fk_contacts_forward": lambda: lib.gqp_fk_contacts_forward(
+                self.hand, p(self.pose_new), p(self.idx_new), Bt, n_c, p(self.link_tf), p(self.cpts), p(self.cnrm), st),
             "object_distance": lambda: lib.gqp_object_distance_forward(
                 self.objset, B, n_c, p(self.cpts), 1.0, p(self.obj_dist), p(self.obj_nrm), p(self.obj_clst),
                 p(self.obj_sign), st),
@@ -376,16 +377,15 @@ class FitEngine:
                 ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist), p(self.obj_nrm), p(self.obj_dgrad),
                 p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop), row("E_fc"), row("E_dis"), p(self.lam),
                 p(self.g_cpts), p(self.g_cnrm), p(self.qp_stop), st),
-            "contacts_backward": lambda: lib.gqp_contacts_backward(self.hand, p(self.idx_new), p(self.g_cpts),
-                                                                   p(self.g_cnrm), Bt, n_c, p(self.g_link_tf), st),
             "hand_distance": lambda: lib.gqp_hand_distance(
                 self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None, row("E_pen"), p(self.pen_scratch),
                 self.weights["E_pen"], p(self.g_link_tf), st),
             "self_pen_joints": lambda: lib.gqp_self_pen_joints(
                 self.hand, p(self.link_tf), p(self.pose_new), Bt, row("E_spen"), row("E_joints"), self.weights["E_spen"],
                 self.weights["E_joints"], p(self.g_link_tf), p(self.g_pose_joints), st),
-            "fk_backward": lambda: lib.gqp_fk_backward(self.hand, p(self.pose_new), p(self.g_link_tf),
-                                                       p(self.g_pose_joints), Bt, p(self.grad_new), st),
+            "fk_contacts_backward": lambda: lib.gqp_fk_contacts_backward(
+                self.hand, p(self.pose_new), p(self.idx_new), p(self.g_cpts), p(self.g_cnrm), p(self.g_link_tf),
+                p(self.g_pose_joints), Bt, n_c, p(self.grad_new), st),
         }
 
     def close(self):

@@ -122,6 +122,17 @@ int gqp_contacts_forward(const GqpHand *h, const float *link_tf, const int32_t *
 int gqp_contacts_backward(const GqpHand *h, const int32_t *idx, const float *grad_cpts, const float *grad_cnrm, int Bt,
                           int n_c, float *grad_link_tf, void *stream);
 
+/* ---- H1-H3 fused, a warp per candidate (what the engine launches): gqp_fk_forward + gqp_contacts_forward in one launch,
+ * and gqp_contacts_backward + gqp_fk_backward in one launch.  idx may be NULL (kinematics only).  The backward READS
+ * grad_link_tf (Bt,n_links,12; what the penetration stages accumulated; may be NULL = zero), adds this candidate's
+ * contact terms in contact order and OVERWRITES grad_pose with the total plus grad_pose_extra (may be NULL); every
+ * reduction has a fixed order (no atomics).  Hands with more than 32 frames fall back to the four separate kernels. */
+int gqp_fk_contacts_forward(const GqpHand *h, const float *pose, const int32_t *idx, int Bt, int n_c, float *link_tf,
+                            float *cpts, float *cnrm, void *stream);
+int gqp_fk_contacts_backward(const GqpHand *h, const float *pose, const int32_t *idx, const float *grad_cpts,
+                             const float *grad_cnrm, float *grad_link_tf, const float *grad_pose_extra, int Bt, int n_c,
+                             float *grad_pose, void *stream);
+
 /* ---- H4: HandModel.cal_distance (hand_model.py:875-987) --------------------------------------------------------------
  * x (n_obj, n_pts, 3): one point set per object, shared by its batch_each candidates (the reference materialises the
  * repeat, object_model.py:181-184; x_stride_candidates != 0 selects a per-candidate (Bt,n_pts,3) set instead).

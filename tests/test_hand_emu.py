@@ -164,3 +164,39 @@ def test_culling_proof_outside_cells_have_positive_sign(emu, hand, oracle_built)
     sign = lambda pts, fv: osdf.compute_sdf_port(pts, fv)[1]
     n_links, n_cells, n_points = cases.check_culling_proof(emu, sign, hand, per_cell=2, n_far=5000)
     assert n_links >= 1 and n_points > 1000
+
+
+@pytest.mark.parametrize("hand", ["allegro", "robotiq2"])
+def test_fused_warp_kernels_match_the_separate_ones(emu, hand):
+    """gqp_fk_contacts_forward / _backward (a warp per candidate, lane = frame) == gqp_fk_forward + gqp_contacts_forward
+    and gqp_contacts_backward + gqp_fk_backward (a thread per candidate)"""
+    from graspqp_b200 import hand_pack, synth
+    pack = hand_pack.load_pack(hand)
+    h = hand_pack.create_hand(emu, pack)
+    B, n_c = 5, 6
+    v, _ = synth.make_mesh("sphere", 100, 1)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, 4)
+    pose, idx = np.ascontiguousarray(pose, np.float32), np.ascontiguousarray(idx, np.int32)
+    L, D = len(pack["mesh_frame"]), pose.shape[1]
+    tf1, tf2 = np.zeros((B, L, 12), np.float32), np.zeros((B, L, 12), np.float32)
+    cp1, cn1, cp2, cn2 = [np.zeros((B, n_c, 3), np.float32) for _ in range(4)]
+    assert emu.gqp_fk_forward(h, ptr(pose), B, ptr(tf1), None) == 0
+    assert emu.gqp_contacts_forward(h, ptr(tf1), ptr(idx), B, n_c, ptr(cp1), ptr(cn1), None) == 0
+    assert emu.gqp_fk_contacts_forward(h, ptr(pose), ptr(idx), B, n_c, ptr(tf2), ptr(cp2), ptr(cn2), None) == 0
+    np.testing.assert_allclose(tf2, tf1, atol=1e-7)
+    np.testing.assert_allclose(cp2, cp1, atol=1e-7)
+    np.testing.assert_allclose(cn2, cn1, atol=1e-7)
+    rng = np.random.default_rng(0)
+    g_cp, g_cn = rng.normal(size=(B, n_c, 3)).astype(np.float32), rng.normal(size=(B, n_c, 3)).astype(np.float32)
+    g_tf0 = rng.normal(size=(B, L, 12)).astype(np.float32)
+    extra = rng.normal(size=(B, D)).astype(np.float32)
+    g_tf = g_tf0.copy()
+    gp1, gp2 = np.zeros((B, D), np.float32), np.zeros((B, D), np.float32)
+    assert emu.gqp_contacts_backward(h, ptr(idx), ptr(g_cp), ptr(g_cn), B, n_c, ptr(g_tf), None) == 0
+    assert emu.gqp_fk_backward(h, ptr(pose), ptr(g_tf), ptr(extra), B, ptr(gp1), None) == 0
+    g_in = g_tf0.copy()
+    assert emu.gqp_fk_contacts_backward(h, ptr(pose), ptr(idx), ptr(g_cp), ptr(g_cn), ptr(g_in), ptr(extra), B, n_c,
+                                        ptr(gp2), None) == 0
+    np.testing.assert_array_equal(g_in, g_tf0)  # read only
+    np.testing.assert_allclose(gp2, gp1, rtol=2e-5, atol=2e-5 * np.abs(gp1).max())
+    emu.gqp_hand_destroy(h)
