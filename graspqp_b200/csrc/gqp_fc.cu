@@ -26,7 +26,7 @@
 #define FC_MIN_BLOCKS 16
 #endif
 #define FC_RED_K 29  // widest reduction (odd: conflict-free column sums)
-#define FC_SM_PER_WARP (32 * FC_RED_K + 32 + 64 * 3)
+#define FC_SM_PER_WARP (32 * FC_RED_K + 64 + 64 * 3)
 
 struct FcParamsDev {
     double mu_f, c0, tw, lo, hi, ridge, svd_gain, values_gain, values_offset;
@@ -37,29 +37,31 @@ struct FcParamsDev {
 
 // all-reduce K doubles across the warp: v[k] <- op over lanes.  Narrow reductions (K <= 6) are shuffle butterflies;
 // wide ones go through shared memory, each of K lanes summing one column in 4 independent chains.
-template <int K, bool IS_MIN>
+// G = 32: the warp holds one candidate; G = 16: two candidates, one per half-warp (n <= 32 variables), every reduction
+// stays inside its half.
+template <int K, bool IS_MIN, int G>
 __device__ __forceinline__ void warp_allreduce(double *sm, double (&v)[K], int lane) {
     if (K <= 6) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
+            for (int o = G / 2; o > 0; o >>= 1) {
                 double t = __shfl_xor_sync(GQP_FULL, v[k], o);
                 v[k] = IS_MIN ? (t < v[k] ? t : v[k]) : v[k] + t;
             }
         }
         return;
     }
-    const int S = K | 1;
+    const int S = K | 1, gl = lane & (G - 1), base = lane - gl;
 #pragma unroll
     for (int k = 0; k < K; ++k) sm[lane * S + k] = v[k];
     __syncwarp();
-    if (lane < K) {
-        double a0 = sm[lane], a1 = sm[S + lane], a2 = sm[2 * S + lane], a3 = sm[3 * S + lane];
+    for (int col = gl; col < K; col += G) {
+        const double *c0 = sm + base * S + col;
+        double a0 = c0[0], a1 = c0[S], a2 = c0[2 * S], a3 = c0[3 * S];
 #pragma unroll
-        for (int r = 4; r < 32; r += 4) {
-            double t0 = sm[r * S + lane], t1 = sm[(r + 1) * S + lane], t2 = sm[(r + 2) * S + lane],
-                   t3 = sm[(r + 3) * S + lane];
+        for (int r = 4; r < G; r += 4) {
+            double t0 = c0[r * S], t1 = c0[(r + 1) * S], t2 = c0[(r + 2) * S], t3 = c0[(r + 3) * S];
             if (IS_MIN) {
                 a0 = t0 < a0 ? t0 : a0; a1 = t1 < a1 ? t1 : a1; a2 = t2 < a2 ? t2 : a2; a3 = t3 < a3 ? t3 : a3;
             } else {
@@ -67,11 +69,11 @@ __device__ __forceinline__ void warp_allreduce(double *sm, double (&v)[K], int l
             }
         }
         double a = IS_MIN ? fmin(fmin(a0, a1), fmin(a2, a3)) : (a0 + a1) + (a2 + a3);
-        sm[32 * FC_RED_K + lane] = a;
+        sm[32 * FC_RED_K + base * 2 + col] = a;
     }
     __syncwarp();
 #pragma unroll
-    for (int k = 0; k < K; ++k) v[k] = sm[32 * FC_RED_K + k];
+    for (int k = 0; k < K; ++k) v[k] = sm[32 * FC_RED_K + base * 2 + k];
     __syncwarp();
 }
 
@@ -215,7 +217,7 @@ __device__ __forceinline__ int fc_batch_stop(const unsigned *gmax, const unsigne
 
 enum { FC_FUSED = 0, FC_SOLVE = 1, FC_FINISH = 2 };
 
-template <int MODE>
+template <int MODE, int G>
 __global__ void __launch_bounds__(FC_WARPS * 32, FC_MIN_BLOCKS)
 fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
               const float *__restrict__ obj_dist, const float *__restrict__ obj_nrm,
@@ -225,8 +227,9 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
               float *__restrict__ trace, FcWorkspace ws, int batch_stop, int32_t *__restrict__ stop_out) {
     __shared__ double smem[FC_WARPS][FC_SM_PER_WARP + 64];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int gl = lane & (G - 1), grp = lane / G, NG = 32 / G;  // lane within its candidate's group, group, groups/warp
     double *sm = smem[warp];
-    double *sm4 = sm + 32 * FC_RED_K + 32;  // (64,4) per-variable scratch
+    double *sm4 = sm + 32 * FC_RED_K + 64;  // (64,4) per-variable scratch
     const int n = 4 * n_c, m = 2 * n;
     int stop = P.max_iter;
     if (MODE == FC_FUSED && stop_iter) stop = *stop_iter;
@@ -236,14 +239,16 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
     }
     const double INF = 1e300;
 
-    for (int b = blockIdx.x * FC_WARPS + warp; b < Bt; b += gridDim.x * FC_WARPS) {
+    for (int wb = blockIdx.x * FC_WARPS + warp; wb * NG < Bt; wb += gridDim.x * FC_WARPS) {
+        const bool live = wb * NG + grp < Bt;  // an odd batch leaves the last warp's second half idle: it computes the
+        const int b = live ? wb * NG + grp : Bt - 1;  // last candidate again and stores nothing
         const int o = b / batch_each;
         // ---- Q1/Q2: friction-cone edges and grasp-matrix columns of this lane's variables ----
         double F[2][6];
         bool valid[2];
 #pragma unroll
         for (int v = 0; v < 2; ++v) {
-            const int j = lane + 32 * v;
+            const int j = gl + G * v;
             valid[v] = j < n;
 #pragma unroll
             for (int i = 0; i < 6; ++i) F[v][i] = 0.0;
@@ -284,7 +289,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
 #pragma unroll
                     for (int j2 = 0; j2 <= i; ++j2) a[tri_ix(i, j2)] += Minv[v] * F[v][i] * F[v][j2];
             }
-            warp_allreduce<21, false>(sm, a, lane);
+            warp_allreduce<21, false, G>(sm, a, lane);
 #pragma unroll
             for (int i = 0; i < 6; ++i) a[tri_ix(i, i)] += 1.0;
             chol6<true>(a);  // I + F M^-1 F': pivots >= 1
@@ -303,7 +308,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
 #pragma unroll
                 for (int i = 0; i < 6; ++i) t[i] += F[v][i] * r[v] * Minv[v];
             }
-            warp_allreduce<6, false>(sm, t, lane);
+            warp_allreduce<6, false, G>(sm, t, lane);
             chol6_solve(L6, t);
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
@@ -338,7 +343,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                     mn[1] = fmin(mn[1], fmin(zu[v], zl[v]));
                 }
             }
-            warp_allreduce<2, true>(sm, mn, lane);
+            warp_allreduce<2, true, G>(sm, mn, lane);
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
                 if (mn[0] < 0.0) { su[v] -= mn[0] - 1.0; sl[v] -= mn[0] - 1.0; }
@@ -371,30 +376,30 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                     du[v] = dl[v] = 1.0;
                 }
             }
-            warp_allreduce<3, false>(sm, acc, lane);
+            warp_allreduce<3, false, G>(sm, acc, lane);
             const double mu = fabs(acc[0]) * inv_m;
             const double res = acc[1] * fc_rsqrt(fmax(acc[1], 1e-300)) + acc[2] * fc_rsqrt(fmax(acc[2], 1e-300)) + m * mu;
-            if (trace && lane == 0) trace[(size_t)b * P.max_iter + it] = (float)res;
+            if (trace && gl == 0 && live) trace[(size_t)b * P.max_iter + it] = (float)res;
             const bool improved = it == 0 || res < best_res;
             if (improved) {
                 best_res = res;
                 best_it = it;
-                if (MODE == FC_SOLVE) {
+                if (MODE == FC_SOLVE && live) {
                     double *sn = ws.snap + ((size_t)b * P.max_iter + it) * 3 * n;
 #pragma unroll
                     for (int v = 0; v < 2; ++v)
                         if (valid[v]) {
-                            const int j = lane + 32 * v;
+                            const int j = gl + G * v;
                             sn[j] = x[v];
                             sn[n + j] = fmax(zu[v], 1e-8) * (su[v] >= 1e-8 ? isu[v] : 1e8);
                             sn[2 * n + j] = fmax(zl[v], 1e-8) * (sl[v] >= 1e-8 ? isl[v] : 1e8);
                         }
-                } else {
+                } else if (MODE != FC_SOLVE) {
 #pragma unroll
                     for (int v = 0; v < 2; ++v) { bx[v] = x[v]; bsu[v] = su[v]; bsl[v] = sl[v]; bzu[v] = zu[v]; bzl[v] = zl[v]; }
                 }
             }
-            if (MODE == FC_SOLVE && lane == 0) {
+            if (MODE == FC_SOLVE && gl == 0 && live) {
                 ws.best_idx[(size_t)b * FC_MAX_ITER + it] = (uint8_t)best_it;
                 // batch statistics: the maximum only grows and the flag only sets, so a plain read filters most atomics
                 const unsigned bits = (unsigned)__float_as_int((float)best_res);
@@ -407,7 +412,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             double ya[6], yc[6];
             solve(du, dl, rx, zu, zl, rzu, rzl, aff, ya);  // rs = z
             double al[1] = {step_lane(zu, zl, su, sl, aff, valid)};
-            warp_allreduce<1, true>(sm, al, lane);
+            warp_allreduce<1, true, G>(sm, al, lane);
             const double a1 = fmin(al[0], 1.0);
             double t3[1] = {0.0};
 #pragma unroll
@@ -415,7 +420,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 if (valid[v])
                     t3[0] += (su[v] + a1 * aff.dsu[v]) * (zu[v] + a1 * aff.dzu[v]) +
                              (sl[v] + a1 * aff.dsl[v]) * (zl[v] + a1 * aff.dzl[v]);
-            warp_allreduce<1, false>(sm, t3, lane);
+            warp_allreduce<1, false, G>(sm, t3, lane);
             const double ratio = t3[0] * fc_rcp(acc[0]);
             const double sig = ratio * ratio * ratio;
             double rs2u[2], rs2l[2];
@@ -432,7 +437,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 aff.dzu[v] += cor.dzu[v]; aff.dzl[v] += cor.dzl[v];
             }
             al[0] = step_lane(zu, zl, su, sl, aff, valid);
-            warp_allreduce<1, true>(sm, al, lane);
+            warp_allreduce<1, true, G>(sm, al, lane);
             const double a2 = fmin(0.999 * al[0], 1.0);
 #pragma unroll
             for (int v = 0; v < 2; ++v) {
@@ -453,7 +458,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
 #pragma unroll
             for (int v = 0; v < 2; ++v)
                 if (valid[v]) {
-                    const int j = lane + 32 * v;
+                    const int j = gl + G * v;
                     bx[v] = sn[j]; bdu[v] = sn[n + j]; bdl[v] = sn[2 * n + j];
                 }
         } else {
@@ -477,7 +482,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                     for (int j2 = 0; j2 <= i; ++j2) red[6 + tri_ix(i, j2)] += F[v][i] * F[v][j2];
                 }
             }
-        warp_allreduce<27, false>(sm, red, lane);
+        warp_allreduce<27, false, G>(sm, red, lane);
         double Fx[6], Lg[21];
         double value = 0.0;
 #pragma unroll
@@ -497,7 +502,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                 piv = (r == r) ? fmin(piv, r) : 0.0;
             }
         }
-        if (piv < 1e-6) {
+        const bool need_qr = piv < 1e-6;
+        if (__any_sync(GQP_FULL, need_qr)) {  // uniform over the warp: the other half (G = 16) runs along, result unused
             // Nearly rank-deficient grasp matrix (contacts on one line, duplicated contact indices: n_c = 4 on parallel
             // pads).  Cholesky of F F' squares the condition number and resolves sigma_min/sigma_max only down to 1e-8,
             // where svdvals (span.py:402) resolves 1e-16, and prod(sigma)^(1/6) magnifies exactly that.  Re-factorise
@@ -517,7 +523,7 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                     double c[6];
 #pragma unroll
                     for (int k = 0; k < 6; ++k) c[k] = (k < j) ? a[0][k] * a[0][j] + a[1][k] * a[1][j] : 0.0;
-                    warp_allreduce<6, false>(sm, c, lane);
+                    warp_allreduce<6, false, G>(sm, c, lane);
 #pragma unroll
                     for (int k = 0; k < 6; ++k)
                         if (k < j) {
@@ -527,17 +533,19 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
                         }
                 }
                 double nn[1] = {a[0][j] * a[0][j] + a[1][j] * a[1][j]};
-                warp_allreduce<1, false>(sm, nn, lane);
+                warp_allreduce<1, false, G>(sm, nn, lane);
                 const double rjj = sqrt(nn[0]);
                 R[j][j] = rjj;
                 const double inv = rjj > 0.0 ? 1.0 / rjj : 0.0;
                 a[0][j] *= inv;
                 a[1][j] *= inv;
             }
+            if (need_qr) {
 #pragma unroll
-            for (int i = 0; i < 6; ++i)
+                for (int i = 0; i < 6; ++i)
 #pragma unroll
-                for (int k = 0; k <= i; ++k) Lg[tri_ix(i, k)] = (k == i) ? 1.0 / R[i][i] : R[k][i];
+                    for (int k = 0; k <= i; ++k) Lg[tri_ix(i, k)] = (k == i) ? 1.0 / R[i][i] : R[k][i];
+            }
         }
         double logdet = 0.0;
 #pragma unroll
@@ -562,14 +570,14 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         const double Efc = P.values_gain * (value + P.values_offset) * ex;
         // ---- E_dis (energy.py:25-28) on lanes < n_c ----
         double edis = 0.0, gpd[3] = {0.0, 0.0, 0.0};
-        if (lane < n_c) {
-            const size_t q = ((size_t)b * n_c + lane) * 3;
+        if (gl < n_c) {
+            const size_t q = ((size_t)b * n_c + gl) * 3;
             double ox = obj_nrm[q], oy = obj_nrm[q + 1], oz = obj_nrm[q + 2];
             double a = 1.0 + (ox * cnrm_hand[q] + oy * cnrm_hand[q + 1] + oz * cnrm_hand[q + 2]);
-            double dd = obj_dist[(size_t)b * n_c + lane];
+            double dd = obj_dist[(size_t)b * n_c + gl];
             double ea = exp(a);
             edis = ea * fabs(dd);
-            if (grad_cnrm) {
+            if (grad_cnrm && live) {
                 double g = P.w_dis * edis;
                 grad_cnrm[q] = (float)(g * ox); grad_cnrm[q + 1] = (float)(g * oy); grad_cnrm[q + 2] = (float)(g * oz);
             }
@@ -579,8 +587,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             }
         }
         double es[1] = {edis};
-        warp_allreduce<1, false>(sm, es, lane);
-        if (lane == 0) {
+        warp_allreduce<1, false, G>(sm, es, lane);
+        if (gl == 0 && live) {
             if (e_fc) e_fc[b] = (float)Efc;
             if (e_dis) e_dis[b] = (float)es[0];
         }
@@ -623,8 +631,8 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
         // ---- per-contact sums: force solution (span.py:414) and d/d(contact point) through tau = tw (r x f) ----
 #pragma unroll
         for (int v = 0; v < 2; ++v) {
-            const int j = lane + 32 * v;
-            if (j < 64) {
+            const int j = gl + G * v + 32 * grp;  // G = 16: the second candidate's variables sit in slots 32..63
+            if (gl + G * v < 64 / NG) {
                 double fx = F[v][0], fy = F[v][1], fz = F[v][2], gx = gF[v][3], gy = gF[v][4], gz = gF[v][5];
                 sm4[4 * j + 0] = valid[v] ? P.tw * (fy * gz - fz * gy) : 0.0;
                 sm4[4 * j + 1] = valid[v] ? P.tw * (fz * gx - fx * gz) : 0.0;
@@ -633,17 +641,17 @@ fc_dis_kernel(FcParamsDev P, const float *__restrict__ cpts, const float *__rest
             }
         }
         __syncwarp();
-        if (lane < n_c) {
+        if (gl < n_c && live) {
             double s[4] = {0.0, 0.0, 0.0, 0.0};
             for (int k = 0; k < 4; ++k)
-                for (int i = 0; i < 4; ++i) s[i] += sm4[4 * (4 * lane + k) + i];
-            const size_t q = ((size_t)b * n_c + lane) * 3;
+                for (int i = 0; i < 4; ++i) s[i] += sm4[4 * (4 * gl + k + 32 * grp) + i];
+            const size_t q = ((size_t)b * n_c + gl) * 3;
             if (grad_cpts) {
                 grad_cpts[q] = (float)(s[0] + gpd[0]);
                 grad_cpts[q + 1] = (float)(s[1] + gpd[1]);
                 grad_cpts[q + 2] = (float)(s[2] + gpd[2]);
             }
-            if (lam_out) lam_out[(size_t)b * n_c + lane] = (float)s[3];
+            if (lam_out) lam_out[(size_t)b * n_c + gl] = (float)s[3];
         }
         __syncwarp();
     }
@@ -702,10 +710,18 @@ extern "C" int gqp_fc_dis_energy(const GqpFcParams *p, const float *cpts, const 
     P.tw = p->torque_weight; P.lo = p->lower; P.hi = p->upper; P.ridge = p->ridge; P.svd_gain = p->svd_gain;
     P.values_gain = p->values_gain; P.values_offset = p->values_offset; P.max_iter = p->max_iter;
     P.w_fc = p->w_fc; P.w_dis = p->w_dis; P.eps = p->eps;
-    int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
-    GQP_LAUNCH(fc_dis_kernel<FC_FUSED>, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
+    // n = 4 n_c <= 32 variables: two candidates per warp (half-warp reductions), else one
+    if (n_c <= 8) {
+        const int grid = ((Bt + 1) / 2 + FC_WARPS - 1) / FC_WARPS;
+        GQP_LAUNCH((fc_dis_kernel<FC_FUSED, 16>), grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
                obj_nrm, obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm, qp_stop_iter,
                qp_trace, FcWorkspace{}, 0, (int32_t *)nullptr);
+    } else {
+        const int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
+        GQP_LAUNCH((fc_dis_kernel<FC_FUSED, 32>), grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
+               obj_nrm, obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm, qp_stop_iter,
+               qp_trace, FcWorkspace{}, 0, (int32_t *)nullptr);
+    }
     GQP_CHECK_LAUNCH("gqp_fc_dis_energy");
     return GQP_OK;
 }
@@ -742,11 +758,20 @@ extern "C" int gqp_fc_solve(const GqpFcParams *p, const float *cpts, const float
 #else
     memset(workspace, 0, FC_WS_HEADER);
 #endif
-    int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
-    GQP_LAUNCH(fc_dis_kernel<FC_SOLVE>, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, (const float *)nullptr,
+    // n = 4 n_c <= 32 variables: two candidates per warp (half-warp reductions), else one
+    if (n_c <= 8) {
+        const int grid = ((Bt + 1) / 2 + FC_WARPS - 1) / FC_WARPS;
+        GQP_LAUNCH((fc_dis_kernel<FC_SOLVE, 16>), grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, (const float *)nullptr,
                (const float *)nullptr, obj_nrm, (const float *)nullptr, cog, Bt, batch_each, n_c, (float *)nullptr,
                (float *)nullptr, (float *)nullptr, (float *)nullptr, (float *)nullptr, (const int32_t *)nullptr,
                (float *)nullptr, ws, 0, (int32_t *)nullptr);
+    } else {
+        const int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
+        GQP_LAUNCH((fc_dis_kernel<FC_SOLVE, 32>), grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, (const float *)nullptr,
+               (const float *)nullptr, obj_nrm, (const float *)nullptr, cog, Bt, batch_each, n_c, (float *)nullptr,
+               (float *)nullptr, (float *)nullptr, (float *)nullptr, (float *)nullptr, (const int32_t *)nullptr,
+               (float *)nullptr, ws, 0, (int32_t *)nullptr);
+    }
     GQP_CHECK_LAUNCH("gqp_fc_solve");
     return GQP_OK;
 }
@@ -763,10 +788,18 @@ extern "C" int gqp_fc_finish(const GqpFcParams *p, const float *cpts, const floa
         return gqp_set_error(GQP_ERR_ARG, "gqp_fc_finish: null pointer");
     if (!e_fc && !e_dis && !lam && !grad_cpts && !grad_cnrm) return gqp_set_error(GQP_ERR_ARG, "gqp_fc_finish: no output");
     FcWorkspace ws = fc_workspace_view(const_cast<void *>(workspace), Bt);
-    int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
-    GQP_LAUNCH(fc_dis_kernel<FC_FINISH>, grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
+    // n = 4 n_c <= 32 variables: two candidates per warp (half-warp reductions), else one
+    if (n_c <= 8) {
+        const int grid = ((Bt + 1) / 2 + FC_WARPS - 1) / FC_WARPS;
+        GQP_LAUNCH((fc_dis_kernel<FC_FINISH, 16>), grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
                obj_nrm, obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm,
                (const int32_t *)nullptr, (float *)nullptr, ws, batch_stop, stop_iter_out);
+    } else {
+        const int grid = (Bt + FC_WARPS - 1) / FC_WARPS;
+        GQP_LAUNCH((fc_dis_kernel<FC_FINISH, 32>), grid, FC_WARPS * 32, 0, (cudaStream_t)stream, P, cpts, cnrm_hand, obj_dist,
+               obj_nrm, obj_dgrad, cog, Bt, batch_each, n_c, e_fc, e_dis, lam, grad_cpts, grad_cnrm,
+               (const int32_t *)nullptr, (float *)nullptr, ws, batch_stop, stop_iter_out);
+    }
     GQP_CHECK_LAUNCH("gqp_fc_finish");
     return GQP_OK;
 }

@@ -739,7 +739,12 @@ static int pen_search_grid() {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    return sms * 8;
+    static int per_sm = 0;  // tuning knob (profiles/r2_notes.md): resident CTAs per SM the search may hold
+    if (per_sm == 0) {
+        const char *e = getenv("GQP_PEN_SEARCH_CTAS");
+        per_sm = e ? std::max(1, std::min(8, atoi(e))) : 8;
+    }
+    return sms * per_sm;
 #else
     return 2;
 #endif

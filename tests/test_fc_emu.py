@@ -73,7 +73,7 @@ def oracle(cp, hn, dist, nrm, dgrad, cog, w_fc=1.0, w_dis=100.0):
     return E.detach().numpy(), E_dis.detach().numpy(), lam.detach().numpy(), cpt.grad.numpy(), hnt.grad.numpy(), info
 
 
-@pytest.mark.parametrize("B,n_c", [(3, 12), (2, 16), (2, 4)])
+@pytest.mark.parametrize("B,n_c", [(3, 12), (2, 16), (2, 4), (3, 4), (3, 8)])  # n_c <= 8: two candidates per warp, odd B
 def test_fc_dis_vs_oracle(emu, B, n_c):
     inp = _inputs(B, n_c, 10 + n_c)
     P = fc_params()
