@@ -126,6 +126,9 @@ def parse():
     ap.add_argument("--global-rms", action="store_true",
                     help="N>1: all-reduce the batch-wide MALA*/qpth statistics every iteration (shard.GlobalStats); the "
                          "default is the reference's practice of one independent process per object group")
+    ap.add_argument("--shard-global", action="store_true",
+                    help="N>1: deal the config's GLOBAL object list (config3: 64 meshes, config4: 256, config5: 32) "
+                         "round-robin over the ranks instead of replicating the per-GPU list (strong scaling)")
     ap.add_argument("--cpu-sample-batch", type=int, default=16)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--sustain", type=int, default=2000,
@@ -250,7 +253,8 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.lib()
     be = engine.TorchBackend(dev)
-    w = workload.build(args.workload, rank=rank, batch_each=args.batch, n_objects=args.objects)
+    w = workload.build(args.workload, rank=rank, batch_each=args.batch, n_objects=args.objects,
+                       world=world if args.shard_global else None)
     B, n_c, O = w["batch_each"], w["n_contact"], len(w["face_verts"])
     Bt = B * O
     t_setup = time.perf_counter()
@@ -395,7 +399,6 @@ def run_b200(args):
     if world == 1 and args.sustain > 0:
         from graspqp_b200 import initializations
         eng.enable_device_init([initializations.convex_hull(fv.reshape(-1, 3)) for fv in w["face_verts"]])
-        cnt_off = int(lib.gqp_hand_distance_counter_offset(O, B, eng.n_pts, 0, be.ptr(eng.pen_scratch)))
         i_pen = engine.TERMS.index("E_pen")
         win, windows, n_resets, n_reset_rows, reset_ms = 250, [], 0, 0, []
         n_total = args.sustain
@@ -421,7 +424,8 @@ def run_b200(args):
                 torch.cuda.synchronize()
                 ms = [a.elapsed_time(b) for a, b in evs2]
                 evs2 = []
-                cnt = eng.pen_scratch.view(torch.int32)[cnt_off:cnt_off + 2].tolist()
+                cnt = eng.pen_counters()
+                eng.assert_ok()
                 windows.append({"iterations": [eng.iteration - len(ms) + 1, eng.iteration],
                                 "ms_per_step": round(float(np.mean(ms)), 4), "ms_max": round(float(np.max(ms)), 4),
                                 "mean_E_pen": round(float(eng.losses[i_pen].mean().item()), 5),
@@ -442,10 +446,14 @@ def run_b200(args):
     # ---- max over ranks, gather ----
     ms_pen = stage_ms["hand_distance"]
     t = torch.tensor([ms_total, ms_e2e, ms_pen], dtype=torch.float64, device=dev)
+    Bt_total, O_total = Bt * world, O * world
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tot = torch.tensor([Bt, O], dtype=torch.int64, device=dev)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        Bt_total, O_total = int(tot[0]), int(tot[1])
         # final grasps of all ranks in global object order (the only data exchange of the path by default)
-        shard.gather_results(eng.pose, eng.energy, eng.idx, O * world, B, rank, world)
+        shard.gather_results(eng.pose, eng.energy, eng.idx, O_total, B, rank, world)
     ms_total, ms_e2e, ms_pen = [float(v) for v in t.tolist()]
     final_energy = float(eng.energy.float().mean().item())
     eng.close()
@@ -507,19 +515,22 @@ def run_b200(args):
                         "frac": alg_bytes / (st_ms[top] * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes": alg_bytes,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
         line = {
-            "metric": METRIC, "value": Bt * world * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+            "metric": METRIC, "value": Bt_total * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True,
+            "scaling": "strong" if (args.shard_global and world > 1) else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
                                    f"{w['faces_per_mesh']} tris), batch {B}/object, n_contact {n_c}, 2500 surface samples",
-                       "candidates_per_gpu": Bt, "l2": "flushed between timed steps (256 MiB write)",
+                       "candidates_per_gpu": Bt, "objects_total": O_total, "candidates_total": Bt_total,
+                       "sharding": ("global object list dealt round-robin over the ranks (shard.objects_of_rank)"
+                                    if args.shard_global else "per-GPU object list replicated per rank"), "l2": "flushed between timed steps (256 MiB write)",
                        "qp_batch_stop": qp_batch_stop, "streams": 2 if overlap else 1, "cuda_graph": bool(graphed),
                        "collectives": ("global rms + qp exit words all-reduced per step" if args.global_rms else
                                        "none on the data path; final all-gather of grasps") if world > 1 else "n/a",
                        "noise": "philox on device (value) / injected from host (e2e)",
                        "e2e_pipeline": "double-buffered, copies on a second stream: upload k+1 and enqueue k+1 before reading back k",
                        "setup_s": round(t_setup, 2), "final_mean_energy": final_energy},
-            "e2e": {"value": Bt * world * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+            "e2e": {"value": Bt_total * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h},
             "gpu_launches": launches, "clocks": clocks,
             "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},

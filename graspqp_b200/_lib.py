@@ -64,6 +64,8 @@ SIGNATURES = {
     "gqp_hand_distance_full": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_hand_distance_backward": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_hand_distance_scratch_floats": (c_uint64, [c_int, c_int, c_int, c_int]),
+    "gqp_hand_distance_scratch_floats_bounded": (c_uint64, [c_int, c_int, c_int, c_int, c_int]),
+    "gqp_hand_distance_bounded": (c_int, [c_void_p, P, P, c_int, c_int, c_int, c_int, P, P, c_float, P, c_int, P]),
     "gqp_hand_distance_counter_offset": (c_uint64, [c_int, c_int, c_int, c_int, P]),
     "gqp_hand_pen_info": (c_int, [c_void_p, P]),
     "gqp_hand_link_grid": (c_int, [c_void_p, c_int, P, P, P, c_int]),

@@ -372,7 +372,7 @@ template <bool TF16>
 __global__ void __launch_bounds__(PEN_THREADS)
 pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, const float *__restrict__ link_tf,
                    const float *__restrict__ x, int n_pts, uint32_t *__restrict__ counter,
-                   const PenItem *__restrict__ items, PenGroup *__restrict__ queue) {
+                   const PenItem *__restrict__ items, PenGroup *__restrict__ queue, unsigned queue_cap) {
     GQP_DYN_SMEM(unsigned char, sm);
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) mbar_init(&bar);
@@ -404,9 +404,14 @@ pen_collect_kernel(const unsigned char *__restrict__ blob, int prefix_bytes, con
         const unsigned em = __ballot_sync(GQP_FULL, need != 0);
         if (em) {
             int base = 0;
-            if (lane == 0) base = (int)atomicAdd(counter, (unsigned)__popc(em));
+            if (lane == 0) {
+                base = (int)atomicAdd(counter, (unsigned)__popc(em));
+                // a bounded queue that fills up sets the overflow word: the caller must treat the result as invalid
+                if ((unsigned)base + (unsigned)__popc(em) > queue_cap) atomicOr(counter + 2, 1u);
+            }
             base = __shfl_sync(GQP_FULL, base, 0);
-            if (need) queue[base + __popc(em & ((1u << lane) - 1u))] = PenGroup{(uint32_t)(b * n_pts + pi), need};
+            const unsigned slot = (unsigned)base + (unsigned)__popc(em & ((1u << lane) - 1u));
+            if (need && slot < queue_cap) queue[slot] = PenGroup{(uint32_t)(b * n_pts + pi), need};
         }
     }
 }
@@ -424,12 +429,13 @@ pen_search_kernel(const unsigned char *__restrict__ blob, const GqpBvhNode *__re
                   const int32_t *__restrict__ face_id, const float *__restrict__ pre, float extent,
                   const float *__restrict__ link_tf, const float *__restrict__ x, int batch_each, int n_pts,
                   int per_candidate_points, const uint32_t *__restrict__ counter, const PenGroup *__restrict__ queue,
-                  unsigned long long *__restrict__ acc, float w_pen, float *__restrict__ grad_link_tf) {
+                  unsigned queue_cap, unsigned long long *__restrict__ acc, float w_pen,
+                  float *__restrict__ grad_link_tf) {
     __shared__ int2 stk[PEN_Q_WARPS * 32 / GQP_GANG][GQP_GANG_STACK];
     const PenHdr *hdr = reinterpret_cast<const PenHdr *>(blob);
     const PenLink *links = reinterpret_cast<const PenLink *>(blob + hdr->links_off);
     const int L = hdr->n_links;
-    const int n_groups = (int)*counter;
+    const int n_groups = (int)min(*counter, queue_cap);
     const int gl = threadIdx.x & (GQP_GANG - 1);
     const bool tf16 = ((uintptr_t)link_tf & 15) == 0;  // 128-bit loads of the link transforms when aligned
     // per-gang state of the sample being searched (identical on the 8 lanes)
@@ -750,9 +756,15 @@ static int pen_search_grid() {
 #endif
 }
 
+// queue capacity of the culled path: samples per candidate on average (0 = n_pts: can never fill up)
+static unsigned long long pen_queue_cap(unsigned long long Bt, int n_pts, int queue_per_candidate) {
+    const int q = queue_per_candidate > 0 ? std::min(queue_per_candidate, n_pts) : n_pts;
+    return Bt * (unsigned long long)q;
+}
 static int hand_distance_impl(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
                               int n_pts, int per_candidate_points, float *dist, int32_t *arg_link, float *dgrad,
-                              float *e_pen, float *scratch, float w_pen, float *grad_link_tf, void *stream) {
+                              float *e_pen, float *scratch, float w_pen, float *grad_link_tf, void *stream,
+                              int queue_per_candidate = 0) {
     if (!h || n_obj < 0 || batch_each < 0 || n_pts <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_distance: bad argument");
     const int Bt = n_obj * batch_each;
     if (Bt == 0) return GQP_OK;
@@ -762,6 +774,8 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
     const int n_rows = per_candidate_points ? Bt : n_obj, cands_per_row = per_candidate_points ? 1 : batch_each;
     const long long n_tasks = (long long)n_rows * n_chunks * ((cands_per_row + PEN_CB - 1) / PEN_CB);
     if (n_tasks > 0x7fffffffLL) return gqp_set_error(GQP_ERR_LIMIT, "gqp_hand_distance: too many point chunks");
+    if ((long long)Bt * n_pts > 0x7fffffffLL)  // queued sample ids are 32-bit (b * n_pts + sample)
+        return gqp_set_error(GQP_ERR_LIMIT, "gqp_hand_distance: candidates x samples exceeds 2^31 (%d x %d)", Bt, n_pts);
     const GqpPenTables *T = h->pen;
     // scratch: [Bt*n_chunks partial sums][n_rows*(n_chunks+1)*4 bounding spheres][Bt link masks]
     float *partial = scratch;
@@ -778,7 +792,8 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
         uint32_t *counter = tail;  // [0] groups queued for the search, [1] work items of the narrow phase
         unsigned long long *acc = reinterpret_cast<unsigned long long *>(tail + 4);
         PenGroup *queue = reinterpret_cast<PenGroup *>(acc + Bt);
-        PenItem *items = reinterpret_cast<PenItem *>(queue + (size_t)Bt * n_pts);
+        const unsigned long long qcap = pen_queue_cap((unsigned long long)Bt, n_pts, queue_per_candidate);
+        PenItem *items = reinterpret_cast<PenItem *>(queue + qcap);
         items = reinterpret_cast<PenItem *>(((uintptr_t)items + 15) & ~(uintptr_t)15);
         rc = gqp_memset_zero(tail, 16 + sizeof(unsigned long long) * (size_t)Bt, stream);
         if (rc != GQP_OK) return rc;
@@ -790,15 +805,15 @@ static int hand_distance_impl(const GqpHand *h, const float *link_tf, const floa
         int grid1 = pen_grid_size(prefix, (long long)Bt * n_chunks, 3);
         if (((uintptr_t)link_tf & 15) == 0) {
             GQP_LAUNCH(pen_collect_kernel<true>, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x,
-                       n_pts, counter, items, queue);
+                       n_pts, counter, items, queue, (unsigned)qcap);
         } else {
             GQP_LAUNCH(pen_collect_kernel<false>, grid1, PEN_THREADS, (size_t)prefix, st, T->d_blob, prefix, link_tf, x,
-                       n_pts, counter, items, queue);
+                       n_pts, counter, items, queue, (unsigned)qcap);
         }
         GQP_CHECK_LAUNCH("gqp_hand_distance/collect");
         GQP_LAUNCH(pen_search_kernel, pen_search_grid(), PEN_Q_WARPS * 32, 0, st, T->d_blob, T->d_wide, T->d_wpre, T->d_tris,
                    T->d_face_id, T->d_pre, T->extent, link_tf, x, batch_each, n_pts, per_candidate_points, counter, queue,
-                   e_pen ? acc : nullptr, w_pen, grad_link_tf);
+                   (unsigned)qcap, e_pen ? acc : nullptr, w_pen, grad_link_tf);
         GQP_CHECK_LAUNCH("gqp_hand_distance/search");
         if (e_pen) {
             GQP_LAUNCH(pen_reduce_fixed_kernel, (Bt + 127) / 128, 128, 0, st, acc, Bt, e_pen);
@@ -975,11 +990,21 @@ extern "C" int gqp_hand_link_planes(const GqpHand *h, int link, float *planes_ho
     return K.n_planes;
 }
 
-extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {
+extern "C" uint64_t gqp_hand_distance_scratch_floats_bounded(int n_obj, int batch_each, int n_pts,
+                                                             int per_candidate_points, int queue_per_candidate) {
     const uint64_t Bt = (uint64_t)n_obj * batch_each, n_chunks = (n_pts + 31) / 32;
     const uint64_t n_rows = per_candidate_points ? Bt : (uint64_t)n_obj;
     // + culled path: counters (4 words + alignment), fixed-point accumulators (2 words each), queue (2 words per
-    // sample), work items of the narrow phase (4 words per candidate and chunk, 16-byte aligned)
-    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16 + 8 + 2 * Bt + 2 * Bt * (uint64_t)n_pts +
-           4 * Bt * n_chunks + 4;
+    // queued sample), work items of the narrow phase (4 words per candidate and chunk, 16-byte aligned)
+    return Bt * n_chunks + n_rows * (n_chunks + 1) * 4 + Bt + 16 + 8 + 2 * Bt +
+           2 * pen_queue_cap(Bt, n_pts, queue_per_candidate) + 4 * Bt * n_chunks + 4;
+}
+extern "C" uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points) {
+    return gqp_hand_distance_scratch_floats_bounded(n_obj, batch_each, n_pts, per_candidate_points, 0);
+}
+extern "C" int gqp_hand_distance_bounded(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
+                                         int n_pts, int per_candidate_points, float *e_pen, float *scratch, float w_pen,
+                                         float *grad_link_tf, int queue_per_candidate, void *stream) {
+    return hand_distance_impl(h, link_tf, x, n_obj, batch_each, n_pts, per_candidate_points, nullptr, nullptr, nullptr,
+                              e_pen, scratch, w_pen, grad_link_tf, stream, queue_per_candidate);
 }

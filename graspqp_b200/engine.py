@@ -122,7 +122,7 @@ class FitEngine:
                  weights=None, friction=0.2, max_limit=20.0, svd_gain=0.1, torque_weight=5.0, switch_possibility=0.4,
                  starting_temperature=18.0, temperature_decay=0.95, annealing_period=30, step_size=0.005,
                  stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1, collectives=None,
-                 overlap=True):
+                 overlap=True, queue_per_candidate=None):
         self.lib, self.be = cdll, backend
         self.pack = pack
         self.n_obj = len(face_verts_list)
@@ -194,7 +194,14 @@ class FitEngine:
         self.ones = be.from_host(np.ones((Bt, n_c), f32))
         self.lam = be.empty((Bt, n_c), f32)
         self.g_pose_joints = be.empty((Bt, D), f32)
-        self.pen_scratch = be.empty((int(cdll.gqp_hand_distance_scratch_floats(self.n_obj, self.batch_each, self.n_pts, 0)),), f32)
+        # survivor queue of the penetration stage: unbounded (n_pts per candidate, 20 KB each) for small batches, 512 per
+        # candidate on average from 64k candidates on (20-45 are observed along a fit; overflow is detected, assert_ok)
+        self.queue_per_candidate = int(queue_per_candidate if queue_per_candidate is not None else
+                                       (0 if Bt < 65536 else 512))
+        self.pen_scratch = be.empty((int(cdll.gqp_hand_distance_scratch_floats_bounded(
+            self.n_obj, self.batch_each, self.n_pts, 0, self.queue_per_candidate)),), f32)
+        self.pen_counter_off = int(cdll.gqp_hand_distance_counter_offset(self.n_obj, self.batch_each, self.n_pts, 0,
+                                                                         be.ptr(self.pen_scratch)))
         self.qp_ws = be.empty(((int(cdll.gqp_fc_workspace_bytes(Bt, n_c, self.fc.max_iter)) + 7) // 8,), np.float64)
         self.qp_stop = be.empty((1,), i32)
         self.reset_all = be.from_host(np.ones(Bt, u8))
@@ -239,8 +246,9 @@ class FitEngine:
                                    p(self.qp_stop), st))
         # the side chain is enqueued AFTER the critical chain: its persistent CTAs then fill what the one-wave
         # object-distance / QP kernels leave free instead of holding the SMs while the critical chain waits
-        self._ck(lib.gqp_hand_distance(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None,
-                                       row("E_pen"), p(self.pen_scratch), self.weights["E_pen"], p(self.g_link_tf), s2))
+        self._ck(lib.gqp_hand_distance_bounded(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0,
+                                               row("E_pen"), p(self.pen_scratch), self.weights["E_pen"],
+                                               p(self.g_link_tf), self.queue_per_candidate, s2))
         self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
                                          self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
                                          p(self.g_pose_joints), s2))
@@ -347,6 +355,22 @@ class FitEngine:
             else:
                 self.step()
 
+    def pen_counters(self):
+        """(samples queued for the exact search, work items, overflow flag) of the last penetration stage; synchronises"""
+        v = self.be.to_host(self.pen_scratch.view(np.int32) if isinstance(self.pen_scratch, np.ndarray)
+                            else self.pen_scratch.view(self.be.torch.int32)[self.pen_counter_off:self.pen_counter_off + 3])
+        if isinstance(self.pen_scratch, np.ndarray):
+            v = v[self.pen_counter_off:self.pen_counter_off + 3]
+        return int(v[0]), int(v[1]), int(v[2])
+
+    def assert_ok(self):
+        """Raises if the bounded survivor queue of the last evaluated iteration overflowed (its E_pen is invalid)."""
+        q, _, over = self.pen_counters()
+        if over:
+            raise _lib.GqpError(f"penetration survivor queue overflowed ({q} samples queued, capacity "
+                                f"{self.queue_per_candidate} per candidate): construct FitEngine with a larger "
+                                "queue_per_candidate (0 = unbounded)")
+
     _STATE = ("pose", "idx", "grad", "ema", "step_count", "energy", "losses")
 
     def snapshot(self):
@@ -377,9 +401,9 @@ class FitEngine:
                 ctypes.byref(self.fc), p(self.cpts), p(self.cnrm), p(self.obj_dist), p(self.obj_nrm), p(self.obj_dgrad),
                 p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop), row("E_fc"), row("E_dis"), p(self.lam),
                 p(self.g_cpts), p(self.g_cnrm), p(self.qp_stop), st),
-            "hand_distance": lambda: lib.gqp_hand_distance(
-                self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, None, row("E_pen"), p(self.pen_scratch),
-                self.weights["E_pen"], p(self.g_link_tf), st),
+            "hand_distance": lambda: lib.gqp_hand_distance_bounded(
+                self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0, row("E_pen"), p(self.pen_scratch),
+                self.weights["E_pen"], p(self.g_link_tf), self.queue_per_candidate, st),
             "self_pen_joints": lambda: lib.gqp_self_pen_joints(
                 self.hand, p(self.link_tf), p(self.pose_new), Bt, row("E_spen"), row("E_joints"), self.weights["E_spen"],
                 self.weights["E_joints"], p(self.g_link_tf), p(self.g_pose_joints), st),

@@ -158,9 +158,20 @@ int gqp_hand_distance_backward(const GqpHand *h, const float *link_tf, const flo
                                int n_pts, int per_candidate_points, const float *grad_dist, const int32_t *arg_link,
                                const float *dgrad, float *grad_link_tf, void *stream);
 uint64_t gqp_hand_distance_scratch_floats(int n_obj, int batch_each, int n_pts, int per_candidate_points);
+/* The culled form (dist == NULL) with a BOUNDED survivor queue: queue_per_candidate samples per candidate ON AVERAGE over
+ * the batch (0 = n_pts, the unbounded default of gqp_hand_distance: 20 KB of scratch per candidate at 2500 samples, where
+ * 20-45 survivors per candidate are observed along a fit).  If the queue fills up, word 2 of the counters
+ * (gqp_hand_distance_counter_offset) is set and e_pen / the gradient of THAT call are invalid: callers check it at
+ * their next synchronisation point (FitEngine.assert_ok) — nothing is dropped silently. */
+uint64_t gqp_hand_distance_scratch_floats_bounded(int n_obj, int batch_each, int n_pts, int per_candidate_points,
+                                                  int queue_per_candidate);
+int gqp_hand_distance_bounded(const GqpHand *h, const float *link_tf, const float *x, int n_obj, int batch_each,
+                              int n_pts, int per_candidate_points, float *e_pen, float *scratch, float w_pen,
+                              float *grad_link_tf, int queue_per_candidate, void *stream);
 
 /* diagnostics: index (in 32-bit words) inside `scratch` of the culled path's counters after gqp_hand_distance(dist = NULL):
- * word 0 = samples that survived culling and were searched exactly, word 1 = (candidate, 32-sample chunk) work items */
+ * word 0 = samples that survived culling and were queued for the exact search, word 1 = (candidate, 32-sample chunk) work
+ * items, word 2 = 1 if a bounded queue overflowed (gqp_hand_distance_bounded) */
 uint64_t gqp_hand_distance_counter_offset(int n_obj, int batch_each, int n_pts, int per_candidate_points,
                                           const void *scratch);
 

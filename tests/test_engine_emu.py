@@ -93,3 +93,27 @@ def test_sub_batch_check_with_batch_wide_statistics(emu):
         wl.build = real
         del wl.CONFIGS["tiny"]
     assert all(r["energy_max"] <= 1e-4 and r["grad_max"] <= 1e-4 for r in rep.values())
+
+
+def test_bounded_survivor_queue_overflow_is_detected(emu):
+    """queue_per_candidate bounds the scratch of the penetration stage; a queue that fills up must be reported, never
+    silently truncated"""
+    from graspqp_b200 import _lib
+    pack, fv, sp, pose, idx = make_case(B=4, n_c=4, n_pts=64)
+    pose = pose.copy()
+    pose[:, :3] *= 0.3  # hands deep inside the object: many samples survive the culling
+    ref = engine.FitEngine(emu, engine.NumpyBackend(), pack, [fv], sp[None], 4, pose, idx.astype(np.int32))
+    q, _, over = ref.pen_counters()
+    assert q > 8 and not over
+    ref.assert_ok()
+    roomy = engine.FitEngine(emu, engine.NumpyBackend(), pack, [fv], sp[None], 4, pose, idx.astype(np.int32),
+                             queue_per_candidate=64)
+    np.testing.assert_array_equal(roomy.losses, ref.losses)
+    roomy.assert_ok()
+    tight = engine.FitEngine(emu, engine.NumpyBackend(), pack, [fv], sp[None], 4, pose, idx.astype(np.int32),
+                             queue_per_candidate=1)
+    assert tight.pen_counters()[2] == 1
+    with pytest.raises(_lib.GqpError):
+        tight.assert_ok()
+    for e in (ref, roomy, tight):
+        e.close()
