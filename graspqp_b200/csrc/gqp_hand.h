@@ -44,7 +44,8 @@ void gqp_bvh_widen(GqpBvhHost &bvh);
 bool gqp_mesh_is_nice(const float *face_verts, int F);
 // Planes under which the "nice mesh => +1 outside" argument fails IN FP32 (gqp_bvh.cpp: gqp_mesh_tie_planes):
 // 4 floats per plane (unit normal, offset n.a); false when the mesh has more than max_planes of them.
-bool gqp_mesh_tie_planes(const float *face_verts, int F, int max_planes, std::vector<float> &planes);
+bool gqp_mesh_tie_planes(const float *face_verts, int F, int max_planes, std::vector<float> &planes,
+                         std::vector<float> &anchors, int max_anchors);
 void gqp_outside_grid_build(const GqpBvhHost &bvh, const float origin[3], float cell, const int dim[3],
                             std::vector<uint32_t> &bits);
 

@@ -27,14 +27,15 @@ struct PenLink {
     int32_t wide_first;  // first wide node of the link's 8-wide tree in GqpPenTables::d_wide
     float lo[3], hi[3];  // bounding box, slightly inflated
     int32_t plane_first, n_planes;  // tie planes of the link (gqp_bvh.cpp: gqp_mesh_tie_planes), float4 each
-    int32_t pad2[2];
+    int32_t anchor_first, n_anchors;  // vertices of the tie faces (float4 each, same table, after the planes)
 };
 // slab behind a tie plane in which the reference's fp32 first-minimum rule may return -1 for an OUTSIDE point:
-// -GQP_TIE_NEG * D <= n.q - a <= GQP_TIE_POS * D, D >= distance of q to the link (sqrt(8 ulp) = 1e-3, doubled; the
-// positive side covers the rounding of the sign's dot product)
-#define GQP_TIE_NEG 2e-3f
+// -GQP_TIE_NEG * D <= n.q - a <= GQP_TIE_POS * D, D >= distance of q to the link (fp32 spacing allows depth / distance up
+// to sqrt(2^-23) = 3.45e-4, 2.43e-4 is the largest seen; the positive side covers the rounding of the sign's dot product)
+#define GQP_TIE_NEG 5e-4f
 #define GQP_TIE_POS 2e-6f
 #define PEN_MAX_PLANES 32
+#define PEN_MAX_ANCHORS 24
 __device__ __forceinline__ float pen_link_reach(const PenLink &K, V3 q) {  // upper bound of |q - any point of the link|
     const V3 ctr = V3{0.5f * (K.lo[0] + K.hi[0]), 0.5f * (K.lo[1] + K.hi[1]), 0.5f * (K.lo[2] + K.hi[2])};
     const V3 h = V3{0.5f * (K.hi[0] - K.lo[0]), 0.5f * (K.hi[1] - K.lo[1]), 0.5f * (K.hi[2] - K.lo[2])};
@@ -45,11 +46,26 @@ __device__ __forceinline__ float pen_link_reach(const PenLink &K, V3 q) {  // up
 // link's planes: nothing in it may be culled
 __device__ __forceinline__ bool pen_in_tie_slab(const PenLink &K, const float4 *planes, V3 q, float rad) {
     if (K.n_planes == 0) return false;
-    const float D = pen_link_reach(K, q) + rad;
+    float D = pen_link_reach(K, q) + rad;
+    bool hit = false;
     for (int i = 0; i < K.n_planes; ++i) {
         const float4 P = planes[K.plane_first + i];
         const float hgt = P.x * q.x + P.y * q.y + P.z * q.z - P.w;
-        if (hgt - rad <= GQP_TIE_POS * D && hgt + rad >= -GQP_TIE_NEG * D) return true;
+        if (hgt - rad <= GQP_TIE_POS * D && hgt + rad >= -GQP_TIE_NEG * D) hit = true;
+    }
+    if (!hit || rad > 0.f) return hit;
+    // a point inside the coarse slab: tighten the distance bound with the nearest anchor vertex and test again
+    float d2 = D * D;
+    for (int i = 0; i < K.n_anchors; ++i) {
+        const float4 A = planes[K.anchor_first + i];
+        const float dx = q.x - A.x, dy = q.y - A.y, dz = q.z - A.z;
+        d2 = fminf(d2, dx * dx + dy * dy + dz * dz);
+    }
+    D = sqrtf(d2) * 1.001f;
+    for (int i = 0; i < K.n_planes; ++i) {
+        const float4 P = planes[K.plane_first + i];
+        const float hgt = P.x * q.x + P.y * q.y + P.z * q.z - P.w;
+        if (hgt <= GQP_TIE_POS * D && hgt >= -GQP_TIE_NEG * D) return true;
     }
     return false;
 }
@@ -643,12 +659,15 @@ int gqp_pen_tables_create(GqpHand *h, const float *face_verts_host) {
                 K.lo[k] = root.lo[k] - 2e-5f;
                 K.hi[k] = root.hi[k] + 2e-5f;
             }
-            std::vector<float> tie;
+            std::vector<float> tie, anchors;
             if (gqp_mesh_is_nice(face_verts_host + 9 * (size_t)f0, F) &&
-                gqp_mesh_tie_planes(face_verts_host + 9 * (size_t)f0, F, PEN_MAX_PLANES, tie)) {
+                gqp_mesh_tie_planes(face_verts_host + 9 * (size_t)f0, F, PEN_MAX_PLANES, tie, anchors, PEN_MAX_ANCHORS)) {
                 K.plane_first = (int)(planes.size() / 4);
                 K.n_planes = (int)(tie.size() / 4);
                 planes.insert(planes.end(), tie.begin(), tie.end());
+                K.anchor_first = (int)(planes.size() / 4);
+                K.n_anchors = (int)(anchors.size() / 4);
+                planes.insert(planes.end(), anchors.begin(), anchors.end());
                 PenGrid G{};
                 float cell = 0.002f;
                 int dim[3];
@@ -984,9 +1003,11 @@ extern "C" int gqp_hand_link_planes(const GqpHand *h, int link, float *planes_ho
         slab_host[1] = GQP_TIE_POS;
     }
     if (planes_host) {
-        if (max_planes < K.n_planes) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_planes: planes_host too small");
-        std::memcpy(planes_host, B.data() + hdr->planes_off + 16 * (size_t)K.plane_first, 16 * (size_t)K.n_planes);
+        if (max_planes < K.n_planes + K.n_anchors) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_link_planes: planes_host too small");
+        std::memcpy(planes_host, B.data() + hdr->planes_off + 16 * (size_t)K.plane_first,
+                    16 * (size_t)(K.n_planes + K.n_anchors));  // the anchors follow the planes in the table
     }
+    if (slab_host) slab_host[2] = (float)K.n_anchors;
     return K.n_planes;
 }
 

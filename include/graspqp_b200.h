@@ -187,10 +187,11 @@ int gqp_hand_link_grid(const GqpHand *h, int link, float *geom_host, int32_t *di
                        int max_words);
 
 /* The link's "tie planes" (4 floats each: unit normal, offset) -> returns their number (>= 0) or a negative error.
- * slab_host[2] (may be NULL) = {NEG, POS}: a point q of the link frame with  -NEG*D <= n.q - offset <= POS*D  for one of
- * the planes (D = |q - box centre| + box half-diagonal) is NEVER culled: behind the extended plane of a face at a
- * right-angle crease the reference's fp32 first-minimum rule can return sign -1 for outside points (csrc/gqp_bvh.cpp:
- * gqp_mesh_tie_planes). */
+ * slab_host[3] (may be NULL) = {NEG, POS, number of anchors}; planes_host then receives the planes followed by the anchor
+ * vertices (xyz0), max_planes counting both.  A point q of the link frame with  -NEG*D <= n.q - offset <= POS*D  for one
+ * of the planes is NEVER culled, first with D = |q - box centre| + box half-diagonal, then (points only) with
+ * D = 1.001 * distance to the nearest anchor: behind the extended plane of a face at a right-angle crease the reference's
+ * fp32 first-minimum rule can return sign -1 for outside points (csrc/gqp_bvh.cpp: gqp_mesh_tie_planes). */
 int gqp_hand_link_planes(const GqpHand *h, int link, float *planes_host, int max_planes, float *slab_host);
 
 /* ---- H5 + E_joints: self_penetration (hand_model.py:989-1040) and joint limits (energy.py:47-54) ------------------

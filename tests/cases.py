@@ -241,20 +241,30 @@ def link_grid(lib, hand, link):
 def link_planes(lib, hand, link):
     n = lib.gqp_hand_link_planes(hand, link, None, 0, None)
     assert n >= 0, lib.gqp_last_error()
-    planes, slab = np.zeros((max(n, 1), 4), np.float32), np.zeros(2, np.float32)
-    assert lib.gqp_hand_link_planes(hand, link, planes.ctypes.data, n, slab.ctypes.data) == n
-    return planes[:n], slab
+    slab = np.zeros(3, np.float32)
+    lib.gqp_hand_link_planes(hand, link, None, 0, slab.ctypes.data)
+    n_a = int(slab[2])
+    table = np.zeros((max(n + n_a, 1), 4), np.float32)
+    assert lib.gqp_hand_link_planes(hand, link, table.ctypes.data, n + n_a, slab.ctypes.data) == n
+    return table[:n], slab[:2], table[n:n + n_a, :3]
 
 
-def in_tie_slab(q, planes, slab, lo, hi):
-    """csrc/gqp_pen.cu:pen_in_tie_slab for points (rad = 0), in fp32 like the kernel"""
+def in_tie_slab(q, planes, slab, lo, hi, anchors=None):
+    """csrc/gqp_pen.cu:pen_in_tie_slab for points (rad = 0), in fp32 like the kernel: the coarse slab (distance bounded by
+    the link's bounding sphere), then the slab with the distance bounded by the nearest anchor vertex"""
     q = np.asarray(q, np.float32)
     if len(planes) == 0:
         return np.zeros(len(q), bool)
     ctr, half = np.float32(0.5) * (lo + hi), np.float32(0.5) * (hi - lo)
     D = np.sqrt(((q - ctr) ** 2).sum(1, dtype=np.float32)) + np.sqrt((half ** 2).sum(dtype=np.float32))
     hgt = q @ planes[:, :3].T - planes[:, 3]
-    return ((hgt <= slab[1] * D[:, None]) & (hgt >= -slab[0] * D[:, None])).any(1)
+    coarse = ((hgt <= slab[1] * D[:, None]) & (hgt >= -slab[0] * D[:, None])).any(1)
+    if anchors is None or len(anchors) == 0:
+        return coarse
+    d2 = np.minimum(D * D, ((q[:, None, :] - anchors[None]) ** 2).sum(-1, dtype=np.float32).min(1))
+    D2 = np.sqrt(d2) * np.float32(1.001)
+    fine = ((hgt <= slab[1] * D2[:, None]) & (hgt >= -slab[0] * D2[:, None])).any(1)
+    return coarse & fine
 
 
 def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0, max_cells=None):
@@ -303,11 +313,22 @@ def check_culling_proof(lib, sign_fn, hand_name, per_cell=4, n_far=20000, seed=0
         far = far[~((far >= lo) & (far <= hi)).all(1)]
         near = (ctr + (rng.random((n_far, 3)) * 2 - 1) * half * 1.3).astype(np.float32)  # just outside the box faces
         near = near[~((near >= lo) & (near <= hi)).all(1)]
-        q = np.concatenate([pts, far, near])
+        extra = [pts, far, near]
+        planes, slab, anchors = link_planes(lib, hand, l)
+        if len(planes):
+            # stress the slab's boundary: points thrown at the planes, heights within +-3e-3 of their distance bound
+            m = n_far // 2
+            base = (ctr + (rng.random((m, 3)) * 2 - 1) * (half + 0.4)).astype(np.float64)
+            k = rng.integers(0, len(planes), m)
+            nk, ak = planes[k, :3].astype(np.float64), planes[k, 3].astype(np.float64)
+            Dk = np.linalg.norm(base - ctr, axis=1) + np.linalg.norm(half)
+            newh = (rng.random(m) * 3.1e-3 - 3e-3) * Dk
+            base = (base + (newh - ((base * nk).sum(1) - ak))[:, None] * nk).astype(np.float32)
+            extra.append(base[~((base >= lo) & (base <= hi)).all(1)])
+        q = np.concatenate(extra)
         # the tie slabs behind the planes of faces at right-angle creases are never culled (gqp_mesh_tie_planes): there
         # the reference's fp32 first-minimum rule CAN say -1 for an outside point; count those as evidence
-        planes, slab = link_planes(lib, hand, l)
-        slab_pts = in_tie_slab(q, planes, slab, lo, hi)
+        slab_pts = in_tie_slab(q, planes, slab, lo, hi, anchors)
         n_slab_neg = 0
         if slab_pts.any():
             n_slab_neg = int((sign_fn(q[slab_pts], fv) != 1).sum())
@@ -364,7 +385,9 @@ def check_benched_state(lib, be, name="config2", iters=(0, 50, 500), per_object=
         out = orc.iterate(t64(us[sub]), torch.tensor(ir[sub]).long(), t64(ua[sub]), grad2_mean=H(eng.grad2_mean),
                           z=H(eng.z)[sub], qp_stop=int(H(eng.qp_stop)[0]))
         cp = H(eng.cpts)
-        ex = lambda r: tol.normal_unstable(cp[sub[r]], w["face_verts"][sub[r] // B])
+        cp_orc = orc.hand.contact_points.detach().numpy()
+        ex = lambda r: (tol.normals_differ(cp[sub[r]], cp_orc[r], w["face_verts"][sub[r] // B]) or
+                        tol.normal_unstable(cp[sub[r]], w["face_verts"][sub[r] // B]))
         lab = f"{name} Bt={Bt} iteration {n}"
         np.testing.assert_array_equal(H(eng.idx_new)[sub], out["idx_prop"].numpy(), err_msg=lab)
         np.testing.assert_allclose(H(eng.pose_new)[sub], out["proposal"].numpy(), rtol=1e-5, atol=1e-5, err_msg=lab)

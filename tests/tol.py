@@ -44,6 +44,18 @@ def normal_unstable(cpts_row, face_verts, jump=2e-6):
     return False
 
 
+def normals_differ(cpts_a, cpts_b, face_verts, jump=2e-6):
+    """Direct form of the same evidence: the two evaluations' OWN contact points of this candidate (fp32 kernel FK vs the
+    oracle's fp64 FK rounded to fp32, a few ulps apart) get object normals from the reference's SDF arithmetic that
+    differ by more than `jump` at some contact."""
+    from oracle import sdf as osdf
+    out = []
+    for c in (cpts_a, cpts_b):
+        _, sg, nr, _ = osdf.compute_sdf_port(np.asarray(c, np.float32).reshape(-1, 3), face_verts)
+        out.append(nr * sg[:, None])
+    return bool(np.abs(out[0] - out[1]).max() > jump)
+
+
 def assert_grad(got, want, label, tol=GRAD_TOL, excuse=None, max_excused=1):
     """excuse(row) -> bool: evidence that the row is a conditioning event (normal_unstable); at most `max_excused` rows
     may exceed the tolerance, each with that evidence."""
