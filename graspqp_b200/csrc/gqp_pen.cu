@@ -35,7 +35,7 @@ struct PenLink {
 #define GQP_TIE_NEG 5e-4f
 #define GQP_TIE_POS 2e-6f
 #define PEN_MAX_PLANES 32
-#define PEN_MAX_ANCHORS 24
+#define PEN_MAX_ANCHORS 8
 __device__ __forceinline__ float pen_link_reach(const PenLink &K, V3 q) {  // upper bound of |q - any point of the link|
     const V3 ctr = V3{0.5f * (K.lo[0] + K.hi[0]), 0.5f * (K.lo[1] + K.hi[1]), 0.5f * (K.lo[2] + K.hi[2])};
     const V3 h = V3{0.5f * (K.hi[0] - K.lo[0]), 0.5f * (K.hi[1] - K.lo[1]), 0.5f * (K.hi[2] - K.lo[2])};
