@@ -77,6 +77,8 @@ SIGNATURES = {
     "gqp_fc_solve": (c_int, [POINTER(GqpFcParams), P, P, P, c_int, c_int, c_int, P, P]),
     "gqp_fc_finish": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, c_int, P, P, P, P, P, P, P]),
     "gqp_mala_stats": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P]),
+    "gqp_mala_stats_noalloc": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P]),
+    "gqp_mala_stats_noalloc_max_floats": (c_uint64, []),
     "gqp_mala_propose": (c_int, [POINTER(GqpMalaParams), P, P, P, P, P, P, c_int, c_int, c_int, c_int, P, P, c_uint64,
                                  c_uint64, P, P, P, P]),
     "gqp_mala_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, P, P, c_uint64, c_uint64,

@@ -220,6 +220,55 @@ extern "C" int gqp_mala_stats(const float *grad, const float *energy, int n_obj,
     return GQP_OK;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) ----------------
+// Callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc)
+// cannot provide gqp_mala_stats' scratch.  This variant keeps it in a file-scope device array: every GPU that loads the
+// library holds GQP_STATS_STATIC_FLOATS * 4 bytes = 256 KB until exit.  All calls share the array, which keeps the last
+// call's contents: nothing in it has to start at zero (every partial sum the final pass reads is written by the first pass
+// of the same call), but two calls that overlap on the GPU (different streams) race on it.
+#define GQP_STATS_STATIC_FLOATS 65536
+static __device__ __align__(256) float g_stats_static[GQP_STATS_STATIC_FLOATS];
+#define GQP_MAX_DEVICES 64
+
+// device address of the array for the CURRENT device, looked up once per device (host code must not pass the symbol itself:
+// there its name is a host-side stand-in, not a device address)
+static int stats_static_ptr(float **out) {
+#ifndef GQP_EMU
+    static float *cache[GQP_MAX_DEVICES] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return gqp_set_error(GQP_ERR_CUDA, "gqp_mala_stats_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= GQP_MAX_DEVICES) return gqp_set_error(GQP_ERR_LIMIT, "gqp_mala_stats_noalloc: device %d out of range", dev);
+    if (!cache[dev]) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_stats_static);
+        if (e != cudaSuccess || !ptr)
+            return gqp_set_error(GQP_ERR_CUDA, "gqp_mala_stats_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        cache[dev] = static_cast<float *>(ptr);
+    }
+    *out = cache[dev];
+#else
+    *out = g_stats_static;
+#endif
+    return GQP_OK;
+}
+
+extern "C" uint64_t gqp_mala_stats_noalloc_max_floats(void) { return GQP_STATS_STATIC_FLOATS; }
+
+extern "C" int gqp_mala_stats_noalloc(const float *grad, const float *energy, int n_obj, int batch_each, int D,
+                                      int clip_grad, float *grad2_mean, float *z, void *stream) {
+    if (n_obj <= 0 || batch_each <= 0 || D <= 0 || !grad || !energy || !grad2_mean || !z)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_mala_stats_noalloc: bad argument");
+    const long long Bt = (long long)n_obj * batch_each, need = (Bt + STATS_ROWS - 1) / STATS_ROWS * D;
+    if (need > GQP_STATS_STATIC_FLOATS)
+        return gqp_set_error(GQP_ERR_LIMIT,
+                             "gqp_mala_stats_noalloc: %lld candidates x %d pose columns need %lld scratch floats, the static "
+                             "array holds %d (use gqp_mala_stats with caller-owned scratch)", Bt, D, need, GQP_STATS_STATIC_FLOATS);
+    float *scratch = nullptr;
+    if (int rc = stats_static_ptr(&scratch)) return rc;
+    return gqp_mala_stats(grad, energy, n_obj, batch_each, D, clip_grad, grad2_mean, z, scratch, stream);
+}
+
 extern "C" int gqp_mala_propose(const GqpMalaParams *p, const float *pose, const float *grad,
                                 const float *grad2_mean, float *ema, int32_t *step, const int32_t *idx, int Bt, int D,
                                 int n_c, int n_cand, const float *u_switch, const int32_t *idx_rand, uint64_t seed,

@@ -256,6 +256,16 @@ typedef struct GqpMalaParams {
 } GqpMalaParams;
 int gqp_mala_stats(const float *grad, const float *energy, int n_obj, int batch_each, int D, int clip_grad,
                    float *grad2_mean, float *z, float *scratch /* ceil(Bt/64)*D floats */, void *stream);
+/* gqp_mala_stats without caller-owned scratch and without ANY allocation (no cudaMalloc / cudaFree / allocating library
+ * call): the scratch is a static 256 KB device array inside the library (gqp_mala_stats_noalloc_max_floats() = 65536
+ * floats; needed: ceil(Bt/64)*D, e.g. 102 400 Allegro candidates), held by every GPU that loads the library until exit.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate (CUDA
+ * graph capture, serving loops).  Sizes beyond the maximum return GQP_ERR_LIMIT.  All calls share the array (it keeps the
+ * last call's contents; nothing in it needs to start at zero): calls that OVERLAP on the GPU (different streams) race.
+ * Same results as gqp_mala_stats, bit for bit. */
+int gqp_mala_stats_noalloc(const float *grad, const float *energy, int n_obj, int batch_each, int D, int clip_grad,
+                           float *grad2_mean, float *z, void *stream);
+uint64_t gqp_mala_stats_noalloc_max_floats(void);
 int gqp_mala_propose(const GqpMalaParams *p_host, const float *pose, const float *grad, const float *grad2_mean,
                      float *ema, int32_t *step, const int32_t *idx, int Bt, int D, int n_c, int n_cand,
                      const float *u_switch, const int32_t *idx_rand, uint64_t seed, uint64_t iteration, float *pose_new,
