@@ -298,9 +298,13 @@ def run_b200(args):
     # K iterations can be shorter than nvidia-smi's 100 ms period: keep the GPU under the SAME load (untimed iterations,
     # the state is restored before the end-to-end loop) until two rows have arrived since the timed region began
     t_load = time.perf_counter()
+    # (with per-step collectives every rank must run the SAME number of iterations, and this loop's trip count depends on
+    # each rank's nvidia-smi timing: a rank-local stage stands in for the load there — r2k: a full step here dead-locked
+    # --global-rms on a collective sequence mismatch until NCCL's 10-minute watchdog)
+    load_fn = eng.step if eng.collectives is None else eng.stage_calls()["hand_distance"]
     while sampler.proc is not None and sampler.count_since(t_timed) < 2 and time.perf_counter() - t_load < 3.0:
         flush.zero_()
-        eng.step()
+        load_fn()
         torch.cuda.synchronize()
     clocks = sampler.stop(t_timed)
     # ---- end-to-end: host noise in pinned memory -> device, step, energy + accept back to the host, every step ----
