@@ -36,7 +36,7 @@ COUNTER_METRICS = [  # collected by an ncu subprocess of THIS run (never from a 
 # stage -> the kernels one call of it launches (names as ncu prints them, prefix match)
 STAGE_KERNELS = {
     "object_distance": ("object_distance_kernel",),
-    "fc_solve": ("fc_dis_kernel<1>", "fc_dis_kernel<(int)1>"),
+    "fc_solve": ("fc_dis_kernel<1,", "fc_dis_kernel<(int)1,"),  # <MODE = FC_SOLVE, candidates per warp>
     "hand_distance": ("pen_bounds_kernel", "pen_broad_kernel", "pen_collect_kernel", "pen_search_kernel",
                       "pen_reduce_fixed_kernel"),
 }
