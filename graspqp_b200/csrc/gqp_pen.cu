@@ -3,17 +3,16 @@
 // energy.py:47-54).
 //
 // This is the dominant stage of a grasp-step: the reference runs n_links brute-force TorchSDF launches over
-// Bt*n_pts points (2500 x 3540 point-face tests per candidate for Allegro).  Here:
-//   * one persistent-style grid; every CTA first pulls the hand's "penetration blob" — link headers, far-field sign
-//     grids and the BVH nodes of ALL links — into shared memory with one TMA bulk copy (cp.async.bulk + mbarrier);
-//   * a warp owns 32 consecutive surface samples of one candidate and walks the links in lockstep;
-//   * per (point, link): world->link transform, then a sign-grid lookup (1 shared-memory word).  A set bit proves
-//     that the reference's sign heuristic yields +1 everywhere in that cell, i.e. the link cannot contribute to
-//     relu(max_l d_l): skip.  Otherwise an exact BVH nearest-face search (same winner as brute force).
-//   * energy partials are written per warp-task and summed in a fixed order (deterministic); the gradient w.r.t. the
-//     link transform is accumulated with atomics only for the few penetrating samples.
-// Bound: FP32/ALU issue + shared-memory latency.  Algorithmic HBM bytes per grasp-step: n_links*48 B of transforms
-// + 4 B of energy; the surface samples (30 KB per object) and triangles stay in L2/L1.
+// Bt*n_pts points (2500 x 3540 point-face tests per candidate for Allegro).  Two paths:
+//   * culled (the engine; E_pen and its gradient only): pen_bounds -> pen_broad (a warp per candidate: row / chunk
+//     bounding spheres vs link boxes) -> pen_collect (a warp per surviving (candidate, chunk): link headers, outside grids
+//     and tie planes in shared memory by one TMA bulk copy; a sample is dropped for a link when it is provably outside it
+//     AND not in a tie slab) -> pen_search (8-lane gangs walk the links' 8-wide trees for the queued samples, exact
+//     winner; energies in 2^-40 m fixed point, gradient by float atomics) -> pen_reduce_fixed;
+//   * dist-returning (HandModel.cal_distance callers): pen_mask -> hand_pen_kernel<false> (every link searched, per-sample
+//     distance / argmax link / gradient stored) -> pen_reduce.
+// Bound: FP32/ALU issue + L1/L2 latency.  Algorithmic HBM bytes per grasp-step: n_links*48 B of transforms + 4 B of
+// energy; the surface samples (30 KB per object) and triangles stay in L2/L1.
 #include "gqp_bvh.cuh"
 #include "gqp_stage.cuh"
 #include "graspqp_b200.h"
