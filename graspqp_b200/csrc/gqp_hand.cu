@@ -4,9 +4,13 @@
 // the autograd walk through them (scripts/fit.py:440).
 //
 // Layout: pose (Bt, 9+dof) row-major as in the reference; link_tf (Bt, n_links, 12) world transforms, one candidate's
-// links contiguous (the consumers assign one candidate to a warp or block).  A thread owns a candidate: the chain is
-// short (19 frames for Allegro), the tables sit in shared memory, per-frame transforms in thread-local arrays.
-// FK is < 0.1 % of a grasp-step's work; it is bound by nothing but launch latency.
+// links contiguous (the consumers assign one candidate to a warp or block).  Two forms:
+//   * the engine's fused kernels (fk_contacts_forward_warp_kernel / fk_contacts_backward_warp_kernel, hands of <= 32
+//     frames): a WARP owns a candidate, lane = frame, the tree is swept depth by depth with shuffles (parents sit in
+//     other lanes), contact gather and its adjoint in the same launch, transforms never leave registers in between;
+//   * the stand-alone gqp_fk_forward / gqp_fk_backward / gqp_contacts_* entry points (HandModel mirror, export, hands
+//     with more frames): a thread owns a candidate, tables in shared memory, per-frame transforms in thread-local arrays.
+// FK is < 0.1 % of a grasp-step's work; it is bound by nothing but launch latency and the length of the chain.
 #include <algorithm>
 
 #include "gqp_common.cuh"
