@@ -29,6 +29,14 @@ class GqpMalaParams(ctypes.Structure):
                                                                         "clip_grad")]
 
 
+class GqpSpanParams(ctypes.Structure):
+    _fields_ = [("kind", c_int32), ("torque_weight", c_float), ("friction", c_float), ("obb_length", c_float),
+                ("scale", c_float), ("enable_density", c_int32), ("w_fc", c_float), ("w_dis", c_float)]
+
+
+SPAN_DEXGRASP, SPAN_TDG = 1, 2
+
+
 class GqpInitParams(ctypes.Structure):
     _fields_ = [(n, c_float) for n in ("distance_lower", "distance_upper", "rotate_lower", "rotate_upper", "pitch_lower",
                                        "pitch_upper", "tilt_lower", "tilt_upper", "jitter_strength", "inflate")] + [
@@ -76,13 +84,18 @@ SIGNATURES = {
     "gqp_fc_workspace_bytes": (c_uint64, [c_int, c_int, c_int]),
     "gqp_fc_solve": (c_int, [POINTER(GqpFcParams), P, P, P, c_int, c_int, c_int, P, P]),
     "gqp_fc_finish": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, c_int, P, P, P, P, P, P, P]),
+    "gqp_span_energy": (c_int, [POINTER(GqpSpanParams), P, P, P, P, P, P, P, c_int, c_int, c_int, c_int, P, P, P, P, P]),
     "gqp_mala_stats": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P]),
     "gqp_mala_stats_noalloc": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P]),
     "gqp_mala_stats_noalloc_max_floats": (c_uint64, []),
     "gqp_mala_propose": (c_int, [POINTER(GqpMalaParams), P, P, P, P, P, P, c_int, c_int, c_int, c_int, P, P, c_uint64,
                                  c_uint64, P, P, P, P]),
     "gqp_mala_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, P, P, c_uint64, c_uint64,
-                                P, P, P, P, P, P, P, P, P, P, P, P, P]),
+                                P, P, P, P, P, P, P, P, P, P, P, P, c_int, P]),
+    "gqp_anneal_propose": (c_int, [POINTER(GqpMalaParams), P, P, P, P, P, c_int, P, c_int, c_int, c_int, c_int, P, P,
+                                   c_uint64, c_uint64, P, P, P, P]),
+    "gqp_anneal_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, c_uint64, c_uint64, c_int,
+                                  P, P, P, P, P, P, P, P, P, P, P, c_int, P]),
     "gqp_mala_reset": (c_int, [c_int, c_int, c_int, P, c_float, P, P, P, P, P, P, P, P, P, P, P]),
     "gqp_init_create": (c_int, [P, P, c_int, POINTER(c_void_p)]),
     "gqp_init_destroy": (None, [c_void_p]),

@@ -18,7 +18,7 @@ int gqp_set_error(int code, const char *fmt, ...) {
 }
 void gqp_count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
-extern "C" int gqp_abi_version(void) { return 1; }
+extern "C" int gqp_abi_version(void) { return 2; }  // 2: after_reset argument of gqp_mala_accept, (f3) entry points
 extern "C" const char *gqp_last_error(void) { return g_err; }
 extern "C" uint64_t gqp_launch_count(void) { return g_launches.load(); }
 

@@ -115,16 +115,19 @@ __global__ void __launch_bounds__(128)
 mala_accept_kernel(GqpMalaParams P, int Bt, int D, int n_c, int n_terms, const float *__restrict__ weights,
                    const float *__restrict__ losses_new, const float *__restrict__ z,
                    const uint8_t *__restrict__ reset_mask, const float *__restrict__ u_accept, uint64_t seed,
-                   uint64_t iteration, const int32_t *__restrict__ step, const float *__restrict__ pose_new,
+                   uint64_t iteration, const int32_t *__restrict__ step, int step_scalar,
+                   const float *__restrict__ pose_new,
                    const int32_t *__restrict__ idx_new, const float *__restrict__ grad_new, float *__restrict__ pose,
                    int32_t *__restrict__ idx, float *__restrict__ grad, float *__restrict__ energy,
                    float *__restrict__ losses, float *__restrict__ new_energy_out, uint8_t *__restrict__ accept_out,
-                   float *__restrict__ temperature_out) {
+                   float *__restrict__ temperature_out, int reject_accumulates) {
     int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= Bt) return;
     float en = 0.f;
     for (int k = 0; k < n_terms; ++k) en += weights[k] * losses_new[(size_t)k * Bt + b];  // fit.py:434-438
-    float T = P.starting_temperature * powf(P.temperature_decay, (float)(step[b] / P.annealing_period));  // :301-303
+    // per-row step counters (MalaStar, :301-303) or one counter for the batch (AnnealingDexGraspNet, :119-121)
+    const int stp = step ? step[b] : step_scalar;
+    float T = P.starting_temperature * powf(P.temperature_decay, (float)(stp / P.annealing_period));
     if (z) T = T * (1.0f + 0.5f * (1.0f + erff(z[b] * 0.70710678118654752f)));                            // :307-309
     float u;
     if (u_accept) u = u_accept[b];
@@ -143,6 +146,9 @@ mala_accept_kernel(GqpMalaParams P, int Bt, int D, int n_c, int n_terms, const f
         for (int c = 0; c < n_c; ++c) idx[(size_t)b * n_c + c] = idx_new[(size_t)b * n_c + c];
         energy[b] = en;  // fit.py:454-458
         for (int k = 0; k < n_terms; ++k) losses[(size_t)k * Bt + b] = losses_new[(size_t)k * Bt + b];
+    } else if (reject_accumulates) {
+        // the iteration after a reset iteration: the reference hands a rejected row old + new gradient (see the header)
+        for (int d = 0; d < D; ++d) grad[(size_t)b * D + d] += grad_new[(size_t)b * D + d];
     }
     if (new_energy_out) new_energy_out[b] = en;
     if (accept_out) accept_out[b] = acc ? 1 : 0;
@@ -291,15 +297,92 @@ extern "C" int gqp_mala_accept(const GqpMalaParams *p, int Bt, int D, int n_c, i
                                const float *u_accept, uint64_t seed, uint64_t iteration, const int32_t *step,
                                const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose,
                                int32_t *idx, float *grad, float *energy, float *losses, float *new_energy_out,
-                               uint8_t *accept_out, float *temperature_out, void *stream) {
+                               uint8_t *accept_out, float *temperature_out, int after_reset, void *stream) {
     if (!p || Bt < 0 || D <= 0 || n_c <= 0 || n_terms <= 0) return gqp_set_error(GQP_ERR_ARG, "gqp_mala_accept: bad argument");
     if (Bt == 0) return GQP_OK;
     if (!weights || !losses_new || !step || !pose_new || !idx_new || !grad_new || !pose || !idx || !grad || !energy ||
         !losses)
         return gqp_set_error(GQP_ERR_ARG, "gqp_mala_accept: null pointer");
     GQP_LAUNCH(mala_accept_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, *p, Bt, D, n_c, n_terms, weights,
-               losses_new, z, reset_mask, u_accept, seed, iteration, step, pose_new, idx_new, grad_new, pose, idx,
-               grad, energy, losses, new_energy_out, accept_out, temperature_out);
+               losses_new, z, reset_mask, u_accept, seed, iteration, step, 0, pose_new, idx_new, grad_new, pose, idx,
+               grad, energy, losses, new_energy_out, accept_out, temperature_out, after_reset != 0);
     GQP_CHECK_LAUNCH("gqp_mala_accept");
+    return GQP_OK;
+}
+
+// ---- (f3) AnnealingDexGraspNet (optimizer.py:11-149; --optimizer dexgraspnet of scripts/fit.py:336-337) --------------------
+// One RMS accumulator (D) and one step counter for the whole batch; no gradient clipping, no NaN handling, no per-row
+// temperature: try_step :70-108, accept_step :110-138, reset_envs is a no-op (:148-149).
+__global__ void __launch_bounds__(128)
+anneal_propose_kernel(GqpMalaParams P, const float *__restrict__ pose, const float *__restrict__ grad,
+                      const float *__restrict__ grad2_mean, const float *__restrict__ ema_in, float *__restrict__ ema_out,
+                      int step, const int32_t *__restrict__ idx, int Bt, int D, int n_c, int n_cand,
+                      const float *__restrict__ u_switch, const int32_t *__restrict__ idx_rand, uint64_t seed,
+                      uint64_t iteration, float *__restrict__ pose_new, int32_t *__restrict__ idx_new,
+                      float *__restrict__ step_size_out) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Bt) return;
+    const float s = P.step_size * powf(P.temperature_decay, (float)(step / P.stepsize_period));  // :81
+    for (int d = 0; d < D; ++d) {
+        const size_t i = (size_t)b * D + d;
+        const float e = P.mu * grad2_mean[d] + (1.0f - P.mu) * ema_in[d];  // :84-86
+        if (b == 0) ema_out[d] = e;  // ema_in stays intact for the other rows: the caller swaps the two buffers
+        pose_new[i] = pose[i] - s * grad[i] / (sqrtf(e) + 1e-6f);  // :88-90
+    }
+    for (int c = 0; c < n_c; ++c) {  // :91-96
+        const size_t i = (size_t)b * n_c + c;
+        float u;
+        int32_t r;
+        if (u_switch) {
+            u = u_switch[i];
+            r = idx_rand[i];
+        } else {
+            Philox p = philox4x32((uint32_t)b, (uint32_t)c, (uint32_t)iteration, (uint32_t)(iteration >> 32),
+                                  (uint32_t)seed, (uint32_t)(seed >> 32));
+            u = u01(p.c[0]);
+            r = (int32_t)(((uint64_t)p.c[1] * (uint64_t)n_cand) >> 32);
+        }
+        idx_new[i] = (u < P.switch_possibility) ? r : idx[i];
+    }
+    if (step_size_out && b == 0) step_size_out[0] = s;
+}
+
+extern "C" int gqp_anneal_propose(const GqpMalaParams *p, const float *pose, const float *grad, const float *grad2_mean,
+                                  const float *ema_in, float *ema_out, int step, const int32_t *idx, int Bt, int D, int n_c,
+                                  int n_cand, const float *u_switch, const int32_t *idx_rand, uint64_t seed,
+                                  uint64_t iteration, float *pose_new, int32_t *idx_new, float *step_size_out,
+                                  void *stream) {
+    if (!p || Bt < 0 || D <= 0 || n_c <= 0 || n_cand <= 0 || step < 0)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_anneal_propose: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!pose || !grad || !grad2_mean || !ema_in || !ema_out || !idx || !pose_new || !idx_new)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_anneal_propose: null pointer");
+    if (ema_in == ema_out)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_anneal_propose: ema_in and ema_out must be different buffers");
+    if ((u_switch == nullptr) != (idx_rand == nullptr))
+        return gqp_set_error(GQP_ERR_ARG, "gqp_anneal_propose: u_switch and idx_rand must be injected together");
+    GQP_LAUNCH(anneal_propose_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, *p, pose, grad, grad2_mean, ema_in,
+               ema_out, step, idx, Bt, D, n_c, n_cand, u_switch, idx_rand, seed, iteration, pose_new, idx_new,
+               step_size_out);
+    GQP_CHECK_LAUNCH("gqp_anneal_propose");
+    return GQP_OK;
+}
+
+extern "C" int gqp_anneal_accept(const GqpMalaParams *p, int Bt, int D, int n_c, int n_terms, const float *weights,
+                                 const float *losses_new, const float *u_accept, uint64_t seed, uint64_t iteration,
+                                 int step, const float *pose_new, const int32_t *idx_new, const float *grad_new,
+                                 float *pose, int32_t *idx, float *grad, float *energy, float *losses,
+                                 float *new_energy_out, uint8_t *accept_out, float *temperature_out, int after_reset,
+                                 void *stream) {
+    if (!p || Bt < 0 || D <= 0 || n_c <= 0 || n_terms <= 0 || step < 0)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_anneal_accept: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!weights || !losses_new || !pose_new || !idx_new || !grad_new || !pose || !idx || !grad || !energy || !losses)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_anneal_accept: null pointer");
+    GQP_LAUNCH(mala_accept_kernel, (Bt + 127) / 128, 128, 0, (cudaStream_t)stream, *p, Bt, D, n_c, n_terms, weights,
+               losses_new, (const float *)nullptr, (const uint8_t *)nullptr, u_accept, seed, iteration,
+               (const int32_t *)nullptr, step, pose_new, idx_new, grad_new, pose, idx, grad, energy, losses,
+               new_energy_out, accept_out, temperature_out, after_reset != 0);
+    GQP_CHECK_LAUNCH("gqp_anneal_accept");
     return GQP_OK;
 }

@@ -41,7 +41,7 @@ class NumpyBackend:
         return np.zeros(shape, dtype)
 
     def from_host(self, a, dtype=None):
-        return np.ascontiguousarray(a, dtype)
+        return np.array(a, dtype=dtype, copy=True, order="C")  # an upload is a copy: the caller's array stays its own
 
     def to_host(self, a):
         return np.array(a, copy=True)
@@ -122,7 +122,17 @@ class FitEngine:
                  weights=None, friction=0.2, max_limit=20.0, svd_gain=0.1, torque_weight=5.0, switch_possibility=0.4,
                  starting_temperature=18.0, temperature_decay=0.95, annealing_period=30, step_size=0.005,
                  stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1, collectives=None,
-                 overlap=True, queue_per_candidate=None):
+                 overlap=True, queue_per_candidate=None, energy_type="graspqp", optimizer="mala_star",
+                 tdg_directions=None, dexgrasp_torque_weight=0.0):
+        """energy_type: graspqp | dexgrasp | tdg (scripts/fit.py:81-88, 344-356); optimizer: mala_star | dexgraspnet
+        (fit.py:74, 334-337).  tdg_directions (P,3): the unit directions TDGEnergy draws at construction (tdg.py:148-150);
+        default: 1000 normalised normal draws from numpy's RandomState(seed), as np.random.seed(seed) makes the reference's.
+        dexgrasp_torque_weight: 0.0 is what the reference's call passes (DexgraspSpanMetric.forward's default)."""
+        if energy_type not in ("graspqp", "dexgrasp", "tdg"):
+            raise ValueError(f"energy_type {energy_type!r}: graspqp, dexgrasp or tdg")
+        if optimizer not in ("mala_star", "dexgraspnet"):
+            raise ValueError(f"optimizer {optimizer!r}: mala_star or dexgraspnet")
+        self.energy_type, self.optimizer = energy_type, optimizer
         self.lib, self.be = cdll, backend
         self.pack = pack
         self.n_obj = len(face_verts_list)
@@ -202,8 +212,25 @@ class FitEngine:
             self.n_obj, self.batch_each, self.n_pts, 0, self.queue_per_candidate)),), f32)
         self.pen_counter_off = int(cdll.gqp_hand_distance_counter_offset(self.n_obj, self.batch_each, self.n_pts, 0,
                                                                          be.ptr(self.pen_scratch)))
-        self.qp_ws = be.empty(((int(cdll.gqp_fc_workspace_bytes(Bt, n_c, self.fc.max_iter)) + 7) // 8,), np.float64)
         self.qp_stop = be.empty((1,), i32)
+        if energy_type == "graspqp":
+            self.qp_ws = be.empty(((int(cdll.gqp_fc_workspace_bytes(Bt, n_c, self.fc.max_iter)) + 7) // 8,), np.float64)
+        else:
+            self.span = _lib.GqpSpanParams(kind=_lib.SPAN_DEXGRASP if energy_type == "dexgrasp" else _lib.SPAN_TDG,
+                                           torque_weight=dexgrasp_torque_weight, friction=0.2, obb_length=0.2, scale=100.0,
+                                           enable_density=1, w_fc=w["E_fc"], w_dis=w["E_dis"])  # tdg.py:219-227, :236
+            self.tdg_dirs, self.n_dirs = None, 0
+            if energy_type == "tdg":
+                if tdg_directions is None:  # tdg.py:44-48 after np.random.seed(seed) (fit.py:159)
+                    d = np.random.RandomState(self.seed).randn(1000, 3)
+                    tdg_directions = d / (np.linalg.norm(d, axis=-1)[:, None] + 1e-8)
+                tdg_directions = np.ascontiguousarray(tdg_directions, f32).reshape(-1, 3)
+                self.tdg_dirs, self.n_dirs = be.from_host(tdg_directions, f32), len(tdg_directions)
+        if optimizer == "dexgraspnet":  # one RMS accumulator for the batch, double-buffered; one step counter (host)
+            self.ema = be.empty((2, D), f32)
+            self.ema_cur, self.anneal_step = 0, 0
+            self.mala.clip_grad = 0  # AnnealingDexGraspNet has none (optimizer.py:70-108)
+        self.prev_reset = False
         self.reset_all = be.from_host(np.ones(Bt, u8))
         self.reset_mask, self.reset_count = be.empty((Bt,), u8), be.empty((1,), i32)
         self.idx_eval = be.empty((Bt, n_c), i32)
@@ -232,6 +259,17 @@ class FitEngine:
                                                  p(self.obj_nrm), p(self.obj_clst), p(self.obj_sign), st))
         self._ck(lib.gqp_object_distance_backward(p(self.ones), p(self.cpts), p(self.obj_clst), p(self.obj_sign),
                                                   Bt * n_c, 1.0, p(self.obj_dgrad), st))
+        if self.energy_type != "graspqp":  # (f3) dexgrasp / tdg energy + E_dis, one launch
+            self._ck(lib.gqp_span_energy(ctypes.byref(self.span), p(self.cpts), p(self.cnrm), p(self.obj_dist),
+                                         p(self.obj_nrm), p(self.obj_dgrad), p(self.cog), p(self.tdg_dirs), self.n_dirs, O,
+                                         B, n_c, row("E_fc"), row("E_dis"), p(self.g_cpts), p(self.g_cnrm), st))
+        else:
+            self._evaluate_graspqp(row)
+        self._evaluate_tail(pose, idx, grad_out, row, overlap, s2)
+
+    def _evaluate_graspqp(self, row):
+        lib, p, st = self.lib, self.be.ptr, self.be.stream
+        n_c, O, B = self.n_c, self.n_obj, self.batch_each
         # Q1-Q4 + E_dis: one interior-point pass that records the batch statistics of qpth's exit test, then the
         # finish pass (value, svd term, energies, analytic backward) from every candidate's best iterate as of the exit
         self._ck(lib.gqp_fc_solve(ctypes.byref(self.fc), p(self.cpts), p(self.obj_nrm), p(self.cog), O, B, n_c,
@@ -244,6 +282,10 @@ class FitEngine:
                                    p(self.obj_dgrad), p(self.cog), O, B, n_c, p(self.qp_ws), int(self.qp_batch_stop),
                                    row("E_fc"), row("E_dis"), p(self.lam), p(self.g_cpts), p(self.g_cnrm),
                                    p(self.qp_stop), st))
+
+    def _evaluate_tail(self, pose, idx, grad_out, row, overlap, s2):
+        lib, be, p, st = self.lib, self.be, self.be.ptr, self.be.stream
+        Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
         # the side chain is enqueued AFTER the critical chain: its persistent CTAs then fill what the one-wave
         # object-distance / QP kernels leave free instead of holding the SMs while the critical chain waits
         self._ck(lib.gqp_hand_distance_bounded(self.hand, p(self.link_tf), p(self.surf), O, B, self.n_pts, 0,
@@ -281,20 +323,30 @@ class FitEngine:
         self._graph = g
         return True
 
-    def _accept(self, z, reset, u_accept):
+    def _accept(self, z, reset, u_accept, after_reset=False):
         lib, p, st = self.lib, self.be.ptr, self.be.stream
+        if self.optimizer == "dexgraspnet":  # no z-score factor, no forced accept (optimizer.py:110-138)
+            self._ck(lib.gqp_anneal_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(TERMS), p(self.w_dev),
+                                           p(self.losses_new), p(u_accept), self.seed, self.iteration, self.anneal_step,
+                                           p(self.pose_new), p(self.idx_new), p(self.grad_new), p(self.pose), p(self.idx),
+                                           p(self.grad), p(self.energy), p(self.losses), p(self.new_energy),
+                                           p(self.accept), p(self.temperature), int(after_reset), st))
+            return
         self._ck(lib.gqp_mala_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(TERMS), p(self.w_dev),
                                      p(self.losses_new), p(z), p(reset), p(u_accept), self.seed, self.iteration,
                                      p(self.step_count), p(self.pose_new), p(self.idx_new), p(self.grad_new),
                                      p(self.pose), p(self.idx), p(self.grad), p(self.energy), p(self.losses),
-                                     p(self.new_energy), p(self.accept), p(self.temperature), st))
+                                     p(self.new_energy), p(self.accept), p(self.temperature), int(after_reset), st))
 
     def _init_energy(self):
         """fit.py:381-396: first energy + backward, then optimizer.zero_grad()."""
         self.be.copy_(self.pose_new, self.pose)
         self.be.copy_(self.idx_new, self.idx)
         self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
-        self._accept(None, self.reset_all, None)
+        if self.optimizer == "dexgraspnet":  # commit everything: u = -1 < exp(.) always
+            self._accept(None, None, self.be.from_host(np.full(self.Bt, -1.0, np.float32)))
+        else:
+            self._accept(None, self.reset_all, None)
         self.first_grad = self.be.to_host(self.grad)
         self._ck(self.lib.gqp_memset_zero(self.be.ptr(self.grad), 4 * self.Bt * self.D, self.be.stream))
 
@@ -309,27 +361,42 @@ class FitEngine:
         iteration are evaluated at the freshly drawn contact indices for EVERY row."""
         lib, p, st = self.lib, self.be.ptr, self.be.stream
         self.iteration += 1
+        after_reset, self.prev_reset = self.prev_reset, reset_init is not None
         self._ck(lib.gqp_mala_stats(p(self.grad), p(self.energy), self.n_obj, self.batch_each, self.D,
                                     self.mala.clip_grad, p(self.grad2_mean), p(self.z), p(self.stats_scratch), st))
         if self.collectives is not None:  # (g**2).mean(0) over the rows of ALL ranks (optimizer.py:231)
             self.collectives.reduce_rms(self.grad2_mean, self.Bt)
-        self._ck(lib.gqp_mala_propose(ctypes.byref(self.mala), p(self.pose), p(self.grad), p(self.grad2_mean),
-                                      p(self.ema), p(self.step_count), p(self.idx), self.Bt, self.D, self.n_c,
-                                      self.n_cand, p(u_switch), p(idx_rand), self.seed, self.iteration,
-                                      p(self.pose_new), p(self.idx_new), p(self.step_size_out), st))
+        if self.optimizer == "dexgraspnet":  # AnnealingDexGraspNet.try_step (optimizer.py:70-108)
+            row = lambda k: p(self.ema) + 4 * self.D * k
+            self._ck(lib.gqp_anneal_propose(ctypes.byref(self.mala), p(self.pose), p(self.grad), p(self.grad2_mean),
+                                            row(self.ema_cur), row(1 - self.ema_cur), self.anneal_step, p(self.idx),
+                                            self.Bt, self.D, self.n_c, self.n_cand, p(u_switch), p(idx_rand), self.seed,
+                                            self.iteration, p(self.pose_new), p(self.idx_new), p(self.step_size_out),
+                                            st))
+            self.ema_cur, self.anneal_step = 1 - self.ema_cur, self.anneal_step + 1
+        else:
+            self._ck(lib.gqp_mala_propose(ctypes.byref(self.mala), p(self.pose), p(self.grad), p(self.grad2_mean),
+                                          p(self.ema), p(self.step_count), p(self.idx), self.Bt, self.D, self.n_c,
+                                          self.n_cand, p(u_switch), p(idx_rand), self.seed, self.iteration,
+                                          p(self.pose_new), p(self.idx_new), p(self.step_size_out), st))
         if reset_init is not None:
             pose_init, idx_init = reset_init
+            ema = self.ema
+            if self.optimizer == "dexgraspnet":  # reset_envs is a no-op there (:148-149): the kernel's per-row restart
+                if getattr(self, "_reset_sink", None) is None:  # of step / ema goes to a sink
+                    self._reset_sink = self.be.empty((self.Bt, self.D), np.float32)
+                ema = self._reset_sink
             self._ck(lib.gqp_mala_reset(self.Bt, self.D, self.n_c, p(self.z), float(z_score_threshold), p(reset_mask),
                                         p(pose_init), p(idx_init), p(self.pose_new), p(self.idx_new), p(self.idx_eval),
-                                        p(self.step_count), p(self.ema), p(self.reset_mask), p(self.reset_count), st))
+                                        p(self.step_count), p(ema), p(self.reset_mask), p(self.reset_count), st))
             self.evaluate(self.pose_new, self.idx_eval, self.losses_new, self.grad_new)
-            self._accept(self.z, self.reset_mask, u_accept)
+            self._accept(self.z, self.reset_mask, u_accept, after_reset)
             return
         if self._graph is not None:
             self._graph.replay()
         else:
             self.evaluate(self.pose_new, self.idx_new, self.losses_new, self.grad_new)
-        self._accept(self.z, None, u_accept)
+        self._accept(self.z, None, u_accept, after_reset)
 
     # ---- (f1) outlier resets with the re-initialisation on the device --------------------------------------------------
     def enable_device_init(self, hull_tris_list, **params):
@@ -376,12 +443,18 @@ class FitEngine:
     def snapshot(self):
         """copy of the optimiser state scripts/fit.py carries between iterations (pose, contact indices, gradient, RMS
         accumulator, step counters, energies) + the iteration number; see restore()"""
-        return {k: self.be.to_host(getattr(self, k)) for k in self._STATE} | {"iteration": self.iteration}
+        extra = {"iteration": self.iteration, "prev_reset": self.prev_reset}
+        if self.optimizer == "dexgraspnet":
+            extra.update(ema_cur=self.ema_cur, anneal_step=self.anneal_step)
+        return {k: self.be.to_host(getattr(self, k)) for k in self._STATE} | extra
 
     def restore(self, snap):
         for k in self._STATE:
             self.be.copy_(getattr(self, k), self.be.from_host(snap[k], snap[k].dtype))
         self.iteration = int(snap["iteration"])
+        self.prev_reset = bool(snap.get("prev_reset", False))
+        if self.optimizer == "dexgraspnet":
+            self.ema_cur, self.anneal_step = int(snap["ema_cur"]), int(snap["anneal_step"])
 
     def stage_calls(self):
         """name -> callable re-running ONE stage of the iteration on the current buffers (per-stage timing in bench.py
@@ -389,7 +462,7 @@ class FitEngine:
         lib, p, st = self.lib, self.be.ptr, self.be.stream
         Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
         row = lambda k: p(self.losses_new) + 4 * Bt * TERMS.index(k)
-        return {
+        calls = {
             "fk_contacts_forward": lambda: lib.gqp_fk_contacts_forward(
                 self.hand, p(self.pose_new), p(self.idx_new), Bt, n_c, p(self.link_tf), p(self.cpts), p(self.cnrm), st),
             "object_distance": lambda: lib.gqp_object_distance_forward(
@@ -411,6 +484,13 @@ class FitEngine:
                 self.hand, p(self.pose_new), p(self.idx_new), p(self.g_cpts), p(self.g_cnrm), p(self.g_link_tf),
                 p(self.g_pose_joints), Bt, n_c, p(self.grad_new), st),
         }
+        if self.energy_type != "graspqp":
+            del calls["fc_solve"], calls["fc_finish"]
+            calls["span_energy"] = lambda: lib.gqp_span_energy(
+                ctypes.byref(self.span), p(self.cpts), p(self.cnrm), p(self.obj_dist), p(self.obj_nrm), p(self.obj_dgrad),
+                p(self.cog), p(self.tdg_dirs), self.n_dirs, O, B, n_c, row("E_fc"), row("E_dis"), p(self.g_cpts),
+                p(self.g_cnrm), st)
+        return calls
 
     def close(self):
         lib = self.lib

@@ -28,6 +28,7 @@ class MalaStar:
         self._g2, self._z = torch.zeros(D, device=dev), torch.zeros(B, device=dev)
         self._scratch = torch.zeros((B + 63) // 64 * D, device=dev)
         self._one = torch.ones(1, device=dev)
+        self._prev_reset = self._reset_now = False
 
     def inject_noise(self, u_switch, idx_rand, u_accept):
         """parity runs: the arrays torch.rand / torch.randint would have produced (optimizer.py:252-257, :305)"""
@@ -86,7 +87,10 @@ class MalaStar:
                                        p(z), p(rm), p(ua), self.seed, self.iteration, self.step.data_ptr(),
                                        pose_new.data_ptr(), idx_new.data_ptr(), grad_new.data_ptr(), pose.data_ptr(),
                                        idx.data_ptr(), grad.data_ptr(), e_old.data_ptr(), losses.data_ptr(), None,
-                                       acc.data_ptr(), T.data_ptr(), self._st()))
+                                       acc.data_ptr(), T.data_ptr(), int(self._prev_reset), self._st()))
+        # the iteration after a reset iteration hands rejected rows old + new gradient (include/graspqp_b200.h,
+        # gqp_mala_accept: after_reset)
+        self._prev_reset, self._reset_now = self._reset_now, False
         with torch.no_grad():  # optimizer.py:325-338: the hand model now holds accepted-or-restored rows
             hm.hand_pose.data.copy_(pose)
             hm.contact_point_indices.copy_(idx.to(hm.contact_point_indices.dtype))
@@ -101,6 +105,7 @@ class MalaStar:
     def reset_envs(self, mask):
         self.step[mask] = 0
         self.ema_grad_hand_pose[mask] = 0
+        self._reset_now = True
 
     def zero_grad(self):
         if self.hand_model.hand_pose.grad is not None:

@@ -238,6 +238,28 @@ int gqp_fc_finish(const GqpFcParams *p_host, const float *cpts, const float *cnr
                   const void *workspace, int batch_stop, float *e_fc, float *e_dis, float *lam, float *grad_cpts,
                   float *grad_cnrm, int32_t *stop_iter_out, void *stream);
 
+/* ---- (f3) the reference's other force-closure energies (scripts/fit.py:344-347) + E_dis, forward and analytic backward in
+ * one launch, a warp per candidate; replaces gqp_fc_solve + gqp_fc_finish for energy_type dexgrasp / tdg. ---------------
+ *   GQP_SPAN_DEXGRASP  metrics/ops/dexgrasp.py:5-69: e_fc = |sum n_i|^2 + tw^2 |sum n_i x (p_i - cog)|^2; torque_weight is
+ *                      0.0 on the reference's path (DexgraspSpanMetric.forward's default; energy.py:34-41 passes none).
+ *   GQP_SPAN_TDG       metrics/ops/tdg.py:57-239: e_fc = scale * mean over the n_dirs unit directions `dirs` (n_dirs,3)
+ *                      (device; TDGEnergy draws 1000 with np.random.randn, :44-48, 148-150) of 1 - cos(W(u), [u;0]);
+ *                      friction = miu_coef[0] = 0.2, obb_length = 0.2, scale = 100, enable_density = 1 (:219-227, :236).
+ * Inputs and outputs as gqp_fc_finish (lam is not produced: the reference returns ones / None there).  n_c <= 32. */
+#define GQP_SPAN_DEXGRASP 1
+#define GQP_SPAN_TDG 2
+typedef struct GqpSpanParams {
+    int32_t kind;
+    float torque_weight;                 /* dexgrasp */
+    float friction, obb_length, scale;   /* tdg */
+    int32_t enable_density;              /* tdg */
+    float w_fc, w_dis;
+} GqpSpanParams;
+int gqp_span_energy(const GqpSpanParams *p_host, const float *cpts, const float *cnrm_hand, const float *obj_dist,
+                    const float *obj_nrm, const float *obj_dgrad, const float *cog, const float *dirs, int n_dirs,
+                    int n_obj, int batch_each, int n_c, float *e_fc, float *e_dis, float *grad_cpts, float *grad_cnrm,
+                    void *stream);
+
 /* ---- M1/M2/M4: MALA* (optimizer.py:199-340) and the caller's bookkeeping (fit.py:403-406, 434-458) -----------------
  * State rows are candidates.  u_switch (Bt,n_c), idx_rand (Bt,n_c) int32, u_accept (Bt): injected noise, or all NULL
  * to draw them from Philox4x32-10 keyed (seed, iteration, row).
@@ -248,7 +270,12 @@ int gqp_fc_finish(const GqpFcParams *p_host, const float *cpts, const float *cnr
  *   entry is zeroed as a whole (:242-244);
  *   idx_new = switch ? idx_rand : idx;  step += 1; step_size_out (Bt) = s_i (may be NULL).
  * gqp_mala_accept: new_energy = sum_k w_k*losses_new[k]; T = T0*decay^(step/period)*(1+Phi(z));
- *   accept = u < exp((E-E')/T) or reset; accepted rows copy pose_new/idx_new/grad_new/energy/losses into the state. */
+ *   accept = u < exp((E-E')/T) or reset; accepted rows copy pose_new/idx_new/grad_new/energy/losses into the state.
+ *   after_reset != 0 (pass it in the iteration that FOLLOWS a reset iteration): rejected rows keep grad + grad_new instead of
+ *   grad.  This restates what the reference does there: its proposals are not detached (optimizer.py:240, hand_model.py:855),
+ *   the pose a reset iteration builds is an autograd leaf (hand_model.py:845-850) whose .grad accumulates in place, and
+ *   old_grad_hand_pose (:268) aliases it — so :338 hands rejected rows old + new gradient.  Pinned by the reference run in
+ *   tests/golden/fit_alt_ref.npz. */
 typedef struct GqpMalaParams {
     float switch_possibility, starting_temperature, temperature_decay, step_size, mu;
     int32_t annealing_period, stepsize_period;
@@ -275,7 +302,25 @@ int gqp_mala_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n_t
                     const float *u_accept, uint64_t seed, uint64_t iteration, const int32_t *step,
                     const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose, int32_t *idx,
                     float *grad, float *energy, float *losses /* (n_terms,Bt) */, float *new_energy_out,
-                    uint8_t *accept_out, float *temperature_out, void *stream);
+                    uint8_t *accept_out, float *temperature_out, int after_reset, void *stream);
+
+/* ---- (f3) AnnealingDexGraspNet (core/optimizer.py:11-149; scripts/fit.py --optimizer dexgraspnet) --------------------------
+ * One RMS accumulator ema (D) and ONE step counter for the whole batch (passed by value: the reference keeps it as a host
+ * int), no clipping, no NaN handling, temperature without the z-score factor, resets do not touch the optimiser.
+ * gqp_anneal_propose: step = the counter BEFORE this try_step (:81); ema_out = mu*grad2_mean + (1-mu)*ema_in (different
+ *   buffers: the caller swaps them); pose_new = pose - s*grad/(sqrt(ema_out)+1e-6); idx_new as gqp_mala_propose;
+ *   *step_size_out (one device float, may be NULL) = s.  grad2_mean from gqp_mala_stats (clip_grad = 0).
+ * gqp_anneal_accept: step = the counter AFTER the try_step (:119-121); accept = u < exp((E-E')/T); commit as
+ *   gqp_mala_accept (after_reset included).  temperature_out (Bt) or NULL. */
+int gqp_anneal_propose(const GqpMalaParams *p_host, const float *pose, const float *grad, const float *grad2_mean,
+                       const float *ema_in, float *ema_out, int step, const int32_t *idx, int Bt, int D, int n_c,
+                       int n_cand, const float *u_switch, const int32_t *idx_rand, uint64_t seed, uint64_t iteration,
+                       float *pose_new, int32_t *idx_new, float *step_size_out, void *stream);
+int gqp_anneal_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n_terms, const float *weights,
+                      const float *losses_new, const float *u_accept, uint64_t seed, uint64_t iteration, int step,
+                      const float *pose_new, const int32_t *idx_new, const float *grad_new, float *pose, int32_t *idx,
+                      float *grad, float *energy, float *losses, float *new_energy_out, uint8_t *accept_out,
+                      float *temperature_out, int after_reset, void *stream);
 
 /* ---- M3: outlier reset (fit.py:408-422: reset_mask = z > threshold; initialize_convex_hull(env_mask); reset_envs) ----
  * Called between gqp_mala_propose and the energy evaluation of a reset iteration.  pose_init (Bt,D) / idx_init (Bt,n_c)

@@ -13,6 +13,7 @@ import numpy as np
 import torch
 
 from .hand import HandOracle, compute_sdf
+from .metrics_alt import TDGOracle, dexgrasp_energy
 from .qp import graspqp_energy
 
 WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_pen=100.0, E_spen=10.0, E_joints=1.0)  # fit.py argparse defaults :90-112
@@ -46,11 +47,21 @@ class ObjectOracle:
         return distance, torch.stack(normals).reshape(-1, n_points, 3)
 
 
-def calculate_energy(hand, obj, svd_gain=0.1, friction=0.2, max_limit=20.0):
+def calculate_energy(hand, obj, svd_gain=0.1, friction=0.2, max_limit=20.0, energy_type="graspqp", tdg=None,
+                     dexgrasp_torque_weight=0.0):
+    """energy_type: graspqp | dexgrasp | tdg (scripts/fit.py:344-356); tdg = a metrics_alt.TDGOracle"""
     distance, contact_normal = obj.cal_distance(hand.contact_points)
     E_dis = ((1 - torch.sum((-contact_normal) * hand.contact_normals, dim=-1)).exp() * distance.abs()).sum(-1)
-    E_fc, lam, info = graspqp_energy(hand.contact_points, contact_normal, obj.cog, friction=friction,
-                                     max_limit=max_limit, svd_gain=svd_gain)
+    info = {}
+    if energy_type == "graspqp":
+        E_fc, lam, info = graspqp_energy(hand.contact_points, contact_normal, obj.cog, friction=friction,
+                                         max_limit=max_limit, svd_gain=svd_gain)
+    elif energy_type == "dexgrasp":
+        E_fc = dexgrasp_energy(hand.contact_points, contact_normal, obj.cog, dexgrasp_torque_weight)
+    elif energy_type == "tdg":
+        E_fc = tdg.energy(hand.contact_points, contact_normal, obj.cog)
+    else:
+        raise ValueError(energy_type)
     th = hand.hand_pose[:, 9:]
     E_joints = torch.sum((th > hand.joints_upper) * (th - hand.joints_upper), dim=-1) + torch.sum(
         (th < hand.joints_lower) * (hand.joints_lower - th), dim=-1)
@@ -120,7 +131,8 @@ class MalaStarOracle:
         self.old["idx"][mask] = h.contact_point_indices[mask]
         self.old["grad"][mask] = 0 * self.old["grad"][mask]
 
-    def accept_step(self, energy, new_energy, u_accept, z_score, reset_mask=None):
+    def accept_step(self, energy, new_energy, u_accept, z_score, reset_mask=None, after_reset=False):
+        """after_reset: the PREVIOUS iteration was a reset iteration — see AFTER_RESET below"""
         h = self.hand
         temperature = self.starting_temperature * self.temperature_decay ** torch.div(
             self.step, self.annealing_period, rounding_mode="floor")
@@ -133,7 +145,69 @@ class MalaStarOracle:
             reject = ~accept
             h.hand_pose[reject] = self.old["pose"][reject]
             h.contact_point_indices[reject] = self.old["idx"][reject]
-            h.hand_pose.grad[reject] = self.old["grad"][reject]
+            old_grad = self.old["grad"] + h.hand_pose.grad if after_reset else self.old["grad"]
+            h.hand_pose.grad[reject] = old_grad[reject]
+        return accept, temperature
+
+
+AFTER_RESET = """A behaviour of the reference that both optimisers share, restated explicitly (the oracle detaches its proposals):
+try_step builds the proposal from hand_model.hand_pose WITHOUT detaching it (optimizer.py:88-90, 240) and
+HandModel.set_parameters keeps `hand_pose.clone()` (hand_model.py:855), so the proposal's graph runs back into the previous
+pose with an identity Jacobian and the backward pass of the new energy also delivers the new gradient to the previous pose.
+Normally that pose is a non-leaf whose retained `.grad` is REPLACED by a new tensor (old + new), which `old_grad_hand_pose`
+(an alias of the old tensor object, :104 / :268) does not see.  But a reset iteration builds the pose with torch.where under
+no_grad and requires_grad = True (hand_model.py:845-850): a LEAF, into whose `.grad` autograd accumulates IN PLACE.  In the
+iteration right after a reset iteration the alias therefore holds old + new gradient, and that is what rejected rows get
+back (:136 / :338).  Seen in the reference runs of tests/golden/fit_alt_ref.npz (make_golden.gen_fit_alt)."""
+
+
+class AnnealingOracle:
+    """AnnealingDexGraspNet, graspqp/src/graspqp/core/optimizer.py:11-149 (--optimizer dexgraspnet): one RMS accumulator
+    and one step counter for the batch, no clipping / NaN handling, temperature without the z-score factor, resets do not
+    touch the optimiser (reset_envs :148-149 is `pass`) and are not force-accepted.
+
+    See AFTER_RESET for what `after_reset` restates."""
+
+    def __init__(self, hand, switch_possibility=0.5, starting_temperature=18.0, temperature_decay=0.95,
+                 annealing_period=30, step_size=0.005, stepsize_period=50, mu=0.98, clip_grad=False):
+        self.hand = hand
+        self.switch_possibility = switch_possibility
+        dt = hand.dtype
+        self.starting_temperature = torch.tensor(starting_temperature, dtype=dt)
+        self.temperature_decay = torch.tensor(temperature_decay, dtype=dt)
+        self.annealing_period, self.step_size_period = annealing_period, stepsize_period
+        self.step_size = torch.tensor(step_size, dtype=dt)
+        self.mu = torch.tensor(mu, dtype=dt)
+        self.step = 0
+        self.ema = torch.zeros(hand.n_dofs + 9, dtype=dt)
+
+    def try_step(self, u_switch, idx_new, grad2_mean=None):
+        h = self.hand
+        s = self.step_size * self.temperature_decay ** (self.step // self.step_size_period)
+        g2 = (h.hand_pose.grad ** 2).mean(0) if grad2_mean is None else torch.as_tensor(grad2_mean, dtype=h.dtype)
+        self.ema = self.mu * g2 + (1 - self.mu) * self.ema
+        hand_pose = (h.hand_pose - s * h.hand_pose.grad / (torch.sqrt(self.ema) + 1e-6)).detach()
+        switch_mask = u_switch < self.switch_possibility
+        idx = h.contact_point_indices.clone()
+        idx[switch_mask] = idx_new[switch_mask]
+        self.old = dict(pose=h.hand_pose, idx=h.contact_point_indices, grad=h.hand_pose.grad)
+        h.set_parameters(hand_pose.requires_grad_(True), idx)
+        self.step += 1
+        return s
+
+    def reset_envs(self, mask):
+        pass
+
+    def accept_step(self, energy, new_energy, u_accept, z_score=None, reset_mask=None, after_reset=False):
+        h = self.hand
+        temperature = self.starting_temperature * self.temperature_decay ** (self.step // self.annealing_period)
+        accept = u_accept < torch.exp((energy - new_energy) / temperature)
+        with torch.no_grad():
+            reject = ~accept
+            h.hand_pose[reject] = self.old["pose"][reject]
+            h.contact_point_indices[reject] = self.old["idx"][reject]
+            old_grad = self.old["grad"] + h.hand_pose.grad if after_reset else self.old["grad"]
+            h.hand_pose.grad[reject] = old_grad[reject]
         return accept, temperature
 
 
@@ -141,14 +215,17 @@ class FitLoopOracle:
     """One object of this class = the state of scripts/fit.py between iterations."""
 
     def __init__(self, pack, face_verts_list, surface_points_list, batch_size_each, hand_pose0, idx0,
-                 dtype=torch.float32, **opt):
+                 dtype=torch.float32, energy_type="graspqp", optimizer="mala_star", tdg_directions=None,
+                 dexgrasp_torque_weight=0.0, **opt):
         self.hand = HandOracle(pack, dtype)
         self.obj = ObjectOracle(face_verts_list, surface_points_list, batch_size_each, dtype)
         self.B = batch_size_each
         self.hand.set_parameters(torch.as_tensor(hand_pose0, dtype=dtype).clone().requires_grad_(True),
                                  torch.as_tensor(idx0).long())
-        self.opt = MalaStarOracle(self.hand, **opt)
-        self.losses, _ = calculate_energy(self.hand, self.obj)
+        self.opt = (MalaStarOracle if optimizer == "mala_star" else AnnealingOracle)(self.hand, **opt)
+        self.ekw = dict(energy_type=energy_type, dexgrasp_torque_weight=dexgrasp_torque_weight,
+                        tdg=TDGOracle(tdg_directions) if energy_type == "tdg" else None)
+        self.losses, _ = calculate_energy(self.hand, self.obj, **self.ekw)
         self.energy = total_energy(self.losses)
         self.energy.sum().backward()
         self.first_grad = self.hand.hand_pose.grad.clone()
@@ -163,7 +240,7 @@ class FitLoopOracle:
         self.hand.hand_pose.grad = torch.as_tensor(grad, dtype=dt).clone()
         self.energy = torch.as_tensor(energy, dtype=dt).clone()
         self.opt.ema = torch.as_tensor(ema, dtype=dt).clone()
-        self.opt.step = torch.as_tensor(step).long().clone()
+        self.opt.step = int(step) if isinstance(self.opt, AnnealingOracle) else torch.as_tensor(step).long().clone()
 
     def iterate(self, u_switch, idx_new, u_accept, reset=None, z_score_threshold=1.0, grad2_mean=None, z=None,
                 qp_stop=None):
@@ -186,7 +263,7 @@ class FitLoopOracle:
             self.opt.reset_envs(reset_mask)
         _qp.FORCE_STOP = qp_stop
         try:
-            new_losses, info = calculate_energy(self.hand, self.obj)
+            new_losses, info = calculate_energy(self.hand, self.obj, **self.ekw)
         finally:
             _qp.FORCE_STOP = None
         new_energy = total_energy(new_losses)
@@ -195,7 +272,9 @@ class FitLoopOracle:
                    new_losses={k: v.detach().clone() for k, v in new_losses.items()}, z=z, s=s,
                    proposal=self.hand.hand_pose.detach().clone(), idx_prop=self.hand.contact_point_indices.clone())
         with torch.no_grad():
-            accept, t = self.opt.accept_step(self.energy, new_energy.detach(), u_accept, z, reset_mask)
+            accept, t = self.opt.accept_step(self.energy, new_energy.detach(), u_accept, z, reset_mask,
+                                             after_reset=getattr(self, "prev_reset", False))
+            self.prev_reset = reset is not None
             self.energy[accept] = new_energy.detach()[accept]
             for k, v in new_losses.items():
                 self.losses[k][accept] = v.detach()[accept]

@@ -238,8 +238,104 @@ def gen_fit_reset(name="fit_reset_ref_f64.npz"):
     print(name, "accepts", [int(out[f"t{t}_accept"].sum()) for t in range(len(plan))])
 
 
+def gen_fit_alt(name="fit_alt_ref.npz"):
+    """(f3) scripts/fit.py:381-458 with the reference's OTHER optimiser and energies, injected noise; "dexanneal" in fp32
+    (calc_e_fc is a TorchScript function with float constants, dexgrasp.py:18-30: it rejects doubles), "tdgmala" in fp64:
+       run "dexanneal": --optimizer dexgraspnet (AnnealingDexGraspNet) + --energy_type dexgrasp, 5 iterations, the 3rd a
+                        reset iteration with an injected mask (resets are neither force-accepted nor seen by this optimiser);
+                        stepsize_period 2 / annealing_period 3 so that both schedules move within the run;
+       run "tdgmala":   MalaStar + --energy_type tdg (1000 directions from numpy seed 7), 3 iterations;
+       run "malareset": MalaStar + graspqp, a reset iteration followed by one with forced rejections (the gradient that
+                        rejected rows keep there is old + new: oracle/pipeline.py AFTER_RESET)."""
+    pack = hand_pack.load_pack("allegro")
+    B, n_c, n_pts, seed = 6, 12, 192, 3
+    v, f = synth.make_mesh("sphere", 400, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.7
+    out = dict(face_verts=fv, surface=sp.astype(np.float32), pose0=pose.astype(np.float32), idx0=idx.astype(np.int32))
+    n_cand = len(pack["cand"])
+    try:
+        for run, dtype, kw, plan in (("dexanneal", torch.float32,
+                                      dict(energy_type="dexgrasp", optimizer="dexgraspnet", switch_possibility=0.5,
+                                           stepsize_period=2, annealing_period=3),
+                                      ["plain", "plain", "reset_mask", "plain", "plain"]),
+                                     ("tdgmala", torch.float64, dict(energy_type="tdg"), ["plain", "plain", "plain"]),
+                                     # MalaStar + graspqp around a reset iteration, with rejections forced in the iteration
+                                     # AFTER it (u_accept 1e30 on two rows): oracle.pipeline.AFTER_RESET
+                                     ("malareset", torch.float64, dict(), ["plain", "reset_mask", "reject", "plain"])):
+            torch.set_default_dtype(dtype)
+            st = rh.make_fit_state(pack, [fv], [sp], B, pose.astype(np.float32), idx, dtype=dtype, **kw)
+            if run == "tdgmala":
+                out["tdg_dirs"] = st.energy_fnc.tdg_energy.target_direction_6D[0, :, :3].numpy().astype(np.float32)
+            rng = np.random.default_rng(11)
+            out[run + "_plan"] = np.array(plan)
+            out[run + "_energy0"] = st.energy.detach().numpy().copy()
+            out[run + "_first_grad"] = st.first_grad.numpy().copy()
+            for t, kind in enumerate(plan):
+                us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, n_cand, (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+                reset = None
+                k0 = f"{run}_t{t}_"
+                if kind == "reject":
+                    ua[[1, 4]] = 1e30  # outside [0,1): rows 1 and 4 are rejected whatever their energies
+                if kind == "reset_mask":
+                    pi, ii = synth.random_grasp_init(pack, [v], B, n_c, 70 + t)
+                    pi[:, :3] *= 0.8
+                    mask = torch.tensor([True, False, True, True, False, False])
+                    reset = (torch.tensor(pi.astype(np.float32)), torch.tensor(ii), mask)
+                    out.update({k0 + "pose_init": pi.astype(np.float32), k0 + "idx_init": ii.astype(np.int32),
+                                k0 + "mask_in": mask.numpy()})
+                o = rh.fit_iterate(st, torch.tensor(us), torch.tensor(ir).long(), torch.tensor(ua), reset=reset)
+                out.update({k0 + "u_switch": us, k0 + "idx_rand": ir, k0 + "u_accept": ua})
+                for k in ("s", "z", "proposal", "idx_prop", "new_energy", "new_grad", "accept", "temperature", "energy",
+                          "pose", "idx", "step", "ema"):
+                    out[k0 + k] = o[k].numpy()
+                for k, v_ in o["new_losses"].items():
+                    out[k0 + "loss_" + k] = v_.numpy()
+            print(name, run, "accepts", [int(out[f"{run}_t{t}_accept"].sum()) for t in range(len(plan))],
+                  "E_fc", out[f"{run}_t0_loss_E_fc"][:3])
+    finally:
+        torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+
+
+def gen_metric_alt():
+    """metric_alt_ref.npz: the reference's DexgraspSpanMetric (metrics/ops/dexgrasp.py) and TDGSpanMetric (metrics/ops/tdg.py)
+    forward + autograd backward in fp32 (TDGEnergy holds fp32 constants), with the 1000 target directions TDGEnergy drew."""
+    ref = rh.load()
+    reg = ref["registry"]
+    out = {}
+    for n_c in (12, 4):
+        rng = np.random.default_rng(200 + n_c)
+        B = 6
+        nrm = rng.normal(size=(B, n_c, 3)); nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
+        nrm[0, 0] = np.array([0.05, 0.998, 0.02]) / np.linalg.norm([0.05, 0.998, 0.02])  # the base switch of tdg.py:101-102
+        nrm[1] = nrm[1, :1] + rng.normal(size=(n_c, 3)) * 0.05                            # one-sided grasp: density != 1/1
+        nrm[1] /= np.linalg.norm(nrm[1], axis=-1, keepdims=True)
+        cp = (-nrm * 0.08 + rng.normal(size=(B, n_c, 3)) * 0.01)
+        cog = rng.normal(size=(B, 3)) * 0.005
+        nrm, cp, cog = [a.astype(np.float32) for a in (nrm, cp, cog)]
+        k = f"nc{n_c}_"
+        out.update({k + "cpts": cp, k + "nrm": nrm, k + "cog": cog})
+        for tw in (0.0, 5.0):
+            cpt = torch.tensor(cp, requires_grad=True)
+            E, _ = reg.DexgraspSpanMetric()(cpt, torch.tensor(nrm), torch.tensor(cog), torque_weight=tw, with_solution=True)
+            E.sum().backward()
+            out.update({k + f"dex_tw{tw:g}_E": E.detach().numpy(), k + f"dex_tw{tw:g}_grad": cpt.grad.numpy()})
+        np.random.seed(7)  # scripts/fit.py:159 seeds numpy before the metric is built
+        m = reg.TDGSpanMetric()
+        out[k + "tdg_dirs"] = m.tdg_energy.target_direction_6D[0, :, :3].numpy().copy()
+        cpt = torch.tensor(cp, requires_grad=True)
+        E, _ = m(cpt, torch.tensor(nrm), torch.tensor(cog))
+        E.sum().backward()
+        out.update({k + "tdg_E": E.detach().numpy(), k + "tdg_grad": cpt.grad.numpy()})
+        print("metric_alt", n_c, "dex", out[k + "dex_tw5_E"][:3], "tdg", out[k + "tdg_E"][:3])
+    np.savez_compressed(os.path.join(HERE, "metric_alt_ref.npz"), **out)
+
+
 if __name__ == "__main__":
     assert rh.available(), "reference not present"
     import subprocess
     subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
-    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset()
+    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset(); gen_metric_alt(); gen_fit_alt()

@@ -70,8 +70,23 @@ class _Noise:
         return self.idx_new[self.mask_for_randint]
 
 
+def tdg_metric(ref, dtype, seed=7):
+    """the reference's TDGSpanMetric with numpy seeded as scripts/fit.py:159 does before it draws its 1000 directions; for an
+    fp64 run the fp32 constants TDGEnergy built (tdg.py:66-81, 148-153) are cast, nothing else is touched"""
+    import numpy as np
+    np.random.seed(seed)
+    m = ref["registry"].TDGSpanMetric()
+    te = m.tdg_energy
+    if dtype != torch.float32:
+        for k in ("rot_base1", "rot_base2", "miu_tensor", "target_direction_6D", "F_center_direction",
+                  "obj_gravity_center", "obj_obb_length"):
+            setattr(te, k, getattr(te, k).to(dtype))
+    return m
+
+
 def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_pose0, idx0, dtype=torch.float32,
-                   friction=0.2, max_limit=20.0, n_cone_vecs=4, svd_gain=0.1, **optim):
+                   friction=0.2, max_limit=20.0, n_cone_vecs=4, svd_gain=0.1, energy_type="graspqp",
+                   optimizer="mala_star", **optim):
     """The state scripts/fit.py holds between iterations, with the REFERENCE MalaStar / calculate_energy / metric."""
     from oracle.hand import HandOracle
     from oracle.pipeline import ObjectOracle, WEIGHTS
@@ -85,10 +100,23 @@ def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_
     cfg = dict(switch_possibility=0.4, starting_temperature=18.0, temperature_decay=0.95, annealing_period=30,
                step_size=0.005, stepsize_period=50, mu=0.98)  # scripts/fit.py argparse defaults
     cfg.update(optim)
-    opt = ref["optimizer"].MalaStar(hand, device="cpu", batch_size=batch_each, **cfg)
+    if optimizer == "mala_star":
+        opt = ref["optimizer"].MalaStar(hand, device="cpu", batch_size=batch_each, **cfg)
+    else:  # scripts/fit.py:336-337
+        opt = ref["optimizer"].AnnealingDexGraspNet(hand, device="cpu", batch_size=batch_each, **cfg)
+        if dtype != torch.float32:  # the class builds its scalars and accumulator as torch.float (optimizer.py:52-68)
+            for k in ("starting_temperature", "temperature_decay", "step_size", "mu", "ema_grad_hand_pose"):
+                setattr(opt, k, getattr(opt, k).to(dtype))
     F = ref["registry"].GraspSpanMetricFactory
-    energy_fnc = F.create(F.MetricType.GRASPQP, solver_kwargs={"friction": friction, "max_limit": max_limit,
-                                                                "n_cone_vecs": n_cone_vecs})
+    if energy_type == "graspqp":  # scripts/fit.py:344-356
+        energy_fnc = F.create(F.MetricType.GRASPQP, solver_kwargs={"friction": friction, "max_limit": max_limit,
+                                                                    "n_cone_vecs": n_cone_vecs})
+    elif energy_type == "dexgrasp":
+        energy_fnc = F.create(F.MetricType.DEXGRASP)
+    elif energy_type == "tdg":
+        energy_fnc = tdg_metric(ref, dtype)
+    else:
+        raise ValueError(energy_type)
     st = types.SimpleNamespace(hand=hand, obj=obj, opt=opt, energy_fnc=energy_fnc, weights=dict(WEIGHTS), B=batch_each,
                                svd_gain=svd_gain, ref=ref)
 
@@ -145,7 +173,8 @@ def fit_iterate(st, u_switch, idx_new, u_accept, reset=None, z_score_threshold=1
                 st.losses[k][accept] = v[accept]
         out.update(accept=accept.clone(), temperature=t.clone(), energy=st.energy.detach().clone(),
                    pose=hand.hand_pose.detach().clone(), idx=hand.contact_point_indices.clone(),
-                   step=opt.step.clone(), ema=opt.ema_grad_hand_pose.clone())
+                   step=opt.step.clone() if torch.is_tensor(opt.step) else torch.tensor(opt.step),
+                   ema=opt.ema_grad_hand_pose.clone())
         if reset_mask is not None:
             out["reset_mask"] = reset_mask.clone()
     finally:

@@ -182,3 +182,119 @@ def check_fit_reset(lib, be):
         np.testing.assert_allclose(H(eng.ema), g[f"t{t}_ema"], rtol=1e-4, atol=1e-9, err_msg=f"ema after iteration {t}")
     eng.close()
     return n_reset
+
+
+def check_metric_alt(lib, be):
+    """(f3) gqp_span_energy against the reference's DexgraspSpanMetric (torque weight 0 — its path's value — and 5) and
+    TDGSpanMetric outputs and autograd gradients: tests/golden/metric_alt_ref.npz (make_golden.gen_metric_alt, fp32 runs of
+    the reference, which holds fp32 constants).  E_dis and its two gradients against the closed form of energy.py:25-28."""
+    import ctypes
+    from graspqp_b200 import _lib
+    g = load("metric_alt_ref")
+    p = be.ptr
+    for n_c in (12, 4):
+        k = f"nc{n_c}_"
+        cp, nrm, cog = g[k + "cpts"], g[k + "nrm"], g[k + "cog"]
+        B = len(cp)
+        rng = np.random.default_rng(1)
+        nh = rng.normal(size=(B, n_c, 3)).astype(np.float32)
+        dist = (rng.normal(size=(B, n_c)) * 0.01).astype(np.float32)
+        dg = rng.normal(size=(B, n_c, 3)).astype(np.float32)
+        d_cp, d_nrm, d_cog, d_nh, d_dist, d_dg = [be.from_host(a, np.float32) for a in (cp, nrm, cog, nh, dist, dg)]
+        d_dirs = be.from_host(g[k + "tdg_dirs"], np.float32)
+        e, ed = be.empty((B,), np.float32), be.empty((B,), np.float32)
+        gc_, gn = be.empty((B, n_c, 3), np.float32), be.empty((B, n_c, 3), np.float32)
+        for kind, tw, key in ((_lib.SPAN_DEXGRASP, 0.0, "dex_tw0"), (_lib.SPAN_DEXGRASP, 5.0, "dex_tw5"),
+                              (_lib.SPAN_TDG, 0.0, "tdg")):
+            P = _lib.GqpSpanParams(kind=kind, torque_weight=tw, friction=0.2, obb_length=0.2, scale=100.0,
+                                   enable_density=1, w_fc=1.0, w_dis=0.0)
+            _lib.check(lib.gqp_span_energy(ctypes.byref(P), p(d_cp), p(d_nh), p(d_dist), p(d_nrm), p(d_dg), p(d_cog),
+                                           p(d_dirs), len(g[k + "tdg_dirs"]), B, 1, n_c, p(e), p(ed), p(gc_), p(gn),
+                                           be.stream), lib)
+            tol.assert_energy(be.to_host(e), g[k + key + "_E"], f"golden {key} n_c={n_c} energy", max_excused=0)
+            want = g[k + key + "_grad"]
+            err = np.abs(be.to_host(gc_) - want).max() / max(np.abs(want).max(), 1e-30)
+            print(f"[grad] golden {key} n_c={n_c}: d/d contact points, error / largest entry {err:.2e}; tolerance 1e-04")
+            assert err < 1e-4
+        P = _lib.GqpSpanParams(kind=_lib.SPAN_DEXGRASP, torque_weight=0.0, friction=0.2, obb_length=0.2, scale=100.0,
+                               enable_density=1, w_fc=0.0, w_dis=100.0)
+        _lib.check(lib.gqp_span_energy(ctypes.byref(P), p(d_cp), p(d_nh), p(d_dist), p(d_nrm), p(d_dg), p(d_cog), None, 0,
+                                       B, 1, n_c, p(e), p(ed), p(gc_), p(gn), be.stream), lib)
+        ea = np.exp(1 + (nrm.astype(np.float64) * nh).sum(-1))
+        np.testing.assert_allclose(be.to_host(ed), (ea * np.abs(dist)).sum(-1), rtol=1e-5)
+        np.testing.assert_allclose(be.to_host(gn), 100 * (ea * np.abs(dist))[..., None] * nrm, rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(be.to_host(gc_), 100 * (ea * np.sign(dist))[..., None] * dg, rtol=1e-4, atol=1e-3)
+    # argument checks of the entry point
+    P = _lib.GqpSpanParams(kind=7)
+    assert lib.gqp_span_energy(ctypes.byref(P), p(d_cp), p(d_nh), p(d_dist), p(d_nrm), None, p(d_cog), None, 0, B, 1, n_c,
+                               p(e), p(ed), None, None, be.stream) != 0
+    P = _lib.GqpSpanParams(kind=_lib.SPAN_TDG, friction=0.2, obb_length=0.2, scale=100.0)
+    assert lib.gqp_span_energy(ctypes.byref(P), p(d_cp), p(d_nh), p(d_dist), p(d_nrm), None, p(d_cog), None, 0, B, 1, n_c,
+                               p(e), p(ed), None, None, be.stream) != 0  # tdg without its direction table
+    assert lib.gqp_span_energy(ctypes.byref(P), p(d_cp), p(d_nh), p(d_dist), p(d_nrm), None, p(d_cog), p(d_dirs), 1000, B, 1,
+                               33, p(e), p(ed), None, None, be.stream) != 0  # n_c beyond 32
+
+
+ALT_RUNS = {
+    "dexanneal": dict(energy_type="dexgrasp", optimizer="dexgraspnet", switch_possibility=0.5, stepsize_period=2,
+                      annealing_period=3),
+    "tdgmala": dict(energy_type="tdg"),
+    "malareset": dict(),
+}
+
+
+def check_fit_alt(lib, be, runs=("dexanneal", "tdgmala", "malareset")):
+    """(f3) the reference's OTHER optimiser / energies and the gradient a rejected row keeps after a reset iteration, against
+    the reference's own AnnealingDexGraspNet, DexgraspSpanMetric, TDGSpanMetric and MalaStar run through scripts/fit.py's loop
+    body: tests/golden/fit_alt_ref.npz (make_golden.gen_fit_alt; "dexanneal" is an fp32 run of the reference, the other two
+    fp64).  -> number of rejected rows seen in iterations that follow a reset iteration."""
+    g = load("fit_alt_ref")
+    pack = hand_pack.load_pack("allegro")
+    B = len(g["pose0"])
+    H = be.to_host
+    n_after = 0
+    for run in runs:
+        kw = dict(ALT_RUNS[run])
+        if run == "tdgmala":
+            kw["tdg_directions"] = g["tdg_dirs"]
+        eng = engine.FitEngine(lib, be, pack, [g["face_verts"]], g["surface"][None], B, g["pose0"], g["idx0"], **kw)
+        tol.assert_energy(H(eng.energy), g[run + "_energy0"], f"golden {run}: first energy")
+        tol.assert_grad(eng.first_grad, g[run + "_first_grad"], f"golden {run}: first gradient")
+        ex = lambda b: tol.normal_unstable(H(eng.cpts)[b], g["face_verts"])
+        prev_reset = False
+        for t, kind in enumerate(g[run + "_plan"]):
+            k0 = f"{run}_t{t}_"
+            kw = {}
+            if kind == "reset_mask":
+                kw["reset_init"] = (be.from_host(g[k0 + "pose_init"], np.float32), be.from_host(g[k0 + "idx_init"], np.int32))
+                kw["reset_mask"] = be.from_host(g[k0 + "mask_in"].astype(np.uint8), np.uint8)
+            eng.step(be.from_host(g[k0 + "u_switch"], np.float32), be.from_host(g[k0 + "idx_rand"], np.int32),
+                     be.from_host(g[k0 + "u_accept"], np.float32), **kw)
+            lbl = f"golden {run}: step {t} ({kind})"
+            np.testing.assert_array_equal(H(eng.idx_new), g[k0 + "idx_prop"], err_msg=lbl)
+            np.testing.assert_allclose(H(eng.pose_new), g[k0 + "proposal"], rtol=1e-4, atol=1e-5, err_msg=lbl)
+            np.testing.assert_allclose(np.broadcast_to(g[k0 + "s"], (B,)) if run == "dexanneal" else g[k0 + "s"],
+                                       H(eng.step_size_out)[:1].repeat(B) if run == "dexanneal" else H(eng.step_size_out),
+                                       rtol=1e-6, err_msg=lbl)
+            tol.assert_energy(H(eng.new_energy), g[k0 + "new_energy"], lbl + " new energy", excuse=ex)
+            for k, name in enumerate(engine.TERMS):
+                np.testing.assert_allclose(H(eng.losses_new)[k], g[k0 + "loss_" + name], rtol=1e-4, atol=1e-6, err_msg=name)
+            tol.assert_grad(H(eng.grad_new), g[k0 + "new_grad"], lbl + " gradient", excuse=ex)
+            np.testing.assert_allclose(H(eng.temperature), np.broadcast_to(g[k0 + "temperature"], (B,)), rtol=1e-4,
+                                       err_msg=lbl)
+            np.testing.assert_array_equal(H(eng.accept).astype(bool), g[k0 + "accept"], err_msg=lbl)
+            np.testing.assert_allclose(H(eng.energy), g[k0 + "energy"], rtol=1e-4, err_msg=lbl)
+            np.testing.assert_allclose(H(eng.pose), g[k0 + "pose"], rtol=1e-4, atol=1e-5, err_msg=lbl)
+            np.testing.assert_array_equal(H(eng.idx), g[k0 + "idx"], err_msg=lbl)
+            if run == "dexanneal":
+                assert eng.anneal_step == int(g[k0 + "step"])
+                np.testing.assert_allclose(H(eng.ema)[eng.ema_cur], g[k0 + "ema"], rtol=1e-4, atol=1e-9, err_msg=lbl)
+            else:
+                np.testing.assert_array_equal(H(eng.step_count), g[k0 + "step"], err_msg=lbl)
+                # the accumulator is a mean of SQUARED gradients: twice their relative error (tolerance 1e-4)
+                np.testing.assert_allclose(H(eng.ema), g[k0 + "ema"], rtol=3e-4, atol=1e-9, err_msg=lbl)
+            if prev_reset:
+                n_after += int((~g[k0 + "accept"]).sum())
+            prev_reset = kind == "reset_mask"
+        eng.close()
+    return n_after

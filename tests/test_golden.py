@@ -117,6 +117,65 @@ def test_oracle_reset_iterations_match_reference():
         np.testing.assert_allclose(orc.opt.ema.numpy(), g[f"t{t}_ema"], rtol=1e-5, atol=1e-12)
 
 
+def test_oracle_other_energies_match_reference():
+    """oracle.metrics_alt (dexgrasp, tdg) vs the reference's DexgraspSpanMetric / TDGSpanMetric (metric_alt_ref.npz, fp32 runs)"""
+    from oracle import metrics_alt as ma
+    g = gc.load("metric_alt_ref")
+    for n_c in (12, 4):
+        k = f"nc{n_c}_"
+        for dt in (torch.float32, torch.float64):
+            cp = torch.tensor(g[k + "cpts"], dtype=dt, requires_grad=True)
+            n, cog = torch.tensor(g[k + "nrm"], dtype=dt), torch.tensor(g[k + "cog"], dtype=dt)
+            tdg = ma.TDGOracle(g[k + "tdg_dirs"])
+            for key, fn in (("dex_tw0", lambda: ma.dexgrasp_energy(cp, n, cog, 0.0)),
+                            ("dex_tw5", lambda: ma.dexgrasp_energy(cp, n, cog, 5.0)), ("tdg", lambda: tdg.energy(cp, n, cog))):
+                cp.grad = None
+                E = fn()
+                E.sum().backward()
+                np.testing.assert_allclose(E.detach().numpy(), g[k + key + "_E"], rtol=2e-6, err_msg=key)
+                want = g[k + key + "_grad"]
+                got = cp.grad.numpy() if cp.grad is not None else np.zeros_like(want)
+                np.testing.assert_allclose(got, want, rtol=0, atol=2e-6 * max(np.abs(want).max(), 1e-30), err_msg=key)
+
+
+def test_oracle_other_optimizer_and_energies_match_reference_loop():
+    """oracle.pipeline with AnnealingOracle / dexgrasp / tdg and the after-reset gradient rule vs the reference's own
+    AnnealingDexGraspNet, metrics and MalaStar in scripts/fit.py's loop body (fit_alt_ref.npz)."""
+    g = gc.load("fit_alt_ref")
+    pack = hand_pack.load_pack("allegro")
+    B = len(g["pose0"])
+    for run, dt in (("dexanneal", torch.float32), ("tdgmala", torch.float64), ("malareset", torch.float64)):
+        kw = dict(gc.ALT_RUNS[run])
+        if run == "tdgmala":
+            kw["tdg_directions"] = g["tdg_dirs"]
+        orc = FitLoopOracle(pack, [g["face_verts"]], [g["surface"]], B, g["pose0"], g["idx0"].astype(np.int64), dtype=dt, **kw)
+        np.testing.assert_allclose(orc.energy.numpy(), g[run + "_energy0"], rtol=1e-6)
+        T = lambda a: torch.tensor(a, dtype=dt)
+        for t, kind in enumerate(g[run + "_plan"]):
+            k = f"{run}_t{t}_"
+            reset = (g[k + "pose_init"], g[k + "idx_init"], g[k + "mask_in"]) if kind == "reset_mask" else None
+            out = orc.iterate(T(g[k + "u_switch"]), torch.tensor(g[k + "idx_rand"]).long(), T(g[k + "u_accept"]), reset=reset)
+            np.testing.assert_array_equal(out["idx_prop"].numpy(), g[k + "idx_prop"])
+            # the proposal of the iteration after a rejected row depends on the gradient that row kept: 1e-6 here means the
+            # after-reset rule (old + new gradient) is the reference's
+            np.testing.assert_allclose(out["proposal"].numpy(), g[k + "proposal"], rtol=1e-6, atol=1e-8, err_msg=k)
+            np.testing.assert_allclose(out["new_energy"].numpy(), g[k + "new_energy"], rtol=1e-6, err_msg=k)
+            gw = g[k + "new_grad"]
+            np.testing.assert_allclose(out["new_grad"].numpy(), gw, rtol=1e-4, atol=1e-5 * np.abs(gw).max(), err_msg=k)
+            np.testing.assert_array_equal(out["accept"].numpy(), g[k + "accept"])
+            np.testing.assert_allclose(np.asarray(out["temperature"]), g[k + "temperature"], rtol=1e-6)
+            np.testing.assert_allclose(orc.opt.ema.numpy(), g[k + "ema"], rtol=1e-5, atol=1e-12)
+
+
+def test_emulated_kernels_other_energies(emu):
+    gc.check_metric_alt(emu, engine.NumpyBackend())
+
+
+def test_emulated_kernels_other_optimizer_and_energies(emu):
+    """AnnealingDexGraspNet + dexgrasp, MalaStar + tdg, and the after-reset gradient rule through the emulated kernels"""
+    assert gc.check_fit_alt(emu, engine.NumpyBackend()) == 3
+
+
 def test_emulated_kernels_sdf(emu):
     gc.check_sdf(emu, engine.NumpyBackend())
 
@@ -157,10 +216,14 @@ def test_golden_vectors_are_reproducible(tmp_path, oracle_built):
     torch.manual_seed(0)
     mg.HERE = str(tmp_path)
     mg.gen_fit_reset()
-    new, old = np.load(tmp_path / "fit_reset_ref_f64.npz"), gc.load("fit_reset_ref_f64")
-    assert sorted(new.files) == sorted(old)
-    for k in new.files:
-        if new[k].dtype.kind == "f":
-            np.testing.assert_allclose(new[k], old[k], rtol=1e-9, atol=1e-12, equal_nan=True, err_msg=k)
-        else:
-            np.testing.assert_array_equal(new[k], old[k], err_msg=k)
+    mg.gen_metric_alt()  # (f3) DexgraspSpanMetric / TDGSpanMetric
+    mg.gen_fit_alt()     # (f3) AnnealingDexGraspNet, the other energies in the loop, the after-reset gradient rule
+    for name in ("fit_reset_ref_f64", "metric_alt_ref", "fit_alt_ref"):
+        new, old = np.load(tmp_path / (name + ".npz")), gc.load(name)
+        assert sorted(new.files) == sorted(old)
+        for k in new.files:
+            if new[k].dtype.kind == "f":
+                np.testing.assert_allclose(new[k], old[k], rtol=1e-6 if new[k].dtype == np.float32 else 1e-9, atol=1e-12,
+                                           equal_nan=True, err_msg=k)
+            else:
+                np.testing.assert_array_equal(new[k], old[k], err_msg=k)
