@@ -1,8 +1,12 @@
 """Force-closure metric registry — graspqp/src/graspqp/metrics/ops/registry.py:92-140 for MetricType.GRASPQP.
 The callable has the reference contract (core/energy.py:35-42):
     energy_fnc(contact_pts, contact_normals, sdf, cog, with_solution=True, svd_gain=0.1) -> (E_fc (Bt), x (Bt,n_c) | None)
-Other metric types (dexgrasp, tdg, handle) are other energy_types: out of this path's scope."""
+MetricType.DEXGRASP and TDG are the reference's other energy_types (scripts/fit.py:344-347) over
+gqp_span_energy; the scipy solvers (GRASPQP_SCIPY, GRASPQP_EUCLIDIAN_SCIPY) are CPU code outside this path."""
 import enum
+
+import numpy as np
+import torch
 
 from . import _lib, ops
 
@@ -25,12 +29,51 @@ class SpanMetricWrapper:
     forward = __call__
 
 
+class DexgraspSpanMetric:
+    """metrics/ops/dexgrasp.py:39-69: E = |sum n_i|^2 + tw^2 |sum n_i x (p_i - cog)|^2; returns (E, ones) with_solution."""
+
+    def __call__(self, contact_pts, contact_normals, cog=None, torque_weight=0.0, with_solution=False, **kwargs):
+        p = _lib.GqpSpanParams(kind=_lib.SPAN_DEXGRASP, torque_weight=float(torque_weight), friction=0.2, obb_length=0.2,
+                               scale=100.0, enable_density=1, w_fc=1.0, w_dis=0.0)
+        e = ops.SpanEnergyFn.apply(contact_pts, contact_normals, cog, p, None)
+        return (e, torch.ones_like(contact_pts[..., 0])) if with_solution else e
+
+    forward = __call__
+
+
+class TDGSpanMetric:
+    """metrics/ops/tdg.py:217-239: 100 * TDGEnergy(miu 0.2, box length 0.2, density weights) over 1000 unit directions drawn
+    with np.random.randn at construction (tdg.py:44-48, 148-150: from numpy's global state, as the reference)."""
+
+    def __init__(self, device="cuda", directions=None):
+        if directions is None:
+            d = np.random.randn(1000, 3)
+            directions = d / (np.linalg.norm(d, axis=-1)[:, None] + 1e-8)
+        self.directions = torch.as_tensor(np.ascontiguousarray(directions, np.float32)).to(device).contiguous()
+
+    def __call__(self, contact_pts, contact_normals, cog=None, torque_weight=0.0, with_solution=False, **kwargs):
+        p = _lib.GqpSpanParams(kind=_lib.SPAN_TDG, torque_weight=0.0, friction=0.2, obb_length=0.2, scale=100.0,
+                               enable_density=1, w_fc=1.0, w_dis=0.0)
+        return ops.SpanEnergyFn.apply(contact_pts, contact_normals, cog, p, self.directions.to(contact_pts.device)), None
+
+    forward = __call__
+
+
 class GraspSpanMetricFactory:
-    class MetricType(enum.Enum):
-        GRASPQP = "graspqp"
+    class MetricType(enum.Enum):  # registry.py:94-99
+        DEXGRASP = 1
+        TDG = 2
+        GRASPQP = 3
+        GRASPQP_SCIPY = 4
+        GRASPQP_EUCLIDIAN_SCIPY = 5
 
     @staticmethod
     def create(metric_type, solver_kwargs=None, **kwargs):
-        if metric_type != GraspSpanMetricFactory.MetricType.GRASPQP:
-            raise NotImplementedError(f"{metric_type}: only energy_type=graspqp is on the accelerated path")
-        return SpanMetricWrapper(**(solver_kwargs or {}))
+        T = GraspSpanMetricFactory.MetricType
+        if metric_type == T.DEXGRASP:
+            return DexgraspSpanMetric()
+        if metric_type == T.TDG:
+            return TDGSpanMetric(**kwargs)
+        if metric_type == T.GRASPQP:
+            return SpanMetricWrapper(**(solver_kwargs or {}))
+        raise NotImplementedError(f"{metric_type}: the scipy solvers are CPU code outside the accelerated path")

@@ -193,3 +193,27 @@ class ForceClosureFn(torch.autograd.Function):
     def backward(ctx, ge, _gl):
         (g,) = ctx.saved_tensors
         return g * ge.to(g.dtype).view(-1, 1, 1), None, None, None
+
+
+class SpanEnergyFn(torch.autograd.Function):
+    """energy_fnc of MetricType.DEXGRASP / TDG (metrics/ops/dexgrasp.py, tdg.py) over gqp_span_energy -> E_fc (Bt)."""
+
+    @staticmethod
+    def forward(ctx, contact_pts, contact_normals, cog, params, dirs):
+        cp, cn, cg = _f32c(contact_pts), _f32c(contact_normals), _f32c(cog)
+        B, n_c = cp.shape[0], cp.shape[1]
+        e, ed = torch.empty(B, device=cp.device), torch.empty(B, device=cp.device)
+        g = torch.empty_like(cp)
+        zeros = torch.zeros(B, n_c, device=cp.device)
+        # cog is per candidate here (energy.py:35-42 passes (Bt,3)): n_obj = B "objects" of one candidate each
+        _chk(_lib.lib().gqp_span_energy(ctypes.byref(params), cp.data_ptr(), cn.data_ptr(), zeros.data_ptr(), cn.data_ptr(),
+                                        None, cg.data_ptr(), dirs.data_ptr() if dirs is not None else None,
+                                        dirs.shape[0] if dirs is not None else 0, B, 1, n_c, e.data_ptr(), ed.data_ptr(),
+                                        g.data_ptr(), None, _st(cp)))
+        ctx.save_for_backward(g)
+        return e
+
+    @staticmethod
+    def backward(ctx, ge):
+        (g,) = ctx.saved_tensors
+        return g * ge.to(g.dtype).view(-1, 1, 1), None, None, None, None

@@ -25,3 +25,58 @@ def test_golden_other_optimizer_and_energies(gpu):
     """AnnealingDexGraspNet + dexgrasp, MalaStar + tdg, MalaStar around a reset iteration (rejected rows keep old + new
     gradient in the iteration after it) vs the reference's own classes in scripts/fit.py's loop body"""
     assert gc.check_fit_alt(*gpu) == 3
+
+
+@pytest.mark.parametrize("energy_type,optimizer", [("dexgrasp", "dexgraspnet"), ("tdg", "mala_star")])
+def test_reference_shaped_loop_with_other_optimizer_and_energies(energy_type, optimizer):
+    """The reference-shaped API (GraspSpanMetricFactory.create(DEXGRASP | TDG), AnnealingDexGraspNet | MalaStar, autograd loop
+    of scripts/fit.py:381-458) vs the fused FitEngine with the same options and the same injected noise."""
+    import numpy as np
+
+    import graspqp_b200 as g
+    from graspqp_b200 import _lib, engine
+    from test_api_gpu import _case, _total
+    B, n_c, T = 8, 12, 3
+    pack, fv, sp, pose, idx = _case(B=B, n_c=n_c)
+    dev = "cuda:0"
+    dirs = np.random.RandomState(5).randn(1000, 3)
+    dirs = (dirs / np.linalg.norm(dirs, axis=-1)[:, None]).astype(np.float32)
+    hand = g.HandModel("allegro", dev)
+    obj = g.ObjectModel(batch_size_each=B, num_samples=len(sp), device=dev)
+    obj.initialize(["sphere"], [fv], sp[None])
+    MT = g.GraspSpanMetricFactory.MetricType
+    energy_fnc = (g.GraspSpanMetricFactory.create(MT.DEXGRASP) if energy_type == "dexgrasp" else
+                  g.GraspSpanMetricFactory.create(MT.TDG, device=dev, directions=dirs))
+    hand.set_parameters(torch.tensor(pose, device=dev).requires_grad_(True), torch.tensor(idx, device=dev))
+    cls = g.AnnealingDexGraspNet if optimizer == "dexgraspnet" else g.MalaStar
+    opt = cls(hand, switch_possibility=0.4, device=dev, batch_size=B)
+    losses = g.calculate_energy(hand, obj, energy_fnc=energy_fnc, method="gendexgrasp", svd_gain=0.1)
+    energy = _total(losses)
+    energy.sum().backward()
+    opt.zero_grad()
+    energy = energy.detach()
+    eng = engine.FitEngine(_lib.lib(), engine.TorchBackend(dev), pack, [fv], sp[None], B, pose, idx.astype(np.int32),
+                           energy_type=energy_type, optimizer=optimizer, tdg_directions=dirs)
+    np.testing.assert_allclose(energy.cpu().numpy(), eng.energy.cpu().numpy(), rtol=1e-5)
+    rng = np.random.default_rng(0)
+    for t in range(T):
+        us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, 92, (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+        d = lambda a: torch.tensor(a, device=dev)
+        opt.inject_noise(d(us), d(ir), d(ua))
+        opt.try_step()
+        Eb = energy.view(-1, B)
+        z = ((Eb - Eb.mean(-1).unsqueeze(-1)) / Eb.std(-1).unsqueeze(-1)).view(-1)
+        opt.zero_grad()
+        new_losses = g.calculate_energy(hand, obj, energy_fnc=energy_fnc, method="gendexgrasp", svd_gain=0.1)
+        new_energy = _total(new_losses)
+        new_energy.sum().backward()
+        with torch.no_grad():
+            accept, temp = opt.accept_step(energy, new_energy, None, z, 1.0)
+            energy[accept] = new_energy.detach()[accept]
+        eng.step(d(us), d(ir), d(ua))
+        np.testing.assert_array_equal(accept.cpu().numpy(), eng.accept.cpu().numpy().astype(bool))
+        np.testing.assert_allclose(new_energy.detach().cpu().numpy(), eng.new_energy.cpu().numpy(), rtol=1e-4)
+        np.testing.assert_allclose(energy.cpu().numpy(), eng.energy.cpu().numpy(), rtol=1e-4)
+        np.testing.assert_allclose(hand.hand_pose.detach().cpu().numpy(), eng.pose.cpu().numpy(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_array_equal(hand.contact_point_indices.cpu().numpy(), eng.idx.cpu().numpy())
+    eng.close()
