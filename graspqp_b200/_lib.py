@@ -14,7 +14,7 @@ class GqpHandDesc(ctypes.Structure):
             "frame_parent", "frame_jtype", "frame_dof", "frame_axis", "frame_joff", "frame_loff", "link_frame",
             "face_offset", "face_verts", "cand", "cand_normal", "cand_link", "spheres", "sphere_link", "joints_lower",
             "joints_upper")] + [("mlp_hidden", c_int32), ("mlp_out", c_int32), ("mlp_lo", c_float),
-                                ("mlp_hi", c_float)] + [(n, c_void_p) for n in ("mlp_w1", "mlp_b1", "mlp_w2", "mlp_b2")]
+                                ("mlp_hi", c_float)] + [(n, c_void_p) for n in ("mlp_w1", "mlp_b1", "mlp_w2", "mlp_b2", "frame_gain")]
 
 
 class GqpFcParams(ctypes.Structure):

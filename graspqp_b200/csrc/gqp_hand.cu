@@ -60,7 +60,7 @@ __device__ __forceinline__ T34 joint_tf(const GqpHandDev &H, int f, const float 
     T34 J = t34_identity();
     int jt = H.frame_jtype[f], d = H.frame_dof[f];
     if (jt == 1) {
-        float th = d >= 0 ? theta[d] : 0.0f;
+        float th = d >= 0 ? theta[d] * H.frame_gain[f] : 0.0f;  // gain 1 unless the joint mimics another (ability hand)
         th = th + 2.0f * ((th > 0.0f ? 1.0f : 0.0f) - 0.5f) * 1e-2f;
         float s, c;
         sincosf(th * 0.5f, &s, &c);
@@ -70,7 +70,7 @@ __device__ __forceinline__ T34 joint_tf(const GqpHandDev &H, int f, const float 
         J.m[4] = two_s * (i * j + k * r); J.m[5] = 1 - two_s * (i * i + k * k); J.m[6] = two_s * (j * k - i * r);
         J.m[8] = two_s * (i * k - j * r); J.m[9] = two_s * (j * k + i * r); J.m[10] = 1 - two_s * (i * i + j * j);
     } else if (jt == 2 && d >= 0) {
-        float th = theta[d];
+        float th = theta[d] * H.frame_gain[f];
         J.m[3] = th * H.frame_axis[f][0]; J.m[7] = th * H.frame_axis[f][1]; J.m[11] = th * H.frame_axis[f][2];
     }
     return J;
@@ -194,9 +194,9 @@ fk_backward_kernel(const GqpHandDev *__restrict__ hand, const float *__restrict_
             V3 a = t34_vec(Bj[f], V3{H.frame_axis[f][0], H.frame_axis[f][1], H.frame_axis[f][2]});
             if (jt == 1) {
                 V3 o = V3{Bj[f].m[3], Bj[f].m[7], Bj[f].m[11]};
-                gp[9 + d] += dot3(a, M - cross3(o, F));
+                gp[9 + d] += H.frame_gain[f] * dot3(a, M - cross3(o, F));
             } else {
-                gp[9 + d] += dot3(a, F);
+                gp[9 + d] += H.frame_gain[f] * dot3(a, F);
             }
         }
         int par = H.frame_parent[f];
@@ -463,6 +463,7 @@ fk_contacts_backward_warp_kernel(const GqpHandDev *__restrict__ hand, const floa
                 const V3 Mv = V3{M[0], M[1], M[2]}, Fv = V3{F[0], F[1], F[2]};
                 if (jt == 1) jg = dot3(a, Mv - cross3(V3{st.Bj.m[3], st.Bj.m[7], st.Bj.m[11]}, Fv));
                 else jg = dot3(a, Fv);
+                jg *= H.frame_gain[f];
             }
         }
         __syncwarp();
@@ -546,6 +547,7 @@ extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
         H.frame_parent[f] = d->frame_parent_host[f];
         H.frame_jtype[f] = d->frame_jtype_host[f];
         H.frame_dof[f] = d->frame_dof_host[f];
+        H.frame_gain[f] = d->frame_gain_host ? d->frame_gain_host[f] : 1.0f;
         H.frame_link[f] = -1;
         if (H.frame_parent[f] >= f || H.frame_dof[f] >= n_q) {
             delete h;

@@ -67,6 +67,7 @@ struct GqpHandDev {
     int32_t frame_parent[GQP_MAX_FRAMES], frame_jtype[GQP_MAX_FRAMES], frame_dof[GQP_MAX_FRAMES];
     int32_t frame_link[GQP_MAX_FRAMES];  // mesh-link id hanging on the frame, or -1
     float frame_axis[GQP_MAX_FRAMES][3];
+    float frame_gain[GQP_MAX_FRAMES];    // joint value = gain * parameter (1 unless GqpHandDesc::frame_gain_host says otherwise)
     float frame_joff[GQP_MAX_FRAMES][12];
     float frame_loff[GQP_MAX_FRAMES][12];
     int32_t link_frame[GQP_MAX_LINKS];

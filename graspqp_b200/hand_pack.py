@@ -54,6 +54,8 @@ def make_desc(pack):
         d.mlp_lo, d.mlp_hi = float(pack["mlp_clamp"][0]), float(pack["mlp_clamp"][1])
         d.mlp_w1, d.mlp_b1 = arr("mlp_w1", np.float32), arr("mlp_b1", np.float32)
         d.mlp_w2, d.mlp_b2 = arr("mlp_w2", np.float32), arr("mlp_b2", np.float32)
+    if "frame_gain" in pack:  # mimic joints (ability hand)
+        d.frame_gain = arr("frame_gain", np.float32)
     return d, keep
 
 

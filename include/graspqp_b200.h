@@ -100,6 +100,10 @@ typedef struct GqpHandDesc {
     int32_t mlp_hidden, mlp_out;
     float mlp_lo, mlp_hi;
     const float *mlp_w1_host, *mlp_b1_host, *mlp_w2_host, *mlp_b2_host;
+    /* (n_frames) or NULL = all 1: the joint of frame f takes gain * hand_pose[:, 9 + frame_dof[f]].  Mimic joints of the
+     * ability hand (hands/ability_hand.py:10-29: the second joint of a finger = 1.05851325 x the first); a Schunk-style
+     * mirrored finger would be gain -1 (hands/schunk.py:31-38). */
+    const float *frame_gain_host;
 } GqpHandDesc;
 
 int gqp_hand_create(const GqpHandDesc *desc, GqpHand **out);

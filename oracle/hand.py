@@ -82,6 +82,8 @@ class HandOracle:
         self.parent = [int(v) for v in pack["frame_parent"]]
         self.jtype = [int(v) for v in pack["frame_jtype"]]
         self.frame_dof = [int(v) for v in pack["frame_dof"]]
+        # mimic joints (hands/ability_hand.py:10-29): joint value = gain * parameter
+        self.frame_gain = [float(v) for v in pack["frame_gain"]] if "frame_gain" in pack else [1.0] * len(self.parent)
         self.axis = g("frame_axis").to(dtype)
         to44 = lambda a: torch.cat([a, torch.tensor([0, 0, 0, 1.0], device=self.device).expand(a.shape[0], 1, 4)], 1).to(dtype)
         self.joff, self.loff = to44(g("frame_joff")), to44(g("frame_loff"))
@@ -122,12 +124,12 @@ class HandOracle:
             world = torch.eye(4, dtype=self.dtype, device=self.device).expand(B, 4, 4) if par < 0 else trans[par]
             d = self.frame_dof[f]
             if self.jtype[f] == 1 and d >= 0:
-                th = theta[:, d:d + 1]
+                th = theta[:, d:d + 1] * self.frame_gain[f]
                 th = th + 2 * ((th > 0).to(self.dtype) - 0.5) * 1e-2
                 quat = torch.cat([torch.cos(th / 2), torch.sin(th / 2) * self.axis[f]], -1)
                 jt = _mat44(quaternion_to_matrix(quat), None, B, self.dtype, self.device)
             elif self.jtype[f] == 2 and d >= 0:
-                jt = _mat44(None, theta[:, d:d + 1] * self.axis[f], B, self.dtype, self.device)
+                jt = _mat44(None, theta[:, d:d + 1] * self.frame_gain[f] * self.axis[f], B, self.dtype, self.device)
             elif self.jtype[f] == 1:  # movable joint that is not in the parameter vector: th_dict.get(name, 0.0)
                 th = torch.zeros(B, 1, dtype=self.dtype, device=self.device)
                 th = th + 2 * ((th > 0).to(self.dtype) - 0.5) * 1e-2

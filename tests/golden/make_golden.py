@@ -107,6 +107,59 @@ def gen_fk():
     np.savez_compressed(os.path.join(HERE, "fk_ref.npz"), **out)
 
 
+def gen_fk_more():
+    """fk_more_ref.npz: pytorch_kinematics FK + contact transforms for the hands of SURVEY 8(f3): robotiq3 (plain chain) and
+    ability_hand, whose 6 parameters are expanded to the chain's 10 joints by the reference's OWN get_all_joint_angles
+    (hands/ability_hand.py:10-29, loaded from its file; its module-level `from graspqp.core import HandModel` is satisfied by
+    a stub: HandModel itself needs trimesh / pytorch3d)."""
+    import importlib.util
+    import types
+    out = {}
+    for hand in ("robotiq3", "ability_hand"):
+        pack = hand_pack.load_pack(hand)
+        chain, frames = rh.pk_chain_from_pack(pack)
+        rng = np.random.default_rng(4)
+        B = 6
+        lo, hi = pack["joints_lower"], pack["joints_upper"]
+        theta = (lo + (hi - lo) * rng.random((B, len(lo)))).astype(np.float32)
+        theta[0] = 0.0
+        theta[1, ::2] = -0.05
+        th = torch.tensor(theta)
+        movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
+        if hand == "ability_hand":
+            rh.load()
+            core = sys.modules.get("graspqp.core")
+            had = hasattr(core, "HandModel")
+            if not had:
+                core.HandModel = type("HandModel", (), {})
+            spec = importlib.util.spec_from_file_location(
+                "ref_ability_hand", os.path.join(rh.REF, "graspqp", "src", "graspqp", "hands", "ability_hand.py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            if not had:
+                del core.HandModel
+            q = mod.get_all_joint_angles(th)  # (B, 10) in chain order
+            assert q.shape[1] == len(movable)
+            th_dict = {f"j{f}": q[:, k] for k, f in enumerate(movable)}
+        else:
+            th_dict = {f"j{f}": th[:, int(pack["frame_dof"][f])] for f in movable}
+        res = chain.forward_kinematics(th_dict)
+        link_m = np.stack([res[f"l{int(f)}"].get_matrix().expand(B, 4, 4).numpy() for f in pack["mesh_frame"]], 1)
+        cp, cn = [], []
+        for li, f in enumerate(pack["mesh_frame"]):
+            m = pack["cand_link"] == li
+            if m.sum() == 0:
+                continue
+            T = res[f"l{int(f)}"]
+            cp.append(T.transform_points(torch.tensor(pack["cand"][m])).expand(B, -1, -1))
+            cn.append(T.transform_normals(torch.tensor(pack["cand_normal"][m])).expand(B, -1, -1))
+        k = hand + "_"
+        out.update({k + "theta": theta, k + "link_matrices": link_m.astype(np.float32),
+                    k + "cand_points": torch.cat(cp, 1).numpy(), k + "cand_normals": torch.cat(cn, 1).numpy()})
+        print("fk_more_ref", hand, link_m.shape)
+    np.savez_compressed(os.path.join(HERE, "fk_more_ref.npz"), **out)
+
+
 def gen_metric():
     ref = rh.load()
     out = {}
@@ -338,4 +391,4 @@ if __name__ == "__main__":
     assert rh.available(), "reference not present"
     import subprocess
     subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
-    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset(); gen_metric_alt(); gen_fit_alt()
+    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset(); gen_metric_alt(); gen_fit_alt(); gen_fk_more()

@@ -49,9 +49,14 @@ def check_sdf(lib, be):
         lib.gqp_mesh_destroy(m)
 
 
+MORE_HANDS = ("robotiq3", "ability_hand")  # fk_more_ref.npz
+
+
 def check_fk(lib, be, hands=("allegro", "shadow_hand", "panda", "robotiq2")):
-    """H2/H3 against pytorch_kinematics' Chain.forward_kinematics and Transform3d.transform_points/normals."""
+    """H2/H3 against pytorch_kinematics' Chain.forward_kinematics and Transform3d.transform_points/normals (for the ability
+    hand: fed by the reference's own get_all_joint_angles, hands/ability_hand.py:10-29)."""
     g = load("fk_ref")
+    g.update(load("fk_more_ref"))
     for name in hands:
         k = "" if name == "allegro" else name + "_"
         pack = hand_pack.load_pack(name)
@@ -69,8 +74,8 @@ def check_fk(lib, be, hands=("allegro", "shadow_hand", "panda", "robotiq2")):
         order = np.argsort(pack["cand_link"], kind="stable").astype(np.int32)
         idx = np.tile(order, (B, 1))
         cp, cn = be.empty((B, C, 3), np.float32), be.empty((B, C, 3), np.float32)
-        _lib.check(lib.gqp_contacts_forward(hand, be.ptr(tf), be.ptr(be.from_host(idx, np.int32)), B, C, be.ptr(cp),
-                                            be.ptr(cn), be.stream), lib)
+        d_idx = be.from_host(idx, np.int32)  # kept alive across the call
+        _lib.check(lib.gqp_contacts_forward(hand, be.ptr(tf), be.ptr(d_idx), B, C, be.ptr(cp), be.ptr(cn), be.stream), lib)
         np.testing.assert_allclose(be.to_host(cp), g[k + "cand_points"], atol=2e-6, err_msg=name)
         np.testing.assert_allclose(be.to_host(cn), g[k + "cand_normals"], atol=5e-6, err_msg=name)
         lib.gqp_hand_destroy(hand)

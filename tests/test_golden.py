@@ -25,9 +25,9 @@ def test_oracle_sdf_port_matches_reference_kernel(oracle_built):
         np.testing.assert_allclose(nr * 2 * np.sqrt(d2)[:, None], 2 * (g[key + "_points"] - cl), atol=5e-7)
 
 
-@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2"])
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2", "robotiq3", "ability_hand"])
 def test_oracle_fk_matches_pytorch_kinematics(hand):
-    g = gc.load("fk_ref")
+    g = gc.load("fk_more_ref" if hand in gc.MORE_HANDS else "fk_ref")
     k = "" if hand == "allegro" else hand + "_"
     pack = hand_pack.load_pack(hand)
     o = HandOracle(pack, torch.float32)
@@ -182,6 +182,11 @@ def test_emulated_kernels_sdf(emu):
 
 def test_emulated_kernels_fk(emu):
     gc.check_fk(emu, engine.NumpyBackend())
+
+
+def test_emulated_kernels_fk_more_hands(emu):
+    """(f3) robotiq3 and the ability hand (mimic joints: GqpHandDesc::frame_gain_host)"""
+    gc.check_fk(emu, engine.NumpyBackend(), hands=gc.MORE_HANDS)
 
 
 def test_emulated_kernels_metric(emu):

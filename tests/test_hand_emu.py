@@ -154,7 +154,7 @@ def test_self_pen_joints(emu, pack, hand):
     np.testing.assert_allclose(gp, p64.grad.numpy(), rtol=1e-3, atol=1e-4)
 
 
-@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2"])
+@pytest.mark.parametrize("hand", ["allegro", "shadow_hand", "panda", "robotiq2", "robotiq3", "ability_hand"])
 def test_culling_proof_outside_cells_have_positive_sign(emu, hand, oracle_built):
     """every SET cell of every link's outside grid, and the region outside the link's box: the reference's brute-force
     sign (TorchSDF arithmetic, oracle port) is +1 for the points drawn there (all set cells; the GPU test draws more
@@ -166,7 +166,7 @@ def test_culling_proof_outside_cells_have_positive_sign(emu, hand, oracle_built)
     assert n_links >= 1 and n_points > 1000
 
 
-@pytest.mark.parametrize("hand", ["allegro", "robotiq2"])
+@pytest.mark.parametrize("hand", ["allegro", "robotiq2", "ability_hand"])
 def test_fused_warp_kernels_match_the_separate_ones(emu, hand):
     """gqp_fk_contacts_forward / _backward (a warp per candidate, lane = frame) == gqp_fk_forward + gqp_contacts_forward
     and gqp_contacts_backward + gqp_fk_backward (a thread per candidate)"""

@@ -80,3 +80,30 @@ def test_reference_shaped_loop_with_other_optimizer_and_energies(energy_type, op
         np.testing.assert_allclose(hand.hand_pose.detach().cpu().numpy(), eng.pose.cpu().numpy(), rtol=1e-4, atol=1e-5)
         np.testing.assert_array_equal(hand.contact_point_indices.cpu().numpy(), eng.idx.cpu().numpy())
     eng.close()
+
+
+# ---- (f3) the remaining hands whose assets the reference ships complete: Robotiq 3F, ability hand (mimic joints) ----
+def test_golden_fk_more_hands(gpu):
+    gc.check_fk(*gpu, hands=gc.MORE_HANDS)
+
+
+@pytest.mark.parametrize("hand,n_c", [("robotiq3", 12), ("ability_hand", 8)])
+def test_engine_vs_oracle_more_hands(gpu, hand, n_c):
+    import cases
+    cases.check_engine_vs_oracle(*gpu, B=8, n_pts=256, n_c=n_c, T=3, seed=5, hand=hand)
+
+
+@pytest.mark.parametrize("hand", ["robotiq3", "ability_hand"])
+def test_hand_distance_more_hands(gpu, hand):
+    import cases
+    cases.check_hand_distance(*gpu, B=32, n_pts=512, hand=hand)
+
+
+@pytest.mark.parametrize("hand", ["robotiq3", "ability_hand"])
+def test_culling_proof_more_hands(gpu, hand):
+    """as test_gpu_parity.test_culling_proof_outside_cells_have_positive_sign, for the link meshes of these hands"""
+    import cases
+    lib, be = gpu
+    sign = lambda pts, fv: cases.sdf_forward(lib, be, pts, fv)[1]
+    n_links, n_cells, n_points = cases.check_culling_proof(lib, sign, hand, per_cell=16, n_far=200000)
+    assert n_links >= 1 and n_points > 100000

@@ -64,6 +64,24 @@ HANDS = {
                  order=["finger_joint", "left_inner_knuckle_joint", "right_inner_knuckle_joint",
                         "right_outer_knuckle_joint", "left_inner_finger_joint", "right_inner_finger_joint"]),
     ),
+    # graspqp/src/graspqp/hands/ability_hand.py: 6 parameters drive the chain's 10 joints POSITIONALLY (get_all_joint_angles,
+    # :10-29: torch.stack in chain order, the second joint of the four fingers = 1.05851325 x the first; the names in that
+    # function's comments do not all match the chain order, the positions are what counts)
+    "ability_hand": dict(
+        urdf="ability_hand/ability_hand.urdf", mesh_dir="ability_hand/urdf_meshes",
+        pen="ability_hand/penetration_points.json", use_collision=True, only_collision=False,
+        joint_filter=["index_q1", "middle_q1", "pinky_q1", "ring_q1", "thumb_q1", "thumb_q2"],
+        positional=[(0, 1.0), (0, 1.05851325), (1, 1.0), (1, 1.05851325), (2, 1.0), (2, 1.05851325), (3, 1.0),
+                    (3, 1.05851325), (4, 1.0), (5, 1.0)],
+        default_state=[0.3, 0.3, 0.3, 0.3, 1, 0], forward_axis="z", up_axis="x", grasp_axis="y",
+    ),
+    # graspqp/src/graspqp/hands/robotiq3.py: 11 plain joints, no coupling
+    "robotiq3": dict(
+        urdf="robotiq3/robotiq_3finger_flat.urdf", mesh_dir="robotiq3/meshes",
+        pen="robotiq3/penetration_points.json", use_collision=True, only_collision=False, joint_filter=None,
+        default_state=[0.2, 0.2, 0.2, 0.2, 0.5, 0.5, 0.3, 0.3, 0.3, 0.0, 0.0],
+        forward_axis="z", up_axis="x", grasp_axis="z",  # robotiq3.py passes no grasp_axis: hand_model.py:470 -> forward
+    ),
 }
 
 
@@ -187,6 +205,19 @@ def build(hand):
     drv = lambda n: coupled.get(n, n)
     frame_dof = [act.index(drv(f["jname"])) if (f["jtype"] != 0 and drv(f["jname"]) in act) else -1 for f in frames]
     extra = {}
+    if cfg.get("positional"):
+        # the j-th non-fixed joint of the chain (DFS order) reads parameter k with gain g: theta_j = g * pose[9 + k]
+        pos = cfg["positional"]
+        assert len(pos) == len(jnames), (len(pos), jnames)
+        movable = [i for i, f in enumerate(frames) if f["jtype"] != 0]
+        frame_dof = [-1] * len(frames)
+        gain = [1.0] * len(frames)
+        for j, i in enumerate(movable):
+            frame_dof[i], gain[i] = pos[j]
+        for k, n in enumerate(act):  # the parameter's own joint is the one that reads it with gain 1
+            i = next(i for i, f in enumerate(frames) if f["jname"] == n)
+            assert frame_dof[i] == k and gain[i] == 1.0, (n, k, frame_dof[i], gain[i])
+        extra["frame_gain"] = np.array(gain, np.float32)
     if cfg.get("mlp"):
         # frame_dof indexes the expanded joint vector q = [clamp(theta_0), net(clamp(theta_0))] instead of the pose row;
         # every non-fixed joint of the chain must be in the network's table (utils/fk.py:41-47 raises otherwise)
