@@ -22,7 +22,7 @@ def __getattr__(name):  # lazy: importing the package must not need torch/CUDA (
     import importlib
     table = {"HandModel": "hand_model", "ObjectModel": "object_model", "GraspSpanMetricFactory": "metrics",
              "calculate_energy": "energy", "MalaStar": "optimizer", "AnnealingDexGraspNet": "optimizer",
-             "FitEngine": "engine"}
+             "FitEngine": "engine", "get_hand_model": "hand_model", "AVAILABLE_HANDS": "hand_model"}
     if name in table:
         return getattr(importlib.import_module("." + table[name], __name__), name)
     raise AttributeError(name)

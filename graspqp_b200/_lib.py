@@ -79,6 +79,7 @@ SIGNATURES = {
     "gqp_hand_link_grid": (c_int, [c_void_p, c_int, P, P, P, c_int]),
     "gqp_hand_link_planes": (c_int, [c_void_p, c_int, P, c_int, P]),
     "gqp_self_pen_joints": (c_int, [c_void_p, P, P, c_int, P, P, c_float, c_float, P, P, P]),
+    "gqp_prior_wall": (c_int, [c_void_p, P, P, c_int, POINTER(c_float * 3), P, P, c_int, c_float, c_float, P, P, P, P, P]),
     "gqp_fc_dis_energy": (c_int, [POINTER(GqpFcParams), P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P, P, P, P, P]),
     "gqp_fc_stop_iter": (c_int, [P, c_int, c_int, c_float, P, P]),
     "gqp_fc_workspace_bytes": (c_uint64, [c_int, c_int, c_int]),

@@ -515,6 +515,84 @@ fk_contacts_backward_warp_kernel(const GqpHandDev *__restrict__ hand, const floa
     }
 }
 
+// ---- (f3) optional energy terms E_prior / E_wall (core/energy.py:68-76, weights --w_prior / --w_wall of scripts/fit.py) ----
+// E_prior = 1 - (R_g a) . (0,0,-1) = 1 + (R_g a)_z with a = HandModel.grasp_axis: the grasp axis should point down.
+// E_wall  = sum over the hand surface samples of |min(z, 0)|: nothing below the table plane z = 0 (hand_model.py:1042-1071).
+// A warp per candidate: lanes stride the surface samples; gradients: d E_wall / d link_tf row 2 by atomics (the buffer the
+// penetration kernels add to), d E_prior / d pose[3:9] through the Gram-Schmidt (lane 0), ADDED to grad_pose.
+__device__ __forceinline__ void gs_backward_row2(const GramSchmidt &gs, float gx_z, float gy_z, float gz_z, V3 &gx, V3 &gy) {
+    // upstream gradient w.r.t. the THIRD ROW of R = [x^ y^ z]: (gx_z, gy_z, gz_z); same chain as fk_backward_kernel
+    V3 gxh = V3{0.f, 0.f, gx_z}, gyh = V3{0.f, 0.f, gy_z}, gz = V3{0.f, 0.f, gz_z};
+    gxh = gxh + cross3(gs.yh, gz);
+    gyh = gyh + cross3(gz, gs.xh);
+    const V3 gyp = (gyh - gs.yh * dot3(gs.yh, gyh)) * (1.0f / gs.ny);
+    gy = gyp;
+    const float gd = -dot3(gs.xh, gyp);
+    gxh = gxh - gyp * gs.d;
+    gxh = gxh + gs.y * gd;
+    gy = gy + gs.xh * gd;
+    gx = (gxh - gs.xh * dot3(gs.xh, gxh)) * (1.0f / gs.nx);
+}
+
+__global__ void __launch_bounds__(128)
+prior_wall_kernel(int n_links, const float *__restrict__ link_tf, const float *__restrict__ pose, int Bt, int D, float ax,
+                  float ay, float az, const float *__restrict__ surf, const int32_t *__restrict__ surf_link, int n_surf,
+                  float w_prior, float w_wall, float *__restrict__ e_prior, float *__restrict__ e_wall,
+                  float *__restrict__ grad_link_tf, float *__restrict__ grad_pose) {
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const bool live = b < Bt;
+    const int bb = live ? b : Bt - 1;
+    float ew = 0.f;
+    if (e_wall || (grad_link_tf && w_wall != 0.f)) {
+        for (int i = lane; i < n_surf; i += 32) {
+            const int l = surf_link[i];
+            const float *W = link_tf + ((size_t)bb * n_links + l) * 12;
+            const V3 p = ld3(surf + 3 * (size_t)i);
+            const float z = W[8] * p.x + W[9] * p.y + W[10] * p.z + W[11];
+            if (z < 0.f) {
+                ew -= z;
+                if (grad_link_tf && live && w_wall != 0.f) {  // d|z|/dz = -1
+                    float *g = grad_link_tf + ((size_t)b * n_links + l) * 12;
+                    atomicAdd(g + 8, -w_wall * p.x);
+                    atomicAdd(g + 9, -w_wall * p.y);
+                    atomicAdd(g + 10, -w_wall * p.z);
+                    atomicAdd(g + 11, -w_wall);
+                }
+            }
+        }
+        ew = warp_sum(ew);
+    }
+    if (lane == 0 && live) {
+        if (e_wall) e_wall[b] = ew;
+        const float *pr = pose + (size_t)b * D;
+        const GramSchmidt gs = gram_schmidt(ld3(pr + 3), ld3(pr + 6));
+        if (e_prior) e_prior[b] = 1.0f + (gs.xh.z * ax + gs.yh.z * ay + gs.z.z * az);
+        if (grad_pose && w_prior != 0.f) {
+            V3 gx, gy;
+            gs_backward_row2(gs, w_prior * ax, w_prior * ay, w_prior * az, gx, gy);
+            float *g = grad_pose + (size_t)b * D;
+            g[3] += gx.x; g[4] += gx.y; g[5] += gx.z;
+            g[6] += gy.x; g[7] += gy.y; g[8] += gy.z;
+        }
+    }
+}
+
+extern "C" int gqp_prior_wall(const GqpHand *h, const float *link_tf, const float *pose, int Bt,
+                              const float *grasp_axis_host, const float *surf, const int32_t *surf_link, int n_surf,
+                              float w_prior, float w_wall, float *e_prior, float *e_wall, float *grad_link_tf,
+                              float *grad_pose, void *stream) {
+    if (!h || Bt < 0 || n_surf < 0 || !grasp_axis_host) return gqp_set_error(GQP_ERR_ARG, "gqp_prior_wall: bad argument");
+    if (Bt == 0) return GQP_OK;
+    if (!link_tf || !pose || (n_surf > 0 && (!surf || !surf_link)))
+        return gqp_set_error(GQP_ERR_ARG, "gqp_prior_wall: null pointer");
+    GQP_LAUNCH(prior_wall_kernel, (Bt + 3) / 4, 128, 0, (cudaStream_t)stream, h->host.n_links, link_tf, pose, Bt,
+               9 + h->host.n_dofs, grasp_axis_host[0], grasp_axis_host[1], grasp_axis_host[2], surf, surf_link, n_surf,
+               w_prior, w_wall, e_prior, e_wall, grad_link_tf, grad_pose);
+    GQP_CHECK_LAUNCH("gqp_prior_wall");
+    return GQP_OK;
+}
+
 // ---- host side ------------------------------------------------------------------------------------------------------
 extern "C" int gqp_hand_create(const GqpHandDesc *d, GqpHand **out) {
     if (!d || !out) return gqp_set_error(GQP_ERR_ARG, "gqp_hand_create: null argument");

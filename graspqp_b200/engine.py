@@ -18,7 +18,9 @@ import numpy as np
 from . import _lib, hand_pack
 
 TERMS = ("E_dis", "E_fc", "E_joints", "E_pen", "E_spen")
-DEFAULT_WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_joints=1.0, E_pen=100.0, E_spen=10.0)  # scripts/fit.py:90-112
+OPTIONAL_TERMS = ("E_prior", "E_wall")  # energy.py:68-77, evaluated when their weight is > 0 (fit.py:373), appended in this order
+DEFAULT_WEIGHTS = dict(E_dis=100.0, E_fc=1.0, E_joints=1.0, E_pen=100.0, E_spen=10.0, E_prior=0.0,
+                       E_wall=0.0)  # scripts/fit.py:77-78, 90-112
 
 
 def morton_order(pts, bits=10):
@@ -123,11 +125,13 @@ class FitEngine:
                  starting_temperature=18.0, temperature_decay=0.95, annealing_period=30, step_size=0.005,
                  stepsize_period=50, mu=0.98, clip_grad=False, qp_batch_stop=True, seed=1, collectives=None,
                  overlap=True, queue_per_candidate=None, energy_type="graspqp", optimizer="mala_star",
-                 tdg_directions=None, dexgrasp_torque_weight=0.0):
+                 tdg_directions=None, dexgrasp_torque_weight=0.0, hand_surface=None):
         """energy_type: graspqp | dexgrasp | tdg (scripts/fit.py:81-88, 344-356); optimizer: mala_star | dexgraspnet
         (fit.py:74, 334-337).  tdg_directions (P,3): the unit directions TDGEnergy draws at construction (tdg.py:148-150);
         default: 1000 normalised normal draws from numpy's RandomState(seed), as np.random.seed(seed) makes the reference's.
-        dexgrasp_torque_weight: 0.0 is what the reference's call passes (DexgraspSpanMetric.forward's default)."""
+        dexgrasp_torque_weight: 0.0 is what the reference's call passes (DexgraspSpanMetric.forward's default).
+        weights E_prior / E_wall > 0 switch those terms on (energy.py:68-77); hand_surface = (points (n,3) in link frames,
+        link (n)) for E_wall, default hand_pack.surface_points(pack) (512 samples, built the reference's way)."""
         if energy_type not in ("graspqp", "dexgrasp", "tdg"):
             raise ValueError(f"energy_type {energy_type!r}: graspqp, dexgrasp or tdg")
         if optimizer not in ("mala_star", "dexgraspnet"):
@@ -182,15 +186,26 @@ class FitEngine:
         f32, i32, u8 = np.float32, np.int32, np.uint8
         self.surf = be.from_host(surface_points_sorted, f32)
         self.cog = be.from_host(surface_points.mean(1, dtype=np.float32), f32)  # object_model.py:64-68
-        self.w_dev = be.from_host(np.array([w[k] for k in TERMS], f32))
+        self.terms = TERMS + tuple(k for k in OPTIONAL_TERMS if w[k] > 0.0)
+        self.w_dev = be.from_host(np.array([w[k] for k in self.terms], f32))
+        self.n_surf = 0
+        if len(self.terms) > len(TERMS):
+            ax = {"x": (1, 0, 0), "y": (0, 1, 0), "z": (0, 0, 1), "-x": (-1, 0, 0), "-y": (0, -1, 0), "-z": (0, 0, -1)}
+            self.grasp_axis = (ctypes.c_float * 3)(*ax[str(pack["axes"][2])])  # HandModel.grasp_axis, hand_model.py:470
+            self.hand_surf = self.hand_surf_link = None
+            if "E_wall" in self.terms:
+                sp_, sl_ = hand_surface if hand_surface is not None else hand_pack.surface_points(pack)
+                assert np.asarray(sl_).min() >= 0 and np.asarray(sl_).max() < self.L
+                self.hand_surf, self.hand_surf_link = be.from_host(sp_, f32), be.from_host(sl_, i32)
+                self.n_surf = len(sl_)
         self.pose = be.from_host(hand_pose, f32)
         self.idx = be.from_host(contact_idx, i32)
         assert tuple(self.pose.shape) == (Bt, D) and tuple(self.idx.shape) == (Bt, n_c)
         self.grad, self.ema = be.empty((Bt, D), f32), be.empty((Bt, D), f32)
         self.step_count = be.empty((Bt,), i32)
-        self.energy, self.losses = be.empty((Bt,), f32), be.empty((len(TERMS), Bt), f32)
+        self.energy, self.losses = be.empty((Bt,), f32), be.empty((len(self.terms), Bt), f32)
         self.pose_new, self.idx_new = be.empty((Bt, D), f32), be.empty((Bt, n_c), i32)
-        self.grad_new, self.losses_new = be.empty((Bt, D), f32), be.empty((len(TERMS), Bt), f32)
+        self.grad_new, self.losses_new = be.empty((Bt, D), f32), be.empty((len(self.terms), Bt), f32)
         self.new_energy, self.accept = be.empty((Bt,), f32), be.empty((Bt,), u8)
         self.temperature, self.step_size_out = be.empty((Bt,), f32), be.empty((Bt,), f32)
         self.z, self.grad2_mean = be.empty((Bt,), f32), be.empty((D,), f32)
@@ -244,7 +259,7 @@ class FitEngine:
         """calculate_energy (core/energy.py:6-66) + backward (fit.py:440) at (pose, idx): 5 terms and d(sum w E)/d pose."""
         lib, be, p, st = self.lib, self.be, self.be.ptr, self.be.stream
         Bt, n_c, O, B = self.Bt, self.n_c, self.n_obj, self.batch_each
-        row = lambda k: p(losses_out) + 4 * Bt * TERMS.index(k)
+        row = lambda k: p(losses_out) + 4 * Bt * self.terms.index(k) if k in self.terms else None
         # H1-H3 in one launch, a warp per candidate: link transforms + the n_c chosen contact points / normals
         self._ck(lib.gqp_fk_contacts_forward(self.hand, p(pose), p(idx), Bt, n_c, p(self.link_tf), p(self.cpts),
                                              p(self.cnrm), st))
@@ -294,6 +309,11 @@ class FitEngine:
         self._ck(lib.gqp_self_pen_joints(self.hand, p(self.link_tf), p(pose), Bt, row("E_spen"), row("E_joints"),
                                          self.weights["E_spen"], self.weights["E_joints"], p(self.g_link_tf),
                                          p(self.g_pose_joints), s2))
+        if len(self.terms) > len(TERMS):  # (f3) E_prior / E_wall: adds to g_link_tf and to g_pose_joints' rotation columns
+            self._ck(lib.gqp_prior_wall(self.hand, p(self.link_tf), p(pose), Bt, ctypes.byref(self.grasp_axis),
+                                        p(self.hand_surf), p(self.hand_surf_link), self.n_surf,
+                                        self.weights["E_prior"], self.weights["E_wall"], row("E_prior"), row("E_wall"),
+                                        p(self.g_link_tf), p(self.g_pose_joints), s2))
         if overlap:
             be.join()
         # contact scatter + analytic J' of the chain in one launch (fixed summation order): reads what the penetration
@@ -326,13 +346,13 @@ class FitEngine:
     def _accept(self, z, reset, u_accept, after_reset=False):
         lib, p, st = self.lib, self.be.ptr, self.be.stream
         if self.optimizer == "dexgraspnet":  # no z-score factor, no forced accept (optimizer.py:110-138)
-            self._ck(lib.gqp_anneal_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(TERMS), p(self.w_dev),
+            self._ck(lib.gqp_anneal_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(self.terms), p(self.w_dev),
                                            p(self.losses_new), p(u_accept), self.seed, self.iteration, self.anneal_step,
                                            p(self.pose_new), p(self.idx_new), p(self.grad_new), p(self.pose), p(self.idx),
                                            p(self.grad), p(self.energy), p(self.losses), p(self.new_energy),
                                            p(self.accept), p(self.temperature), int(after_reset), st))
             return
-        self._ck(lib.gqp_mala_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(TERMS), p(self.w_dev),
+        self._ck(lib.gqp_mala_accept(ctypes.byref(self.mala), self.Bt, self.D, self.n_c, len(self.terms), p(self.w_dev),
                                      p(self.losses_new), p(z), p(reset), p(u_accept), self.seed, self.iteration,
                                      p(self.step_count), p(self.pose_new), p(self.idx_new), p(self.grad_new),
                                      p(self.pose), p(self.idx), p(self.grad), p(self.energy), p(self.losses),

@@ -106,3 +106,18 @@ class HandModel:
         B = self.hand_pose.shape[0]
         idx = torch.arange(self.n_contact_candidates, device=self.device, dtype=torch.int32).repeat(B, 1)
         return ops.ContactsFn.apply(self.current_status, idx, self)[0]
+
+
+# graspqp/src/graspqp/hands/__init__.py:13-28 (registry names -> hand packs).  "schunk2" is not built: the reference ships no
+# contact_infos.json for it (HandModel would sample it with trimesh at construction) and its meshes are COLLADA files.
+_REGISTRY = {"robotiq3": "robotiq3", "panda": "panda", "allegro": "allegro", "ability_hand": "ability_hand",
+             "shadow_hand": "shadow_hand", "robotiq2": "robotiq2"}
+AVAILABLE_HANDS = list(_REGISTRY.keys())
+
+
+def get_hand_model(hand_name, device, **kwargs):
+    if hand_name not in _REGISTRY:
+        raise KeyError(f"hand {hand_name!r}: available {AVAILABLE_HANDS}")
+    if kwargs.get("grasp_type") not in (None, "all", "default"):
+        raise NotImplementedError("grasp_type filters of the contact links (eigengrasps.json) are not compiled into the packs")
+    return HandModel(_REGISTRY[hand_name], device)

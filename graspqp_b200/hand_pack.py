@@ -64,3 +64,40 @@ def create_hand(cdll, pack):
     h = ctypes.c_void_p()
     _lib.check(cdll.gqp_hand_create(ctypes.byref(d), ctypes.byref(h)), cdll)
     return h
+
+
+def surface_points(pack, n_surface_points=512, seed=42):
+    """The hand surface samples E_wall reads (HandModel.get_surface_points, hand_model.py:1042-1071): per link
+    int(area / total_area * n) points, the remainder to the first link, each link's set = farthest point sampling (start
+    index 0) of 100x as many area-uniform samples (hand_model.py:603-629).  The reference draws the dense cloud with
+    pytorch3d under torch.manual_seed(42); here numpy's RandomState(seed) draws it, so the point SET differs from the
+    reference's while its construction is the same.  Setup-time host work.  -> (points (n,3) float32 in link frames,
+    link (n) int32 ascending)."""
+    fv = np.asarray(pack["face_verts"], np.float64).reshape(-1, 3, 3)
+    off = np.asarray(pack["face_offset"])
+    L = len(off) - 1
+    tri_area = 0.5 * np.linalg.norm(np.cross(fv[:, 1] - fv[:, 0], fv[:, 2] - fv[:, 0]), axis=1)
+    areas = np.array([tri_area[off[l]:off[l + 1]].sum() for l in range(L)])
+    num = [int(a / areas.sum() * n_surface_points) for a in areas]
+    num[0] += n_surface_points - sum(num)
+    pts, link = [], []
+    for l in range(L):
+        k = num[l]
+        if k == 0:
+            continue
+        rng = np.random.RandomState(seed)
+        a = tri_area[off[l]:off[l + 1]]
+        f = rng.choice(len(a), size=100 * k, p=a / a.sum())
+        u, v = rng.rand(100 * k), rng.rand(100 * k)
+        s = np.sqrt(u)
+        t = fv[off[l]:off[l + 1]][f]
+        dense = ((1 - s)[:, None] * t[:, 0] + (s * (1 - v))[:, None] * t[:, 1] + (s * v)[:, None] * t[:, 2]).astype(np.float32)
+        sel, mind, cur = np.zeros(k, np.int64), np.full(len(dense), np.inf, np.float32), 0
+        for i in range(k):
+            sel[i] = cur
+            d = dense - dense[cur]
+            mind = np.minimum(mind, (d * d).sum(1))
+            cur = int(np.argmax(mind))
+        pts.append(dense[sel])
+        link.append(np.full(k, l, np.int32))
+    return np.concatenate(pts, 0).astype(np.float32), np.concatenate(link, 0)

@@ -205,6 +205,17 @@ int gqp_self_pen_joints(const GqpHand *h, const float *link_tf, const float *pos
                         float *e_joints, float w_spen, float w_joints, float *grad_link_tf, float *grad_pose_joints,
                         void *stream);
 
+/* ---- (f3) the optional terms E_prior / E_wall (core/energy.py:68-76; --w_prior / --w_wall, both 0 by default) --------------
+ * e_prior (Bt) = 1 - (R_g grasp_axis) . (0,0,-1), grasp_axis_host[3] = HandModel.grasp_axis (hand_model.py:470);
+ * e_wall (Bt) = sum_i |min(z_i, 0)| over the n_surf hand surface samples `surf` (n_surf,3, device, link frames) of links
+ * `surf_link` (n_surf, device) — HandModel.get_surface_points (hand_model.py:1042-1071).  ACCUMULATES w_wall*d(e_wall) into
+ * grad_link_tf (atomics) and ADDS w_prior*d(e_prior)/d(pose[:,3:9]) to grad_pose (Bt, 9+n_dofs); both may be NULL.
+ * Call it after gqp_self_pen_joints (which overwrites grad_pose) and before gqp_fk_contacts_backward.  surf_link entries must
+ * be valid link ids.  E_manipulativity (energy.py:78-87) is not offered: scripts/fit.py's weight_dict has no entry for it. */
+int gqp_prior_wall(const GqpHand *h, const float *link_tf, const float *pose, int Bt, const float *grasp_axis_host,
+                   const float *surf, const int32_t *surf_link, int n_surf, float w_prior, float w_wall, float *e_prior,
+                   float *e_wall, float *grad_link_tf, float *grad_pose, void *stream);
+
 /* ---- Q1-Q4 + E_dis: force-closure QP (span.py:263-415, qp_solver.py:60-134, registry.py:31-89) and contact-distance
  * energy (energy.py:25-28), forward + analytic backward in one launch, a warp per candidate. -----------------------
  * cpts/cnrm_hand (Bt,n_c,3) from gqp_contacts_forward; obj_dist (Bt,n_c), obj_nrm (Bt,n_c,3) from

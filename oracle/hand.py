@@ -101,6 +101,11 @@ class HandOracle:
         self.n_contact_candidates = len(self.cand)
         self.L = len(self.mesh_frame)
         self.hand_pose = None
+        # HandModel.grasp_axis (hand_model.py:459-470) and the surface samples of get_surface_points (:1042-1071); the
+        # samples are injected (graspqp_b200.hand_pack.surface_points builds a table the reference's way)
+        ax = {"x": (1, 0, 0), "y": (0, 1, 0), "z": (0, 0, 1), "-x": (-1, 0, 0), "-y": (0, -1, 0), "-z": (0, 0, -1)}
+        self.grasp_axis = torch.tensor(ax[str(pack["axes"][2])], dtype=dtype, device=self.device)
+        self.surface_pts = self.surface_link = None
         # hands/robotiq2.py:9-13 + utils/fk.py:23-51: Linear(1,10)-Tanh-Linear(10,5) joint-coupling network
         self.mlp = None
         if "mlp_w1" in pack:
@@ -178,6 +183,22 @@ class HandOracle:
         idx = contact_point_indices.unsqueeze(-1).expand(-1, -1, 3)
         self.contact_points = pts.gather(1, idx)
         self.contact_normals = nrm.gather(1, idx)
+
+    def set_surface_points(self, pts, link):
+        self.surface_pts = torch.as_tensor(pts).to(self.dtype).to(self.device)
+        self.surface_link = torch.as_tensor(link).long().to(self.device)
+
+    def get_surface_points(self):
+        """hand_model.py:1042-1071: link-frame samples -> world, links in mesh order"""
+        out = []
+        for li in range(self.L):
+            m = self.surface_link == li
+            if m.sum() == 0:
+                continue
+            T = self.link_matrix(li)
+            out.append(self.surface_pts[m] @ T[:, :3, :3].transpose(1, 2) + T[:, :3, 3].unsqueeze(1))
+        pts = torch.cat(out, -2)
+        return pts @ self.global_rotation.transpose(1, 2) + self.global_translation.unsqueeze(1)
 
     def cal_distance(self, x, per_link=False):
         x = (x - self.global_translation.unsqueeze(1)) @ self.global_rotation

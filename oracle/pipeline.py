@@ -48,7 +48,7 @@ class ObjectOracle:
 
 
 def calculate_energy(hand, obj, svd_gain=0.1, friction=0.2, max_limit=20.0, energy_type="graspqp", tdg=None,
-                     dexgrasp_torque_weight=0.0):
+                     dexgrasp_torque_weight=0.0, energy_names=()):
     """energy_type: graspqp | dexgrasp | tdg (scripts/fit.py:344-356); tdg = a metrics_alt.TDGOracle"""
     distance, contact_normal = obj.cal_distance(hand.contact_points)
     E_dis = ((1 - torch.sum((-contact_normal) * hand.contact_normals, dim=-1)).exp() * distance.abs()).sum(-1)
@@ -70,7 +70,14 @@ def calculate_energy(hand, obj, svd_gain=0.1, friction=0.2, max_limit=20.0, ener
     d[d <= 0] = 0
     E_pen = d.sum(-1)
     E_spen = hand.self_penetration()
-    return dict(E_dis=E_dis, E_fc=E_fc, E_joints=E_joints, E_pen=E_pen, E_spen=E_spen), info
+    losses = dict(E_dis=E_dis, E_fc=E_fc, E_joints=E_joints, E_pen=E_pen, E_spen=E_spen)
+    if "E_prior" in energy_names:  # energy.py:68-74
+        forward_axis = (hand.global_rotation @ hand.grasp_axis.view(1, -1, 1)).view(-1, 3)
+        axis_prior = torch.tensor([0, 0, -1], dtype=hand.dtype).view(1, 3)
+        losses["E_prior"] = 1 - torch.sum(forward_axis * axis_prior, dim=-1)
+    if "E_wall" in energy_names:  # energy.py:75-77
+        losses["E_wall"] = hand.get_surface_points()[..., -1].clamp(max=0.0).abs().sum(-1)
+    return losses, info
 
 
 def total_energy(losses, weights=WEIGHTS):
@@ -216,17 +223,24 @@ class FitLoopOracle:
 
     def __init__(self, pack, face_verts_list, surface_points_list, batch_size_each, hand_pose0, idx0,
                  dtype=torch.float32, energy_type="graspqp", optimizer="mala_star", tdg_directions=None,
-                 dexgrasp_torque_weight=0.0, **opt):
+                 dexgrasp_torque_weight=0.0, weights=None, hand_surface=None, **opt):
+        """weights: overrides of WEIGHTS; terms E_prior / E_wall are evaluated when their weight is > 0 (fit.py:373);
+        hand_surface = (points, link) for E_wall"""
         self.hand = HandOracle(pack, dtype)
+        if hand_surface is not None:
+            self.hand.set_surface_points(*hand_surface)
+        self.weights = dict(WEIGHTS)
+        self.weights.update(weights or {})
         self.obj = ObjectOracle(face_verts_list, surface_points_list, batch_size_each, dtype)
         self.B = batch_size_each
         self.hand.set_parameters(torch.as_tensor(hand_pose0, dtype=dtype).clone().requires_grad_(True),
                                  torch.as_tensor(idx0).long())
         self.opt = (MalaStarOracle if optimizer == "mala_star" else AnnealingOracle)(self.hand, **opt)
         self.ekw = dict(energy_type=energy_type, dexgrasp_torque_weight=dexgrasp_torque_weight,
-                        tdg=TDGOracle(tdg_directions) if energy_type == "tdg" else None)
+                        tdg=TDGOracle(tdg_directions) if energy_type == "tdg" else None,
+                        energy_names=[k for k in ("E_prior", "E_wall") if self.weights.get(k, 0.0) > 0.0])
         self.losses, _ = calculate_energy(self.hand, self.obj, **self.ekw)
-        self.energy = total_energy(self.losses)
+        self.energy = total_energy(self.losses, self.weights)
         self.energy.sum().backward()
         self.first_grad = self.hand.hand_pose.grad.clone()
         self.hand.hand_pose.grad.zero_()  # fit.py:396
@@ -266,7 +280,7 @@ class FitLoopOracle:
             new_losses, info = calculate_energy(self.hand, self.obj, **self.ekw)
         finally:
             _qp.FORCE_STOP = None
-        new_energy = total_energy(new_losses)
+        new_energy = total_energy(new_losses, self.weights)
         new_energy.sum().backward()
         out = dict(energy_before=self.energy.detach().clone(), new_energy=new_energy.detach().clone(), new_grad=self.hand.hand_pose.grad.clone(),
                    new_losses={k: v.detach().clone() for k, v in new_losses.items()}, z=z, s=s,

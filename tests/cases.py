@@ -441,3 +441,39 @@ def check_benched_state(lib, be, name="config2", iters=(0, 50, 500), per_object=
         print(f"[benched] {lab}: {report[n]}")
     eng.close()
     return report
+
+
+def check_optional_terms(lib, be, B=4, n_pts=64, n_c=12, T=2, seed=3, hand="allegro", w_prior=5.0, w_wall=50.0):
+    """(f3) E_prior / E_wall (core/energy.py:68-77) switched on by their weights: engine vs fp64 oracle, per-term energies,
+    total energy, gradient, accept decisions.  Both sides read the same hand surface samples.  -> (mean E_prior, mean E_wall)"""
+    pack = hand_pack.load_pack(hand)
+    v, f = synth.make_mesh("sphere", 200, seed)
+    fv = synth.face_vertices(v, f)
+    sp = synth.sample_surface(v, f, n_pts, seed=seed)
+    pose, idx = synth.random_grasp_init(pack, [v], B, n_c, seed)
+    pose[:, :3] *= 0.7
+    w = dict(E_prior=w_prior, E_wall=w_wall)
+    surf = hand_pack.surface_points(pack, 128)
+    eng = engine.FitEngine(lib, be, pack, [fv], sp[None], B, pose, idx.astype(np.int32), weights=w, hand_surface=surf)
+    orc = FitLoopOracle(pack, [fv], [sp], B, pose, idx, dtype=torch.float64, weights=w, hand_surface=surf)
+    H = be.to_host
+    assert eng.terms == engine.TERMS + tuple(k for k in engine.OPTIONAL_TERMS if w[k] > 0)
+    tol.assert_energy(H(eng.energy), orc.energy.numpy(), f"{hand} optional terms: initial energy")
+    for k, name in enumerate(eng.terms):
+        np.testing.assert_allclose(H(eng.losses)[k], orc.losses[name].numpy(), rtol=1e-4, atol=1e-6, err_msg=name)
+    tol.assert_grad(eng.first_grad, orc.first_grad.numpy(), f"{hand} optional terms: first gradient")
+    ex = lambda b: tol.normal_unstable(H(eng.cpts)[b], fv)
+    rng = np.random.default_rng(0)
+    for t in range(T):
+        us, ir, ua = rng.random((B, n_c), dtype=np.float32), rng.integers(0, len(pack["cand"]), (B, n_c)).astype(np.int32), rng.random(B, dtype=np.float32)
+        eng.step(be.from_host(us), be.from_host(ir), be.from_host(ua))
+        out = orc.iterate(torch.tensor(us, dtype=torch.float64), torch.tensor(ir).long(), torch.tensor(ua, dtype=torch.float64))
+        for k, name in enumerate(eng.terms):
+            np.testing.assert_allclose(H(eng.losses_new)[k], out["new_losses"][name].numpy(), rtol=1e-4, atol=1e-6, err_msg=name)
+        tol.assert_energy(H(eng.new_energy), out["new_energy"].numpy(), f"{hand} optional terms: step {t} new energy", excuse=ex)
+        tol.assert_grad(H(eng.grad_new), out["new_grad"].numpy(), f"{hand} optional terms: step {t} gradient", excuse=ex)
+        np.testing.assert_array_equal(H(eng.accept).astype(bool), out["accept"].numpy())
+    ep = float(H(eng.losses_new)[eng.terms.index("E_prior")].mean()) if w_prior > 0 else 0.0
+    ew = float(H(eng.losses_new)[eng.terms.index("E_wall")].mean()) if w_wall > 0 else 0.0
+    eng.close()
+    return ep, ew

@@ -117,3 +117,12 @@ def test_bounded_survivor_queue_overflow_is_detected(emu):
         tight.assert_ok()
     for e in (ref, roomy, tight):
         e.close()
+
+
+@pytest.mark.parametrize("hand,n_c,w_wall", [("allegro", 12, 50.0), ("panda", 4, 0.0)])
+def test_optional_terms_prior_and_wall(emu, hand, n_c, w_wall):
+    """(f3) E_prior / E_wall (core/energy.py:68-77) through gqp_prior_wall vs the fp64 oracle; Panda's grasp axis is its
+    forward axis (no grasp_axis passed, hand_model.py:470)"""
+    import cases
+    ep, ew = cases.check_optional_terms(emu, engine.NumpyBackend(), hand=hand, n_c=n_c, w_wall=w_wall)
+    assert ep > 0 and (ew > 0) == (w_wall > 0)

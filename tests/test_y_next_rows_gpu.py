@@ -107,3 +107,10 @@ def test_culling_proof_more_hands(gpu, hand):
     sign = lambda pts, fv: cases.sdf_forward(lib, be, pts, fv)[1]
     n_links, n_cells, n_points = cases.check_culling_proof(lib, sign, hand, per_cell=16, n_far=200000)
     assert n_links >= 1 and n_points > 100000
+
+
+def test_optional_terms_prior_and_wall(gpu):
+    """(f3) E_prior / E_wall through gqp_prior_wall vs the fp64 oracle, 512 hand surface samples"""
+    import cases
+    ep, ew = cases.check_optional_terms(*gpu, B=16, n_pts=256, T=3)
+    assert ep > 0 and ew > 0

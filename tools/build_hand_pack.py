@@ -50,7 +50,7 @@ HANDS = {
         urdf="panda/franka_panda.urdf", mesh_dir="panda/meshes",
         pen="panda/penetration_points.json", use_collision=True, only_collision=False,
         joint_filter=["panda_finger_joint1"], coupled={"panda_finger_joint2": "panda_finger_joint1"},
-        default_state=[0.04], forward_axis="z", up_axis="x", grasp_axis="y",
+        default_state=[0.04], forward_axis="z", up_axis="x", grasp_axis="z",  # none passed: hand_model.py:470 -> forward
     ),
     # graspqp/src/graspqp/hands/robotiq2.py: the single parameter "finger_joint" is clamped to [-0.05, 0.8] and a small
     # network (utils/fk.py:23-51, Linear(1,10)-Tanh-Linear(10,5)) gives the other five joints of the closed linkage.
@@ -58,7 +58,8 @@ HANDS = {
     "robotiq2": dict(
         urdf="robotiq2/robotiq_2f140.urdf", mesh_dir="robotiq2/meshes",
         pen="robotiq2/penetration_points.json", use_collision=True, only_collision=False,
-        joint_filter=["finger_joint"], default_state=[0.0], forward_axis="z", up_axis="x", grasp_axis="y",
+        joint_filter=["finger_joint"], default_state=[0.0], forward_axis="z", up_axis="x",
+        grasp_axis="z",  # none passed: hand_model.py:470 -> forward
         mlp=dict(weights="robotiq2/robotiq2f_fk.pth", clamp=[-0.05, 0.8],
                  # utils/fk.py:13-20: column order of cat([clamped parameter, network output])
                  order=["finger_joint", "left_inner_knuckle_joint", "right_inner_knuckle_joint",
