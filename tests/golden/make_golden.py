@@ -298,6 +298,7 @@ def gen_fit_alt(name="fit_alt_ref.npz"):
                         reset iteration with an injected mask (resets are neither force-accepted nor seen by this optimiser);
                         stepsize_period 2 / annealing_period 3 so that both schedules move within the run;
        run "tdgmala":   MalaStar + --energy_type tdg (1000 directions from numpy seed 7), 3 iterations;
+       run "priorwall": MalaStar + graspqp with the optional terms E_prior / E_wall on;
        run "malareset": MalaStar + graspqp, a reset iteration followed by one with forced rejections (the gradient that
                         rejected rows keep there is old + new: oracle/pipeline.py AFTER_RESET)."""
     pack = hand_pack.load_pack("allegro")
@@ -317,9 +318,16 @@ def gen_fit_alt(name="fit_alt_ref.npz"):
                                      ("tdgmala", torch.float64, dict(energy_type="tdg"), ["plain", "plain", "plain"]),
                                      # MalaStar + graspqp around a reset iteration, with rejections forced in the iteration
                                      # AFTER it (u_accept 1e30 on two rows): oracle.pipeline.AFTER_RESET
-                                     ("malareset", torch.float64, dict(), ["plain", "reset_mask", "reject", "plain"])):
+                                     ("malareset", torch.float64, dict(), ["plain", "reset_mask", "reject", "plain"]),
+                                     # the reference's energy.py:68-77 with --w_prior 5 --w_wall 50 (HandOracle supplies
+                                     # global_rotation, grasp_axis and get_surface_points over the stored sample table)
+                                     ("priorwall", torch.float64, dict(weights=dict(E_prior=5.0, E_wall=50.0),
+                                                                       hand_surface=hand_pack.surface_points(pack, 128)),
+                                      ["plain", "plain"])):
             torch.set_default_dtype(dtype)
             st = rh.make_fit_state(pack, [fv], [sp], B, pose.astype(np.float32), idx, dtype=dtype, **kw)
+            if run == "priorwall":
+                out["hand_surf"], out["hand_surf_link"] = kw["hand_surface"]
             if run == "tdgmala":
                 out["tdg_dirs"] = st.energy_fnc.tdg_energy.target_direction_6D[0, :, :3].numpy().astype(np.float32)
             rng = np.random.default_rng(11)

@@ -86,12 +86,14 @@ def tdg_metric(ref, dtype, seed=7):
 
 def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_pose0, idx0, dtype=torch.float32,
                    friction=0.2, max_limit=20.0, n_cone_vecs=4, svd_gain=0.1, energy_type="graspqp",
-                   optimizer="mala_star", **optim):
+                   optimizer="mala_star", weights=None, hand_surface=None, **optim):
     """The state scripts/fit.py holds between iterations, with the REFERENCE MalaStar / calculate_energy / metric."""
     from oracle.hand import HandOracle
     from oracle.pipeline import ObjectOracle, WEIGHTS
     ref = load()
     hand = HandOracle(pack, dtype)
+    if hand_surface is not None:
+        hand.set_surface_points(*hand_surface)
     obj = ObjectOracle(face_verts_list, surface_points_list, batch_each, dtype)
     obj.device = torch.device("cpu")
     obj.object_scale_tensor = torch.ones(len(face_verts_list), batch_each, dtype=dtype)
@@ -117,7 +119,7 @@ def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_
         energy_fnc = tdg_metric(ref, dtype)
     else:
         raise ValueError(energy_type)
-    st = types.SimpleNamespace(hand=hand, obj=obj, opt=opt, energy_fnc=energy_fnc, weights=dict(WEIGHTS), B=batch_each,
+    st = types.SimpleNamespace(hand=hand, obj=obj, opt=opt, energy_fnc=energy_fnc, weights=dict(WEIGHTS, **(weights or {})), B=batch_each,
                                svd_gain=svd_gain, ref=ref)
 
     def energies():

@@ -245,10 +245,11 @@ ALT_RUNS = {
                       annealing_period=3),
     "tdgmala": dict(energy_type="tdg"),
     "malareset": dict(),
+    "priorwall": dict(weights=dict(E_prior=5.0, E_wall=50.0)),
 }
 
 
-def check_fit_alt(lib, be, runs=("dexanneal", "tdgmala", "malareset")):
+def check_fit_alt(lib, be, runs=("dexanneal", "tdgmala", "malareset", "priorwall")):
     """(f3) the reference's OTHER optimiser / energies and the gradient a rejected row keeps after a reset iteration, against
     the reference's own AnnealingDexGraspNet, DexgraspSpanMetric, TDGSpanMetric and MalaStar run through scripts/fit.py's loop
     body: tests/golden/fit_alt_ref.npz (make_golden.gen_fit_alt; "dexanneal" is an fp32 run of the reference, the other two
@@ -262,6 +263,8 @@ def check_fit_alt(lib, be, runs=("dexanneal", "tdgmala", "malareset")):
         kw = dict(ALT_RUNS[run])
         if run == "tdgmala":
             kw["tdg_directions"] = g["tdg_dirs"]
+        if run == "priorwall":
+            kw["hand_surface"] = (g["hand_surf"], g["hand_surf_link"])
         eng = engine.FitEngine(lib, be, pack, [g["face_verts"]], g["surface"][None], B, g["pose0"], g["idx0"], **kw)
         tol.assert_energy(H(eng.energy), g[run + "_energy0"], f"golden {run}: first energy")
         tol.assert_grad(eng.first_grad, g[run + "_first_grad"], f"golden {run}: first gradient")
@@ -282,7 +285,7 @@ def check_fit_alt(lib, be, runs=("dexanneal", "tdgmala", "malareset")):
                                        H(eng.step_size_out)[:1].repeat(B) if run == "dexanneal" else H(eng.step_size_out),
                                        rtol=1e-6, err_msg=lbl)
             tol.assert_energy(H(eng.new_energy), g[k0 + "new_energy"], lbl + " new energy", excuse=ex)
-            for k, name in enumerate(engine.TERMS):
+            for k, name in enumerate(eng.terms):
                 np.testing.assert_allclose(H(eng.losses_new)[k], g[k0 + "loss_" + name], rtol=1e-4, atol=1e-6, err_msg=name)
             tol.assert_grad(H(eng.grad_new), g[k0 + "new_grad"], lbl + " gradient", excuse=ex)
             np.testing.assert_allclose(H(eng.temperature), np.broadcast_to(g[k0 + "temperature"], (B,)), rtol=1e-4,

@@ -144,10 +144,13 @@ def test_oracle_other_optimizer_and_energies_match_reference_loop():
     g = gc.load("fit_alt_ref")
     pack = hand_pack.load_pack("allegro")
     B = len(g["pose0"])
-    for run, dt in (("dexanneal", torch.float32), ("tdgmala", torch.float64), ("malareset", torch.float64)):
+    for run, dt in (("dexanneal", torch.float32), ("tdgmala", torch.float64), ("malareset", torch.float64),
+                    ("priorwall", torch.float64)):
         kw = dict(gc.ALT_RUNS[run])
         if run == "tdgmala":
             kw["tdg_directions"] = g["tdg_dirs"]
+        if run == "priorwall":
+            kw["hand_surface"] = (g["hand_surf"], g["hand_surf_link"])
         orc = FitLoopOracle(pack, [g["face_verts"]], [g["surface"]], B, g["pose0"], g["idx0"].astype(np.int64), dtype=dt, **kw)
         np.testing.assert_allclose(orc.energy.numpy(), g[run + "_energy0"], rtol=1e-6)
         T = lambda a: torch.tensor(a, dtype=dt)
