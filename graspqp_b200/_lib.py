@@ -97,6 +97,7 @@ SIGNATURES = {
                                    c_uint64, c_uint64, P, P, P, P]),
     "gqp_anneal_accept": (c_int, [POINTER(GqpMalaParams), c_int, c_int, c_int, c_int, P, P, P, c_uint64, c_uint64, c_int,
                                   P, P, P, P, P, P, P, P, P, P, P, c_int, P]),
+    "gqp_entropy_stats": (c_int, [P, c_int, c_int, P, P, P, P, P]),
     "gqp_mala_reset": (c_int, [c_int, c_int, c_int, P, c_float, P, P, P, P, P, P, P, P, P, P, P]),
     "gqp_init_create": (c_int, [P, P, c_int, POINTER(c_void_p)]),
     "gqp_init_destroy": (None, [c_void_p]),

@@ -386,3 +386,110 @@ extern "C" int gqp_anneal_accept(const GqpMalaParams *p, int Bt, int D, int n_c,
     GQP_CHECK_LAUNCH("gqp_anneal_accept");
     return GQP_OK;
 }
+
+
+// ---- (f4) entropy statistics of a batch (HandModel.joint_entropy / pose_entropy, hand_model.py:698-760; --log_entropy) ----
+// 32-bin histograms (torch.histc: values outside [lo, hi] are dropped, hi falls into the last bin) over the rows of the batch:
+// every joint between its limits, the translation components in [-0.1, 0.1], the rotation as the spherical coordinates
+// (r, theta, phi) of its rotation vector.  A block per histogram, integer counts through shared-memory atomics (exact, any
+// order), entropy -sum p log p by thread 0.  roma.rotmat_to_rotvec (absent here) is restated: unit quaternion with w >= 0,
+// angle = 2 atan2(|v|, w), rotvec = angle * v / |v|.
+#define ENT_BINS 32
+__device__ __forceinline__ V3 ent_rotvec(V3 x, V3 y) {
+    // utils/transforms.py:5-13 (special Gram-Schmidt), columns (x^, y^, z)
+    const float nx = sqrtf(dot3(x, x));
+    const V3 xh = x * (1.0f / nx);
+    V3 yp = y - xh * dot3(xh, y);
+    const V3 yh = yp * (1.0f / sqrtf(dot3(yp, yp)));
+    const V3 zh = cross3(xh, yh);
+    const float m00 = xh.x, m10 = xh.y, m20 = xh.z, m01 = yh.x, m11 = yh.y, m21 = yh.z, m02 = zh.x, m12 = zh.y, m22 = zh.z;
+    float qx, qy, qz, qw;
+    const float tr = m00 + m11 + m22;
+    if (tr > 0.f) {
+        const float s4 = 2.0f * sqrtf(tr + 1.0f);
+        qw = 0.25f * s4; qx = (m21 - m12) / s4; qy = (m02 - m20) / s4; qz = (m10 - m01) / s4;
+    } else if (m00 > m11 && m00 > m22) {
+        const float s4 = 2.0f * sqrtf(1.0f + m00 - m11 - m22);
+        qw = (m21 - m12) / s4; qx = 0.25f * s4; qy = (m01 + m10) / s4; qz = (m02 + m20) / s4;
+    } else if (m11 > m22) {
+        const float s4 = 2.0f * sqrtf(1.0f + m11 - m00 - m22);
+        qw = (m02 - m20) / s4; qx = (m01 + m10) / s4; qy = 0.25f * s4; qz = (m12 + m21) / s4;
+    } else {
+        const float s4 = 2.0f * sqrtf(1.0f + m22 - m00 - m11);
+        qw = (m10 - m01) / s4; qx = (m02 + m20) / s4; qy = (m12 + m21) / s4; qz = 0.25f * s4;
+    }
+    if (qw < 0.f) { qx = -qx; qy = -qy; qz = -qz; qw = -qw; }
+    const float vn = sqrtf(qx * qx + qy * qy + qz * qz);
+    const float angle = 2.0f * atan2f(vn, qw);
+    const float half = 0.5f * angle;
+    const float scale = fabsf(angle) <= 1e-3f ? 2.0f + angle * angle / 12.0f + 7.0f * angle * angle * angle * angle / 2880.0f
+                                              : angle / sinf(half);
+    return v3(scale * qx, scale * qy, scale * qz);
+}
+
+__global__ void __launch_bounds__(256)
+entropy_hist_kernel(const float *__restrict__ pose, int Bt, int D, int n_dofs, const float *__restrict__ lower,
+                    const float *__restrict__ upper, float *__restrict__ ent /* (n_dofs + 6) */) {
+    __shared__ int hist[ENT_BINS];
+    const int qn = blockIdx.x;  // [0, n_dofs): joints; then translation x, y, z; then r, theta, phi
+    if (threadIdx.x < ENT_BINS) hist[threadIdx.x] = 0;
+    __syncthreads();
+    float lo, hi;
+    if (qn < n_dofs) { lo = lower[qn]; hi = upper[qn]; }
+    else if (qn < n_dofs + 3) { lo = -0.1f; hi = 0.1f; }
+    else if (qn < n_dofs + 5) { lo = 0.f; hi = 3.14159265358979323846f; }
+    else { lo = -3.14159265358979323846f; hi = 3.14159265358979323846f; }
+    for (int b = threadIdx.x; b < Bt; b += blockDim.x) {
+        const float *pr = pose + (size_t)b * D;
+        float v;
+        if (qn < n_dofs) v = pr[9 + qn];
+        else if (qn < n_dofs + 3) v = pr[qn - n_dofs];
+        else {
+            const V3 rv = ent_rotvec(ld3(pr + 3), ld3(pr + 6));
+            const float r = sqrtf(dot3(rv, rv));
+            if (qn == n_dofs + 3) v = r;
+            else if (qn == n_dofs + 4) v = acosf(rv.z / r);
+            else v = (rv.y > 0.f ? 1.f : (rv.y < 0.f ? -1.f : 0.f)) * acosf(rv.x / sqrtf(rv.x * rv.x + rv.y * rv.y));
+        }
+        if (v >= lo && v <= hi) {  // NaN fails both: dropped, as histc does
+            int bin = (int)((v - lo) * (float)ENT_BINS / (hi - lo));
+            if (bin >= ENT_BINS) bin = ENT_BINS - 1;
+            atomicAdd(&hist[bin], 1);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int total = 0;
+        for (int k = 0; k < ENT_BINS; ++k) total += hist[k];
+        float e = 0.f;
+        for (int k = 0; k < ENT_BINS; ++k)
+            if (hist[k] > 0) {
+                const float pk = (float)hist[k] / (float)total;
+                e -= pk * logf(pk);
+            }
+        ent[qn] = e;
+    }
+}
+
+__global__ void entropy_final_kernel(const float *__restrict__ ent, int n_dofs, float *__restrict__ out3) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    float j = 0.f, t = 0.f, r = 0.f;
+    for (int k = 0; k < n_dofs; ++k) j += ent[k] / (float)n_dofs;
+    for (int k = 0; k < 3; ++k) {
+        t += ent[n_dofs + k] / 3.0f;
+        r += ent[n_dofs + 3 + k] / 3.0f;
+    }
+    out3[0] = j; out3[1] = t; out3[2] = r;
+}
+
+extern "C" int gqp_entropy_stats(const float *pose, int Bt, int n_dofs, const float *joints_lower, const float *joints_upper,
+                                 float *scratch, float *out3, void *stream) {
+    if (Bt <= 0 || n_dofs <= 0 || !pose || !joints_lower || !joints_upper || !scratch || !out3)
+        return gqp_set_error(GQP_ERR_ARG, "gqp_entropy_stats: bad argument");
+    GQP_LAUNCH(entropy_hist_kernel, n_dofs + 6, 256, 0, (cudaStream_t)stream, pose, Bt, 9 + n_dofs, n_dofs, joints_lower,
+               joints_upper, scratch);
+    GQP_CHECK_LAUNCH("gqp_entropy_stats");
+    GQP_LAUNCH(entropy_final_kernel, 1, 32, 0, (cudaStream_t)stream, scratch, n_dofs, out3);
+    GQP_CHECK_LAUNCH("gqp_entropy_stats/final");
+    return GQP_OK;
+}

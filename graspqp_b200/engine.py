@@ -442,6 +442,19 @@ class FitEngine:
             else:
                 self.step()
 
+    def entropy(self):
+        """(f4) HandModel.joint_entropy / pose_entropy of the current batch (hand_model.py:698-760; fit.py:462-471 logs them
+        with --log_entropy) -> dict with joints / translation / rotation entropy and fit.py's `total`; synchronises."""
+        be, p = self.be, self.be.ptr
+        if getattr(self, "_ent", None) is None:
+            self._ent = (be.empty((self.dof + 6,), np.float32), be.empty((3,), np.float32),
+                         be.from_host(self.pack["joints_lower"], np.float32),
+                         be.from_host(self.pack["joints_upper"], np.float32))
+        scratch, out, lo, hi = self._ent
+        self._ck(self.lib.gqp_entropy_stats(p(self.pose), self.Bt, self.dof, p(lo), p(hi), p(scratch), p(out), be.stream))
+        j, t, r = [float(v) for v in be.to_host(out)]
+        return {"joints_entropy": j, "translation_entropy": t, "rotation_entropy": r, "total": 0.5 * j + 0.5 * (t + r)}
+
     def pen_counters(self):
         """(samples queued for the exact search, work items, overflow flag) of the last penetration stage; synchronises"""
         v = self.be.to_host(self.pen_scratch.view(np.int32) if isinstance(self.pen_scratch, np.ndarray)

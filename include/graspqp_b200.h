@@ -337,6 +337,14 @@ int gqp_anneal_accept(const GqpMalaParams *p_host, int Bt, int D, int n_c, int n
                       float *grad, float *energy, float *losses, float *new_energy_out, uint8_t *accept_out,
                       float *temperature_out, int after_reset, void *stream);
 
+/* ---- (f4) entropy statistics of the batch (HandModel.joint_entropy / pose_entropy, hand_model.py:698-760; --log_entropy) ----
+ * 32-bin histograms over ALL Bt rows (torch.histc semantics): every joint between its limits (joints_lower / joints_upper:
+ * DEVICE arrays of n_dofs), translation components in [-0.1, 0.1], rotation as (r, theta, phi) of its rotation vector.
+ * out3 (device): [joints_entropy, translation_entropy, rotation_entropy]; scratch: n_dofs + 6 floats (per-histogram
+ * entropies).  roma.rotmat_to_rotvec is restated (w >= 0 quaternion): PARITY UNPINNED for the rotation part. */
+int gqp_entropy_stats(const float *pose, int Bt, int n_dofs, const float *joints_lower, const float *joints_upper,
+                      float *scratch, float *out3, void *stream);
+
 /* ---- M3: outlier reset (fit.py:408-422: reset_mask = z > threshold; initialize_convex_hull(env_mask); reset_envs) ----
  * Called between gqp_mala_propose and the energy evaluation of a reset iteration.  pose_init (Bt,D) / idx_init (Bt,n_c)
  * hold a fresh initialisation of EVERY row (initialize_convex_hull recomputes all rows, core/initializations.py:15-193:
