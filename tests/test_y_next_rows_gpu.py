@@ -114,3 +114,41 @@ def test_optional_terms_prior_and_wall(gpu):
     import cases
     ep, ew = cases.check_optional_terms(*gpu, B=16, n_pts=256, T=3)
     assert ep > 0 and ew > 0
+
+
+# ---- (f4) batch driver pieces on the device ----
+def test_entropy_statistics(gpu):
+    import numpy as np
+    from graspqp_b200 import _lib, hand_pack, synth
+    from oracle import entropy as oe
+    lib, be = gpu
+    pack = hand_pack.load_pack("shadow_hand")
+    v, _ = synth.make_mesh("sphere", 200, 3)
+    B = 4096
+    pose, _ = synth.random_grasp_init(pack, [v], B, 12, 3)
+    dof = len(pack["joints_lower"])
+    d_pose, lo, hi = be.from_host(pose, np.float32), be.from_host(pack["joints_lower"], np.float32), be.from_host(pack["joints_upper"], np.float32)
+    scratch, out = be.empty((dof + 6,), np.float32), be.empty((3,), np.float32)
+    _lib.check(lib.gqp_entropy_stats(be.ptr(d_pose), B, dof, be.ptr(lo), be.ptr(hi), be.ptr(scratch), be.ptr(out), be.stream), lib)
+    hp = torch.tensor(pose, dtype=torch.float32)
+    je = float(oe.joint_entropy(hp, torch.tensor(pack["joints_lower"]), torch.tensor(pack["joints_upper"])))
+    te, re_ = [float(x) for x in oe.pose_entropy(hp)]
+    got = be.to_host(out)
+    print(f"[entropy] joints {got[0]:.5f} / {je:.5f}  translation {got[1]:.5f} / {te:.5f}  rotation {got[2]:.5f} / {re_:.5f}")
+    assert abs(got[0] - je) < 1e-3 and abs(got[1] - te) < 1e-3 and abs(got[2] - re_) < 1e-3
+
+
+def test_fit_batch_end_to_end(gpu, tmp_path):
+    """(f4) two objects from OBJ files on disk -> device initialisation -> 40 iterations with a reset epoch -> export to the
+    reference's result path -> the driver's scan skips them"""
+    import numpy as np
+    from graspqp_b200 import batch
+    from test_batch import _dataset
+    root, names = str(tmp_path), ["obj_a", "obj_b"]
+    _dataset(root, names)
+    r = batch.fit_batch(root, names, hand="allegro", n_contact=12, batch_size=64, n_iter=40, n_surface=512, reset_epochs=10,
+                        log_entropy=True, device="cuda:0")
+    assert len(r["paths"]) == 2 and np.isfinite(r["mean_energy"]) and r["entropy"]["total"] > 0
+    d = torch.load(r["paths"][0], weights_only=False)
+    assert d["values"].shape == (64,) and d["parameters"]["root_pose"].shape == (64, 7)
+    assert batch.scan_assets(root, "allegro", 12, "graspqp", step=40) == ([], names)
