@@ -35,7 +35,7 @@ class MalaStar:
         self._noise = (u_switch.float().contiguous(), idx_rand.to(torch.int32).contiguous(), u_accept.float().contiguous())
 
     def _st(self):
-        return ctypes.c_void_p(torch.cuda.current_stream(self.step.device).cuda_stream)
+        return ctypes.c_void_p(torch.cuda.current_stream(self._g2.device).cuda_stream)
 
     def try_step(self):
         lib, hm = _lib.lib(), self.hand_model

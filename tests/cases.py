@@ -102,7 +102,7 @@ def check_hand_distance(lib, be, B=64, n_pts=2500, seed=5, hand="allegro"):
     lib.gqp_hand_destroy(hand)
 
 
-def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=False, hand="allegro"):
+def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=False, hand="allegro", max_excused=1):
     pack = hand_pack.load_pack(hand)
     v, f = synth.make_mesh("hull" if hull else "sphere", 400, seed)
     fv = synth.face_vertices(v, f)
@@ -122,8 +122,10 @@ def check_engine_vs_oracle(lib, be, B=8, n_pts=256, n_c=12, T=4, seed=3, hull=Fa
         eng.step(be.from_host(us), be.from_host(ir), be.from_host(ua))
         out = orc.iterate(torch.tensor(us, dtype=torch.float64), torch.tensor(ir).long(), torch.tensor(ua, dtype=torch.float64))
         np.testing.assert_array_equal(H(eng.idx_new), out["idx_prop"].numpy())
-        tol.assert_energy(H(eng.new_energy), out["new_energy"].numpy(), f"{hand} n_c={n_c} step {t} new energy", excuse=ex)
-        tol.assert_grad(H(eng.grad_new), out["new_grad"].numpy(), f"{hand} n_c={n_c} step {t} gradient", excuse=ex)
+        tol.assert_energy(H(eng.new_energy), out["new_energy"].numpy(), f"{hand} n_c={n_c} step {t} new energy", excuse=ex,
+                          max_excused=max_excused)
+        tol.assert_grad(H(eng.grad_new), out["new_grad"].numpy(), f"{hand} n_c={n_c} step {t} gradient", excuse=ex,
+                        max_excused=max_excused)
         np.testing.assert_array_equal(H(eng.accept).astype(bool), out["accept"].numpy())
         np.testing.assert_allclose(H(eng.energy), orc.energy.numpy(), rtol=tol.ENERGY_RTOL)
         np.testing.assert_allclose(H(eng.pose), orc.hand.hand_pose.detach().numpy(), rtol=1e-4, atol=1e-5)
@@ -411,6 +413,16 @@ def check_benched_state(lib, be, name="config2", iters=(0, 50, 500), per_object=
             keep = np.array([r not in excused or term in ("E_pen", "E_spen", "E_joints") for r in range(len(sub))])
             err = np.abs(got - want)
             ok = (err <= 1e-4 * np.abs(want) + 1e-6) | (engine.DEFAULT_WEIGHTS[term] * err <= 1e-4 * e_tot)
+            if term in ("E_fc", "E_dis"):
+                # these two read the object normal unit(p - c): a row whose two evaluations do not see the same normals (the
+                # evidence functions of tests/tol.py) is a conditioning event of the reference's formulation for THIS term
+                # even when its total energy still agrees; each such row needs the evidence, at most len/8 of them
+                cond = [r for r in np.nonzero(keep & ~ok)[0] if ex(r)]
+                for r in cond:
+                    print(f"[benched] {lab} {term}: row {r} {got[r]:.6g} vs {want[r]:.6g} — object normals of the two "
+                          "evaluations differ at one of its contacts (excused)")
+                assert len(cond) <= max(1, len(sub) // 8), f"{lab} {term}: {len(cond)} rows with differing normals"
+                ok[cond] = True
             assert ok[keep].all(), f"{lab} {term}: {got[keep & ~ok]} vs {want[keep & ~ok]}"
         ge_probe = tol.grad_error(H(eng.grad_new)[sub], out["new_grad"].numpy())
         for r in np.nonzero(ge_probe.max(1) > tol.GRAD_TOL)[0]:  # diagnostics before the assertion

@@ -90,7 +90,9 @@ def test_golden_fk_more_hands(gpu):
 @pytest.mark.parametrize("hand,n_c", [("robotiq3", 12), ("ability_hand", 8)])
 def test_engine_vs_oracle_more_hands(gpu, hand, n_c):
     import cases
-    cases.check_engine_vs_oracle(*gpu, B=8, n_pts=256, n_c=n_c, T=3, seed=5, hand=hand)
+    # the Robotiq 3F's flat finger pads put several contacts of a candidate within 1e-4 m of the 400-face sphere after two
+    # steps: up to 3 of the 8 rows then carry the nearest-face-tie evidence of tests/tol.py (seen on the B200: 1.1e-4..2.0e-4)
+    cases.check_engine_vs_oracle(*gpu, B=8, n_pts=256, n_c=n_c, T=3, seed=5, hand=hand, max_excused=3)
 
 
 @pytest.mark.parametrize("hand", ["robotiq3", "ability_hand"])
