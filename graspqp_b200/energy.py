@@ -22,7 +22,12 @@ def calculate_energy(hand_model, object_model, energy_fnc=None, energy_names=(),
     d = hand_model.cal_distance(object_model.surface_points_tensor * object_model.object_scale)
     losses["E_pen"] = torch.relu(d).sum(-1)  # energy.py:60-61
     losses["E_spen"] = hand_model.self_penetration()
-    for name in ("E_prior", "E_wall", "E_manipulativity"):
-        if name in energy_names:
-            raise NotImplementedError(f"{name} is off in scripts/fit.py's defaults and outside the accelerated path")
+    if "E_prior" in energy_names:  # energy.py:68-74: the grasp axis should point down
+        forward_axis = (hand_model.global_rotation @ hand_model.grasp_axis.view(1, -1, 1)).view(-1, 3)
+        axis_prior = torch.tensor([0, 0, -1], dtype=torch.float, device=forward_axis.device).view(1, 3)
+        losses["E_prior"] = 1 - torch.sum(forward_axis * axis_prior, dim=-1)
+    if "E_wall" in energy_names:   # energy.py:75-77: nothing below the table plane z = 0
+        losses["E_wall"] = hand_model.get_surface_points()[..., -1].clamp(max=0.0).abs().sum(-1)
+    if "E_manipulativity" in energy_names:
+        raise NotImplementedError("E_manipulativity: scripts/fit.py's weight_dict has no entry for it (the term raises there)")
     return losses

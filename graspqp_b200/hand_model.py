@@ -38,6 +38,11 @@ class HandModel:
         self._actuated_joints_names = [str(s) for s in self.pack["joint_names"]]
         self._contact_links = [str(s) for s in self.pack["mesh_names"]]
         self.mesh_names = self._contact_links
+        ax = {"x": (1, 0, 0), "y": (0, 1, 0), "z": (0, 0, 1), "-x": (-1, 0, 0), "-y": (0, -1, 0), "-z": (0, 0, -1)}
+        axes = [str(a) for a in self.pack["axes"]]
+        vec = lambda a: torch.tensor(ax[a], dtype=torch.float32, device=self.device)
+        self.forward_axis, self.up_axis, self.grasp_axis = vec(axes[0]), vec(axes[1]), vec(axes[2])  # hand_model.py:459-470
+        self._surf = None  # hand surface samples for get_surface_points (E_wall), built on first use
         self.hand_pose = None
         self.contact_point_indices = None
         self.contact_points = self.contact_normals = None
@@ -72,12 +77,12 @@ class HandModel:
             raise ValueError("nan in hand_pose")
         self.global_translation = self.hand_pose[:, 0:3]
         self.current_status = ops.FkFn.apply(self.hand_pose, self)
-        with torch.no_grad():  # attribute only; the kernels carry R_g inside current_status
-            x, y = self.hand_pose[:, 3:6], self.hand_pose[:, 6:9]
-            x = x / x.norm(dim=-1, keepdim=True)
-            y = y - (x * y).sum(-1, keepdim=True) * x
-            y = y / y.norm(dim=-1, keepdim=True)
-            self.global_rotation = torch.stack((x, y, torch.cross(x, y, dim=-1)), dim=-1)
+        # an attribute for callers (E_prior reads it, energy.py:68-74); the kernels carry R_g inside current_status
+        x, y = self.hand_pose[:, 3:6], self.hand_pose[:, 6:9]
+        x = x / x.norm(dim=-1, keepdim=True)
+        y = y - (x * y).sum(-1, keepdim=True) * x
+        y = y / y.norm(dim=-1, keepdim=True)
+        self.global_rotation = torch.stack((x, y, torch.cross(x, y, dim=-1)), dim=-1)
         gather_idx = self.contact_point_indices
         if contact_point_indices is not None:
             # hand_model.py:816-831: with env_mask the MEMBER is merged, but the contact points of this call are gathered
@@ -100,6 +105,16 @@ class HandModel:
     def self_penetration(self):
         """hand_model.py:989-1040."""
         return ops.SelfPenFn.apply(self.current_status, self.hand_pose, self)
+
+    def get_surface_points(self):
+        """hand_model.py:1042-1071: world positions of the hand surface samples (Bt, n, 3); the sample table is
+        hand_pack.surface_points (512 samples, built the reference's way from a different random stream)."""
+        if self._surf is None:
+            pts, link = hand_pack.surface_points(self.pack)
+            self._surf = (torch.as_tensor(pts, device=self.device), torch.as_tensor(link, device=self.device).long())
+        pts, link = self._surf
+        tf = self.current_status.view(self.current_status.shape[0], self.n_links, 3, 4)[:, link]  # (Bt, n, 3, 4)
+        return (tf[..., :3] @ pts.unsqueeze(-1)).squeeze(-1) + tf[..., 3]
 
     def get_contact_candidates(self):
         """hand_model.py:1220-1267: world positions of ALL contact candidates (Bt, C, 3)."""

@@ -154,3 +154,37 @@ def test_fit_batch_end_to_end(gpu, tmp_path):
     d = torch.load(r["paths"][0], weights_only=False)
     assert d["values"].shape == (64,) and d["parameters"]["root_pose"].shape == (64, 7)
     assert batch.scan_assets(root, "allegro", 12, "graspqp", step=40) == ([], names)
+
+
+def test_reference_shaped_energy_with_prior_and_wall():
+    """graspqp_b200.calculate_energy(energy_names=[E_prior, E_wall]) under torch autograd (HandModel.global_rotation,
+    grasp_axis, get_surface_points) vs the fused engine's gqp_prior_wall: energies and d/d hand_pose"""
+    import numpy as np
+
+    import graspqp_b200 as g
+    from graspqp_b200 import _lib, engine, hand_pack
+    from test_api_gpu import _case
+    B, n_c = 8, 12
+    pack, fv, sp, pose, idx = _case(B=B, n_c=n_c)
+    dev = "cuda:0"
+    W = dict(E_dis=100.0, E_fc=1.0, E_pen=100.0, E_spen=10.0, E_joints=1.0, E_prior=5.0, E_wall=50.0)
+    hand = g.HandModel("allegro", dev)
+    obj = g.ObjectModel(batch_size_each=B, num_samples=len(sp), device=dev)
+    obj.initialize(["sphere"], [fv], sp[None])
+    energy_fnc = g.GraspSpanMetricFactory.create(g.GraspSpanMetricFactory.MetricType.GRASPQP,
+                                                 solver_kwargs={"friction": 0.2, "max_limit": 20.0, "n_cone_vecs": 4})
+    hand.set_parameters(torch.tensor(pose, device=dev).requires_grad_(True), torch.tensor(idx, device=dev))
+    losses = g.calculate_energy(hand, obj, energy_fnc=energy_fnc, energy_names=["E_prior", "E_wall"], method="gendexgrasp")
+    assert list(losses)[-2:] == ["E_prior", "E_wall"]
+    energy = sum(W[k] * v for k, v in losses.items())
+    energy.sum().backward()
+    eng = engine.FitEngine(_lib.lib(), engine.TorchBackend(dev), pack, [fv], sp[None], B, pose, idx.astype(np.int32),
+                           weights=dict(E_prior=5.0, E_wall=50.0), hand_surface=hand_pack.surface_points(pack))
+    for k, name in enumerate(eng.terms):
+        np.testing.assert_allclose(losses[name].detach().cpu().numpy(), eng.losses[k].cpu().numpy(), rtol=1e-4, atol=1e-6,
+                                   err_msg=name)
+    assert float(losses["E_wall"].mean()) > 0
+    np.testing.assert_allclose(energy.detach().cpu().numpy(), eng.energy.cpu().numpy(), rtol=1e-5)
+    g0 = eng.first_grad
+    np.testing.assert_allclose(hand.hand_pose.grad.cpu().numpy(), g0, rtol=1e-3, atol=1e-4 * np.abs(g0).max())
+    eng.close()

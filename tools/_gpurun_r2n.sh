@@ -7,5 +7,5 @@ tail -5 gpurun_out/r2n_pytest_new.log
 timeout 200 python -m pytest tests -m gpu -x -q > gpurun_out/r2n_pytest_all.log 2>&1
 echo "all rc=$?" | tee -a gpurun_out/r2n_pytest_all.log
 tail -3 gpurun_out/r2n_pytest_all.log
-timeout 100 python bench.py --steps 20 --warmup 5 --no-counters --no-gpu-baseline --no-api-loop --skip-cpu-baseline --sustain 0 > gpurun_out/r2n_bench_short.json 2> gpurun_out/r2n_bench_short.err
-echo "bench rc=$?"; tail -c 600 gpurun_out/r2n_bench_short.json
+true
+
