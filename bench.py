@@ -39,7 +39,13 @@ STAGE_KERNELS = {
     "fc_solve": ("fc_dis_kernel<1,", "fc_dis_kernel<(int)1,"),  # <MODE = FC_SOLVE, candidates per warp>
     "hand_distance": ("pen_bounds_kernel", "pen_broad_kernel", "pen_collect_kernel", "pen_search_kernel",
                       "pen_reduce_fixed_kernel"),
+    "span_energy": ("span_alt_kernel",),  # --energy-type dexgrasp | tdg: replaces fc_solve + fc_finish
 }
+
+
+def stages_of(energy_type):
+    return [st for st in STAGE_KERNELS if (st == "span_energy") == (energy_type != "graspqp") or
+            st in ("object_distance", "hand_distance")]
 
 
 def collect_counters(args, at_iteration):
@@ -55,7 +61,7 @@ def collect_counters(args, at_iteration):
     out = tempfile.NamedTemporaryFile(suffix=".csv", delete=False).name
     cmd = [ncu, "--metrics", ",".join(COUNTER_METRICS), "--clock-control", "none", "--profile-from-start", "off", "--csv",
            "--log-file", out, sys.executable, os.path.abspath(__file__), "--count-mode", "--workload", args.workload,
-           "--count-at", str(at_iteration)]
+           "--count-at", str(at_iteration), "--energy-type", args.energy_type, "--optimizer", args.optimizer]
     if args.batch:
         cmd += ["--batch", str(args.batch)]
     if args.objects:
@@ -72,12 +78,13 @@ def collect_counters(args, at_iteration):
         return None, "ncu wrote no launch table"
     H = rows[hdr]
     ki, mi, vi = H.index("Kernel Name"), H.index("Metric Name"), H.index("Metric Value")
-    sums = {st: {} for st in STAGE_KERNELS}
+    sums = {st: {} for st in stages_of(args.energy_type)}
     for row in rows[hdr + 1:]:
         if len(row) <= vi:
             continue
         name = row[ki].replace("void ", "")
-        for st, ks in STAGE_KERNELS.items():
+        for st in sums:
+            ks = STAGE_KERNELS[st]
             if any(name.startswith(k) for k in ks):
                 try:
                     sums[st][row[mi]] = sums[st].get(row[mi], 0.0) + float(row[vi].replace(",", ""))
@@ -98,13 +105,14 @@ def run_count_mode(args):
     torch.cuda.set_device(dev)
     lib, be = _lib.lib(), engine.TorchBackend(dev)
     w = workload.build(args.workload, batch_each=args.batch, n_objects=args.objects)
-    eng = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], w["batch_each"], w["pose"], w["idx"], seed=1)
+    eng = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], w["batch_each"], w["pose"], w["idx"], seed=1,
+                           energy_type=args.energy_type, optimizer=args.optimizer)
     for _ in range(args.count_at):
         eng.step()
     torch.cuda.synchronize()
     calls = eng.stage_calls()
     torch.cuda.profiler.start()
-    for st in STAGE_KERNELS:
+    for st in stages_of(args.energy_type):
         _lib.check(calls[st](), lib)
     torch.cuda.synchronize()
     torch.cuda.profiler.stop()
@@ -121,6 +129,10 @@ def parse():
     ap.add_argument("--batch", type=int, default=None, help="override candidates per object")
     ap.add_argument("--objects", type=int, default=None, help="override objects per GPU")
     ap.add_argument("--no-qp-batch-stop", action="store_true")
+    ap.add_argument("--energy-type", default="graspqp", choices=["graspqp", "dexgrasp", "tdg"],
+                    help="scripts/fit.py --energy_type (SURVEY 8(f3)); the headline metric is quoted on graspqp")
+    ap.add_argument("--optimizer", default="mala_star", choices=["mala_star", "dexgraspnet"],
+                    help="scripts/fit.py --optimizer (SURVEY 8(f3))")
     ap.add_argument("--no-graph", action="store_true", help="do not replay the energy evaluation from a CUDA graph")
     ap.add_argument("--no-overlap", action="store_true", help="run the penetration chain on the main stream too")
     ap.add_argument("--global-rms", action="store_true",
@@ -261,7 +273,7 @@ def run_b200(args):
     eng = engine.FitEngine(lib, be, w["pack"], w["face_verts"], w["surface"], B, w["pose"], w["idx"],
                            qp_batch_stop=not args.no_qp_batch_stop, seed=1 + rank,
                            collectives=shard.GlobalStats() if (world > 1 and args.global_rms) else None,
-                           overlap=not args.no_overlap)
+                           overlap=not args.no_overlap, energy_type=args.energy_type, optimizer=args.optimizer)
     graphed = (not args.no_graph) and eng.capture()
     qp_batch_stop, overlap = eng.qp_batch_stop, eng.overlap
     torch.cuda.synchronize()
@@ -479,7 +491,8 @@ def run_b200(args):
         sms = torch.cuda.get_device_properties(dev).multi_processor_count
         sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
         kernels = {}
-        for st in STAGE_KERNELS:
+        stages = stages_of(args.energy_type)
+        for st in stages:
             row = {"ms": round(st_ms[st], 4)}
             if counters:
                 c = counters[st]
@@ -494,10 +507,11 @@ def run_b200(args):
                             "lanes_per_inst": g("smsp__thread_inst_executed.sum") / max(g("smsp__inst_executed.sum"), 1.0),
                             "dram_bytes": g("dram__bytes_read.sum") + g("dram__bytes_write.sum")})
             kernels[st] = row
-        top = max(STAGE_KERNELS, key=lambda st: st_ms[st])
+        top = max(stages, key=lambda st: st_ms[st])
         fp = "fp64" if top == "fc_solve" else "fp32"
         alg_bytes = {"hand_distance": Bt * (L * 48 + 4 + 4 * ((n_pts + 31) // 32)) + O * n_pts * 12,
-                     "object_distance": Bt * n_c * (12 + 36), "fc_solve": Bt * n_c * 24 + Bt * 12 * 3 * 4 * n_c * 8}[top]
+                     "object_distance": Bt * n_c * (12 + 36), "fc_solve": Bt * n_c * 24 + Bt * 12 * 3 * 4 * n_c * 8,
+                     "span_energy": Bt * (n_c * 76 + 8)}[top]
         roof = {"bound": fp, "kernel": f"{top} ({' + '.join(k.split('<')[0] for k in STAGE_KERNELS[top][:5] if '(int)' not in k)}): "
                                        "the longest stage of an iteration at the sustained state",
                 "achieved": kernels[top].get(fp + "_tflops"), "peak": fp32_peak_tflops if fp == "fp32" else fp64_peak_tflops,
@@ -523,7 +537,8 @@ def run_b200(args):
             "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True,
             "scaling": "strong" if (args.shard_global and world > 1) else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
+            "config": {"energy_type": args.energy_type, "optimizer": args.optimizer,
+                       "workload": f"{args.workload}: {w['hand']}, {O} meshes/GPU ({','.join(w['kinds'])}; "
                                    f"{w['faces_per_mesh']} tris), batch {B}/object, n_contact {n_c}, 2500 surface samples",
                        "candidates_per_gpu": Bt, "objects_total": O_total, "candidates_total": Bt_total,
                        "sharding": ("global object list dealt round-robin over the ranks (shard.objects_of_rank)"
