@@ -9,11 +9,15 @@
 // rows depend on the contact points, so d E/d p_i = rho_i / 0.2 * sum_u f_i(u) x s(u) with s(u) = dE/dW_tau(u).
 //
 // Layout: lanes stride the P directions (coalesced reads of the (P,3) table, which stays in L1/L2: 12 KB); the n_c contact
-// frames, lever arms and weights of the candidate sit in shared memory (13 floats per contact).  f_i(u) is evaluated twice
-// per direction (the sum W(u), then the gradient once s(u) is known); the per-contact gradient sums are registers, the
-// kernel is instantiated for n_c <= 4 / 8 / 16 / 32.
-// Bound: FP32 issue — 2 x P x n_c cone evaluations of ~60 flop per candidate (1.4 MFLOP at P = 1000, n_c = 12); HBM bytes per
+// frames, lever arms and weights of the candidate sit in shared memory (13 floats per contact).  The n_c forces f_i(u) of a
+// direction and the per-contact gradient sums are registers: the kernel is instantiated for n_c <= 4 / 8 / 16 / 32 (the last
+// one re-evaluates f_i(u) for the gradient instead).
+// Bound: FP32 issue — P x n_c cone evaluations of ~60 flop per candidate (0.7 MFLOP at P = 1000, n_c = 12); HBM bytes per
 // candidate: the n_c contacts in (150 B each) and their gradients out.
+// Measured on a B200 at config 2 (8192 candidates, n_c = 12, P = 1000; profiles/r2p, r2q, r2r): cone forces evaluated twice
+// 1.045 ms (25 % of the FP32 FMA probe, 58 % of lane-issue slots); kept in registers between the sum and the gradient
+// (150 registers, 12 warps per SM) 0.785 ms; + the direction normalised with one rsqrt instead of sqrt and a division
+// 0.678 ms; capping at 128 registers for 16 warps per SM spills and gains nothing (0.688 ms).
 #include "gqp_common.cuh"
 #include "graspqp_b200.h"
 
@@ -30,12 +34,15 @@ __device__ __forceinline__ V3 span_unit(V3 v) {  // tdg.py:37-39: v / clamp(|v|,
     const float n = sqrtf(dot3(v, v));
     return v * (1.0f / fmaxf(n, 1e-12f));
 }
+// the same through the hardware reciprocal square root (2 ulp): one MUFU instead of a square root and a division
+__device__ __forceinline__ V3 span_unit_fast(V3 v) { return v * rsqrtf(fmaxf(dot3(v, v), 1e-24f)); }
 
 // the point of the normalised cone {(1, y, z): |(y,z)| <= mu} (and its scaled copies for directions behind the contact)
 // that the reference picks for the direction u: tdg.py:173-195, then rotated to the world frame
 __device__ __forceinline__ V3 span_cone_force(const SpanContact &c, V3 u, float mu, float cos_ba) {
-    V3 d = span_unit(v3(c.a0[0] * u.x + c.a0[1] * u.y + c.a0[2] * u.z, c.a1[0] * u.x + c.a1[1] * u.y + c.a1[2] * u.z,
-                        c.a2[0] * u.x + c.a2[1] * u.y + c.a2[2] * u.z));
+    const V3 raw = v3(c.a0[0] * u.x + c.a0[1] * u.y + c.a0[2] * u.z, c.a1[0] * u.x + c.a1[1] * u.y + c.a1[2] * u.z,
+                      c.a2[0] * u.x + c.a2[1] * u.y + c.a2[2] * u.z);
+    const V3 d = span_unit_fast(raw);
     const float proj = d.x;
     const float pn = sqrtf(d.y * d.y + d.z * d.z);
     float cy, cz, cx = 1.0f;
@@ -78,7 +85,9 @@ __device__ __forceinline__ float span_e_dis(const GqpSpanParams &P, bool has, bo
 }
 
 // NC: compile-time bound of n_c (4, 8, 16, 32) — the per-contact gradient sums of a lane's directions are NC x 3 registers
-template <int NC>
+// KEEP: the n_c world-frame cone forces of a direction stay in registers between the sum W(u) and the gradient (NC x 3 more
+// registers per lane) instead of being evaluated a second time
+template <int NC, bool KEEP>
 __global__ void __launch_bounds__(SPAN_WARPS * 32)
 span_alt_kernel(GqpSpanParams P, const float *__restrict__ cpts, const float *__restrict__ cnrm_hand,
                 const float *__restrict__ obj_dist, const float *__restrict__ obj_nrm,
@@ -145,24 +154,40 @@ span_alt_kernel(GqpSpanParams P, const float *__restrict__ cpts, const float *__
         for (int u = lane; u < n_dirs; u += 32) {
             const V3 d = ld3(dirs + (size_t)u * 3);
             V3 Wf = v3(0.f, 0.f, 0.f), Wt = v3(0.f, 0.f, 0.f);
-            for (int i = 0; i < n_c; ++i) {
-                const SpanContact &c = sc[w][i];
-                const V3 f = span_cone_force(c, d, P.friction, cos_ba) * c.rho;
-                Wf = Wf + f;
-                Wt = Wt + cross3(v3(c.r[0], c.r[1], c.r[2]), f);
+            V3 fk[KEEP ? NC : 1];
+            if (KEEP) {
+#pragma unroll
+                for (int i = 0; i < NC; ++i)
+                    if (i < n_c) {
+                        const SpanContact &c = sc[w][i];
+                        const V3 f = span_cone_force(c, d, P.friction, cos_ba) * c.rho;
+                        fk[KEEP ? i : 0] = f;
+                        Wf = Wf + f;
+                        Wt = Wt + cross3(v3(c.r[0], c.r[1], c.r[2]), f);
+                    }
+            } else {
+                for (int i = 0; i < n_c; ++i) {
+                    const SpanContact &c = sc[w][i];
+                    const V3 f = span_cone_force(c, d, P.friction, cos_ba) * c.rho;
+                    Wf = Wf + f;
+                    Wt = Wt + cross3(v3(c.r[0], c.r[1], c.r[2]), f);
+                }
             }
             const float w2 = dot3(Wf, Wf) + dot3(Wt, Wt);
             const float wn = sqrtf(w2);
             esum += 1.0f - dot3(Wf, d) / fmaxf(wn, 1e-12f);
-            // d E/d r_i += rho_i f_i(u) x s(u),  s(u) = (W_f.u) W_tau / |W|^3 (x scale/P below); f_i is re-evaluated
-            // rather than kept: n_c x 3 more registers per lane for the NC = 16 / 32 instances
+            // d E/d r_i += rho_i f_i(u) x s(u),  s(u) = (W_f.u) W_tau / |W|^3 (x scale/P below)
             if (grad_cpts && wn > 1e-12f) {
                 const V3 s = Wt * (dot3(Wf, d) / (w2 * wn));
 #pragma unroll
                 for (int i = 0; i < NC; ++i)
                     if (i < n_c) {
-                        const SpanContact &c = sc[w][i];
-                        g[i] = g[i] + cross3(span_cone_force(c, d, P.friction, cos_ba) * c.rho, s);
+                        if (KEEP) {
+                            g[i] = g[i] + cross3(fk[KEEP ? i : 0], s);
+                        } else {
+                            const SpanContact &c = sc[w][i];
+                            g[i] = g[i] + cross3(span_cone_force(c, d, P.friction, cos_ba) * c.rho, s);
+                        }
                     }
             }
         }
@@ -204,13 +229,14 @@ extern "C" int gqp_span_energy(const GqpSpanParams *p, const float *cpts, const 
     if (!cpts || !cnrm_hand || !obj_dist || !obj_nrm || !cog)
         return gqp_set_error(GQP_ERR_ARG, "gqp_span_energy: null pointer");
     const int grid = (int)((Bt + SPAN_WARPS - 1) / SPAN_WARPS);
-#define SPAN_GO(NC)                                                                                                   \
-    GQP_LAUNCH(span_alt_kernel<NC>, grid, SPAN_WARPS * 32, 0, (cudaStream_t)stream, *p, cpts, cnrm_hand, obj_dist,    \
-               obj_nrm, obj_dgrad, cog, dirs, n_dirs, (int)Bt, batch_each, n_c, e_fc, e_dis, grad_cpts, grad_cnrm)
-    if (n_c <= 4) SPAN_GO(4);
-    else if (n_c <= 8) SPAN_GO(8);
-    else if (n_c <= 16) SPAN_GO(16);
-    else SPAN_GO(32);
+#define SPAN_GO(NC, KEEP)                                                                                             \
+    GQP_LAUNCH((span_alt_kernel<NC, KEEP>), grid, SPAN_WARPS * 32, 0, (cudaStream_t)stream, *p, cpts, cnrm_hand,      \
+               obj_dist, obj_nrm, obj_dgrad, cog, dirs, n_dirs, (int)Bt, batch_each, n_c, e_fc, e_dis, grad_cpts,     \
+               grad_cnrm)
+    if (n_c <= 4) SPAN_GO(4, true);
+    else if (n_c <= 8) SPAN_GO(8, true);
+    else if (n_c <= 16) SPAN_GO(16, true);
+    else SPAN_GO(32, false);  // 96 + 96 registers of forces and sums would spill: the cone forces are re-evaluated
 #undef SPAN_GO
     GQP_CHECK_LAUNCH("gqp_span_energy");
     return GQP_OK;
