@@ -30,7 +30,7 @@ def test_quaternion_matches_scipy():
     np.testing.assert_allclose(q, want, atol=1e-12)
 
 
-@pytest.mark.parametrize("hand", ["allegro", "panda"])
+@pytest.mark.parametrize("hand", ["allegro", "panda", "ability_hand"])
 def test_contact_jacobian_and_joint_velocities(emu, hand):
     check_jacobian_and_velocities(emu, None, hand)
 
@@ -79,6 +79,38 @@ def test_jacobian_linear_part_is_pk_jacobian():
         return torch.stack([res[f"l{i}"].get_matrix()[:, :3, 3].expand(2, 3) for i in range(len(frames))], 1)
     Jt = torch.autograd.functional.jacobian(lambda t: pos(t).sum(0), th).permute(2, 0, 1, 3)
     np.testing.assert_allclose(J[:, :, :3, :].numpy(), Jt.numpy(), atol=1e-6)
+
+
+def test_ability_hand_coupled_jacobian_is_the_references():
+    """hands/ability_hand.py:36-42 (calculate_jacobian: active columns + 1.05851325 x the mimic joints' columns of pk's
+    Jacobian) == d(link position)/d(the 6 parameters) through the pack's frame_gain — what the FK backward kernels compute."""
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("reference only in the build container")
+    import importlib.util
+    import types
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import ref_harness as rh
+    rh.load()
+    core = sys.modules["graspqp.core"]
+    had = hasattr(core, "HandModel")
+    if not had:
+        core.HandModel = type("HandModel", (), {})  # the module only names it in an annotation; the class needs trimesh
+    spec = importlib.util.spec_from_file_location(
+        "ref_ability_hand_j", os.path.join(rh.REF, "graspqp", "src", "graspqp", "hands", "ability_hand.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    if not had:
+        del core.HandModel
+    pack = hand_pack.load_pack("ability_hand")
+    chain, frames = rh.pk_chain_from_pack(pack, torch.float32)  # pk's vectorised Jacobian mixes in float32 constants
+    th = torch.tensor(np.random.default_rng(1).uniform(0.2, 0.9, (2, 6)), dtype=torch.float32)
+    Jref = mod.calculate_jacobian(th, types.SimpleNamespace(chain=chain))  # (2, n_frames, 6, 6 parameters)
+    o = HandOracle(pack, torch.float32)
+
+    def pos(t):
+        return torch.stack([m[:, :3, 3] for m in o.fk(t)], 1)  # (2, n_frames, 3): frame_gain applied inside
+    Jt = torch.autograd.functional.jacobian(lambda t: pos(t).sum(0), th).permute(2, 0, 1, 3)
+    np.testing.assert_allclose(Jref[:, :, :3, :].numpy(), Jt.numpy(), atol=2e-6)
 
 
 def test_export_writes_the_reference_dict(emu, tmp_path):
