@@ -8,8 +8,10 @@ Jacobian IS d(contact point)/d(joint parameter) (checked against pk in tests/tes
 global rotation R_g  pinv_l(J_hand) R_g' v == pinv_l(R_g J_hand) v, so here the WORLD-frame Jacobian comes straight from
 the kernels that already carry the analytic J' of the kinematic chain: row (contact c, axis k) of J is gqp_fk_backward
 applied to a one-hot cotangent on contact c — 3 n_c passes of two launches each, once per export, nothing new on the
-per-iteration path.  Couplings (Panda's mirrored fingers, the Robotiq 2F-140 network) are inside those kernels, which is
-what the reference's per-hand `jacobian_fnc` (hands/panda.py:17-26) does by hand.
+per-iteration path.  Fixed-gain couplings (Panda's mirrored fingers, the ability hand's mimic joints) are inside those kernels,
+which is what the reference's per-hand `jacobian_fnc` (hands/panda.py:17-26, hands/ability_hand.py:36-42) sums by hand; for the
+Robotiq 2F-140 the reference's jacobian_fnc is NOT the derivative through its coupling network (hands/robotiq2.py:17-20) and
+`contact_jacobian` reproduces what it returns instead.
 """
 import ctypes
 import os
@@ -60,21 +62,49 @@ class Exporter:
 
     # ---- world-frame contact Jacobian d(contact point)/d(joint parameter): (Bt, n, 3, dof) ----
     def contact_jacobian(self, idx):
+        """(Bt, n, 3, dof).  Hands whose parameters reach the joints through fixed gains (Panda, ability hand) or directly:
+        the chain-rule derivative, which is what their jacobian_fnc sums by hand (hands/panda.py:17-26,
+        hands/ability_hand.py:36-42).  The Robotiq 2F-140 (coupling network): the reference's jacobian_fnc does not
+        differentiate the network, it returns pk's column of `finger_joint` minus that of `right_outer_knuckle_joint` at the
+        expanded joints (hands/robotiq2.py:17-20) — reproduced as such."""
+        eng = self.eng
+        if "mlp_w1" not in eng.pack:
+            return self._jacobian_rows(eng.hand, eng.pose, eng.dof, idx)
+        from . import hand_pack
+        be = eng.be
+        if getattr(self, "_qhand", None) is None:
+            self._qpack = hand_pack.expanded_pack(eng.pack)
+            self._qhand = hand_pack.create_hand(eng.lib, self._qpack)
+        pose = be.to_host(eng.pose)
+        q = hand_pack.joint_vector(eng.pack, pose[:, 9:])
+        Jq = self._jacobian_rows(self._qhand, be.from_host(np.concatenate([pose[:, :9], q], 1), np.float32), q.shape[1], idx)
+        J = None
+        for col, wgt in hand_pack.reference_jacobian_columns(eng.pack):
+            J = wgt * Jq[..., col:col + 1] if J is None else J + wgt * Jq[..., col:col + 1]
+        return J
+
+    def close(self):
+        if getattr(self, "_qhand", None) is not None:
+            self.eng.lib.gqp_hand_destroy(self._qhand)
+            self._qhand = None
+
+    def _jacobian_rows(self, hand, pose, dof, idx):
+        """row (contact c, axis k) of d(contact point)/d(joint parameter) = the FK backward kernels on a one-hot cotangent"""
         eng, lib, be = self.eng, self.eng.lib, self.eng.be
         p, st = be.ptr, be.stream
         Bt, n = idx.shape
         link_tf = be.empty((Bt, eng.L, 12), np.float32)
-        _lib.check(lib.gqp_fk_forward(eng.hand, p(eng.pose), Bt, p(link_tf), st), lib)
+        _lib.check(lib.gqp_fk_forward(hand, p(pose), Bt, p(link_tf), st), lib)
         g_cp, g_cn = be.empty((Bt, n, 3), np.float32), be.empty((Bt, n, 3), np.float32)
-        g_tf, g_pose = be.empty((Bt, eng.L, 12), np.float32), be.empty((Bt, eng.D), np.float32)
-        J = be.empty((Bt, n, 3, eng.dof), np.float32)
+        g_tf, g_pose = be.empty((Bt, eng.L, 12), np.float32), be.empty((Bt, 9 + dof), np.float32)
+        J = be.empty((Bt, n, 3, dof), np.float32)
         for c in range(n):
             for k in range(3):
                 g_cp[...] = 0
                 g_cp[:, c, k] = 1.0
                 g_tf[...] = 0
-                _lib.check(lib.gqp_contacts_backward(eng.hand, p(idx), p(g_cp), p(g_cn), Bt, n, p(g_tf), st), lib)
-                _lib.check(lib.gqp_fk_backward(eng.hand, p(eng.pose), p(g_tf), None, Bt, p(g_pose), st), lib)
+                _lib.check(lib.gqp_contacts_backward(hand, p(idx), p(g_cp), p(g_cn), Bt, n, p(g_tf), st), lib)
+                _lib.check(lib.gqp_fk_backward(hand, p(pose), p(g_tf), None, Bt, p(g_pose), st), lib)
                 J[:, c, k, :] = g_pose[:, 9:]
         return J
 
@@ -148,4 +178,5 @@ class Exporter:
             path = os.path.join(d, code + f"{suffix}.dexgrasp.pt")
             torch.save(data, path)
             paths.append(path)
+        self.close()
         return paths

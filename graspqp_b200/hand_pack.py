@@ -66,6 +66,39 @@ def create_hand(cdll, pack):
     return h
 
 
+def joint_vector(pack, theta):
+    """utils/fk.py:23-51 for a hand with a coupling network: theta (B,1) -> q (B, 1 + mlp_out) = [c, W2 tanh(w1 c + b1) + b2],
+    c = clamp(theta); host numpy (the kernels evaluate the same inside the FK)."""
+    th = np.asarray(theta, np.float32).reshape(-1, 1)
+    c = np.clip(th, pack["mlp_clamp"][0], pack["mlp_clamp"][1])
+    h = np.tanh(c * np.asarray(pack["mlp_w1"], np.float32).reshape(1, -1) + np.asarray(pack["mlp_b1"], np.float32))
+    return np.concatenate([c, h @ np.asarray(pack["mlp_w2"], np.float32).T + np.asarray(pack["mlp_b2"], np.float32)], 1)
+
+
+def expanded_pack(pack):
+    """The same hand with the EXPANDED joint vector q as its parameters and no coupling network: what the reference's
+    per-hand jacobian_fnc differentiates (hands/robotiq2.py:17-20 takes pk's Jacobian at the expanded joints)."""
+    n_q = 1 + len(pack["mlp_b2"])
+    out = {k: v for k, v in pack.items() if not k.startswith("mlp_")}
+    out["joints_lower"] = np.full(n_q, -1e30, np.float32)
+    out["joints_upper"] = np.full(n_q, 1e30, np.float32)
+    out["default_state"] = np.zeros(n_q, np.float32)
+    names = [""] * n_q
+    for f, d in enumerate(pack["frame_dof"]):
+        if int(pack["frame_jtype"][f]) != 0 and d >= 0:
+            names[int(d)] = str(pack["frame_joint"][f])
+    out["joint_names"] = np.array(names)
+    return out
+
+
+def reference_jacobian_columns(pack):
+    """For a hand with a coupling network the reference does NOT differentiate through the network: its jacobian_fnc
+    (hands/robotiq2.py:17-20) returns column 0 minus column 3 of pk's Jacobian at the expanded joints, columns counted in the
+    chain's joint order.  -> [(column of q, weight), ...]"""
+    movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
+    return [(int(pack["frame_dof"][movable[0]]), 1.0), (int(pack["frame_dof"][movable[3]]), -1.0)]
+
+
 def surface_points(pack, n_surface_points=512, seed=42):
     """The hand surface samples E_wall reads (HandModel.get_surface_points, hand_model.py:1042-1071): per link
     int(area / total_area * n) points, the remainder to the first link, each link's set = farthest point sampling (start

@@ -30,7 +30,7 @@ def test_quaternion_matches_scipy():
     np.testing.assert_allclose(q, want, atol=1e-12)
 
 
-@pytest.mark.parametrize("hand", ["allegro", "panda", "ability_hand"])
+@pytest.mark.parametrize("hand", ["allegro", "panda", "ability_hand", "robotiq2"])
 def test_contact_jacobian_and_joint_velocities(emu, hand):
     check_jacobian_and_velocities(emu, None, hand)
 
@@ -41,15 +41,27 @@ def check_jacobian_and_velocities(lib, be, hand, B=3, n_c=4):
     ex = export.Exporter(eng)
     J = H(ex.contact_jacobian(eng.idx))  # (Bt, n_c, 3, dof), world frame
     # oracle: autograd through the restated HandModel (pk FK incl. the +-0.01 rad perturbation)
-    o = HandOracle(pack, torch.float64)
     hp = torch.tensor(H(eng.pose), dtype=torch.float64)
     idx = torch.tensor(H(eng.idx)).long()
+    if "mlp_w1" in pack:
+        # Robotiq 2F-140: the reference's jacobian_fnc (hands/robotiq2.py:17-20) = column(finger_joint) - column(right outer
+        # knuckle) of the Jacobian w.r.t. the EXPANDED joints, not the derivative through the coupling network
+        o = HandOracle(hand_pack.expanded_pack(pack), torch.float64)
+        th0 = torch.tensor(hand_pack.joint_vector(pack, H(eng.pose)[:, 9:]), dtype=torch.float64)
+    else:
+        o = HandOracle(pack, torch.float64)
+        th0 = hp[:, 9:].clone()
 
     def cpts(theta):
         o.set_parameters(torch.cat([hp[:, :9], theta], 1), idx)
         return o.contact_points
-    Jw = torch.autograd.functional.jacobian(lambda th: cpts(th).sum(0), hp[:, 9:].clone())  # (n_c,3,Bt,dof)
-    Jw = Jw.permute(2, 0, 1, 3).numpy()
+    Jw = torch.autograd.functional.jacobian(lambda th: cpts(th).sum(0), th0)  # (n_c,3,Bt,dof)
+    Jw = Jw.permute(2, 0, 1, 3)
+    if "mlp_w1" in pack:
+        Jw = sum(wgt * Jw[..., col:col + 1] for col, wgt in hand_pack.reference_jacobian_columns(pack))
+        o = HandOracle(pack, torch.float64)
+        o.set_parameters(hp, idx)  # the global rotation below
+    Jw = Jw.numpy()
     np.testing.assert_allclose(J, Jw, atol=2e-6)
     # get_req_joint_velocities restated in the reference's own frame conventions (hand frame + rotated directions)
     Rg = o.global_rotation.detach()
@@ -59,6 +71,7 @@ def check_jacobian_and_velocities(lib, be, hand, B=3, n_c=4):
     want = (export.pinv(Jh.flatten(1, 2)) @ vh.flatten(1, 2).unsqueeze(-1)).squeeze(-1)
     theta, res, ee = ex.get_req_joint_velocities(eng.be.from_host(v.float().numpy(), np.float32), eng.idx, return_ee_vel=True)
     np.testing.assert_allclose(theta.cpu().numpy(), want.numpy(), rtol=2e-3, atol=2e-4 * np.abs(want.numpy()).max())
+    ex.close()
     eng.close()
 
 
@@ -111,6 +124,47 @@ def test_ability_hand_coupled_jacobian_is_the_references():
         return torch.stack([m[:, :3, 3] for m in o.fk(t)], 1)  # (2, n_frames, 3): frame_gain applied inside
     Jt = torch.autograd.functional.jacobian(lambda t: pos(t).sum(0), th).permute(2, 0, 1, 3)
     np.testing.assert_allclose(Jref[:, :, :3, :].numpy(), Jt.numpy(), atol=2e-6)
+
+
+def test_robotiq2_jacobian_is_the_references():
+    """hands/robotiq2.py:17-20 (calculate_jacobian over pk's Jacobian at the joints its own robotiq2f140_fk expands) ==
+    the column combination export.contact_jacobian applies (hand_pack.reference_jacobian_columns) to the Jacobian w.r.t. the
+    expanded joints"""
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("reference only in the build container")
+    import importlib.util
+    import types
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import ref_harness as rh
+    rh.load()
+    core = sys.modules["graspqp.core"]
+    had = hasattr(core, "HandModel")
+    if not had:
+        core.HandModel = type("HandModel", (), {})
+    try:
+        spec = importlib.util.spec_from_file_location(
+            "ref_robotiq2_j", os.path.join(rh.REF, "graspqp", "src", "graspqp", "hands", "robotiq2.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        if not had:
+            del core.HandModel
+    pack = hand_pack.load_pack("robotiq2")
+    chain, frames = rh.pk_chain_from_pack(pack, torch.float32)
+    movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
+    names = [str(pack["frame_joint"][f]) for f in movable]  # HandModel.joints_names: DFS over non-fixed joints
+    th = torch.tensor([[0.1], [0.45], [0.9]], dtype=torch.float32)  # the last one beyond the clamp
+    with torch.no_grad():
+        Jref = mod.calculate_jacobian(th, types.SimpleNamespace(chain=chain, joints_names=names))  # (3, n_frames, 6, 1)
+    qpack = hand_pack.expanded_pack(pack)
+    o = HandOracle(qpack, torch.float32)
+    q = torch.tensor(hand_pack.joint_vector(pack, th.numpy()))
+
+    def pos(t):
+        return torch.stack([m[:, :3, 3] for m in o.fk(t)], 1)
+    Jq = torch.autograd.functional.jacobian(lambda t: pos(t).sum(0), q).permute(2, 0, 1, 3)  # (3, n_frames, 3, 6)
+    J = sum(wgt * Jq[..., col:col + 1] for col, wgt in hand_pack.reference_jacobian_columns(pack))
+    np.testing.assert_allclose(Jref[:, :, :3, :].numpy(), J.numpy(), atol=2e-6)
 
 
 def test_export_writes_the_reference_dict(emu, tmp_path):
