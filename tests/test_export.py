@@ -183,3 +183,50 @@ def test_export_writes_the_reference_dict(emu, tmp_path):
     np.testing.assert_allclose(d["parameters"]["root_pose"][:, 3:].norm(dim=1).numpy(), 1.0, atol=1e-6)
     assert all(torch.isfinite(v).all() for v in d["full_grasp_velocities"].values())
     eng.close()
+
+
+def test_exported_file_is_read_by_the_references_loader(emu, tmp_path):
+    """(f2) round trip: the .dexgrasp.pt written here goes through the reference's own consumer,
+    graspqp_isaaclab/utils/data.py:105-165 (get_saved_poses), with the joint order of its Isaac Lab asset configuration
+    (graspqp_isaaclab/assets/allegro.py:9-26).  The module's Isaac Lab / matplotlib / transforms3d imports are stubbed (none of
+    them is used by that function); the simulator itself is unavailable on this box."""
+    ref = "/root/reference/graspqp_isaaclab/src/graspqp_isaaclab"
+    if not os.path.isdir(ref):
+        pytest.skip("reference only in the build container")
+    import ast
+    import importlib.util
+    import types
+    stubs = {}
+    for name in ("isaaclab", "isaaclab.sim", "isaaclab.assets", "isaaclab.assets.articulation", "isaaclab.utils",
+                 "isaaclab.utils.math", "transforms3d", "transforms3d.euler", "matplotlib"):
+        stubs[name] = sys.modules.get(name)
+        sys.modules[name] = types.ModuleType(name)
+    sys.modules["isaaclab.assets.articulation"].Articulation = object
+    sys.modules["isaaclab.utils.math"].quat_from_matrix = None
+    sys.modules["transforms3d.euler"].euler2mat = None
+    sys.modules["matplotlib"].cm = None
+    try:
+        spec = importlib.util.spec_from_file_location("ref_isaaclab_data", os.path.join(ref, "utils", "data.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        for name, old in stubs.items():
+            if old is None:
+                del sys.modules[name]
+            else:
+                sys.modules[name] = old
+    tree = ast.parse(open(os.path.join(ref, "assets", "allegro.py")).read())
+    names = next(ast.literal_eval(n.value) for n in tree.body if isinstance(n, ast.Assign)
+                 and getattr(n.targets[0], "id", "") == "ALLEGRO_HAND_ACTUATED_JOINT_NAMES")
+    pack, eng, fv = _engine(emu, "allegro", B=4, n_c=4)
+    assert sorted(names) == sorted(str(s) for s in pack["joint_names"])
+    path = export.Exporter(eng).export_poses(str(tmp_path), ["obj_a"], "allegro", suffix="_step_7000")[0]
+    art = types.SimpleNamespace(cfg=types.SimpleNamespace(actuated_joints_expr=names))
+    hand_poses, joint_positions, velocities, energies = mod.get_saved_poses(path, art, num_grasps=3, energy_th=-1e3)
+    order = np.argsort(np.asarray(eng.energy), kind="stable")[:3]  # sorted by energy, best first
+    np.testing.assert_allclose(energies.numpy(), np.asarray(eng.energy)[order], rtol=1e-6)
+    np.testing.assert_allclose(hand_poses[:, :3].numpy(), np.asarray(eng.pose)[order, :3], rtol=1e-6)
+    col = [list(str(s) for s in pack["joint_names"]).index(n) for n in names]  # the asset's joint order
+    np.testing.assert_allclose(joint_positions.numpy(), np.asarray(eng.pose)[order][:, 9:][:, col], rtol=1e-6)
+    assert velocities.shape == (3, 16) and torch.isfinite(velocities).all()
+    eng.close()
