@@ -361,6 +361,54 @@ def gen_fit_alt(name="fit_alt_ref.npz"):
     np.savez_compressed(os.path.join(HERE, name), **out)
 
 
+MODEL_HANDS = ("allegro", "shadow_hand", "panda", "ability_hand", "robotiq3")
+
+
+def models_case(hand, seed=3):
+    """inputs of gen_models / the tests that read models_ref.npz: poses close to a 400-face sphere with the joints pushed towards
+    their upper limits for half of the rows (self-penetration active), object surface samples, hand surface samples"""
+    pack = hand_pack.load_pack(hand)
+    v, f = synth.make_mesh("sphere", 400, seed)
+    B = 4
+    pose, idx = synth.random_grasp_init(pack, [v], B, 4, seed)
+    pose[:, :3] *= 0.6
+    lo, hi = pack["joints_lower"], pack["joints_upper"]
+    pose[B // 2:, 9:] = (lo + 0.92 * (hi - lo))[None]
+    sp = synth.sample_surface(v, f, 96, seed=seed)
+    return pack, synth.face_vertices(v, f), pose.astype(np.float32), idx, sp.astype(np.float32), hand_pack.surface_points(pack, 64)
+
+
+def gen_models():
+    """models_ref.npz: the reference's OWN HandModel.cal_distance / self_penetration / get_surface_points / joint_entropy /
+    pose_entropy and ObjectModel.cal_distance (forward + autograd backward), run on instances made without their constructors
+    and filled from the hand packs (ref_harness.reference_hand / reference_object).  fp32, as the reference runs."""
+    HandModel, ObjectModel = rh.load_models()
+    out = {}
+    for hand in MODEL_HANDS:
+        pack, fv, pose, idx, sp, surf = models_case(hand)
+        B = len(pose)
+        h = rh.reference_hand(pack, pose, surface=surf)
+        x = torch.tensor(sp).unsqueeze(0).repeat(B, 1, 1)
+        d = HandModel.cal_distance(h, x)
+        e = HandModel.self_penetration(h)
+        s = HandModel.get_surface_points(h)
+        (torch.relu(d).sum() + e.sum() + s[..., 2].clamp(max=0).abs().sum()).backward()
+        te, re_ = HandModel.pose_entropy(h)
+        k = hand + "_"
+        out.update({k + "hand_distance": d.detach().numpy(), k + "e_spen": e.detach().numpy(),
+                    k + "surface_points": s.detach().numpy(), k + "grad": h.hand_pose.grad.numpy().copy(),
+                    k + "entropy": np.array([float(HandModel.joint_entropy(h)), float(te), float(re_)], np.float32)})
+        # ObjectModel.cal_distance at this hand's contact candidates' world positions (any points would do)
+        o = rh.reference_object([fv], B)
+        pts = s[:, :12].detach().clone().requires_grad_(True)
+        dist, nrm = ObjectModel.cal_distance(o, pts)
+        dist.abs().sum().backward()
+        out.update({k + "obj_points": pts.detach().numpy(), k + "obj_distance": dist.detach().numpy(),
+                    k + "obj_normals": nrm.detach().numpy(), k + "obj_grad": pts.grad.numpy().copy()})
+        print("models_ref", hand, "max depth", float(d.max()), "E_spen", e.detach().numpy().round(4))
+    np.savez_compressed(os.path.join(HERE, "models_ref.npz"), **out)
+
+
 def gen_metric_alt():
     """metric_alt_ref.npz: the reference's DexgraspSpanMetric (metrics/ops/dexgrasp.py) and TDGSpanMetric (metrics/ops/tdg.py)
     forward + autograd backward in fp32 (TDGEnergy holds fp32 constants), with the 1000 target directions TDGEnergy drew."""
@@ -399,4 +447,4 @@ if __name__ == "__main__":
     assert rh.available(), "reference not present"
     import subprocess
     subprocess.check_call(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")], stdout=subprocess.DEVNULL)
-    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset(); gen_metric_alt(); gen_fit_alt(); gen_fk_more()
+    gen_sdf(); gen_fk(); gen_solver_kat(); gen_metric(); gen_fit(); gen_fit(torch.float64, "fit_ref_f64.npz"); gen_fit_reset(); gen_metric_alt(); gen_fit_alt(); gen_fk_more(); gen_models()

@@ -26,6 +26,8 @@ import os
 import sys
 import types
 
+import numpy as np
+
 import torch
 
 REF = os.environ.get("GRASPQP_REFERENCE", "/root/reference")
@@ -210,3 +212,85 @@ def pk_chain_from_pack(pack, dtype=torch.float32):
     roots = [f for f in range(n) if int(pack["frame_parent"][f]) < 0]
     assert len(roots) == 1
     return ref["pk_chain"].Chain(frames[roots[0]], dtype=dtype), frames
+
+
+# ---- the reference's OWN HandModel / ObjectModel methods on instances filled from a hand pack --------------------------
+def load_models():
+    """-> (HandModel, ObjectModel) classes of the reference.  Their modules import trimesh, pytorch3d and torchsdf at module
+    level (absent here); those are only needed by the CONSTRUCTORS (URDF / mesh parsing, surface sampling), so they are
+    stubbed and the constructors are never run: instances are made with __new__ and filled from the hand pack
+    (`reference_hand` / `reference_object` below), then the reference's own methods run on them — cal_distance,
+    self_penetration, get_surface_points, joint_entropy, pose_entropy, ObjectModel.cal_distance.  torchsdf.compute_sdf is
+    oracle.hand.compute_sdf: the port of the TorchSDF kernel that tests/test_golden.py pins bit-exactly against the
+    reference kernel body itself."""
+    import importlib
+    load()
+    from oracle import hand as ohand
+    for name in ("pytorch3d", "pytorch3d.ops", "pytorch3d.structures", "trimesh"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["pytorch3d"].ops = sys.modules["pytorch3d.ops"]
+    sys.modules["pytorch3d"].structures = sys.modules["pytorch3d.structures"]
+    sdf = sys.modules.setdefault("torchsdf", types.ModuleType("torchsdf"))
+    if not hasattr(sdf, "compute_sdf"):
+        sdf.compute_sdf = ohand.compute_sdf
+        sdf.index_vertices_by_faces = lambda v, f: v[f.long()]
+    roma = sys.modules["roma"]
+    if not hasattr(roma, "rotmat_to_rotvec"):  # pose_entropy only; restated (PARITY UNPINNED for that one call)
+        from oracle import entropy as oent
+        roma.rotmat_to_rotvec = oent.rotmat_to_rotvec
+    os.environ.setdefault("SDF_BACKEND", "TORCHSDF")
+    hm = importlib.import_module("graspqp.core.hand_model")
+    om = importlib.import_module("graspqp.core.object_model")
+    return hm.HandModel, om.ObjectModel
+
+
+def reference_hand(pack, hand_pose, contact_idx=None, surface=None, dtype=torch.float32):
+    """A reference HandModel instance (no constructor) in the state HandModel.set_parameters leaves it in
+    (hand_model.py:833-873): hand_pose, global_translation / rotation, current_status = the reference chain's FK."""
+    import collections
+    HandModel, _ = load_models()
+    ref = load()
+    chain, frames = pk_chain_from_pack(pack, dtype)
+    h = HandModel.__new__(HandModel)
+    h.device = torch.device("cpu")
+    t = lambda a: torch.as_tensor(np.asarray(a), dtype=dtype)
+    names = [str(s) for s in pack["mesh_names"]]
+    off = np.asarray(pack["face_offset"])
+    fv = np.asarray(pack["face_verts"], np.float32).reshape(-1, 3, 3)
+    h.mesh = collections.OrderedDict()
+    for li, name in enumerate(names):
+        m = {"face_verts": t(fv[off[li]:off[li + 1]]), "vertices": t(fv[off[li]:off[li + 1]].reshape(-1, 3)),
+             "penetration_keypoints": t(pack["spheres"][pack["sphere_link"] == li][:, :3].reshape(-1, 3)),
+             "contact_candidates": t(pack["cand"][pack["cand_link"] == li].reshape(-1, 3)),
+             "normal_candidates": t(pack["cand_normal"][pack["cand_link"] == li].reshape(-1, 3))}
+        if surface is not None:
+            m["surface_points"] = t(surface[0][surface[1] == li].reshape(-1, 3))
+        h.mesh[name] = m
+    h.sphere_scales = t(pack["spheres"][np.argsort(pack["sphere_link"], kind="stable")][:, 3])
+    h.penetration_keypoints_expanded = torch.zeros(1, len(pack["spheres"]), 3)   # read for its shape only (:1000-1007)
+    h.global_index_to_link_index_penetration_expanded = None                     # read, never used
+    h.joints_lower, h.joints_upper = t(pack["joints_lower"]), t(pack["joints_upper"])
+    h.hand_pose = torch.as_tensor(hand_pose, dtype=dtype).clone().requires_grad_(True)
+    h.global_translation = h.hand_pose[:, 0:3]
+    h.global_rotation = ref["transforms"].robust_compute_rotation_matrix_from_ortho6d(h.hand_pose[:, 3:9])
+    th = h.hand_pose[:, 9:]
+    movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
+    gain = pack["frame_gain"] if "frame_gain" in pack else np.ones(len(pack["frame_parent"]), np.float32)
+    assert "mlp_w1" not in pack, "use the hand's own joint_calc_fnc for the coupling network"
+    res = chain.forward_kinematics({f"j{f}": th[:, int(pack["frame_dof"][f])] * float(gain[f]) for f in movable
+                                    if int(pack["frame_dof"][f]) >= 0})
+    h.current_status = {name: res[f"l{int(f)}"] for name, f in zip(names, pack["mesh_frame"])}
+    return h
+
+
+def reference_object(face_verts_list, batch_size_each, dtype=torch.float32):
+    """A reference ObjectModel instance (no constructor) with what cal_distance reads (object_model.py:186-255)"""
+    _, ObjectModel = load_models()
+    o = ObjectModel.__new__(ObjectModel)
+    o.device = torch.device("cpu")
+    o.batch_size_each = batch_size_each
+    o.sdf_library = "TORCHSDF"
+    o.object_mesh_list = [None] * len(face_verts_list)
+    o.object_face_verts_list = [torch.as_tensor(np.asarray(f, np.float32).reshape(-1, 3, 3)) for f in face_verts_list]
+    o.object_scale_tensor = torch.ones(len(face_verts_list), batch_size_each, dtype=dtype)
+    return o

@@ -306,3 +306,74 @@ def check_fit_alt(lib, be, runs=("dexanneal", "tdgmala", "malareset", "priorwall
             prev_reset = kind == "reset_mask"
         eng.close()
     return n_after
+
+
+MODEL_HANDS = ("allegro", "shadow_hand", "panda", "ability_hand", "robotiq3")
+
+
+def models_case(hand, seed=3):
+    """the inputs make_golden.gen_models used (same construction; the fixture stores only the reference's outputs)"""
+    from graspqp_b200 import synth
+    pack = hand_pack.load_pack(hand)
+    v, f = synth.make_mesh("sphere", 400, seed)
+    B = 4
+    pose, idx = synth.random_grasp_init(pack, [v], B, 4, seed)
+    pose[:, :3] *= 0.6
+    lo, hi = pack["joints_lower"], pack["joints_upper"]
+    pose[B // 2:, 9:] = (lo + 0.92 * (hi - lo))[None]
+    sp = synth.sample_surface(v, f, 96, seed=seed)
+    return pack, synth.face_vertices(v, f), pose.astype(np.float32), idx, sp.astype(np.float32), hand_pack.surface_points(pack, 64)
+
+
+def check_models(lib, be, hands=MODEL_HANDS):
+    """H4 / H5 / O1 kernels against the reference's OWN HandModel.cal_distance, self_penetration and ObjectModel.cal_distance
+    (tests/golden/models_ref.npz, make_golden.gen_models: the reference methods run on instances filled from the hand packs).
+    Distances: the kernels answer max over links of the same per-link TorchSDF arithmetic -> 1e-6 absolute (the link transforms
+    come from the fp32 FK kernel, a few ulps from pytorch_kinematics'); E_spen 1e-5; object distance / normals of the given
+    points to 1 ulp (same points in, K1 arithmetic bit-exact, one square root on top)."""
+    g = load("models_ref")
+    p = be.ptr
+    for hand in hands:
+        pack, fv, pose, idx, sp, surf = models_case(hand)
+        k = hand + "_"
+        B, n_pts = len(pose), len(sp)
+        h = hand_pack.create_hand(lib, pack)
+        L = len(pack["mesh_frame"])
+        d_pose, tf = be.from_host(pose, np.float32), be.empty((B, L, 12), np.float32)
+        _lib.check(lib.gqp_fk_forward(h, p(d_pose), B, p(tf), be.stream), lib)
+        # H4, dist-returning path: per-sample signed depth (the surface samples are per OBJECT: n_obj = 1, batch_each = B)
+        x = be.from_host(sp[None], np.float32)
+        dist, arg = be.empty((B, n_pts), np.float32), be.empty((B, n_pts), np.int32)
+        dg = be.empty((B, n_pts, 3), np.float32)
+        sc = be.empty((int(lib.gqp_hand_distance_scratch_floats(1, B, n_pts, 0)),), np.float32)
+        _lib.check(lib.gqp_hand_distance_full(h, p(tf), p(x), 1, B, n_pts, 0, p(dist), p(arg), p(dg), p(sc), be.stream), lib)
+        want = g[k + "hand_distance"]
+        err = np.abs(be.to_host(dist) - want).max()
+        print(f"[models] {hand}: HandModel.cal_distance max |error| {err:.2e} m (max depth {want.max():.4f})")
+        assert err < 1e-6
+        # H5
+        e_spen, e_j = be.empty((B,), np.float32), be.empty((B,), np.float32)
+        _lib.check(lib.gqp_self_pen_joints(h, p(tf), p(d_pose), B, p(e_spen), p(e_j), 1.0, 1.0, None, None, be.stream), lib)
+        np.testing.assert_allclose(be.to_host(e_spen), g[k + "e_spen"], rtol=1e-4, atol=1e-6, err_msg=hand)
+        # O1 at the stored points
+        pts = g[k + "obj_points"]
+        m = ctypes.c_void_p()
+        fv9 = np.ascontiguousarray(fv, np.float32).reshape(-1, 9)
+        _lib.check(lib.gqp_mesh_create(fv9.ctypes.data, len(fv9), ctypes.byref(m)), lib)
+        arr = (ctypes.c_void_p * 1)(m.value)
+        objset = ctypes.c_void_p()
+        _lib.check(lib.gqp_objset_create(ctypes.cast(arr, ctypes.c_void_p), 1, ctypes.byref(objset)), lib)
+        n = pts.shape[1]
+        d_pts = be.from_host(pts, np.float32)
+        od, on = be.empty((B, n), np.float32), be.empty((B, n, 3), np.float32)
+        oc, osg = be.empty((B, n, 3), np.float32), be.empty((B, n), np.int32)
+        _lib.check(lib.gqp_object_distance_forward(objset, B, n, p(d_pts), 1.0, p(od), p(on), p(oc), p(osg), be.stream), lib)
+        # d2 is bit-exact (K1); torch's CPU sqrt, which made the fixture, is not always the correctly rounded one: 1 ulp
+        np.testing.assert_allclose(be.to_host(od), g[k + "obj_distance"], rtol=2e-7, atol=0, err_msg=hand)
+        np.testing.assert_allclose(be.to_host(on), g[k + "obj_normals"], rtol=0, atol=2e-7, err_msg=hand)
+        ones, ograd = be.from_host(np.sign(g[k + "obj_distance"]).astype(np.float32), np.float32), be.empty((B, n, 3), np.float32)
+        _lib.check(lib.gqp_object_distance_backward(p(ones), p(d_pts), p(oc), p(osg), B * n, 1.0, p(ograd), be.stream), lib)
+        np.testing.assert_allclose(be.to_host(ograd), g[k + "obj_grad"], rtol=1e-5, atol=1e-6, err_msg=hand)
+        lib.gqp_objset_destroy(objset)
+        lib.gqp_mesh_destroy(m)
+        lib.gqp_hand_destroy(h)

@@ -179,6 +179,45 @@ def test_emulated_kernels_other_optimizer_and_energies(emu):
     assert gc.check_fit_alt(emu, engine.NumpyBackend()) == 3
 
 
+@pytest.mark.parametrize("hand", gc.MODEL_HANDS)
+def test_oracle_models_match_reference_methods(hand):
+    """oracle.hand.HandOracle.cal_distance / self_penetration / get_surface_points, oracle.pipeline.ObjectOracle.cal_distance
+    and oracle.entropy vs the reference's OWN HandModel / ObjectModel methods (models_ref.npz): forward bit-exact in fp32,
+    autograd gradients to 1e-6 of the largest entry"""
+    from oracle import entropy as oe
+    from oracle.pipeline import ObjectOracle
+    g = gc.load("models_ref")
+    pack, fv, pose, idx, sp, surf = gc.models_case(hand)
+    k = hand + "_"
+    B = len(pose)
+    o = HandOracle(pack, torch.float32)
+    o.set_surface_points(*surf)
+    o.set_parameters(torch.tensor(pose).requires_grad_(True), torch.tensor(idx).long())
+    x = torch.tensor(sp).unsqueeze(0).repeat(B, 1, 1)
+    d, e, s = o.cal_distance(x), o.self_penetration(), o.get_surface_points()
+    np.testing.assert_array_equal(d.detach().numpy(), g[k + "hand_distance"])
+    np.testing.assert_allclose(e.detach().numpy(), g[k + "e_spen"], rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(s.detach().numpy(), g[k + "surface_points"], atol=2e-8)
+    (torch.relu(d).sum() + e.sum() + s[..., 2].clamp(max=0).abs().sum()).backward()
+    gw = g[k + "grad"]
+    np.testing.assert_allclose(o.hand_pose.grad.numpy(), gw, rtol=0, atol=1e-6 * np.abs(gw).max())
+    je = float(oe.joint_entropy(o.hand_pose.detach(), o.joints_lower, o.joints_upper))
+    te, re_ = [float(t) for t in oe.pose_entropy(o.hand_pose.detach())]
+    np.testing.assert_allclose([je, te, re_], g[k + "entropy"], rtol=1e-6)
+    obj = ObjectOracle([fv], [sp], B, torch.float32)
+    pts = torch.tensor(g[k + "obj_points"]).requires_grad_(True)
+    dist, nrm = obj.cal_distance(pts)
+    dist.abs().sum().backward()
+    np.testing.assert_array_equal(dist.detach().numpy(), g[k + "obj_distance"])
+    np.testing.assert_array_equal(nrm.detach().numpy(), g[k + "obj_normals"])
+    np.testing.assert_allclose(pts.grad.numpy(), g[k + "obj_grad"], rtol=1e-6, atol=1e-9)
+
+
+def test_emulated_kernels_models(emu):
+    """H4 / H5 / O1 kernels vs the reference's own HandModel.cal_distance / self_penetration / ObjectModel.cal_distance"""
+    gc.check_models(emu, engine.NumpyBackend())
+
+
 def test_emulated_kernels_sdf(emu):
     gc.check_sdf(emu, engine.NumpyBackend())
 
@@ -226,7 +265,8 @@ def test_golden_vectors_are_reproducible(tmp_path, oracle_built):
     mg.gen_fit_reset()
     mg.gen_metric_alt()  # (f3) DexgraspSpanMetric / TDGSpanMetric
     mg.gen_fit_alt()     # (f3) AnnealingDexGraspNet, the other energies in the loop, the after-reset gradient rule
-    for name in ("fit_reset_ref_f64", "metric_alt_ref", "fit_alt_ref"):
+    mg.gen_models()      # the reference's own HandModel / ObjectModel methods on pack-filled instances
+    for name in ("fit_reset_ref_f64", "metric_alt_ref", "fit_alt_ref", "models_ref"):
         new, old = np.load(tmp_path / (name + ".npz")), gc.load(name)
         assert sorted(new.files) == sorted(old)
         for k in new.files:

@@ -189,3 +189,9 @@ def test_reference_shaped_energy_with_prior_and_wall():
     g0 = eng.first_grad
     np.testing.assert_allclose(hand.hand_pose.grad.cpu().numpy(), g0, rtol=1e-3, atol=1e-4 * np.abs(g0).max())
     eng.close()
+
+
+def test_golden_models(gpu):
+    """H4 / H5 / O1 kernels vs the reference's OWN HandModel.cal_distance, self_penetration and ObjectModel.cal_distance run on
+    instances filled from the hand packs (tests/golden/models_ref.npz), five hands"""
+    gc.check_models(*gpu)
