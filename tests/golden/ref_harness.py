@@ -88,17 +88,24 @@ def tdg_metric(ref, dtype, seed=7):
 
 def make_fit_state(pack, face_verts_list, surface_points_list, batch_each, hand_pose0, idx0, dtype=torch.float32,
                    friction=0.2, max_limit=20.0, n_cone_vecs=4, svd_gain=0.1, energy_type="graspqp",
-                   optimizer="mala_star", weights=None, hand_surface=None, **optim):
+                   optimizer="mala_star", weights=None, hand_surface=None, models="oracle", **optim):
     """The state scripts/fit.py holds between iterations, with the REFERENCE MalaStar / calculate_energy / metric."""
     from oracle.hand import HandOracle
     from oracle.pipeline import ObjectOracle, WEIGHTS
     ref = load()
-    hand = HandOracle(pack, dtype)
-    if hand_surface is not None:
-        hand.set_surface_points(*hand_surface)
-    obj = ObjectOracle(face_verts_list, surface_points_list, batch_each, dtype)
-    obj.device = torch.device("cpu")
-    obj.object_scale_tensor = torch.ones(len(face_verts_list), batch_each, dtype=dtype)
+    if models == "reference":
+        # the reference's OWN HandModel / ObjectModel (instances without constructors, filled from the pack): every method
+        # the loop calls — set_parameters, fk, cal_distance, self_penetration, ObjectModel.cal_distance — is the reference's
+        assert hand_surface is None
+        hand = reference_hand_model(pack, dtype)
+        obj = reference_object_model(face_verts_list, surface_points_list, batch_each, dtype)
+    else:
+        hand = HandOracle(pack, dtype)
+        if hand_surface is not None:
+            hand.set_surface_points(*hand_surface)
+        obj = ObjectOracle(face_verts_list, surface_points_list, batch_each, dtype)
+        obj.device = torch.device("cpu")
+        obj.object_scale_tensor = torch.ones(len(face_verts_list), batch_each, dtype=dtype)
     hand.set_parameters(torch.as_tensor(hand_pose0, dtype=dtype).clone().requires_grad_(True),
                         torch.as_tensor(idx0).long())
     cfg = dict(switch_possibility=0.4, starting_temperature=18.0, temperature_decay=0.95, annealing_period=30,
@@ -202,7 +209,7 @@ def pk_chain_from_pack(pack, dtype=torch.float32):
     frames = []
     for f in range(n):
         j = frame.Joint(name=f"j{f}", offset=t3d(pack["frame_joff"][f]), joint_type=jt[int(pack["frame_jtype"][f])],
-                        axis=[float(v) for v in pack["frame_axis"][f]])
+                        axis=[float(v) for v in pack["frame_axis"][f]], dtype=dtype)
         l = frame.Link(name=f"l{f}", offset=t3d(pack["frame_loff"][f]))
         frames.append(frame.Frame(name=f"f{f}", link=l, joint=j, children=[]))
     for f in range(n):
@@ -293,4 +300,70 @@ def reference_object(face_verts_list, batch_size_each, dtype=torch.float32):
     o.object_mesh_list = [None] * len(face_verts_list)
     o.object_face_verts_list = [torch.as_tensor(np.asarray(f, np.float32).reshape(-1, 3, 3)) for f in face_verts_list]
     o.object_scale_tensor = torch.ones(len(face_verts_list), batch_size_each, dtype=dtype)
+    return o
+
+
+def _hand_module(name):
+    """graspqp/src/graspqp/hands/<name>.py loaded from its file (for its calculate_joints / calculate_jacobian); its
+    `from graspqp.core import HandModel` is satisfied by the class load_models() imported"""
+    import importlib.util
+    HandModel, _ = load_models()
+    core = sys.modules["graspqp.core"]
+    had = hasattr(core, "HandModel")
+    if not had:
+        core.HandModel = HandModel
+    try:
+        spec = importlib.util.spec_from_file_location("ref_hand_" + name, os.path.join(REF, "graspqp", "src", "graspqp", "hands", name + ".py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        if not had:
+            del core.HandModel
+    return mod
+
+
+def reference_hand_model(pack, dtype=torch.float32):
+    """A reference HandModel instance made without its constructor, with everything HandModel.set_parameters, fk,
+    _set_contact_idxs, get_contact_candidates, cal_distance, self_penetration and get_surface_points read
+    (hand_model.py:762-1071), filled from the hand pack.  Links are keyed l<frame> (the names of pk_chain_from_pack's chain).
+    The per-hand joint_calc_fnc is the reference's own (hands/panda.py, ability_hand.py, robotiq2.py)."""
+    import collections
+    HandModel, _ = load_models()
+    chain, frames = pk_chain_from_pack(pack, dtype)
+    h = HandModel.__new__(HandModel)
+    h.device = torch.device("cpu")
+    t = lambda a: torch.as_tensor(np.asarray(a), dtype=dtype)
+    off = np.asarray(pack["face_offset"])
+    fv = np.asarray(pack["face_verts"], np.float32).reshape(-1, 3, 3)
+    h.mesh = collections.OrderedDict()
+    for li, f in enumerate(pack["mesh_frame"]):
+        h.mesh[f"l{int(f)}"] = {
+            "face_verts": t(fv[off[li]:off[li + 1]]), "vertices": t(fv[off[li]:off[li + 1]].reshape(-1, 3)),
+            "penetration_keypoints": t(pack["spheres"][pack["sphere_link"] == li][:, :3].reshape(-1, 3)),
+            "contact_candidates": t(pack["cand"][pack["cand_link"] == li].reshape(-1, 3)),
+            "normal_candidates": t(pack["cand_normal"][pack["cand_link"] == li].reshape(-1, 3))}
+    order = np.argsort(pack["sphere_link"], kind="stable")
+    h.sphere_scales = t(pack["spheres"][order][:, 3])
+    h.penetration_keypoints = t(pack["spheres"][order][:, :3].reshape(-1, 3))
+    h.global_index_to_link_index_penetration = torch.as_tensor(np.asarray(pack["sphere_link"])[order]).long()
+    h.joints_lower, h.joints_upper = t(pack["joints_lower"]), t(pack["joints_upper"])
+    h.n_dofs, h.n_contact_candidates = len(pack["joints_lower"]), len(pack["cand"])
+    h.chain = chain
+    name = str(pack["name"])
+    h.joint_calc_fnc = _hand_module(name).calculate_joints if name in ("panda", "ability_hand", "robotiq2") else None
+    movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
+    if "frame_joint" in pack:
+        h.joints_names = [str(pack["frame_joint"][f]) for f in movable]  # robotiq2f140_fk reads it (utils/fk.py:41-47)
+    h.hand_pose = h.contact_point_indices = h.contact_points = h.contact_normals = None
+    h.dtype = dtype
+    return h
+
+
+def reference_object_model(face_verts_list, surface_points_list, batch_size_each, dtype=torch.float32):
+    """reference_object + what calculate_energy reads of an ObjectModel (energy.py:16-62): cog, surface_points_tensor"""
+    o = reference_object(face_verts_list, batch_size_each, dtype)
+    sp = torch.stack([torch.as_tensor(s, dtype=dtype) for s in surface_points_list], 0)
+    o.surface_points_tensor = sp.repeat_interleave(batch_size_each, dim=0)  # object_model.py:181-184
+    o._cog = None                                                           # the reference's own property computes it (:64-68)
+    o.dtype = dtype
     return o

@@ -275,3 +275,55 @@ def test_golden_vectors_are_reproducible(tmp_path, oracle_built):
                                            equal_nan=True, err_msg=k)
             else:
                 np.testing.assert_array_equal(new[k], old[k], err_msg=k)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference is only present in the build container")
+def test_reference_model_classes_reproduce_the_fixtures(oracle_built):
+    """The loop fixtures were generated with oracle.hand.HandOracle / oracle.pipeline.ObjectOracle standing in for the
+    reference's HandModel / ObjectModel (whose constructors need trimesh / pytorch3d).  Here the SAME runs are repeated with the
+    reference's OWN classes — instances made without constructors and filled from the hand pack
+    (ref_harness.reference_hand_model / reference_object_model), so that set_parameters (incl. env_mask), fk, cal_distance,
+    self_penetration and ObjectModel.cal_distance are the reference's methods — and must reproduce the committed numbers:
+    energies, proposals, accept decisions, poses; gradients to summation-order rounding."""
+    import sys
+    sys.path.insert(0, gc.GOLDEN)
+    import ref_harness as rh
+    pack = hand_pack.load_pack("allegro")
+
+    def replay(g, prefix, plan, dtype, z_thr=1.0, nan_at=None, **kw):
+        B = len(g["pose0"])
+        if dtype == torch.float64:
+            torch.set_default_dtype(torch.float64)
+        try:
+            st = rh.make_fit_state(pack, [g["face_verts"]], [g["surface"]], B, g["pose0"], g["idx0"].astype(np.int64),
+                                   dtype=dtype, models="reference", **kw)
+            tt = lambda a: torch.tensor(a, dtype=dtype)
+            rtol = 1e-6 if dtype == torch.float32 else 1e-8  # fp64: pk and the restatement order a few products differently
+            for t, kind in enumerate(plan):
+                k = f"{prefix}t{t}_"
+                if kind == "nan":
+                    st.hand.hand_pose.grad[1, 4] = float("nan")
+                    st.hand.hand_pose.grad[2, 11] = 1e4
+                reset = None
+                if str(kind).startswith("reset"):
+                    mask = torch.tensor(g[k + "mask_in"]) if k + "mask_in" in g else None
+                    reset = (tt(g[k + "pose_init"]), torch.tensor(g[k + "idx_init"]), mask)
+                o = rh.fit_iterate(st, tt(g[k + "u_switch"]), torch.tensor(g[k + "idx_rand"]).long(), tt(g[k + "u_accept"]),
+                                   reset=reset, z_score_threshold=z_thr)
+                np.testing.assert_array_equal(o["idx_prop"].numpy(), g[k + "idx_prop"], err_msg=k)
+                np.testing.assert_allclose(o["proposal"].numpy(), g[k + "proposal"], rtol=rtol, atol=1e-7, err_msg=k)
+                np.testing.assert_allclose(o["new_energy"].numpy(), g[k + "new_energy"], rtol=10 * rtol, err_msg=k)
+                gw = g[k + "new_grad"]
+                np.testing.assert_allclose(o["new_grad"].numpy(), gw, rtol=0, atol=1e-5 * np.abs(gw).max(), err_msg=k)
+                np.testing.assert_array_equal(o["accept"].numpy(), g[k + "accept"], err_msg=k)
+                np.testing.assert_allclose(o["pose"].numpy(), g[k + "pose"], rtol=rtol, atol=1e-7, err_msg=k)
+                np.testing.assert_array_equal(o["idx"].numpy(), g[k + "idx"], err_msg=k)
+        finally:
+            torch.set_default_dtype(torch.float32)
+
+    replay(gc.load("fit_ref_f32"), "", ["plain"] * 4, torch.float32)
+    g = gc.load("fit_reset_ref_f64")
+    replay(g, "", [str(s) for s in g["plan"]], torch.float64, z_thr=0.3, clip_grad=True)
+    g = gc.load("fit_alt_ref")
+    replay(g, "dexanneal_", [str(s) for s in g["dexanneal_plan"]], torch.float32, **gc.ALT_RUNS["dexanneal"])
+    replay(g, "malareset_", [str(s) for s in g["malareset_plan"]], torch.float64)
