@@ -88,3 +88,134 @@ def test_engine_reset_step_with_device_init(emu):
     assert (eng.step_count[mask] == 0).all() and (eng.step_count[~mask] == 2).all()
     assert (eng.ema[mask] == 0).all() and eng.accept[mask].all()
     eng.close()
+
+
+@pytest.mark.skipif(not __import__("os").path.isdir("/root/reference"), reason="the reference is only present in the build container")
+@pytest.mark.parametrize("hand", ["allegro", "panda"])
+def test_oracle_init_matches_the_reference_function(hand):
+    """The reference's OWN initialize_convex_hull (core/initializations.py:15-193), run as is, with its geometry back ends
+    replaced by the oracle's pieces and its random draws injected:
+        trimesh.Trimesh / .convex_hull / .face_normals / .nearest.on_surface -> hull triangles; closest point by the pinned
+                                                                               point-triangle arithmetic (oracle.sdf)
+        trimesh.sample.sample_surface_even                                   -> oracle.init.sample_pool on injected uniforms
+        pytorch3d.ops.sample_farthest_points                                 -> oracle.init.fps
+        transforms3d.euler.euler2mat                                         -> oracle.init.euler_rxyz
+        torch.rand / randint / Tensor.uniform_ (inside trunc_normal_)        -> the injected draws
+    What this pins is everything in between, which is the reference's code: the look-at construction, the inward normal from
+    the closest hull point, distance / Euler jitter, the order of the rotations, the truncated normal (torch's own), the layout
+    of hand_pose, and HandModel.set_parameters on the result."""
+    import importlib
+    import os
+    import sys
+    import types
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import ref_harness as rh
+    from oracle import sdf as osdf
+    rh.load_models()
+    pack = hand_pack.load_pack(hand)
+    B, n_c, pool_factor, seed = 8, 4, 100, 2  # the function hard-codes 100 * batch_size_each pool samples (:54)
+    meshes = [synth.make_mesh(k, 400, seed + i) for i, k in enumerate(("box", "hull"))]
+    hulls = [oinit.convex_hull(v) for v, _ in meshes]
+    O, dof = len(hulls), len(pack["joints_lower"])
+    rng = np.random.default_rng(seed)
+    u_pool = rng.random((O, pool_factor * B, 3), dtype=np.float32)
+    u_pose = rng.random((O * B, 4 + dof), dtype=np.float32)
+    idx_rand = rng.integers(0, len(pack["cand"]), (O * B, n_c)).astype(np.int64)
+    want_pose, want_idx, picks = oinit.initialize_convex_hull(pack, hulls, B, n_c, u_pool, u_pose, idx_rand, pool_factor=pool_factor)
+
+    # ---- stand-ins for the absent geometry packages ----
+    state = {"obj": -1}
+
+    class FakeMesh:
+        def __init__(self, vertices=None, faces=None, tris=None):
+            if tris is None:
+                tris = np.asarray(vertices, np.float64)[np.asarray(faces)]
+            self.tris = np.asarray(tris, np.float32)
+            self.vertices = self.tris.reshape(-1, 3).astype(np.float64)
+            self.faces = np.arange(len(self.vertices)).reshape(-1, 3)
+            self.face_normals = oinit.hull_tables(self.tris)[0].astype(np.float64)
+            self.nearest = types.SimpleNamespace(on_surface=self._on_surface)
+
+        @property
+        def convex_hull(self):
+            return self
+
+        def remove_degenerate_faces(self):
+            return np.ones(len(self.faces), bool)
+
+        def _on_surface(self, pts):
+            _, _, _, cl = osdf.compute_sdf_port(np.asarray(pts, np.float32), self.tris)
+            return cl.astype(np.float64), None, None
+
+    def sample_surface_even(mesh, count):
+        state["obj"] += 1
+        normals, cdf = oinit.hull_tables(mesh.tris)
+        pts, face = oinit.sample_pool(mesh.tris, normals, cdf, u_pool[state["obj"]][:count], inflate=0.0)
+        return pts.astype(np.float64), face
+
+    def sample_farthest_points(points, K, random_start_point=False):
+        assert not random_start_point
+        p32 = points[0].numpy().astype(np.float32)
+        sel = oinit.fps(p32, K)
+        return torch.as_tensor(p32[sel]).unsqueeze(0), torch.as_tensor(sel).unsqueeze(0)
+
+    def euler2mat(ai, aj, ak, axes="sxyz"):
+        assert axes == "rxyz"
+        return oinit.euler_rxyz(np.array([float(ai)], np.float32), np.array([float(aj)], np.float32),
+                                np.array([float(ak)], np.float32))[0]
+
+    tm = sys.modules["trimesh"]
+    tm.Trimesh, tm.sample = FakeMesh, types.SimpleNamespace(sample_surface_even=sample_surface_even)
+    sys.modules["pytorch3d.ops"].sample_farthest_points = sample_farthest_points
+    t3d = sys.modules.setdefault("transforms3d", types.ModuleType("transforms3d"))
+    t3d.euler = types.SimpleNamespace(euler2mat=euler2mat)
+    mod = importlib.import_module("graspqp.core.initializations")
+
+    # ---- injected noise: torch.rand (4 per object), torch.randint (contacts), Tensor.uniform_ (trunc_normal_, per joint) ----
+    calls = {"rand": 0, "joint": 0}
+
+    class Noise:
+        def __getattr__(self, k):
+            return getattr(torch, k)
+
+        def rand(self, size, **kw):
+            o, c = divmod(calls["rand"], 4)
+            calls["rand"] += 1
+            return torch.tensor(u_pose[o * B:(o + 1) * B, c])
+
+        def randint(self, high, size, **kw):
+            return torch.tensor(idx_rand)
+
+    real_uniform = torch.Tensor.uniform_
+
+    def uniform_(self, a=0.0, b=1.0, **kw):  # torch/nn/init.py: tensor.uniform_(2l - 1, 2u - 1) of column `joint`
+        j = calls["joint"]
+        calls["joint"] += 1
+        with torch.no_grad():
+            self.copy_(torch.tensor(u_pose[:, 4 + j]) * (b - a) + a)
+        return self
+
+    h = rh.reference_hand_model(pack)
+    ax = {"x": (1, 0, 0), "y": (0, 1, 0), "z": (0, 0, 1)}
+    h.forward_axis = torch.tensor(ax[str(pack["axes"][0])], dtype=torch.float)
+    h.up_axis = torch.tensor(ax[str(pack["axes"][1])], dtype=torch.float)
+    h.default_state = torch.tensor(np.asarray(pack["default_state"], np.float32))
+    obj = types.SimpleNamespace(object_mesh_list=[FakeMesh(tris=t) for t in hulls], batch_size_each=B,
+                                object_scale_tensor=torch.ones(O, B), data_root_path="/data/release")
+    D = dict(oinit.DEFAULTS)
+    args = types.SimpleNamespace(n_contact=n_c, **{k: D[k] for k in D if k not in ("inflate", "pool_factor")})
+    mod.torch, torch.Tensor.uniform_ = Noise(), uniform_
+    try:
+        mod.initialize_convex_hull(h, obj, args)
+    finally:
+        mod.torch, torch.Tensor.uniform_ = torch, real_uniform
+    got = h.hand_pose.detach().numpy()
+    print(f"[init] {hand}: reference function vs oracle: translation {np.abs(got[:, :3] - want_pose[:, :3]).max():.1e}, "
+          f"rotation {np.abs(got[:, 3:9] - want_pose[:, 3:9]).max():.1e}, joints {np.abs(got[:, 9:] - want_pose[:, 9:]).max():.1e}; "
+          f"calls: rand {calls['rand']}, uniform_ {calls['joint']}, surface samplings {state['obj'] + 1}")
+    assert calls["rand"] == 4 * O and calls["joint"] == dof and state["obj"] + 1 == O
+    np.testing.assert_array_equal(h.contact_point_indices.numpy(), want_idx)
+    np.testing.assert_allclose(got[:, :3], want_pose[:, :3], atol=1e-6)    # translation
+    np.testing.assert_allclose(got[:, 3:9], want_pose[:, 3:9], atol=5e-6)  # two rotation columns
+    np.testing.assert_allclose(got[:, 9:], want_pose[:, 9:], atol=3e-6)    # joints (torch's own erfinv on both sides here)
+    assert h.contact_points.shape == (O * B, n_c, 3)                       # HandModel.set_parameters ran on the result
