@@ -354,6 +354,13 @@ def reference_hand_model(pack, dtype=torch.float32):
     movable = [f for f in range(len(pack["frame_jtype"])) if int(pack["frame_jtype"][f]) != 0]
     if "frame_joint" in pack:
         h.joints_names = [str(pack["frame_joint"][f]) for f in movable]  # robotiq2f140_fk reads it (utils/fk.py:41-47)
+    # what get_contact_jacobian / get_req_joint_velocities read (hand_model.py:632-647, 772-777, 1079-1218)
+    assert (np.diff(np.asarray(pack["cand_link"])) >= 0).all(), "candidates are stored in link order"
+    h.global_index_to_link_index = torch.as_tensor(np.asarray(pack["cand_link"])).long()
+    h.r_contact_body_frames = t(pack["cand"])
+    mesh_frames = set(int(f) for f in pack["mesh_frame"])
+    h._used_links_mask = [f in mesh_frames for f in range(len(pack["frame_parent"]))]  # chain frames in DFS order
+    h.jacobian_fnc = _hand_module(name).calculate_jacobian if name in ("panda", "ability_hand", "robotiq2") else None
     h.hand_pose = h.contact_point_indices = h.contact_points = h.contact_normals = None
     h.dtype = dtype
     return h

@@ -230,3 +230,34 @@ def test_exported_file_is_read_by_the_references_loader(emu, tmp_path):
     np.testing.assert_allclose(joint_positions.numpy(), np.asarray(eng.pose)[order][:, 9:][:, col], rtol=1e-6)
     assert velocities.shape == (3, 16) and torch.isfinite(velocities).all()
     eng.close()
+
+
+@pytest.mark.parametrize("hand", ["allegro", "panda", "robotiq2", "ability_hand"])
+def test_joint_velocities_match_the_references_own_method(emu, hand):
+    """(f2) Exporter.get_req_joint_velocities / contact_jacobian (FK backward kernels, world frame) vs the reference's OWN
+    HandModel.get_req_joint_velocities and get_contact_jacobian (hand_model.py:1079-1218: pk's vectorised link Jacobian, the
+    per-hand jacobian_fnc, omega x r per contact, hand frame, damped pinv) run on a constructor-less instance filled from the
+    pack (ref_harness.reference_hand_model), which first runs the reference's set_parameters on the engine's state."""
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("reference only in the build container")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import ref_harness as rh
+    HandModel, _ = rh.load_models()
+    pack, eng, fv = _engine(emu, hand, B=3, n_c=4)
+    H = eng.be.to_host
+    h = rh.reference_hand_model(pack)
+    idx = torch.tensor(H(eng.idx)).long()
+    HandModel.set_parameters(h, torch.tensor(H(eng.pose)), idx)
+    v = torch.tensor(np.random.default_rng(0).normal(size=(eng.Bt, eng.n_c, 3)).astype(np.float32))
+    with torch.no_grad():
+        theta_r, res_r, ee_r = HandModel.get_req_joint_velocities(h, v, idx, return_ee_vel=True)
+        J_r = HandModel.get_contact_jacobian(h, idx)  # (Bt, n_c, 3, dof), world frame
+    ex = export.Exporter(eng)
+    J = H(ex.contact_jacobian(eng.idx))
+    np.testing.assert_allclose(J, J_r.numpy(), atol=3e-6)
+    theta, res, ee = ex.get_req_joint_velocities(eng.be.from_host(v.numpy(), np.float32), eng.idx, return_ee_vel=True)
+    scale = np.abs(theta_r.numpy()).max()
+    np.testing.assert_allclose(theta.cpu().numpy(), theta_r.numpy(), rtol=2e-3, atol=2e-4 * scale)
+    np.testing.assert_allclose(ee.cpu().numpy(), ee_r.numpy(), rtol=2e-3, atol=2e-4 * np.abs(ee_r.numpy()).max())
+    ex.close()
+    eng.close()
