@@ -126,3 +126,30 @@ def test_optional_terms_prior_and_wall(emu, hand, n_c, w_wall):
     import cases
     ep, ew = cases.check_optional_terms(emu, engine.NumpyBackend(), hand=hand, n_c=n_c, w_wall=w_wall)
     assert ep > 0 and (ew > 0) == (w_wall > 0)
+
+
+def test_new_entry_points_check_their_arguments(emu):
+    """(f3)/(f4) entry points: empty batches are a no-op, bad arguments are refused with a message (no launch)"""
+    import ctypes
+    from graspqp_b200 import _lib
+    f, i = np.zeros(64, np.float32), np.zeros(64, np.int32)
+    p = lambda a: a.ctypes.data
+    S = _lib.GqpSpanParams(kind=_lib.SPAN_DEXGRASP, friction=0.2, obb_length=0.2, scale=100.0)
+    assert emu.gqp_span_energy(ctypes.byref(S), None, None, None, None, None, None, None, 0, 0, 4, 4, None, None, None, None, None) == 0
+    assert emu.gqp_span_energy(ctypes.byref(S), p(f), p(f), p(f), p(f), None, p(f), None, 0, 1, 1, 0, p(f), p(f), None, None, None) != 0
+    assert b"n_c" in emu.gqp_last_error()
+    M = _lib.GqpMalaParams(switch_possibility=0.5, starting_temperature=18.0, temperature_decay=0.95, step_size=0.005, mu=0.98,
+                           annealing_period=30, stepsize_period=50, clip_grad=0)
+    # an empty batch is fine; ema_in == ema_out is refused (every row must read the OLD accumulator)
+    assert emu.gqp_anneal_propose(ctypes.byref(M), None, None, None, None, None, 0, None, 0, 25, 4, 92, None, None, 1, 1, None,
+                                  None, None, None) == 0
+    assert emu.gqp_anneal_propose(ctypes.byref(M), p(f), p(f), p(f), p(f), p(f), 0, p(i), 1, 25, 4, 92, None, None, 1, 1, p(f),
+                                  p(i), None, None) != 0
+    assert b"different buffers" in emu.gqp_last_error()
+    assert emu.gqp_anneal_propose(ctypes.byref(M), p(f), p(f), p(f), p(f), p(f[32:]), -1, p(i), 1, 25, 4, 92, None, None, 1, 1,
+                                  p(f), p(i), None, None) != 0  # negative step counter
+    assert emu.gqp_anneal_accept(ctypes.byref(M), 0, 25, 4, 5, None, None, None, 1, 1, 0, None, None, None, None, None, None,
+                                 None, None, None, None, None, 0, None) == 0
+    assert emu.gqp_entropy_stats(p(f), 0, 16, p(f), p(f), p(f), p(f), None) != 0   # no rows: nothing to histogram
+    assert emu.gqp_entropy_stats(p(f), 2, 16, p(f), p(f), None, p(f), None) != 0   # scratch is required
+    assert emu.gqp_prior_wall(None, p(f), p(f), 1, None, None, None, 0, 1.0, 1.0, None, None, None, None, None) != 0
